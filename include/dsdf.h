@@ -1,0 +1,142 @@
+/*
+ * dsdf.h -- C ABI of the B200-native DeepSDF decoder hot path (libdsdf_b200.so).
+ *
+ * Drop-in boundary for ONE path of anonymous-submission01/medical-shape-disentanglement:
+ * forward/backward of networks/deep_sdf_decoder.Decoder (8x512, latent 256, latent_in=[4]) over
+ * (latent, xyz) SDF samples, the auto-decoder optimisation step around it, and the grid decode
+ * inside deep_sdf/mesh.create_mesh.  Plain pointers and sizes only; no torch types.  All device
+ * pointers are CUDA device memory on the handle's device; every launch goes to the `stream`
+ * argument (a cudaStream_t passed as void*), no hidden synchronisation, no allocation of caller
+ * tensors.  Every entry returns 0 on success or a negative DSDF_E* code; the message is
+ * available from dsdf_last_error().  There is no CPU fallback anywhere in the library.
+ *
+ * Each entry cites the reference interface it replaces (file:line under /root/reference).
+ */
+#ifndef DSDF_H_
+#define DSDF_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DSDF_OK 0
+#define DSDF_EINVAL (-1)      /* bad argument / unsupported configuration            */
+#define DSDF_ECUDA (-2)       /* CUDA runtime error (message has the CUDA string)    */
+#define DSDF_ENOMEM (-3)      /* workspace too small / allocation failure            */
+#define DSDF_EUNSUPPORTED (-4)/* valid reference config outside the fused path       */
+
+#define DSDF_NUM_LIN 9
+
+typedef struct dsdf_handle_s* dsdf_handle;
+
+/* Network configuration == the NetworkSpecs the reference passes to
+ * Decoder(latent_size, **specs["NetworkSpecs"]) (train_deep_sdf.py:348,
+ * networks/deep_sdf_decoder.py:10-71).  Supported: latent_size 256, 8 hidden layers of 512,
+ * latent_in == 4, xyz_in_all false, use_tanh false; weight_norm_mask bit l set <=> lin l is
+ * wrapped by nn.utils.weight_norm (norm_layers with weight_norm=true). */
+typedef struct {
+  int32_t latent_size;
+  int32_t hidden;
+  int32_t num_hidden;
+  int32_t latent_in;
+  uint32_t weight_norm_mask;
+  int32_t device;            /* CUDA device ordinal */
+} dsdf_config;
+
+/* Parameter addressing: one flat fp32 device buffer holding every decoder parameter with the
+ * reference's shapes (state_dict of networks/deep_sdf_decoder.Decoder):
+ *   w_off[l]: linL.weight [out,in]  (or linL.weight_v when weight-normalised)
+ *   g_off[l]: linL.weight_g [out,1] (or -1)
+ *   b_off[l]: linL.bias [out]
+ * Offsets are in elements.  Gradients / Adam state use the same addressing. */
+typedef struct {
+  int64_t w_off[DSDF_NUM_LIN];
+  int64_t g_off[DSDF_NUM_LIN];
+  int64_t b_off[DSDF_NUM_LIN];
+  int64_t total;             /* elements in the flat buffer */
+} dsdf_param_layout;
+
+/* arch.Decoder(latent_size, **NetworkSpecs)  (train_deep_sdf.py:348) */
+int dsdf_create(const dsdf_config* cfg, dsdf_handle* out);
+int dsdf_destroy(dsdf_handle h);
+const char* dsdf_last_error(dsdf_handle h);
+/* number of SMs the persistent kernels are launched on (for workspace sizing / reports) */
+int dsdf_num_sms(dsdf_handle h);
+
+/* Fold the fp32 master parameters into the bf16 tensor-core images (weight-norm g/||v|| folded,
+ * lin4 columns remapped, xyz/bias hi-lo split).  Must be called after every parameter update and
+ * before forward/train calls.  Replaces the per-call nn.utils.weight_norm pre-forward hook
+ * (networks/deep_sdf_decoder.py:49-53). */
+int dsdf_set_weights(dsdf_handle h, const float* params, const dsdf_param_layout* layout,
+                     void* stream);
+
+/* Decoder.forward(input[N, L+3]) -> [N,1], inference (networks/deep_sdf_decoder.py:74-109). */
+int dsdf_forward_dense(dsdf_handle h, const float* input, int64_t n, float* out, void* stream);
+
+/* decode_sdf(decoder, latent_vector, queries) (deep_sdf/utils.py:86-97) generalised to
+ * scene-contiguous segments: row r uses latent table[seg_ids[r / rows_per_seg]] and
+ * xyz = xyz[r*xyz_stride + 0..2].  n_seg == 1, seg_ids == NULL means "one latent for all rows"
+ * (table points at that latent). */
+int dsdf_forward_segments(dsdf_handle h, const float* table, const int64_t* seg_ids,
+                          int64_t n_seg, int64_t rows_per_seg, const float* xyz,
+                          int64_t xyz_stride, int64_t n, float* out, void* stream);
+
+/* create_mesh grid + decode loop (deep_sdf/mesh.py:38-71): SDF at linear grid indices
+ * [lo, hi) of the N^3 lattice, coordinates generated on the fly bit-exactly as the reference's
+ * fp32 torch expressions (including the true-division shear of mesh.py:46-47).  Sharding by
+ * voxel slab == calling with disjoint [lo,hi). */
+int dsdf_decode_grid(dsdf_handle h, const float* latent, int32_t grid_n, int64_t lo, int64_t hi,
+                     float* out, void* stream);
+/* the coordinates the grid decode uses (for bookkeeping tests): xyz[hi-lo][3] */
+int dsdf_grid_coords(dsdf_handle h, int32_t grid_n, int64_t lo, int64_t hi, float* xyz,
+                     void* stream);
+
+/* Workspace (device bytes) needed by dsdf_train_fwd_bwd for up to max_rows rows in up to
+ * max_segments segments. */
+size_t dsdf_train_workspace_bytes(dsdf_handle h, int64_t max_rows, int64_t max_segments);
+
+/* One fused gather + forward + clamped-L1 loss + code regulariser + backward of the
+ * auto-decoder step body (train_deep_sdf.py:598-616,731) over n_seg scene-contiguous segments
+ * of rows_per_seg rows (rows_per_seg % 128 == 0):
+ *   sdf_data [n_seg*rows_per_seg, 4] = (x,y,z,sdf)            (train_deep_sdf.py:555-567)
+ *   table    [num_scenes, 256] latent codes, rows seg_ids[b] are read (already max_norm-renormed:
+ *            call dsdf_renorm_rows first, train_deep_sdf.py:429,598)
+ *   n_total  global row count the loss is normalised by (train_deep_sdf.py:558,606; under
+ *            scene sharding = sum over ranks)
+ *   reg_lambda_ramp = CodeRegularizationLambda * min(1, epoch/100) (0 disables; :609-613)
+ * Outputs: grads (flat, dsdf_param_layout addressing, OVERWRITTEN), lat_grad [num_scenes,256]
+ * (dense, OVERWRITTEN: zero for scenes not in the batch, as nn.Embedding(sparse=False)),
+ * pred [n] (tanh output, un-clamped), loss_out[0] = L1 term, loss_out[1] = regulariser term. */
+int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const float* table,
+                       int64_t num_scenes, const int64_t* seg_ids, int64_t n_seg,
+                       int64_t rows_per_seg, const float* sdf_data, int64_t n_total,
+                       float clamp_dist, float reg_lambda_ramp, void* workspace,
+                       size_t workspace_bytes, float* grads, float* lat_grad, float* pred,
+                       float* loss_out, void* stream);
+
+/* nn.Embedding(max_norm) lookup side effect (train_deep_sdf.py:429,598): rows seg_ids[b] with
+ * norm > max_norm are scaled in place by max_norm/(norm+1e-7). */
+int dsdf_renorm_rows(dsdf_handle h, float* table, const int64_t* seg_ids, int64_t n_seg,
+                     float max_norm, void* stream);
+
+/* torch.nn.utils.clip_grad_norm_(params, max_norm) + torch.optim.Adam step
+ * (train_deep_sdf.py:780-784, 445-454) over one flat buffer.  max_norm <= 0: no clipping.
+ * scratch: >= 8 KiB device scratch; scratch[0] = grad norm, scratch[1] = clip coef on return.
+ * `step` is the 1-based Adam step count. */
+int dsdf_clip_adam(dsdf_handle h, float* params, float* grads, float* exp_avg, float* exp_avg_sq,
+                   int64_t n, float max_norm, float lr, float beta1, float beta2, float eps,
+                   int64_t step, float* scratch, void* stream);
+
+/* Descriptor self-test: one-tile GEMMs through the same UMMA descriptor helpers.
+ * kind 0: K-major  A[128x64] (1 SUB), B[128x64] (1 SUB) -> D[128][128] = A B^T
+ * kind 1: MN-major A (2 SUBs), B (4 SUBs), K = rows 0..31 -> D[128][256] = A^T B */
+int dsdf_selftest_gemm(int32_t kind, const void* a_img, const void* b_img, float* d_out,
+                       void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DSDF_H_ */

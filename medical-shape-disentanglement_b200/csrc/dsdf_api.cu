@@ -1,0 +1,486 @@
+// C-ABI entry points (include/dsdf.h) of the B200-native DeepSDF hot path.
+// Host side only orchestrates launches on the caller's stream; all arithmetic is in the
+// sm_100a kernels (fwd_kernel.cuh, bwd_kernel.cuh, wgrad_kernel.cuh, small_kernels.cuh,
+// fold_kernels.cuh).  There is deliberately no CPU path: if no CUDA device / kernel image is
+// available every entry fails with DSDF_ECUDA.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/dsdf.h"
+#include "bwd_kernel.cuh"
+#include "fold_kernels.cuh"
+#include "fwd_kernel.cuh"
+#include "layout.cuh"
+#include "selftest.cuh"
+#include "small_kernels.cuh"
+#include "wgrad_kernel.cuh"
+
+using namespace dsdf;
+
+struct dsdf_handle_s {
+  dsdf_config cfg;
+  int device = 0;
+  int num_sms = 0;
+  std::string err;
+  // handle-owned device buffers (bf16 shadows + small fp32 derived state)
+  uint8_t* fwd_img = nullptr;
+  uint8_t* dg_img = nullptr;
+  float* weff = nullptr;
+  float* scale = nullptr;
+  float* inv_norm = nullptr;
+  WgItem* wg_items = nullptr;
+  int wg_items_cap = 0;
+  long long wg_items_tiles = -1;
+  int wg_n_items = 0;
+  WgLayout wg_layout{};
+  ParamLayout pl{};
+  bool weights_set = false;
+  bool attrs_set = false;
+};
+
+static thread_local std::string g_err;
+
+#define DSDF_FAIL(h, code, ...)                         \
+  do {                                                  \
+    char _b[512];                                       \
+    snprintf(_b, sizeof(_b), __VA_ARGS__);              \
+    if (h) (h)->err = _b;                               \
+    g_err = _b;                                         \
+    return (code);                                      \
+  } while (0)
+
+#define CU(h, expr)                                                                    \
+  do {                                                                                 \
+    cudaError_t _e = (expr);                                                           \
+    if (_e != cudaSuccess)                                                             \
+      DSDF_FAIL(h, DSDF_ECUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), \
+                __FILE__, __LINE__);                                                   \
+  } while (0)
+
+static int set_kernel_attrs(dsdf_handle h) {
+  if (h->attrs_set) return DSDF_OK;
+  CU(h, cudaFuncSetAttribute(k_forward<MODE_DENSE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmemBytes));
+  CU(h, cudaFuncSetAttribute(k_forward<MODE_TABLE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmemBytes));
+  CU(h, cudaFuncSetAttribute(k_forward<MODE_GRID, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmemBytes));
+  CU(h, cudaFuncSetAttribute(k_forward<MODE_TABLE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmemBytes));
+  CU(h, cudaFuncSetAttribute(k_backward, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmemBytes));
+  CU(h, cudaFuncSetAttribute(k_wgrad, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgSmemBytes));
+  CU(h, cudaFuncSetAttribute(k_selftest_gemm, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
+  h->attrs_set = true;
+  return DSDF_OK;
+}
+
+extern "C" int dsdf_create(const dsdf_config* cfg, dsdf_handle* out) {
+  if (!cfg || !out) DSDF_FAIL((dsdf_handle) nullptr, DSDF_EINVAL, "null argument");
+  if (cfg->latent_size != kLatent || cfg->hidden != kHidden || cfg->num_hidden != 8 ||
+      cfg->latent_in != kSkipLayer)
+    DSDF_FAIL((dsdf_handle) nullptr, DSDF_EUNSUPPORTED,
+              "unsupported NetworkSpecs: fused path needs latent 256, dims [512]*8, latent_in [4] "
+              "(got latent %d hidden %d layers %d latent_in %d)",
+              cfg->latent_size, cfg->hidden, cfg->num_hidden, cfg->latent_in);
+  if (cfg->weight_norm_mask & ~0xFFu)
+    DSDF_FAIL((dsdf_handle) nullptr, DSDF_EUNSUPPORTED, "weight_norm on lin8 is not a reference configuration");
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    DSDF_FAIL((dsdf_handle) nullptr, DSDF_ECUDA, "no CUDA device: %s (there is no CPU fallback)",
+              cudaGetErrorString(e));
+  dsdf_handle h = new dsdf_handle_s();
+  h->cfg = *cfg;
+  h->device = cfg->device;
+  cudaDeviceProp prop;
+  if ((e = cudaSetDevice(h->device)) != cudaSuccess ||
+      (e = cudaGetDeviceProperties(&prop, h->device)) != cudaSuccess) {
+    delete h;
+    DSDF_FAIL((dsdf_handle) nullptr, DSDF_ECUDA, "device %d: %s", cfg->device, cudaGetErrorString(e));
+  }
+  if (prop.major != 10) {
+    delete h;
+    DSDF_FAIL((dsdf_handle) nullptr, DSDF_ECUDA,
+              "device %d is sm_%d%d; this library is built for sm_100a (B200) only",
+              cfg->device, prop.major, prop.minor);
+  }
+  h->num_sms = prop.multiProcessorCount;
+  bool ok = cudaMalloc(&h->fwd_img, (size_t)kFwdTilesTotal * kSubBytes) == cudaSuccess &&
+            cudaMalloc(&h->dg_img, (size_t)kDgTilesTotal * kSubBytes) == cudaSuccess &&
+            cudaMalloc(&h->weff, (size_t)(kWeffElems + 16) * 4) == cudaSuccess &&
+            cudaMalloc(&h->scale, (size_t)kScaleElems * 4) == cudaSuccess &&
+            cudaMalloc(&h->inv_norm, (size_t)kScaleElems * 4) == cudaSuccess;
+  if (!ok) {
+    dsdf_destroy(h);
+    DSDF_FAIL((dsdf_handle) nullptr, DSDF_ENOMEM, "cudaMalloc of weight shadows failed");
+  }
+  int rc = set_kernel_attrs(h);
+  if (rc != DSDF_OK) {
+    std::string m = h->err;
+    dsdf_destroy(h);
+    g_err = m;
+    return rc;
+  }
+  *out = h;
+  return DSDF_OK;
+}
+
+extern "C" int dsdf_destroy(dsdf_handle h) {
+  if (!h) return DSDF_OK;
+  cudaFree(h->fwd_img);
+  cudaFree(h->dg_img);
+  cudaFree(h->weff);
+  cudaFree(h->scale);
+  cudaFree(h->inv_norm);
+  cudaFree(h->wg_items);
+  delete h;
+  return DSDF_OK;
+}
+
+extern "C" const char* dsdf_last_error(dsdf_handle h) { return h ? h->err.c_str() : g_err.c_str(); }
+extern "C" int dsdf_num_sms(dsdf_handle h) { return h ? h->num_sms : 0; }
+
+extern "C" int dsdf_set_weights(dsdf_handle h, const float* params, const dsdf_param_layout* lay,
+                                void* stream) {
+  if (!h || !params || !lay) DSDF_FAIL(h, DSDF_EINVAL, "null argument");
+  cudaStream_t st = (cudaStream_t)stream;
+  for (int l = 0; l < kNumLin; ++l) {
+    const bool wn = (h->cfg.weight_norm_mask >> l) & 1u;
+    if (wn != (lay->g_off[l] >= 0))
+      DSDF_FAIL(h, DSDF_EINVAL, "layout/weight_norm_mask mismatch at lin%d", l);
+    h->pl.w[l] = lay->w_off[l];
+    h->pl.g[l] = lay->g_off[l];
+    h->pl.b[l] = lay->b_off[l];
+  }
+  k_rowscale<<<(kScaleElems * 32 + 255) / 256, 256, 0, st>>>(params, h->pl, h->scale, h->inv_norm);
+  k_weff<<<(unsigned)((kWeffElems + 255) / 256), 256, 0, st>>>(params, h->pl, h->scale, h->weff);
+  const long long c1 = (long long)kFwdTilesTotal * (kSubBytes / 16);
+  k_fold_fwd<<<(unsigned)((c1 + 255) / 256), 256, 0, st>>>(h->weff, params, h->pl, h->fwd_img);
+  const long long c2 = (long long)kDgTilesTotal * (kSubBytes / 16);
+  k_fold_dgrad<<<(unsigned)((c2 + 255) / 256), 256, 0, st>>>(h->weff, h->dg_img);
+  CU(h, cudaGetLastError());
+  h->weights_set = true;
+  return DSDF_OK;
+}
+
+static unsigned grid_for(dsdf_handle h, long long n_rows) {
+  const long long tiles = (n_rows + kTileM - 1) / kTileM;
+  return (unsigned)(tiles < h->num_sms ? tiles : h->num_sms);
+}
+
+extern "C" int dsdf_forward_dense(dsdf_handle h, const float* input, int64_t n, float* out,
+                                  void* stream) {
+  if (!h || !input || !out) DSDF_FAIL(h, DSDF_EINVAL, "null argument");
+  if (!h->weights_set) DSDF_FAIL(h, DSDF_EINVAL, "dsdf_set_weights has not been called");
+  if (n <= 0) return DSDF_OK;
+  FwdArgs a;
+  memset(&a, 0, sizeof(a));
+  a.wimg = h->fwd_img;
+  a.w8 = h->weff + weff_off(8);
+  a.b8 = h->weff + kWeffElems;  // see k_copy_b8 below
+  a.n_rows = n;
+  a.input = input;
+  a.out = out;
+  k_forward<MODE_DENSE, false><<<grid_for(h, n), kFwdThreads, kFwdSmemBytes, (cudaStream_t)stream>>>(a);
+  CU(h, cudaGetLastError());
+  return DSDF_OK;
+}
+
+extern "C" int dsdf_forward_segments(dsdf_handle h, const float* table, const int64_t* seg_ids,
+                                     int64_t n_seg, int64_t rows_per_seg, const float* xyz,
+                                     int64_t xyz_stride, int64_t n, float* out, void* stream) {
+  if (!h || !table || !xyz || !out) DSDF_FAIL(h, DSDF_EINVAL, "null argument");
+  if (!h->weights_set) DSDF_FAIL(h, DSDF_EINVAL, "dsdf_set_weights has not been called");
+  if (xyz_stride < 3) DSDF_FAIL(h, DSDF_EINVAL, "xyz_stride must be >= 3");
+  if (seg_ids && (n_seg <= 0 || rows_per_seg <= 0 || n_seg * rows_per_seg < n))
+    DSDF_FAIL(h, DSDF_EINVAL, "segments do not cover n rows");
+  if (n <= 0) return DSDF_OK;
+  FwdArgs a;
+  memset(&a, 0, sizeof(a));
+  a.wimg = h->fwd_img;
+  a.w8 = h->weff + weff_off(8);
+  a.b8 = h->weff + kWeffElems;
+  a.n_rows = n;
+  a.table = table;
+  a.seg_ids = (const long long*)seg_ids;
+  a.rows_per_seg = seg_ids ? rows_per_seg : n;
+  a.xyzs = xyz;
+  a.xyz_stride = xyz_stride;
+  a.out = out;
+  k_forward<MODE_TABLE, false><<<grid_for(h, n), kFwdThreads, kFwdSmemBytes, (cudaStream_t)stream>>>(a);
+  CU(h, cudaGetLastError());
+  return DSDF_OK;
+}
+
+extern "C" int dsdf_decode_grid(dsdf_handle h, const float* latent, int32_t grid_n, int64_t lo,
+                                int64_t hi, float* out, void* stream) {
+  if (!h || !latent || !out) DSDF_FAIL(h, DSDF_EINVAL, "null argument");
+  if (!h->weights_set) DSDF_FAIL(h, DSDF_EINVAL, "dsdf_set_weights has not been called");
+  const long long n3 = (long long)grid_n * grid_n * grid_n;
+  if (grid_n < 2 || lo < 0 || hi > n3 || lo > hi) DSDF_FAIL(h, DSDF_EINVAL, "bad grid range");
+  if (hi == lo) return DSDF_OK;
+  FwdArgs a;
+  memset(&a, 0, sizeof(a));
+  a.wimg = h->fwd_img;
+  a.w8 = h->weff + weff_off(8);
+  a.b8 = h->weff + kWeffElems;
+  a.n_rows = hi - lo;
+  a.table = latent;
+  a.grid_n = grid_n;
+  a.grid_lo = lo;
+  a.voxel_size = (float)(2.0 / (grid_n - 1));
+  a.out = out;
+  k_forward<MODE_GRID, false><<<grid_for(h, a.n_rows), kFwdThreads, kFwdSmemBytes, (cudaStream_t)stream>>>(a);
+  CU(h, cudaGetLastError());
+  return DSDF_OK;
+}
+
+__global__ void k_grid_coords(int n, long long lo, long long cnt, float vs, float* xyz) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= cnt) return;
+  float x, y, z;
+  grid_xyz(lo + i, n, vs, x, y, z);
+  xyz[i * 3] = x;
+  xyz[i * 3 + 1] = y;
+  xyz[i * 3 + 2] = z;
+}
+
+extern "C" int dsdf_grid_coords(dsdf_handle h, int32_t grid_n, int64_t lo, int64_t hi, float* xyz,
+                                void* stream) {
+  if (!h || !xyz || grid_n < 2 || lo > hi) DSDF_FAIL(h, DSDF_EINVAL, "bad argument");
+  const long long cnt = hi - lo;
+  if (cnt == 0) return DSDF_OK;
+  k_grid_coords<<<(unsigned)((cnt + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      grid_n, lo, cnt, (float)(2.0 / (grid_n - 1)), xyz);
+  CU(h, cudaGetLastError());
+  return DSDF_OK;
+}
+
+// ------------------------------------------------------------------------------------ training
+namespace {
+struct Ws {
+  uint8_t* xstash;
+  uint8_t* dystash;
+  float* g;
+  float* tile_partials;
+  float* tile_colsum;
+  float* cta_partials;
+  float* wg_partials;
+  float* seg_sum;
+  float* dlat_seg;
+  float* seg_norm;
+  float* dweff;
+  size_t total;
+};
+inline size_t al(size_t x) { return (x + 1023) & ~(size_t)1023; }
+
+constexpr int kWgMaxItems = 26 * 8;
+
+Ws carve(uint8_t* base, long long max_rows, long long max_seg, int num_sms) {
+  const size_t tiles = (size_t)((max_rows + kTileM - 1) / kTileM);
+  Ws w;
+  size_t o = 0;
+  auto take = [&](size_t bytes) { uint8_t* p = base ? base + o : nullptr; o += al(bytes); return p; };
+  w.xstash = take(tiles * kStashTileBytes);
+  w.dystash = take(tiles * kStashTileBytes);
+  w.g = (float*)take(tiles * kTileM * 4);
+  w.tile_partials = (float*)take(tiles * 2 * 4);
+  w.tile_colsum = (float*)take(tiles * 2 * kHidden * 4);
+  w.cta_partials = (float*)take((size_t)num_sms * kCtaPartialFloats * 4);
+  w.wg_partials = (float*)take((size_t)kWgMaxItems * kTileM * kHidden * 4);
+  w.seg_sum = (float*)take((size_t)max_seg * 2 * kHidden * 4);
+  w.dlat_seg = (float*)take((size_t)max_seg * kLatent * 4);
+  w.seg_norm = (float*)take((size_t)max_seg * 4);
+  w.dweff = (float*)take((size_t)kWeffElems * 4);
+  w.total = o;
+  return w;
+}
+}  // namespace
+
+extern "C" size_t dsdf_train_workspace_bytes(dsdf_handle h, int64_t max_rows, int64_t max_segments) {
+  if (!h) return 0;
+  return carve(nullptr, max_rows, max_segments, h->num_sms).total + 1024;
+}
+
+// wgrad work items for `tiles` row tiles: layers 1..7, out chunks, K splits
+static int build_wg_items(dsdf_handle h, long long tiles, cudaStream_t st) {
+  if (h->wg_items_tiles == tiles) return DSDF_OK;
+  int base_items = 0;
+  for (int l = 1; l <= 7; ++l) base_items += (l == 3) ? 2 : 4;   // 26
+  int n_split = h->num_sms / base_items;
+  if (n_split < 1) n_split = 1;
+  if (n_split > 8) n_split = 8;
+  if (n_split > tiles) n_split = (int)(tiles > 0 ? tiles : 1);
+  std::vector<WgItem> items;
+  int idx = 0;
+  for (int l = 1; l <= 7; ++l) {
+    h->wg_layout.item_base[l] = idx;
+    const int n_oc = (l == 3) ? 2 : 4;
+    for (int oc = 0; oc < n_oc; ++oc)
+      for (int s = 0; s < n_split; ++s) {
+        WgItem it;
+        it.layer = l;
+        it.oc = oc;
+        it.n_sub = (l == 4) ? 4 : 8;
+        it.split = s;
+        it.tile_lo = tiles * s / n_split;
+        it.tile_hi = tiles * (s + 1) / n_split;
+        items.push_back(it);
+        ++idx;
+      }
+  }
+  h->wg_layout.item_base[0] = 0;
+  h->wg_layout.n_split = n_split;
+  if ((int)items.size() > h->wg_items_cap) {
+    cudaFree(h->wg_items);
+    CU(h, cudaMalloc(&h->wg_items, items.size() * sizeof(WgItem)));
+    h->wg_items_cap = (int)items.size();
+  }
+  CU(h, cudaMemcpyAsync(h->wg_items, items.data(), items.size() * sizeof(WgItem),
+                        cudaMemcpyHostToDevice, st));
+  CU(h, cudaStreamSynchronize(st));  // items vector goes out of scope; once per shape change
+  h->wg_n_items = (int)items.size();
+  h->wg_items_tiles = tiles;
+  return DSDF_OK;
+}
+
+extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const float* table,
+                                  int64_t num_scenes, const int64_t* seg_ids, int64_t n_seg,
+                                  int64_t rows_per_seg, const float* sdf_data, int64_t n_total,
+                                  float clamp_dist, float reg_lambda_ramp, void* workspace,
+                                  size_t workspace_bytes, float* grads, float* lat_grad,
+                                  float* pred, float* loss_out, void* stream) {
+  if (!h || !params || !table || !seg_ids || !sdf_data || !workspace || !grads || !lat_grad ||
+      !pred || !loss_out)
+    DSDF_FAIL(h, DSDF_EINVAL, "null argument");
+  if (!h->weights_set) DSDF_FAIL(h, DSDF_EINVAL, "dsdf_set_weights has not been called");
+  if (n_seg <= 0 || rows_per_seg <= 0 || rows_per_seg % kTileM != 0)
+    DSDF_FAIL(h, DSDF_EUNSUPPORTED,
+              "fused step needs scene-contiguous segments with SamplesPerScene %% 128 == 0 (got %lld)",
+              (long long)rows_per_seg);
+  if (n_total <= 0) DSDF_FAIL(h, DSDF_EINVAL, "n_total must be positive");
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long n = n_seg * rows_per_seg;
+  const long long tiles = n / kTileM;
+  const int tiles_per_seg = (int)(rows_per_seg / kTileM);
+  uint8_t* base = (uint8_t*)(((uintptr_t)workspace + 1023) & ~(uintptr_t)1023);
+  Ws w = carve(base, n, n_seg, h->num_sms);
+  if ((size_t)(base - (uint8_t*)workspace) + w.total > workspace_bytes)
+    DSDF_FAIL(h, DSDF_ENOMEM, "workspace too small: need %zu bytes, have %zu", w.total + 1024,
+              workspace_bytes);
+  int rc = build_wg_items(h, tiles, st);
+  if (rc != DSDF_OK) return rc;
+
+  const float inv_n = 1.0f / (float)n_total;
+  const unsigned grid = grid_for(h, n);
+
+  // ---- forward (gather + 9 layers + tanh + clamped L1 + dL/ds), stashing activations
+  FwdArgs fa;
+  memset(&fa, 0, sizeof(fa));
+  fa.wimg = h->fwd_img;
+  fa.w8 = h->weff + weff_off(8);
+  fa.b8 = h->weff + kWeffElems;
+  fa.n_rows = n;
+  fa.table = table;
+  fa.seg_ids = (const long long*)seg_ids;
+  fa.rows_per_seg = rows_per_seg;
+  fa.xyzs = sdf_data;
+  fa.xyz_stride = 4;
+  fa.out = pred;
+  fa.xstash = w.xstash;
+  fa.gout = w.g;
+  fa.tile_partials = w.tile_partials;
+  fa.fused_loss = 1;
+  fa.clamp_dist = clamp_dist;
+  fa.inv_n_total = inv_n;
+  k_forward<MODE_TABLE, true><<<grid, kFwdThreads, kFwdSmemBytes, st>>>(fa);
+
+  // ---- backward dgrad chain + reducers
+  BwdArgs ba;
+  memset(&ba, 0, sizeof(ba));
+  ba.n_rows = n;
+  ba.dgimg = h->dg_img;
+  ba.w8 = h->weff + weff_off(8);
+  ba.g = w.g;
+  ba.xstash = w.xstash;
+  ba.dystash = w.dystash;
+  ba.xyz = sdf_data;
+  ba.xyz_stride = 4;
+  ba.tile_colsum = w.tile_colsum;
+  ba.cta_partials = w.cta_partials;
+  k_backward<<<grid, kBwdThreads, kBwdSmemBytes, st>>>(ba);
+
+  // ---- wgrad GEMMs (lin1..lin7) + split-K reduction
+  WgArgs wa;
+  wa.items = h->wg_items;
+  wa.xstash = w.xstash;
+  wa.dystash = w.dystash;
+  wa.partials = w.wg_partials;
+  k_wgrad<<<h->wg_n_items, kWgThreads, kWgSmemBytes, st>>>(wa);
+  k_reduce_wgrad<<<dim3(kHidden, 7), kHidden, 0, st>>>(w.wg_partials, h->wg_layout, w.dweff);
+
+  // ---- segmented (scene-contiguous) reductions: latent grads, latent columns of dW0/dW4, biases
+  const float reg_coef = reg_lambda_ramp * (float)rows_per_seg * inv_n;
+  k_seg_colsum<<<dim3((unsigned)n_seg, 2), kHidden, 0, st>>>(w.tile_colsum, tiles_per_seg, w.seg_sum);
+  k_lat_grad_seg<<<(unsigned)n_seg, kLatent, 0, st>>>(w.seg_sum, h->weff, table,
+                                                      (const long long*)seg_ids, reg_coef,
+                                                      w.dlat_seg, w.seg_norm);
+  CU(h, cudaMemsetAsync(lat_grad, 0, (size_t)num_scenes * kLatent * 4, st));
+  k_lat_grad_scatter<<<1, kLatent, 0, st>>>(w.dlat_seg, (const long long*)seg_ids, (int)n_seg, lat_grad);
+  k_dw_latent<<<dim3(kHidden, 2), kLatent, 0, st>>>(w.seg_sum, table, (const long long*)seg_ids,
+                                                    (int)n_seg, w.dweff);
+  k_reduce_cta<<<1, kHidden, 0, st>>>(w.cta_partials, (int)grid, w.seg_sum, (int)n_seg,
+                                      w.tile_partials, tiles, h->pl, grads, w.dweff);
+  k_param_grads<<<(kScaleElems * 32 + 255) / 256, 256, 0, st>>>(w.dweff, params, h->pl, h->scale,
+                                                                h->inv_norm, grads);
+  k_loss<<<1, 1024, 0, st>>>(w.tile_partials, tiles, inv_n, w.seg_norm, (int)n_seg, reg_coef, loss_out);
+  CU(h, cudaGetLastError());
+  return DSDF_OK;
+}
+
+extern "C" int dsdf_renorm_rows(dsdf_handle h, float* table, const int64_t* seg_ids, int64_t n_seg,
+                                float max_norm, void* stream) {
+  if (!h || !table || !seg_ids) DSDF_FAIL(h, DSDF_EINVAL, "null argument");
+  if (n_seg <= 0) return DSDF_OK;
+  k_renorm_rows<<<1, kLatent, 0, (cudaStream_t)stream>>>(table, (const long long*)seg_ids, (int)n_seg, max_norm);
+  CU(h, cudaGetLastError());
+  return DSDF_OK;
+}
+
+extern "C" int dsdf_clip_adam(dsdf_handle h, float* params, float* grads, float* exp_avg,
+                              float* exp_avg_sq, int64_t n, float max_norm, float lr, float beta1,
+                              float beta2, float eps, int64_t step, float* scratch, void* stream) {
+  if (!h || !params || !grads || !exp_avg || !exp_avg_sq || !scratch)
+    DSDF_FAIL(h, DSDF_EINVAL, "null argument");
+  if (step < 1) DSDF_FAIL(h, DSDF_EINVAL, "Adam step count is 1-based");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int nb = 1024;
+  float* part = scratch + 16;
+  k_sqnorm_partial<<<nb, 256, 0, st>>>(grads, n, part);
+  k_clip_coef<<<1, 256, 0, st>>>(part, nb, max_norm, scratch);
+  const double bc1 = 1.0 - pow((double)beta1, (double)step);
+  const double bc2 = 1.0 - pow((double)beta2, (double)step);
+  const float step_size = (float)((double)lr / bc1);
+  const float bc2_sqrt = (float)sqrt(bc2);
+  const unsigned blocks = (unsigned)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
+  k_adam<<<blocks, 256, 0, st>>>(params, grads, exp_avg, exp_avg_sq, n, scratch, step_size,
+                                 bc2_sqrt, beta1, beta2, eps, max_norm > 0.f ? 1 : 0);
+  CU(h, cudaGetLastError());
+  return DSDF_OK;
+}
+
+extern "C" int dsdf_selftest_gemm(int32_t kind, const void* a_img, const void* b_img, float* d_out,
+                                  void* stream) {
+  if (!a_img || !b_img || !d_out || kind < 0 || kind > 1) {
+    g_err = "bad argument";
+    return DSDF_EINVAL;
+  }
+  cudaError_t e = cudaFuncSetAttribute(k_selftest_gemm, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536);
+  if (e != cudaSuccess) { g_err = cudaGetErrorString(e); return DSDF_ECUDA; }
+  k_selftest_gemm<<<1, 128, 65536, (cudaStream_t)stream>>>(kind, (const uint8_t*)a_img,
+                                                           (const uint8_t*)b_img, d_out);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) { g_err = cudaGetErrorString(e); return DSDF_ECUDA; }
+  return DSDF_OK;
+}

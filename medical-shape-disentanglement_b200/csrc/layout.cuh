@@ -1,0 +1,100 @@
+// Data layout shared by every kernel of the DeepSDF hot path.
+//
+// Network (reference networks/deep_sdf_decoder.py:25-46 with dims=[512]*8, latent 256,
+// latent_in=[4]): lin0 259->512, lin1,2 512->512, lin3 512->253, lin4 512->512 with input
+// [x3(253) | latent(256) | xyz(3)], lin5..7 512->512, lin8 512->1.
+//
+// On-chip / in-HBM activation tile ("image"): 128 rows x 64 bf16 columns = 16 KB "SUB",
+// in the canonical UMMA SWIZZLE_128B layout:
+//     byte(r, c) = (r/8)*1024 + (r%8)*128 + (((c/8) ^ (r%8)) * 16) + (c%8)*2
+// The same bytes are a K-major operand (rows = M or N, columns = K; forward / dgrad) and an
+// MN-major operand (rows = K, columns = M or N; wgrad), so activations stashed by the forward
+// and backward kernels are consumed by the wgrad kernel without any re-layout.
+// A 128-row activation tile with 512 features = 8 consecutive SUBs (128 KB).
+//
+// Padded layer geometry used by the tensor-core kernels ("pad" order):
+//   lin0 : K = latent(256)                         N = 512   + E
+//   lin3 :                                          N = 256   (253 real + 3 zero rows)
+//   lin4 : K = [x3(256: 253 real + 3 zero) | latent(256)]     + E
+//   E    : one extra K-step of 16 columns
+//          [xh xh xh | xl xl xl | xh xh xh | 1 | 1 | 0 x5]  (A side: xyz split hi/lo bf16, ones)
+//          [wh wh wh | wh wh wh | wl wl wl | bh| bl| 0 x5]  (B side: xyz weights hi/lo, bias hi/lo)
+//          => x*w to ~2^-17 relative and the bias added inside the MMA for every layer.
+#pragma once
+#include <stdint.h>
+
+namespace dsdf {
+
+constexpr int kLatent = 256;
+constexpr int kHidden = 512;
+constexpr int kNumLin = 9;       // lin0..lin8
+constexpr int kSkipLayer = 4;    // latent_in = [4]
+constexpr int kX3 = 253;         // out features of lin3
+constexpr int kIn0 = 259;
+
+constexpr int kTileM = 128;      // rows per tile (= TMEM lanes)
+constexpr int kSubCols = 64;     // bf16 columns per SUB (128 B rows)
+constexpr int kSubBytes = kTileM * kSubCols * 2;  // 16384
+constexpr int kTileBytes = 8 * kSubBytes;         // 131072: 128 rows x 512 bf16
+
+// byte offset of element (r, c) inside one SUB (r < 128, c < 64)
+__host__ __device__ __forceinline__ uint32_t sub_off(uint32_t r, uint32_t c) {
+  return (r >> 3) * 1024u + (r & 7u) * 128u + ((((c >> 3) ^ r) & 7u) << 4) + ((c & 7u) << 1);
+}
+// byte offset of 16-byte chunk `ch` (8 bf16) of row r inside one SUB
+__host__ __device__ __forceinline__ uint32_t sub_chunk_off(uint32_t r, uint32_t ch) {
+  return (r >> 3) * 1024u + (r & 7u) * 128u + (((ch ^ r) & 7u) << 4);
+}
+
+// ---- forward weight image -------------------------------------------------------------
+// per layer l (0..7): KB(l) k-blocks x NC(l) n-chunks of B tiles [128 n x 64 k] (one SUB each,
+// r = n local, c = k local), ordered kb-major then nc; followed by one E tile (SUB) holding,
+// for n-chunk j, its 16 E columns at c = 16*j .. 16*j+15.
+__host__ __device__ constexpr int fwd_kb(int l) { return l == 0 ? 4 : 8; }
+__host__ __device__ constexpr int fwd_nc(int l) { return l == 3 ? 2 : 4; }
+__host__ __device__ constexpr int fwd_tiles(int l) { return fwd_kb(l) * fwd_nc(l) + 1; }
+__host__ __device__ constexpr int fwd_tile_base(int l) {
+  int b = 0;
+  for (int i = 0; i < l; ++i) b += fwd_tiles(i);
+  return b;
+}
+constexpr int kFwdTilesTotal = fwd_tile_base(8);  // 17+33+33+17+33+33+33+33 = 232
+
+// ---- dgrad weight image (W^T) -----------------------------------------------------------
+// layer l (1..7): D[r, i] = sum_o dY[r,o] W[o,i];  B tiles [128 i x 64 o], ordered kb(o)-major
+// then nc(i).  "scene mode" only needs i in the x3 part for lin4 (NC = 2).
+// lin0 / full lin4 (general dense-input backward) are appended after the scene-mode tiles.
+__host__ __device__ constexpr int dg_kb(int l) { return l == 3 ? 4 : 8; }   // out / 64
+__host__ __device__ constexpr int dg_nc(int l) { return l == 4 ? 2 : 4; }   // in(pad) / 128
+__host__ __device__ constexpr int dg_tiles(int l) { return l == 0 ? 0 : dg_kb(l) * dg_nc(l); }
+__host__ __device__ constexpr int dg_tile_base(int l) {
+  int b = 0;
+  for (int i = 1; i < l; ++i) b += dg_tiles(i);
+  return b;
+}
+constexpr int kDgTilesTotal = dg_tile_base(8);  // 32+32+16+16+32+32+32 = 192
+
+// padded K index of layer l -> reference input column (or -1 for a zero pad column)
+__host__ __device__ __forceinline__ int pad_to_ref_col(int l, int kk) {
+  if (l == 0) return kk;  // kk < 256: latent
+  if (l == kSkipLayer) {
+    if (kk < 256) return kk < kX3 ? kk : -1;
+    return kX3 + (kk - 256);  // latent part: ref cols 253..508
+  }
+  return kk;
+}
+__host__ __device__ constexpr int ref_in(int l) { return l == 0 ? kIn0 : kHidden; }
+__host__ __device__ constexpr int ref_out(int l) { return l == 3 ? kX3 : (l == 8 ? 1 : kHidden); }
+// reference column of xyz component e (0..2) for layers with an xyz input, else -1
+__host__ __device__ constexpr int xyz_col(int l, int e) {
+  return l == 0 ? 256 + e : (l == kSkipLayer ? 509 + e : -1);
+}
+
+// ---- activation stash in HBM ---------------------------------------------------------------
+// X stash : [tile][slot 0..7][8 SUB]  slot s = input of lin(s+1) (= relu output of lin s);
+//           slot 3 (input of lin4) holds only the x3 part in SUB 0..3.
+// dY stash: [tile][slot 0..7][8 SUB]  slot l = gradient w.r.t. the pre-activation of lin l
+//           (l = 1..7 used in scene mode; lin3 has 4 SUBs).
+constexpr size_t kStashTileBytes = 8 * (size_t)kTileBytes;  // 1 MiB per 128-row tile
+
+}  // namespace dsdf

@@ -1,0 +1,11 @@
+"""dsdf_b200: B200-native (sm_100a) implementation of the DeepSDF auto-decoder hot path of
+anonymous-submission01/medical-shape-disentanglement, behind the reference's `Decoder` API.
+
+Python here is host-side plumbing only (device memory, streams, torch.distributed); the
+arithmetic is in libdsdf_b200.so (hand-written tcgen05/TMEM/TMA-engine CUDA, csrc/), reached
+through the C ABI declared in include/dsdf.h.
+"""
+from ._lib import DsdfError, LIB_PATH  # noqa: F401
+from .decoder import Decoder  # noqa: F401
+from .trainer import FusedTrainer, StepConfig  # noqa: F401
+from .mesh import create_mesh_sdf, decode_grid_sharded  # noqa: F401

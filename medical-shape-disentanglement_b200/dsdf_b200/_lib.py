@@ -1,0 +1,88 @@
+"""ctypes binding of libdsdf_b200.so (include/dsdf.h).
+
+The library is the product: if it is missing or fails to load, importing the compute entry
+points raises -- there is no PyTorch/CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libdsdf_b200.so")
+
+DSDF_NUM_LIN = 9
+
+EXPORTS = [
+    "dsdf_create", "dsdf_destroy", "dsdf_last_error", "dsdf_num_sms", "dsdf_set_weights",
+    "dsdf_forward_dense", "dsdf_forward_segments", "dsdf_decode_grid", "dsdf_grid_coords",
+    "dsdf_train_workspace_bytes", "dsdf_train_fwd_bwd", "dsdf_renorm_rows", "dsdf_clip_adam",
+    "dsdf_selftest_gemm",
+]
+
+
+class DsdfConfig(C.Structure):
+    _fields_ = [("latent_size", C.c_int32), ("hidden", C.c_int32), ("num_hidden", C.c_int32),
+                ("latent_in", C.c_int32), ("weight_norm_mask", C.c_uint32), ("device", C.c_int32)]
+
+
+class DsdfParamLayout(C.Structure):
+    _fields_ = [("w_off", C.c_int64 * DSDF_NUM_LIN), ("g_off", C.c_int64 * DSDF_NUM_LIN),
+                ("b_off", C.c_int64 * DSDF_NUM_LIN), ("total", C.c_int64)]
+
+
+class DsdfError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def lib():
+    """Load (once) and return the C library with argtypes set."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise DsdfError(
+            f"{LIB_PATH} not found: build it with `python medical-shape-disentanglement_b200/build.py` "
+            "(there is no CPU / PyTorch fallback for this path)")
+    L = C.CDLL(LIB_PATH)
+    vp, i64, i32, f32, sz = C.c_void_p, C.c_int64, C.c_int32, C.c_float, C.c_size_t
+    L.dsdf_create.argtypes = [C.POINTER(DsdfConfig), C.POINTER(vp)]
+    L.dsdf_create.restype = C.c_int
+    L.dsdf_destroy.argtypes = [vp]
+    L.dsdf_destroy.restype = C.c_int
+    L.dsdf_last_error.argtypes = [vp]
+    L.dsdf_last_error.restype = C.c_char_p
+    L.dsdf_num_sms.argtypes = [vp]
+    L.dsdf_num_sms.restype = C.c_int
+    L.dsdf_set_weights.argtypes = [vp, vp, C.POINTER(DsdfParamLayout), vp]
+    L.dsdf_set_weights.restype = C.c_int
+    L.dsdf_forward_dense.argtypes = [vp, vp, i64, vp, vp]
+    L.dsdf_forward_dense.restype = C.c_int
+    L.dsdf_forward_segments.argtypes = [vp, vp, vp, i64, i64, vp, i64, i64, vp, vp]
+    L.dsdf_forward_segments.restype = C.c_int
+    L.dsdf_decode_grid.argtypes = [vp, vp, i32, i64, i64, vp, vp]
+    L.dsdf_decode_grid.restype = C.c_int
+    L.dsdf_grid_coords.argtypes = [vp, i32, i64, i64, vp, vp]
+    L.dsdf_grid_coords.restype = C.c_int
+    L.dsdf_train_workspace_bytes.argtypes = [vp, i64, i64]
+    L.dsdf_train_workspace_bytes.restype = sz
+    L.dsdf_train_fwd_bwd.argtypes = [vp, vp, vp, i64, vp, i64, i64, vp, i64, f32, f32, vp, sz,
+                                     vp, vp, vp, vp, vp]
+    L.dsdf_train_fwd_bwd.restype = C.c_int
+    L.dsdf_renorm_rows.argtypes = [vp, vp, vp, i64, f32, vp]
+    L.dsdf_renorm_rows.restype = C.c_int
+    L.dsdf_clip_adam.argtypes = [vp, vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, i64, vp, vp]
+    L.dsdf_clip_adam.restype = C.c_int
+    L.dsdf_selftest_gemm.argtypes = [i32, vp, vp, vp, vp]
+    L.dsdf_selftest_gemm.restype = C.c_int
+    _lib = L
+    return L
+
+
+def check(rc: int, handle=None) -> None:
+    if rc != 0:
+        msg = lib().dsdf_last_error(handle)
+        raise DsdfError(f"libdsdf_b200 error {rc}: {msg.decode() if msg else '?'}")

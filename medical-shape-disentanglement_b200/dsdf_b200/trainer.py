@@ -1,0 +1,198 @@
+"""Fused auto-decoder training step: the body of the reference's hot loop
+(train_deep_sdf.py:551-616, 731, 780-784) as a handful of CUDA launches through the C ABI.
+
+    trainer = FusedTrainer(decoder, num_scenes, StepConfig(...))
+    for epoch ...:
+        for sdf_data[B,P,4], indices[B] in loader:        # same tensors the reference loop sees
+            stats = trainer.step(sdf_data, indices, epoch)
+
+State that the reference checkpoints (train_deep_sdf.py:32-79) stays in torch tensors with the
+reference's shapes: `decoder.state_dict()`, `trainer.lat_vecs` (an nn.Embedding with
+max_norm=CodeBound) and Adam moments addressable in torch.optim.Adam's state_dict format
+(`optimizer_state_dict()`).
+
+Multi-GPU (one process per GPU): scenes are owned by ranks; every rank steps on its own scenes'
+samples and latent codes (latent grads never leave the rank) and only the flat decoder gradient
+is all-reduced (SUM, F9: the loss is normalised by the *global* row count).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from dataclasses import dataclass
+from typing import Dict, Optional
+
+import torch
+
+from . import _lib
+from .decoder import LATENT, Decoder, _stream_ptr
+
+
+@dataclass
+class StepConfig:
+    """Subset of specs.json read by the step (train_deep_sdf.py:276-285, 243, 346)."""
+    clamp_dist: float = 0.1                 # ClampingDistance
+    code_reg: bool = True                   # CodeRegularization
+    code_reg_lambda: float = 1e-4           # CodeRegularizationLambda
+    code_bound: Optional[float] = None      # CodeBound
+    grad_clip: Optional[float] = None       # GradientClipNorm
+    code_init_std: float = 1.0              # CodeInitStdDev
+    lr_decoder: float = 5e-4                # LearningRateSchedule[0] (Step)
+    lr_latent: float = 1e-3                 # LearningRateSchedule[1] (Step)
+    lr_interval: int = 500
+    lr_factor: float = 0.5
+    betas: tuple = (0.9, 0.999)
+    eps: float = 1e-8
+
+    @staticmethod
+    def from_specs(specs: dict) -> "StepConfig":
+        sch = specs["LearningRateSchedule"]
+        for s in sch[:2]:
+            if s["Type"] != "Step":
+                raise NotImplementedError(f"LearningRateSchedule type {s['Type']}: pass lr explicitly to step()")
+        return StepConfig(
+            clamp_dist=specs["ClampingDistance"],
+            code_reg=specs.get("CodeRegularization", True),
+            code_reg_lambda=specs.get("CodeRegularizationLambda", 1e-4),
+            code_bound=specs.get("CodeBound", None),
+            grad_clip=specs.get("GradientClipNorm", None),
+            code_init_std=specs.get("CodeInitStdDev", 1.0),
+            lr_decoder=sch[0]["Initial"], lr_latent=sch[1]["Initial"],
+            lr_interval=sch[0]["Interval"], lr_factor=sch[0]["Factor"],
+        )
+
+
+class FusedTrainer:
+    def __init__(self, decoder: Decoder, num_scenes: int, cfg: StepConfig,
+                 process_group=None, latents: Optional[torch.Tensor] = None):
+        self.decoder = decoder
+        self.cfg = cfg
+        self.num_scenes = num_scenes
+        self.pg = process_group
+        dev = next(decoder.parameters()).device
+        if dev.type != "cuda":
+            raise _lib.DsdfError("FusedTrainer needs the decoder on a CUDA device (no CPU path)")
+        self.device = dev
+        # train_deep_sdf.py:429-435
+        self.lat_vecs = torch.nn.Embedding(num_scenes, LATENT, max_norm=cfg.code_bound)
+        if latents is None:
+            torch.nn.init.normal_(self.lat_vecs.weight.data, 0.0, cfg.code_init_std / math.sqrt(LATENT))
+        else:
+            self.lat_vecs.weight.data.copy_(latents)
+        self.lat_vecs = self.lat_vecs.to(dev)
+        flat = decoder.flat_params()
+        self.grads = torch.zeros_like(flat)
+        self.exp_avg = torch.zeros_like(flat)
+        self.exp_avg_sq = torch.zeros_like(flat)
+        self.lat_grad = torch.zeros_like(self.lat_vecs.weight.data)
+        self.lat_exp_avg = torch.zeros_like(self.lat_grad)
+        self.lat_exp_avg_sq = torch.zeros_like(self.lat_grad)
+        self.step_count = 0
+        self.scratch = torch.zeros(4096, dtype=torch.float32, device=dev)
+        self.scratch_lat = torch.zeros(4096, dtype=torch.float32, device=dev)
+        self.loss_buf = torch.zeros(4, dtype=torch.float32, device=dev)
+        self._ws = None
+        self._ws_key = None
+        self._pred = None
+
+    # ---------------------------------------------------------------- helpers
+    def lr(self, which: int, epoch: int) -> float:
+        c = self.cfg
+        init = c.lr_decoder if which == 0 else c.lr_latent
+        return init * (c.lr_factor ** (epoch // c.lr_interval))   # lr_scheduling.py:16-24
+
+    def _workspace(self, h, rows: int, segs: int):
+        key = (rows, segs)
+        if self._ws_key != key:
+            nbytes = _lib.lib().dsdf_train_workspace_bytes(h, rows, segs)
+            self._ws = None
+            self._ws = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+            self._pred = torch.empty(rows, dtype=torch.float32, device=self.device)
+            self._ws_key = key
+        return self._ws
+
+    # ---------------------------------------------------------------- the step
+    def forward_backward(self, sdf_data: torch.Tensor, indices: torch.Tensor, epoch: int,
+                         n_total: Optional[int] = None):
+        """gather + forward + loss + backward; fills self.grads / self.lat_grad (no optimiser)."""
+        L = _lib.lib()
+        c = self.cfg
+        dec = self.decoder
+        h = dec.sync_weights()
+        flat = dec.flat_params()
+        if self.grads.data_ptr() == 0 or self.grads.numel() != flat.numel():
+            raise RuntimeError("decoder parameters were re-laid out after the trainer was built")
+        assert sdf_data.is_cuda and indices.is_cuda, "inputs must already be on the GPU"
+        sdf = sdf_data.reshape(-1, 4).contiguous().float()
+        ids = indices.reshape(-1).contiguous().to(torch.int64)
+        n_seg = ids.numel()
+        rows = sdf.shape[0]
+        p = rows // n_seg
+        if n_total is None:
+            n_total = rows
+            if self.pg is not None:
+                n_total = rows * torch.distributed.get_world_size(self.pg)
+        ws = self._workspace(h, rows, n_seg)
+        st = _stream_ptr(self.device)
+        table = self.lat_vecs.weight.data
+        with torch.cuda.device(self.device):
+            if c.code_bound is not None:
+                _lib.check(L.dsdf_renorm_rows(h, table.data_ptr(), ids.data_ptr(), n_seg,
+                                              float(c.code_bound), st), h)
+            ramp = c.code_reg_lambda * min(1, epoch / 100) if c.code_reg else 0.0
+            _lib.check(L.dsdf_train_fwd_bwd(
+                h, flat.data_ptr(), table.data_ptr(), self.num_scenes, ids.data_ptr(), n_seg, p,
+                sdf.data_ptr(), int(n_total), float(c.clamp_dist), float(ramp), ws.data_ptr(),
+                ws.numel(), self.grads.data_ptr(), self.lat_grad.data_ptr(),
+                self._pred.data_ptr(), self.loss_buf.data_ptr(), st), h)
+        return self._pred
+
+    def step(self, sdf_data: torch.Tensor, indices: torch.Tensor, epoch: int,
+             n_total: Optional[int] = None, lr_decoder: Optional[float] = None,
+             lr_latent: Optional[float] = None) -> Dict[str, torch.Tensor]:
+        L = _lib.lib()
+        c = self.cfg
+        self.forward_backward(sdf_data, indices, epoch, n_total)
+        if self.pg is not None and torch.distributed.get_world_size(self.pg) > 1:
+            # only the ~1.84 M-element decoder gradient crosses NVLink; SUM (F9)
+            torch.distributed.all_reduce(self.grads, op=torch.distributed.ReduceOp.SUM, group=self.pg)
+        self.step_count += 1
+        h = self.decoder.handle()
+        flat = self.decoder.flat_params()
+        st = _stream_ptr(self.device)
+        lr0 = self.lr(0, epoch) if lr_decoder is None else lr_decoder
+        lr1 = self.lr(1, epoch) if lr_latent is None else lr_latent
+        b1, b2 = c.betas
+        with torch.cuda.device(self.device):
+            _lib.check(L.dsdf_clip_adam(
+                h, flat.data_ptr(), self.grads.data_ptr(), self.exp_avg.data_ptr(),
+                self.exp_avg_sq.data_ptr(), flat.numel(),
+                float(c.grad_clip) if c.grad_clip is not None else 0.0, float(lr0), b1, b2, c.eps,
+                self.step_count, self.scratch.data_ptr(), st), h)
+            table = self.lat_vecs.weight.data
+            _lib.check(L.dsdf_clip_adam(
+                h, table.data_ptr(), self.lat_grad.data_ptr(), self.lat_exp_avg.data_ptr(),
+                self.lat_exp_avg_sq.data_ptr(), table.numel(), 0.0, float(lr1), b1, b2, c.eps,
+                self.step_count, self.scratch_lat.data_ptr(), st), h)
+        self.decoder.sync_weights(force=True)
+        # device scalars, no host sync: [0] L1 term, [1] regulariser term (this rank's share)
+        return {"sdf_loss": self.loss_buf[0], "reg_loss": self.loss_buf[1],
+                "grad_norm": self.scratch[0]}
+
+    # ---------------------------------------------------------------- checkpoint interchange
+    def optimizer_state_dict(self) -> dict:
+        """torch.optim.Adam-format state (param order: decoder.parameters(), then lat_vecs)."""
+        state = {}
+        off = 0
+        plist = list(self.decoder.parameters())
+        for i, p in enumerate(plist):
+            n = p.numel()
+            state[i] = {"step": torch.tensor(float(self.step_count)),
+                        "exp_avg": self.exp_avg[off:off + n].view(p.shape).clone(),
+                        "exp_avg_sq": self.exp_avg_sq[off:off + n].view(p.shape).clone()}
+            off += n
+        state[len(plist)] = {"step": torch.tensor(float(self.step_count)),
+                             "exp_avg": self.lat_exp_avg.clone(),
+                             "exp_avg_sq": self.lat_exp_avg_sq.clone()}
+        groups = [{"params": list(range(len(plist)))}, {"params": [len(plist)]}]
+        return {"state": state, "param_groups": groups}
