@@ -91,7 +91,8 @@ def forward():
                 x = torch.cat([torch.randn(n, 256, generator=g) * 0.06, torch.rand(n, 3, generator=g) * 2 - 1], 1)
                 ref = deepsdf.forward({k: v.to(dev) for k, v in params.items()}, spec, x.to(dev))
                 t0 = time.time()
-                out = dec(x.to(dev))
+                with torch.no_grad():
+                    out = dec(x.to(dev))
                 torch.cuda.synchronize()
                 err = (out - ref).abs().max().item()
                 print(f"forward wn={wn} scale={scale} n={n}: max err {err:.3e}  ref range [{ref.min().item():.3f},{ref.max().item():.3f}]  ({time.time()-t0:.3f}s)")
@@ -172,8 +173,14 @@ def train(wn=True, S=8, B=4, P=256, steps=3):
         torch.cuda.synchronize()
         print("   grad norm ref", float(gn), "ours", st["grad_norm"].item())
         pf = torch.cat([orc.params[n_].data.flatten() for n_, _ in dec.named_parameters()])
-        print("   param max diff after Adam", (dec.flat_params() - pf).abs().max().item(),
+        d = (dec.flat_params() - pf).abs()
+        print("   param diff after Adam: max", d.max().item(), "mean", d.mean().item(), "(lr 5e-4)",
               " latent max diff", (tr.lat_vecs.weight.data - orc.lat_vecs.weight.data).abs().max().item())
+        # re-synchronise both sides so the next iteration compares gradients at identical weights
+        with torch.no_grad():
+            for n_, p_ in dec.named_parameters():
+                p_.copy_(orc.params[n_].data)
+            tr.lat_vecs.weight.data.copy_(orc.lat_vecs.weight.data)
 
 
 if __name__ == "__main__":
