@@ -130,6 +130,14 @@ int dsdf_clip_adam(dsdf_handle h, float* params, float* grads, float* exp_avg, f
                    int64_t n, float max_norm, float lr, float beta1, float beta2, float eps,
                    int64_t step, float* scratch, void* stream);
 
+/* Per-kernel timing of dsdf_train_fwd_bwd with CUDA events recorded on the caller's stream
+ * (the stream the kernels are launched on).  After enable(1) every call records 5 events;
+ * read() synchronises on them and returns, summed over the n_calls recorded calls, the
+ * milliseconds of ms_sum[0] forward kernel, [1] backward (dgrad chain) kernel, [2] wgrad kernel,
+ * [3] the small reduction kernels.  enable(0/1) also clears the recorded events. */
+int dsdf_profile_enable(dsdf_handle h, int32_t enable);
+int dsdf_profile_read(dsdf_handle h, float* ms_sum, int32_t* n_calls);
+
 /* Descriptor self-test: one-tile GEMMs through the same UMMA descriptor helpers.
  * kind 0: K-major  A[128x64] (1 SUB), B[128x64] (1 SUB) -> D[128][128] = A B^T
  * kind 1: MN-major A (2 SUBs), B (4 SUBs), K = rows 0..31 -> D[128][256] = A^T B */

@@ -41,7 +41,20 @@ struct dsdf_handle_s {
   ParamLayout pl{};
   bool weights_set = false;
   bool attrs_set = false;
+  // optional per-kernel timing (CUDA events on the caller's stream), see dsdf_profile_*
+  bool profile = false;
+  std::vector<cudaEvent_t> prof_events;   // 5 per dsdf_train_fwd_bwd call
 };
+constexpr int kProfEventsPerCall = 5;
+constexpr int kProfMaxCalls = 512;
+
+static void prof_mark(dsdf_handle h, cudaStream_t st) {
+  if (!h->profile || (int)h->prof_events.size() >= kProfMaxCalls * kProfEventsPerCall) return;
+  cudaEvent_t e;
+  if (cudaEventCreate(&e) != cudaSuccess) return;
+  cudaEventRecord(e, st);
+  h->prof_events.push_back(e);
+}
 
 static thread_local std::string g_err;
 
@@ -134,6 +147,7 @@ extern "C" int dsdf_destroy(dsdf_handle h) {
   cudaFree(h->scale);
   cudaFree(h->inv_norm);
   cudaFree(h->wg_items);
+  for (cudaEvent_t e : h->prof_events) cudaEventDestroy(e);
   delete h;
   return DSDF_OK;
 }
@@ -394,7 +408,10 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   fa.fused_loss = 1;
   fa.clamp_dist = clamp_dist;
   fa.inv_n_total = inv_n;
+  const bool prof = h->profile && (int)h->prof_events.size() + kProfEventsPerCall <= kProfMaxCalls * kProfEventsPerCall;
+  if (prof) prof_mark(h, st);
   k_forward<MODE_TABLE, true><<<grid, kFwdThreads, kFwdSmemBytes, st>>>(fa);
+  if (prof) prof_mark(h, st);
 
   // ---- backward dgrad chain + reducers
   BwdArgs ba;
@@ -410,6 +427,7 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   ba.tile_colsum = w.tile_colsum;
   ba.cta_partials = w.cta_partials;
   k_backward<<<grid, kBwdThreads, kBwdSmemBytes, st>>>(ba);
+  if (prof) prof_mark(h, st);
 
   // ---- wgrad GEMMs (lin1..lin7) + split-K reduction
   WgArgs wa;
@@ -418,6 +436,7 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   wa.dystash = w.dystash;
   wa.partials = w.wg_partials;
   k_wgrad<<<h->wg_n_items, kWgThreads, kWgSmemBytes, st>>>(wa);
+  if (prof) prof_mark(h, st);
   k_reduce_wgrad<<<dim3(kHidden, 7), kHidden, 0, st>>>(w.wg_partials, h->wg_layout, w.dweff);
 
   // ---- segmented (scene-contiguous) reductions: latent grads, latent columns of dW0/dW4, biases
@@ -435,7 +454,33 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   k_param_grads<<<(kScaleElems * 32 + 255) / 256, 256, 0, st>>>(w.dweff, params, h->pl, h->scale,
                                                                 h->inv_norm, grads);
   k_loss<<<1, 1024, 0, st>>>(w.tile_partials, tiles, inv_n, w.seg_norm, (int)n_seg, reg_coef, loss_out);
+  if (prof) prof_mark(h, st);
   CU(h, cudaGetLastError());
+  return DSDF_OK;
+}
+
+extern "C" int dsdf_profile_enable(dsdf_handle h, int32_t enable) {
+  if (!h) return DSDF_EINVAL;
+  for (cudaEvent_t e : h->prof_events) cudaEventDestroy(e);
+  h->prof_events.clear();
+  h->profile = enable != 0;
+  return DSDF_OK;
+}
+
+extern "C" int dsdf_profile_read(dsdf_handle h, float* ms_sum, int32_t* n_calls) {
+  if (!h || !ms_sum || !n_calls) DSDF_FAIL(h, DSDF_EINVAL, "null argument");
+  const int calls = (int)h->prof_events.size() / kProfEventsPerCall;
+  for (int k = 0; k < 4; ++k) ms_sum[k] = 0.f;
+  for (int c = 0; c < calls; ++c) {
+    cudaEvent_t* e = &h->prof_events[(size_t)c * kProfEventsPerCall];
+    CU(h, cudaEventSynchronize(e[4]));
+    for (int k = 0; k < 4; ++k) {
+      float ms = 0.f;
+      CU(h, cudaEventElapsedTime(&ms, e[k], e[k + 1]));
+      ms_sum[k] += ms;
+    }
+  }
+  *n_calls = calls;
   return DSDF_OK;
 }
 

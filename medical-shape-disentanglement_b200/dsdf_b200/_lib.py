@@ -17,7 +17,7 @@ EXPORTS = [
     "dsdf_create", "dsdf_destroy", "dsdf_last_error", "dsdf_num_sms", "dsdf_set_weights",
     "dsdf_forward_dense", "dsdf_forward_segments", "dsdf_decode_grid", "dsdf_grid_coords",
     "dsdf_train_workspace_bytes", "dsdf_train_fwd_bwd", "dsdf_renorm_rows", "dsdf_clip_adam",
-    "dsdf_selftest_gemm",
+    "dsdf_selftest_gemm", "dsdf_profile_enable", "dsdf_profile_read",
 ]
 
 
@@ -78,6 +78,10 @@ def lib():
     L.dsdf_clip_adam.restype = C.c_int
     L.dsdf_selftest_gemm.argtypes = [i32, vp, vp, vp, vp]
     L.dsdf_selftest_gemm.restype = C.c_int
+    L.dsdf_profile_enable.argtypes = [vp, i32]
+    L.dsdf_profile_enable.restype = C.c_int
+    L.dsdf_profile_read.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_int32)]
+    L.dsdf_profile_read.restype = C.c_int
     _lib = L
     return L
 

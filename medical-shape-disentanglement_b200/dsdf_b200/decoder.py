@@ -192,6 +192,8 @@ class Decoder(nn.Module):
         x = input.detach().contiguous().float()
         n = x.shape[0]
         out = torch.empty(n, dtype=torch.float32, device=x.device)
+        if n == 0:
+            return out.view(0, 1)
         with torch.cuda.device(x.device):
             _lib.check(_lib.lib().dsdf_forward_dense(h, x.data_ptr(), n, out.data_ptr(),
                                                      _stream_ptr(x.device)), h)
@@ -207,6 +209,8 @@ class Decoder(nn.Module):
         q = queries.detach().contiguous().float()
         n = q.shape[0]
         out = torch.empty(n, dtype=torch.float32, device=q.device)
+        if n == 0:
+            return out.view(0, 1)
         with torch.cuda.device(q.device):
             _lib.check(_lib.lib().dsdf_forward_segments(h, lat.data_ptr(), None, 1, n, q.data_ptr(),
                                                         q.shape[1], n, out.data_ptr(),

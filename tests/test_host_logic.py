@@ -1,0 +1,112 @@
+"""CPU tests of the host side: reference-compatible module surface, configuration errors,
+parameter addressing, the C-ABI library's exports (no compute calls without a GPU)."""
+import ctypes as C
+import os
+import re
+
+import pytest
+import torch
+
+import dsdf_b200
+from common import spec_for
+from dsdf_b200 import _lib, dist
+from dsdf_b200.trainer import StepConfig
+from oracle import deepsdf
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+KW = dict(dims=[512] * 8, dropout=[], dropout_prob=0.2, latent_in=[4], xyz_in_all=False,
+          use_tanh=False, latent_dropout=False, weight_norm=True)
+
+
+@pytest.mark.parametrize("wn", [False, True])
+def test_decoder_has_reference_parameters(wn):
+    torch.manual_seed(0)
+    dec = dsdf_b200.Decoder(256, norm_layers=list(range(8)) if wn else [], **KW)
+    p = deepsdf.init_params(spec_for(wn), seed=0)
+    sd = dec.state_dict()
+    assert list(sd.keys()) == list(p.keys())
+    for k in sd:
+        assert torch.equal(sd[k], p[k]), k          # same RNG stream as the reference ctor
+    assert [n for n, _ in dec.named_parameters()] == list(p.keys())
+
+
+def test_flat_parameter_views_and_layout():
+    dec = dsdf_b200.Decoder(256, norm_layers=list(range(8)), **KW)
+    before = {k: v.clone() for k, v in dec.state_dict().items()}
+    flat = dec.flat_params()
+    assert flat.numel() == 1843195 == dec._layout.total
+    off = 0
+    for name, p in dec.named_parameters():
+        assert p.data_ptr() == flat.data_ptr() + 4 * off
+        assert torch.equal(p.data, before[name])
+        off += p.numel()
+    lay = dec._layout
+    assert lay.g_off[8] == -1 and all(lay.g_off[l] >= 0 for l in range(8))
+    # load_state_dict keeps the views (in-place copy)
+    dec.load_state_dict({k: v * 2 for k, v in before.items()})
+    assert dec.flat_params().data_ptr() == flat.data_ptr()
+    assert torch.equal(dec.lin3.weight_v.data, before["lin3.weight_v"] * 2)
+
+
+@pytest.mark.parametrize("kw,key", [
+    (dict(dims=[256] * 8), "dims"), (dict(latent_in=[2]), "latent_in"), (dict(xyz_in_all=True), "xyz_in_all"),
+    (dict(use_tanh=True), "use_tanh"), (dict(latent_dropout=True), "latent_dropout"),
+    (dict(weight_norm=False, norm_layers=[0, 1]), "norm_layers"),
+])
+def test_unsupported_specs_raise_naming_the_key(kw, key):
+    args = dict(KW); args.setdefault("norm_layers", []); args.update(kw)
+    with pytest.raises(NotImplementedError, match=key):
+        dsdf_b200.Decoder(256, **args)
+    with pytest.raises(NotImplementedError, match="CodeLength"):
+        dsdf_b200.Decoder(128, norm_layers=[], **KW)
+
+
+def test_no_cpu_fallback():
+    dec = dsdf_b200.Decoder(256, norm_layers=[], **KW)
+    with pytest.raises(dsdf_b200.DsdfError):
+        dec(torch.zeros(4, 259))
+
+
+def test_library_loads_and_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "dsdf.h")).read()
+    declared = sorted(set(re.findall(r"\b(dsdf_[a-z_0-9]+)\s*\(", hdr)))
+    assert len(declared) >= 16
+    L = _lib.lib()
+    for name in declared:
+        assert hasattr(L, name), name
+    assert sorted(_lib.EXPORTS) == declared
+    assert C.sizeof(_lib.DsdfConfig) == 24 and C.sizeof(_lib.DsdfParamLayout) == 8 * 28
+
+
+def test_create_fails_loudly_without_gpu():
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    cfg = _lib.DsdfConfig(256, 512, 8, 4, 0, 0)
+    h = C.c_void_p()
+    rc = _lib.lib().dsdf_create(C.byref(cfg), C.byref(h))
+    assert rc == -2 and b"no CPU fallback" in _lib.lib().dsdf_last_error(None)
+    # unsupported network -> DSDF_EUNSUPPORTED before touching the device
+    cfg = _lib.DsdfConfig(128, 512, 8, 4, 0, 0)
+    assert _lib.lib().dsdf_create(C.byref(cfg), C.byref(h)) == -4
+
+
+def test_step_config_from_reference_specs():
+    import json
+    specs = json.loads("""{"ClampingDistance":0.1,"CodeRegularization":true,"CodeRegularizationLambda":1e-4,
+      "CodeBound":1.0,"GradientClipNorm":1.0,"LearningRateSchedule":[
+      {"Type":"Step","Initial":0.0005,"Interval":500,"Factor":0.5},{"Type":"Step","Initial":0.001,"Interval":500,"Factor":0.5}]}""")
+    c = StepConfig.from_specs(specs)
+    assert (c.clamp_dist, c.code_bound, c.grad_clip, c.lr_decoder, c.lr_latent) == (0.1, 1.0, 1.0, 5e-4, 1e-3)
+
+
+def test_scene_partition_is_a_partition():
+    for S, W in [(800, 8), (16, 3), (7, 8), (4096, 4)]:
+        seen = []
+        for r in range(W):
+            o = dist.owned_scenes(S, r, W)
+            seen += list(o)
+            for s in o:
+                assert dist.owner_of(s, S, W) == r
+        assert seen == list(range(S))
+    assert sum(dist.local_batch(64, r, 8) for r in range(8)) == 64
+    assert sum(dist.local_batch(24, r, 8) for r in range(8)) == 24
