@@ -148,15 +148,19 @@ class Decoder(nn.Module):
         return h
 
     def _release(self):
-        if getattr(self, "_handle", None) is not None:
+        h = self.__dict__.get("_handle", None)
+        if h is not None:
+            self.__dict__["_handle"] = None      # plain dict write: safe during interpreter teardown
             try:
-                _lib.lib().dsdf_destroy(self._handle)
+                _lib.lib().dsdf_destroy(h)
             except Exception:
                 pass
-            self._handle = None
 
     def __del__(self):
-        self._release()
+        try:
+            self._release()
+        except Exception:
+            pass
 
     def sync_weights(self, force: bool = False):
         """Fold fp32 masters -> bf16 tensor-core images if any parameter changed."""

@@ -297,7 +297,9 @@ def test_loss_trajectory_free_running_within_reproducibility_horizon():
     """Free-running 500 steps, fused path vs oracle, each with its own optimiser state.  The
     comparison is meaningful only while the reference reproduces itself: a second oracle whose
     initial latents are perturbed by 1e-6 (relative) defines the horizon = first step where it
-    deviates from the oracle by > 0.5 %.  Up to that horizon the fused path must stay within 1 %."""
+    deviates from the oracle by > 1e-4 (the 1e-6 perturbation amplified 100x by the dynamics; the
+    fused path's own bf16 perturbation is ~1e-4 in the loss, so 100x of it is the 1 % bound).
+    Up to that horizon the fused path must stay within 1 %."""
     S, B, P = 16, 8, 2048
     lr = 0.02
     torch.manual_seed(0)
@@ -322,7 +324,7 @@ def test_loss_trajectory_free_running_within_reproducibility_horizon():
         b.append(st["sdf_loss"] + st["reg_loss"])
     a = np.array(a); c = np.array(c); b = torch.stack(b).cpu().numpy()
     dev_ref = np.abs(c - a) / a
-    horizon = int(np.argmax(dev_ref > 0.005)) if (dev_ref > 0.005).any() else 500
+    horizon = int(np.argmax(dev_ref > 1e-4)) if (dev_ref > 1e-4).any() else 500
     rel = np.abs(b - a) / a
     print("reproducibility horizon", horizon, "max rel within horizon", rel[:horizon].max())
     assert horizon >= 100
