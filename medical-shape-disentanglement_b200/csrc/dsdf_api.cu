@@ -7,6 +7,7 @@
 
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -15,6 +16,7 @@
 #include "bwd_kernel.cuh"
 #include "fold_kernels.cuh"
 #include "fwd_kernel.cuh"
+#include "fwd2_kernel.cuh"
 #include "layout.cuh"
 #include "selftest.cuh"
 #include "small_kernels.cuh"
@@ -30,6 +32,11 @@ struct dsdf_handle_s {
   // handle-owned device buffers (bf16 shadows + small fp32 derived state)
   uint8_t* fwd_img = nullptr;
   uint8_t* dg_img = nullptr;
+  uint8_t* w2_img = nullptr;     // v2 forward K-step stream
+  uint8_t* scene_e = nullptr;    // fold-mode per-segment E steps for the inference entries
+  long long scene_e_cap = 0;     // segments
+  int fwd_cl = 2;                // cluster size of the forward chain (DSDF_FWD_CL = 1|2|4)
+  bool fwd_v1 = false;           // DSDF_FWD_V1=1: previous-generation forward kernel (A/B timing)
   float* weff = nullptr;
   float* scale = nullptr;
   float* inv_norm = nullptr;
@@ -39,6 +46,7 @@ struct dsdf_handle_s {
   int wg_n_items = 0;
   WgLayout wg_layout{};
   ParamLayout pl{};
+  const float* params_ptr = nullptr;   // caller's flat fp32 parameters at the last dsdf_set_weights
   bool weights_set = false;
   bool attrs_set = false;
   // optional per-kernel timing (CUDA events on the caller's stream), see dsdf_profile_*
@@ -81,6 +89,16 @@ static int set_kernel_attrs(dsdf_handle h) {
   CU(h, cudaFuncSetAttribute(k_forward<MODE_TABLE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmemBytes));
   CU(h, cudaFuncSetAttribute(k_forward<MODE_GRID, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmemBytes));
   CU(h, cudaFuncSetAttribute(k_forward<MODE_TABLE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmemBytes));
+#define F2ATTR(MODE, FOLD, TRAIN)                                                                                   \
+  CU(h, cudaFuncSetAttribute(k_forward2<MODE, FOLD, TRAIN, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kF2SmemBytes)); \
+  CU(h, cudaFuncSetAttribute(k_forward2<MODE, FOLD, TRAIN, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kF2SmemBytes)); \
+  CU(h, cudaFuncSetAttribute(k_forward2<MODE, FOLD, TRAIN, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kF2SmemBytes));
+  F2ATTR(MODE_DENSE, false, false)
+  F2ATTR(MODE_TABLE, false, false)
+  F2ATTR(MODE_TABLE, true, false)
+  F2ATTR(MODE_GRID, true, false)
+  F2ATTR(MODE_TABLE, true, true)
+#undef F2ATTR
   CU(h, cudaFuncSetAttribute(k_backward, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmemBytes));
   CU(h, cudaFuncSetAttribute(k_wgrad, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgSmemBytes));
   CU(h, cudaFuncSetAttribute(k_selftest_gemm, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
@@ -119,7 +137,13 @@ extern "C" int dsdf_create(const dsdf_config* cfg, dsdf_handle* out) {
               cfg->device, prop.major, prop.minor);
   }
   h->num_sms = prop.multiProcessorCount;
+  if (const char* e = getenv("DSDF_FWD_CL")) {
+    const int cl = atoi(e);
+    if (cl == 1 || cl == 2 || cl == 4) h->fwd_cl = cl;
+  }
+  if (const char* e = getenv("DSDF_FWD_V1")) h->fwd_v1 = atoi(e) != 0;
   bool ok = cudaMalloc(&h->fwd_img, (size_t)kFwdTilesTotal * kSubBytes) == cudaSuccess &&
+            cudaMalloc(&h->w2_img, (size_t)kW2Steps * kStepBytes) == cudaSuccess &&
             cudaMalloc(&h->dg_img, (size_t)kDgTilesTotal * kSubBytes) == cudaSuccess &&
             cudaMalloc(&h->weff, (size_t)(kWeffElems + 16) * 4) == cudaSuccess &&
             cudaMalloc(&h->scale, (size_t)kScaleElems * 4) == cudaSuccess &&
@@ -143,6 +167,8 @@ extern "C" int dsdf_destroy(dsdf_handle h) {
   if (!h) return DSDF_OK;
   cudaFree(h->fwd_img);
   cudaFree(h->dg_img);
+  cudaFree(h->w2_img);
+  cudaFree(h->scene_e);
   cudaFree(h->weff);
   cudaFree(h->scale);
   cudaFree(h->inv_norm);
@@ -171,9 +197,12 @@ extern "C" int dsdf_set_weights(dsdf_handle h, const float* params, const dsdf_p
   k_weff<<<(unsigned)((kWeffElems + 255) / 256), 256, 0, st>>>(params, h->pl, h->scale, h->weff);
   const long long c1 = (long long)kFwdTilesTotal * (kSubBytes / 16);
   k_fold_fwd<<<(unsigned)((c1 + 255) / 256), 256, 0, st>>>(h->weff, params, h->pl, h->fwd_img);
+  const long long c3 = (long long)kW2Steps * (kStepBytes / 16);
+  k_fold_fwd2<<<(unsigned)((c3 + 255) / 256), 256, 0, st>>>(h->weff, params, h->pl, h->w2_img);
   const long long c2 = (long long)kDgTilesTotal * (kSubBytes / 16);
   k_fold_dgrad<<<(unsigned)((c2 + 255) / 256), 256, 0, st>>>(h->weff, h->dg_img);
   CU(h, cudaGetLastError());
+  h->params_ptr = params;
   h->weights_set = true;
   return DSDF_OK;
 }
@@ -181,6 +210,48 @@ extern "C" int dsdf_set_weights(dsdf_handle h, const float* params, const dsdf_p
 static unsigned grid_for(dsdf_handle h, long long n_rows) {
   const long long tiles = (n_rows + kTileM - 1) / kTileM;
   return (unsigned)(tiles < h->num_sms ? tiles : h->num_sms);
+}
+
+// ---- v2 forward launcher: persistent grid of clusters ------------------------------------------
+template <int MODE, bool FOLD, bool TRAIN, int CL>
+static cudaError_t launch_fwd2_cl(dsdf_handle h, const FwdArgs& a, cudaStream_t st) {
+  const long long tiles = (a.n_rows + kTileM - 1) / kTileM;
+  long long g = tiles < h->num_sms ? tiles : h->num_sms;
+  g = (g / CL) * CL;
+  if (g < CL) g = CL;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3((unsigned)g);
+  cfg.blockDim = dim3(kF2Threads);
+  cfg.dynamicSmemBytes = kF2SmemBytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CL;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, k_forward2<MODE, FOLD, TRAIN, CL>, a);
+}
+template <int MODE, bool FOLD, bool TRAIN>
+static cudaError_t launch_fwd2(dsdf_handle h, const FwdArgs& a, cudaStream_t st) {
+  const long long tiles = (a.n_rows + kTileM - 1) / kTileM;
+  int cl = h->fwd_cl;
+  while (cl > 1 && tiles < cl) cl >>= 1;
+  if (cl == 4) return launch_fwd2_cl<MODE, FOLD, TRAIN, 4>(h, a, st);
+  if (cl == 2) return launch_fwd2_cl<MODE, FOLD, TRAIN, 2>(h, a, st);
+  return launch_fwd2_cl<MODE, FOLD, TRAIN, 1>(h, a, st);
+}
+// per-segment E steps for the fold-mode inference entries (handle-owned, grown on demand)
+static int ensure_scene_e(dsdf_handle h, long long n_seg) {
+  if (n_seg <= h->scene_e_cap) return DSDF_OK;
+  cudaFree(h->scene_e);
+  h->scene_e = nullptr;
+  h->scene_e_cap = 0;
+  CU(h, cudaMalloc(&h->scene_e, (size_t)n_seg * kSceneESteps * kStepBytes));
+  h->scene_e_cap = n_seg;
+  return DSDF_OK;
 }
 
 extern "C" int dsdf_forward_dense(dsdf_handle h, const float* input, int64_t n, float* out,
@@ -196,7 +267,12 @@ extern "C" int dsdf_forward_dense(dsdf_handle h, const float* input, int64_t n, 
   a.n_rows = n;
   a.input = input;
   a.out = out;
-  k_forward<MODE_DENSE, false><<<grid_for(h, n), kFwdThreads, kFwdSmemBytes, (cudaStream_t)stream>>>(a);
+  a.w2img = h->w2_img;
+  if (h->fwd_v1) {
+    k_forward<MODE_DENSE, false><<<grid_for(h, n), kFwdThreads, kFwdSmemBytes, (cudaStream_t)stream>>>(a);
+  } else {
+    CU(h, (launch_fwd2<MODE_DENSE, false, false>(h, a, (cudaStream_t)stream)));
+  }
   CU(h, cudaGetLastError());
   return DSDF_OK;
 }
@@ -222,7 +298,21 @@ extern "C" int dsdf_forward_segments(dsdf_handle h, const float* table, const in
   a.xyzs = xyz;
   a.xyz_stride = xyz_stride;
   a.out = out;
-  k_forward<MODE_TABLE, false><<<grid_for(h, n), kFwdThreads, kFwdSmemBytes, (cudaStream_t)stream>>>(a);
+  a.w2img = h->w2_img;
+  if (h->fwd_v1) {
+    k_forward<MODE_TABLE, false><<<grid_for(h, n), kFwdThreads, kFwdSmemBytes, (cudaStream_t)stream>>>(a);
+  } else if (!seg_ids || rows_per_seg % kTileM == 0) {
+    // every 128-row tile lies inside one segment: fold W[:, latent] z into a per-segment bias
+    const long long ns = seg_ids ? n_seg : 1;
+    int rc = ensure_scene_e(h, ns);
+    if (rc != DSDF_OK) return rc;
+    a.scene_e = h->scene_e;
+    k_scene_fold<<<dim3((unsigned)ns, 2), 512, 0, (cudaStream_t)stream>>>(
+        h->weff, h->params_ptr, h->pl, table, (const long long*)seg_ids, h->scene_e);
+    CU(h, (launch_fwd2<MODE_TABLE, true, false>(h, a, (cudaStream_t)stream)));
+  } else {
+    CU(h, (launch_fwd2<MODE_TABLE, false, false>(h, a, (cudaStream_t)stream)));
+  }
   CU(h, cudaGetLastError());
   return DSDF_OK;
 }
@@ -245,7 +335,17 @@ extern "C" int dsdf_decode_grid(dsdf_handle h, const float* latent, int32_t grid
   a.grid_lo = lo;
   a.voxel_size = (float)(2.0 / (grid_n - 1));
   a.out = out;
-  k_forward<MODE_GRID, false><<<grid_for(h, a.n_rows), kFwdThreads, kFwdSmemBytes, (cudaStream_t)stream>>>(a);
+  a.w2img = h->w2_img;
+  if (h->fwd_v1) {
+    k_forward<MODE_GRID, false><<<grid_for(h, a.n_rows), kFwdThreads, kFwdSmemBytes, (cudaStream_t)stream>>>(a);
+  } else {
+    int rc = ensure_scene_e(h, 1);
+    if (rc != DSDF_OK) return rc;
+    a.scene_e = h->scene_e;
+    k_scene_fold<<<dim3(1, 2), 512, 0, (cudaStream_t)stream>>>(h->weff, h->params_ptr, h->pl, latent,
+                                                               nullptr, h->scene_e);
+    CU(h, (launch_fwd2<MODE_GRID, true, false>(h, a, (cudaStream_t)stream)));
+  }
   CU(h, cudaGetLastError());
   return DSDF_OK;
 }
@@ -285,6 +385,7 @@ struct Ws {
   float* dlat_seg;
   float* seg_norm;
   float* dweff;
+  uint8_t* scene_e;
   size_t total;
 };
 inline size_t al(size_t x) { return (x + 1023) & ~(size_t)1023; }
@@ -307,6 +408,7 @@ Ws carve(uint8_t* base, long long max_rows, long long max_seg, int num_sms) {
   w.dlat_seg = (float*)take((size_t)max_seg * kLatent * 4);
   w.seg_norm = (float*)take((size_t)max_seg * 4);
   w.dweff = (float*)take((size_t)kWeffElems * 4);
+  w.scene_e = take((size_t)max_seg * kSceneESteps * kStepBytes);
   w.total = o;
   return w;
 }
@@ -410,7 +512,15 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   fa.inv_n_total = inv_n;
   const bool prof = h->profile && (int)h->prof_events.size() + kProfEventsPerCall <= kProfMaxCalls * kProfEventsPerCall;
   if (prof) prof_mark(h, st);
-  k_forward<MODE_TABLE, true><<<grid, kFwdThreads, kFwdSmemBytes, st>>>(fa);
+  fa.w2img = h->w2_img;
+  fa.scene_e = w.scene_e;
+  if (h->fwd_v1) {
+    k_forward<MODE_TABLE, true><<<grid, kFwdThreads, kFwdSmemBytes, st>>>(fa);
+  } else {
+    k_scene_fold<<<dim3((unsigned)n_seg, 2), 512, 0, st>>>(h->weff, params, h->pl, table,
+                                                          (const long long*)seg_ids, w.scene_e);
+    CU(h, (launch_fwd2<MODE_TABLE, true, true>(h, fa, st)));
+  }
   if (prof) prof_mark(h, st);
 
   // ---- backward dgrad chain + reducers

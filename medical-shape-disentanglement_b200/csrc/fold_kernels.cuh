@@ -162,3 +162,101 @@ __global__ void k_fold_dgrad(const float* __restrict__ weff, uint8_t* __restrict
 }
 
 }  // namespace dsdf
+
+namespace dsdf {
+
+// E-step row of output feature o of layer l with bias value `bias`:
+// [wxh wyh wzh | wxh wyh wzh | wxl wyl wzl | bh | bl | 0 x5]  (two 16 B chunks)
+__device__ __forceinline__ void e_step_row(const float* weff, int l, int o, bool o_valid,
+                                           float bias, uint4& c0, uint4& c1) {
+  float v[16];
+#pragma unroll
+  for (int e = 0; e < 16; ++e) v[e] = 0.f;
+  if (o_valid) {
+#pragma unroll
+    for (int e = 0; e < 3; ++e) {
+      const int xc = xyz_col(l, e);
+      if (xc >= 0) {
+        const float w = weff_at(weff, l, o, xc);
+        const float wh = __bfloat162float(__float2bfloat16_rn(w));
+        v[e] = wh; v[3 + e] = wh; v[6 + e] = w - wh;
+      }
+    }
+    const float bh = __bfloat162float(__float2bfloat16_rn(bias));
+    v[9] = bh; v[10] = bias - bh;
+  }
+  c0 = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+  c1 = make_uint4(pack_bf16x2(v[8], v[9]), pack_bf16x2(v[10], v[11]), pack_bf16x2(v[12], v[13]), pack_bf16x2(v[14], v[15]));
+}
+
+// v2 forward K-step stream (layout.cuh): one thread per 16-byte chunk
+__global__ void k_fold_fwd2(const float* __restrict__ weff, const float* __restrict__ params,
+                            ParamLayout pl, uint8_t* __restrict__ img) {
+  const long long cidx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long total = (long long)kW2Steps * (kStepBytes / 16);
+  if (cidx >= total) return;
+  const int step = (int)(cidx / (kStepBytes / 16));
+  const int within = (int)(cidx % (kStepBytes / 16));
+  const int n = ((within >> 4) << 3) | (within & 7);   // [n/8][k/8][n%8]
+  const int kc = (within >> 3) & 1;
+  int l = 0;
+  while (l + 1 < 8 && step >= w2_layer_base(l + 1)) ++l;
+  const int sl = step - w2_layer_base(l);
+  const int h = sl / w2_half_steps(l), s = sl % w2_half_steps(l);
+  const int o = h * 256 + n;
+  const bool ov = o < ref_out(l);
+  uint4 w;
+  if (s == 0) {
+    uint4 c0, c1;
+    e_step_row(weff, l, o, ov, ov ? params[pl.b[l] + o] : 0.f, c0, c1);
+    w = kc == 0 ? c0 : c1;
+  } else {
+    float vals[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int ic = pad_to_ref_col(l, (s - 1) * 16 + kc * 8 + e);
+      vals[e] = (ov && ic >= 0) ? weff_at(weff, l, o, ic) : 0.f;
+    }
+    w.x = pack_bf16x2(vals[0], vals[1]); w.y = pack_bf16x2(vals[2], vals[3]);
+    w.z = pack_bf16x2(vals[4], vals[5]); w.w = pack_bf16x2(vals[6], vals[7]);
+  }
+  *reinterpret_cast<uint4*>(img + (size_t)step * kStepBytes + (size_t)within * 16) = w;
+}
+
+// Fold mode: per-segment E steps of lin0 / lin4 with bias' = b + W[:, latent] z_seg (fp32).
+// grid (n_seg, 2), 512 threads; warp w computes rows o = w, w+16, ... (coalesced over the latent).
+// seg_ids == nullptr: one segment whose latent is `table` itself.
+__global__ void __launch_bounds__(512) k_scene_fold(const float* __restrict__ weff,
+                                                    const float* __restrict__ params, ParamLayout pl,
+                                                    const float* __restrict__ table,
+                                                    const long long* __restrict__ seg_ids,
+                                                    uint8_t* __restrict__ scene_e) {
+  __shared__ float z[kLatent];
+  __shared__ float bias[kHidden];
+  const int b = blockIdx.x, which = blockIdx.y;
+  const int l = which == 0 ? 0 : kSkipLayer;
+  const int lat0 = which == 0 ? 0 : kX3;   // first latent column in the reference weight
+  const float* zr = table + (seg_ids ? seg_ids[b] * kLatent : 0);
+  if (threadIdx.x < kLatent) z[threadIdx.x] = zr[threadIdx.x];
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int o = warp; o < kHidden; o += 16) {
+    const float* wr = weff + weff_off(l) + (size_t)o * ref_in(l) + lat0;
+    float acc = 0.f;
+#pragma unroll
+    for (int k = 0; k < kLatent / 32; ++k) acc = fmaf(wr[lane + 32 * k], z[lane + 32 * k], acc);
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, s);
+    if (lane == 0) bias[o] = acc + params[pl.b[l] + o];
+  }
+  __syncthreads();
+  const int o = threadIdx.x, h = o >> 8, n = o & 255;
+  uint4 c0, c1;
+  e_step_row(weff, l, o, true, bias[o], c0, c1);
+  uint8_t* dst = scene_e + ((size_t)b * kSceneESteps + which * 2 + h) * kStepBytes +
+                 (size_t)(n >> 3) * 256 + (size_t)(n & 7) * 16;
+  *reinterpret_cast<uint4*>(dst) = c0;
+  *reinterpret_cast<uint4*>(dst + 128) = c1;
+}
+
+}  // namespace dsdf

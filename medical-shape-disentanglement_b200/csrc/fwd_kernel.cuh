@@ -35,6 +35,8 @@ struct FwdArgs {
   float voxel_size;
   // weights
   const uint8_t* wimg;  // forward weight image (layout.cuh)
+  const uint8_t* w2img;    // v2 K-step stream (layout.cuh)
+  const uint8_t* scene_e;  // v2 fold mode: per-segment E steps [seg][kSceneESteps][kStepBytes]
   const float* w8;      // [512] effective lin8 weight (fp32)
   const float* b8;      // [1]
   // outputs

@@ -60,6 +60,35 @@ __host__ __device__ constexpr int fwd_tile_base(int l) {
 }
 constexpr int kFwdTilesTotal = fwd_tile_base(8);  // 17+33+33+17+33+33+33+33 = 232
 
+// ---- v2 forward weight stream ("K-step image") ----------------------------------------------
+// The v2 forward chain consumes B as a stream of K-steps: one step = [256 n x 16 k] bf16 = 8 KB in
+// the canonical no-swizzle K-major UMMA layout (8 n-rows x 16 B core matrices, 128 B each):
+//     byte(n, k) = (n/8)*256 + (k/8)*128 + (n%8)*16 + (k%8)*2          (LBO = 128, SBO = 256)
+// Per layer l (0..7) and output half h (n in [256h, 256h+256); lin3 has only h = 0):
+//     step 0      : E step  [wxh wyh wzh | wxh wyh wzh | wxl wyl wzl | bh | bl | 0 x5]
+//     step 1 + s  : padded-K columns 16s .. 16s+15 of W_l   (pad order: pad_to_ref_col)
+// lin4's first 16 W steps are the x3 part, the last 16 the latent part; lin0 has 16 (latent).
+// In "fold" mode (all rows of a tile share one latent) the latent steps are skipped and the E
+// steps of lin0/lin4 come from a per-segment image with bias' = b + W[:, latent] z (fp32, hi/lo).
+constexpr int kStepBytes = 8192;
+__host__ __device__ __forceinline__ uint32_t step_off(uint32_t n, uint32_t k) {
+  return (n >> 3) * 256u + (k >> 3) * 128u + (n & 7u) * 16u + (k & 7u) * 2u;
+}
+__host__ __device__ constexpr int w2_ksteps(int l) { return l == 0 ? 16 : 32; }
+__host__ __device__ constexpr int w2_halves(int l) { return l == 3 ? 1 : 2; }
+__host__ __device__ constexpr int w2_half_steps(int l) { return 1 + w2_ksteps(l); }
+__host__ __device__ constexpr int w2_layer_base(int l) {
+  int b = 0;
+  for (int i = 0; i < l; ++i) b += w2_halves(i) * w2_half_steps(i);
+  return b;
+}
+__host__ __device__ constexpr int w2_step(int l, int h, int s) {
+  return w2_layer_base(l) + h * w2_half_steps(l) + s;
+}
+constexpr int kW2Steps = w2_layer_base(8);  // 34 + 66*2 + 33 + 66*4 = 463 steps = 3.79 MB
+// per-segment E image (fold mode): [seg][which: lin0, lin4][h] steps
+constexpr int kSceneESteps = 4;
+
 // ---- dgrad weight image (W^T) -----------------------------------------------------------
 // layer l (1..7): D[r, i] = sum_o dY[r,o] W[o,i];  B tiles [128 i x 64 o], ordered kb(o)-major
 // then nc(i).  "scene mode" only needs i in the x3 part for lin4 (NC = 2).
