@@ -138,11 +138,27 @@ int dsdf_clip_adam(dsdf_handle h, float* params, float* grads, float* exp_avg, f
 int dsdf_profile_enable(dsdf_handle h, int32_t enable);
 int dsdf_profile_read(dsdf_handle h, float* ms_sum, int32_t* n_calls);
 
+/* Diagnostics (no reference counterpart): with DSDF_DBG=1 in the environment at dsdf_create the
+ * persistent kernels accumulate per-CTA cycle counters (16 u64 per SM: MMA-issuer total / waits,
+ * producer waits, epilogue waits).  Copies up to max_words counters to host memory `out`,
+ * clears them, returns the number of words (or a negative error).  Synchronises the device. */
+int dsdf_debug_read(dsdf_handle h, uint64_t* out, int32_t max_words);
+
 /* Descriptor self-test: one-tile GEMMs through the same UMMA descriptor helpers.
  * kind 0: K-major  A[128x64] (1 SUB), B[128x64] (1 SUB) -> D[128][128] = A B^T
  * kind 1: MN-major A (2 SUBs), B (4 SUBs), K = rows 0..31 -> D[128][256] = A^T B */
 int dsdf_selftest_gemm(int32_t kind, const void* a_img, const void* b_img, float* d_out,
                        void* stream);
+
+/* Diagnostics: tensor-pipe issue-rate micro-benchmark (iters tcgen05.mma M=128 N=256 K=16 on n_cta
+ * CTAs); cycles_host[n_cta] = cycles per CTA.  kind bit0: SWIZZLE_128B B operand, bit1: commit per
+ * MMA, bit2: N=128.  Synchronises the device. */
+int dsdf_selftest_mma_rate(int32_t kind, int32_t iters, int32_t n_cta, uint64_t* cycles_host);
+
+/* Diagnostics builds only (-DDSDF_HANG_TRAP): barrier waits that spin for seconds write
+ * (block, thread, barrier smem address, parity) records into this mapped host buffer and trap.
+ * buf[0] = record count, records at buf[4 + 4*i].  DSDF_EUNSUPPORTED in the product build. */
+int dsdf_debug_hang_buffer(uint32_t** host_ptr);
 
 #ifdef __cplusplus
 }

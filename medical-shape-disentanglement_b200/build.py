@@ -14,6 +14,12 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "dsdf_b200", "libdsdf_b200.so")
+# diagnostics variants: DSDF_BUILD_VARIANT=name DSDF_BUILD_DEFS="-DDSDF_DBG_BUILD -DDSDF_ABLATE=1"
+# builds dsdf_b200/libdsdf_b200.<name>.so (loaded with DSDF_LIB=<path>); never the product library
+VARIANT = os.environ.get("DSDF_BUILD_VARIANT", "")
+EXTRA = os.environ.get("DSDF_BUILD_DEFS", "").split()
+if VARIANT:
+    OUT = os.path.join(HERE, "dsdf_b200", f"libdsdf_b200.{VARIANT}.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
@@ -36,14 +42,15 @@ def needs_build() -> bool:
 def build_lib(force: bool = False, verbose: bool = False) -> str:
     if not force and not needs_build():
         return OUT
-    cmd = [NVCC] + FLAGS + ["-o", OUT, os.path.join(CSRC, "dsdf_api.cu")]
+    cmd = [NVCC] + FLAGS + EXTRA + ["-o", OUT, os.path.join(CSRC, "dsdf_api.cu")]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if verbose or r.returncode != 0:
         sys.stderr.write(r.stdout + r.stderr)
     if r.returncode != 0:
         raise RuntimeError("nvcc failed building libdsdf_b200.so")
-    with open(os.path.join(HERE, "dsdf_b200", "ptxas_report.txt"), "w") as f:
-        f.write(r.stdout + r.stderr)
+    if not VARIANT:
+        with open(os.path.join(HERE, "dsdf_b200", "ptxas_report.txt"), "w") as f:
+            f.write(r.stdout + r.stderr)
     return OUT
 
 

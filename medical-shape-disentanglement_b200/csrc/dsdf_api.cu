@@ -17,6 +17,7 @@
 #include "fold_kernels.cuh"
 #include "fwd_kernel.cuh"
 #include "fwd2_kernel.cuh"
+#include "fwd3_kernel.cuh"
 #include "layout.cuh"
 #include "selftest.cuh"
 #include "small_kernels.cuh"
@@ -35,8 +36,11 @@ struct dsdf_handle_s {
   uint8_t* w2_img = nullptr;     // v2 forward K-step stream
   uint8_t* scene_e = nullptr;    // fold-mode per-segment E steps for the inference entries
   long long scene_e_cap = 0;     // segments
-  int fwd_cl = 2;                // cluster size of the forward chain (DSDF_FWD_CL = 1|2|4)
+  int fwd_cl = 2;                // cluster size of the v2 forward chain (DSDF_FWD_CL = 1|2|4)
+  int fwd_ver = 3;               // DSDF_FWD_VER=2: previous-generation forward kernel (A/B timing)
+  int fwd_cg = 2;                // DSDF_FWD_CG=1: never pair CTAs (cta_group::1 only)
   bool fwd_v1 = false;           // DSDF_FWD_V1=1: previous-generation forward kernel (A/B timing)
+  unsigned long long* dbg = nullptr;   // DSDF_DBG=1: per-CTA cycle counters (dsdf_debug_read)
   float* weff = nullptr;
   float* scale = nullptr;
   float* inv_norm = nullptr;
@@ -99,6 +103,15 @@ static int set_kernel_attrs(dsdf_handle h) {
   F2ATTR(MODE_GRID, true, false)
   F2ATTR(MODE_TABLE, true, true)
 #undef F2ATTR
+#define F3ATTR(MODE, FOLD, TRAIN)                                                                                   \
+  CU(h, cudaFuncSetAttribute(k_forward3<MODE, FOLD, TRAIN, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, F3<1>::kSmemBytes)); \
+  CU(h, cudaFuncSetAttribute(k_forward3<MODE, FOLD, TRAIN, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, F3<2>::kSmemBytes));
+  F3ATTR(MODE_DENSE, false, false)
+  F3ATTR(MODE_TABLE, false, false)
+  F3ATTR(MODE_TABLE, true, false)
+  F3ATTR(MODE_GRID, true, false)
+  F3ATTR(MODE_TABLE, true, true)
+#undef F3ATTR
   CU(h, cudaFuncSetAttribute(k_backward, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmemBytes));
   CU(h, cudaFuncSetAttribute(k_wgrad, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgSmemBytes));
   CU(h, cudaFuncSetAttribute(k_selftest_gemm, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
@@ -142,6 +155,12 @@ extern "C" int dsdf_create(const dsdf_config* cfg, dsdf_handle* out) {
     if (cl == 1 || cl == 2 || cl == 4) h->fwd_cl = cl;
   }
   if (const char* e = getenv("DSDF_FWD_V1")) h->fwd_v1 = atoi(e) != 0;
+  if (const char* e = getenv("DSDF_FWD_VER")) h->fwd_ver = atoi(e) == 2 ? 2 : 3;
+  if (const char* e = getenv("DSDF_FWD_CG")) h->fwd_cg = atoi(e) == 1 ? 1 : 2;
+  if (const char* e = getenv("DSDF_DBG")) {
+    if (atoi(e) != 0 && cudaMalloc(&h->dbg, (size_t)h->num_sms * kDbgSlots * 8) == cudaSuccess)
+      cudaMemset(h->dbg, 0, (size_t)h->num_sms * kDbgSlots * 8);
+  }
   bool ok = cudaMalloc(&h->fwd_img, (size_t)kFwdTilesTotal * kSubBytes) == cudaSuccess &&
             cudaMalloc(&h->w2_img, (size_t)kW2Steps * kStepBytes) == cudaSuccess &&
             cudaMalloc(&h->dg_img, (size_t)kDgTilesTotal * kSubBytes) == cudaSuccess &&
@@ -173,6 +192,7 @@ extern "C" int dsdf_destroy(dsdf_handle h) {
   cudaFree(h->scale);
   cudaFree(h->inv_norm);
   cudaFree(h->wg_items);
+  cudaFree(h->dbg);
   for (cudaEvent_t e : h->prof_events) cudaEventDestroy(e);
   delete h;
   return DSDF_OK;
@@ -243,6 +263,37 @@ static cudaError_t launch_fwd2(dsdf_handle h, const FwdArgs& a, cudaStream_t st)
   if (cl == 2) return launch_fwd2_cl<MODE, FOLD, TRAIN, 2>(h, a, st);
   return launch_fwd2_cl<MODE, FOLD, TRAIN, 1>(h, a, st);
 }
+// ---- v3 forward launcher: persistent grid, CTA pairs (cta_group::2) when `pair_ok` -------------
+template <int MODE, bool FOLD, bool TRAIN, int CG>
+static cudaError_t launch_fwd3_cg(dsdf_handle h, const FwdArgs& a, cudaStream_t st) {
+  const long long tiles = (a.n_rows + kTileM - 1) / kTileM;
+  long long g = tiles < h->num_sms ? tiles : h->num_sms;
+  g = (g / CG) * CG;
+  if (g < CG) g = CG;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3((unsigned)g);
+  cfg.blockDim = dim3(kF3Threads);
+  cfg.dynamicSmemBytes = F3<CG>::kSmemBytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CG;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, k_forward3<MODE, FOLD, TRAIN, CG>, a);
+}
+// pair_ok: both tiles of a pair may share the B operand (always true unless FOLD segments are
+// shorter than 256 rows-aligned, see callers)
+template <int MODE, bool FOLD, bool TRAIN>
+static cudaError_t launch_fwd(dsdf_handle h, const FwdArgs& a, cudaStream_t st, bool pair_ok) {
+  if (h->fwd_ver == 2) return launch_fwd2<MODE, FOLD, TRAIN>(h, a, st);
+  const long long tiles = (a.n_rows + kTileM - 1) / kTileM;
+  if (pair_ok && h->fwd_cg == 2 && tiles >= 2) return launch_fwd3_cg<MODE, FOLD, TRAIN, 2>(h, a, st);
+  return launch_fwd3_cg<MODE, FOLD, TRAIN, 1>(h, a, st);
+}
 // per-segment E steps for the fold-mode inference entries (handle-owned, grown on demand)
 static int ensure_scene_e(dsdf_handle h, long long n_seg) {
   if (n_seg <= h->scene_e_cap) return DSDF_OK;
@@ -268,10 +319,11 @@ extern "C" int dsdf_forward_dense(dsdf_handle h, const float* input, int64_t n, 
   a.input = input;
   a.out = out;
   a.w2img = h->w2_img;
+  a.dbg = h->dbg;
   if (h->fwd_v1) {
     k_forward<MODE_DENSE, false><<<grid_for(h, n), kFwdThreads, kFwdSmemBytes, (cudaStream_t)stream>>>(a);
   } else {
-    CU(h, (launch_fwd2<MODE_DENSE, false, false>(h, a, (cudaStream_t)stream)));
+    CU(h, (launch_fwd<MODE_DENSE, false, false>(h, a, (cudaStream_t)stream, true)));
   }
   CU(h, cudaGetLastError());
   return DSDF_OK;
@@ -299,6 +351,7 @@ extern "C" int dsdf_forward_segments(dsdf_handle h, const float* table, const in
   a.xyz_stride = xyz_stride;
   a.out = out;
   a.w2img = h->w2_img;
+  a.dbg = h->dbg;
   if (h->fwd_v1) {
     k_forward<MODE_TABLE, false><<<grid_for(h, n), kFwdThreads, kFwdSmemBytes, (cudaStream_t)stream>>>(a);
   } else if (!seg_ids || rows_per_seg % kTileM == 0) {
@@ -309,9 +362,9 @@ extern "C" int dsdf_forward_segments(dsdf_handle h, const float* table, const in
     a.scene_e = h->scene_e;
     k_scene_fold<<<dim3((unsigned)ns, 2), 512, 0, (cudaStream_t)stream>>>(
         h->weff, h->params_ptr, h->pl, table, (const long long*)seg_ids, h->scene_e);
-    CU(h, (launch_fwd2<MODE_TABLE, true, false>(h, a, (cudaStream_t)stream)));
+    CU(h, (launch_fwd<MODE_TABLE, true, false>(h, a, (cudaStream_t)stream, !seg_ids || rows_per_seg % (2 * kTileM) == 0)));
   } else {
-    CU(h, (launch_fwd2<MODE_TABLE, false, false>(h, a, (cudaStream_t)stream)));
+    CU(h, (launch_fwd<MODE_TABLE, false, false>(h, a, (cudaStream_t)stream, true)));
   }
   CU(h, cudaGetLastError());
   return DSDF_OK;
@@ -336,6 +389,7 @@ extern "C" int dsdf_decode_grid(dsdf_handle h, const float* latent, int32_t grid
   a.voxel_size = (float)(2.0 / (grid_n - 1));
   a.out = out;
   a.w2img = h->w2_img;
+  a.dbg = h->dbg;
   if (h->fwd_v1) {
     k_forward<MODE_GRID, false><<<grid_for(h, a.n_rows), kFwdThreads, kFwdSmemBytes, (cudaStream_t)stream>>>(a);
   } else {
@@ -344,7 +398,7 @@ extern "C" int dsdf_decode_grid(dsdf_handle h, const float* latent, int32_t grid
     a.scene_e = h->scene_e;
     k_scene_fold<<<dim3(1, 2), 512, 0, (cudaStream_t)stream>>>(h->weff, h->params_ptr, h->pl, latent,
                                                                nullptr, h->scene_e);
-    CU(h, (launch_fwd2<MODE_GRID, true, false>(h, a, (cudaStream_t)stream)));
+    CU(h, (launch_fwd<MODE_GRID, true, false>(h, a, (cudaStream_t)stream, true)));
   }
   CU(h, cudaGetLastError());
   return DSDF_OK;
@@ -386,6 +440,7 @@ struct Ws {
   float* seg_norm;
   float* dweff;
   uint8_t* scene_e;
+  uint32_t* relu_mask;
   size_t total;
 };
 inline size_t al(size_t x) { return (x + 1023) & ~(size_t)1023; }
@@ -409,6 +464,7 @@ Ws carve(uint8_t* base, long long max_rows, long long max_seg, int num_sms) {
   w.seg_norm = (float*)take((size_t)max_seg * 4);
   w.dweff = (float*)take((size_t)kWeffElems * 4);
   w.scene_e = take((size_t)max_seg * kSceneESteps * kStepBytes);
+  w.relu_mask = (uint32_t*)take(tiles * 8 * 16 * kTileM * 4);
   w.total = o;
   return w;
 }
@@ -450,6 +506,7 @@ static int build_wg_items(dsdf_handle h, long long tiles, cudaStream_t st) {
   h->wg_layout.n_split = n_split;
   if ((int)items.size() > h->wg_items_cap) {
     cudaFree(h->wg_items);
+  cudaFree(h->dbg);
     CU(h, cudaMalloc(&h->wg_items, items.size() * sizeof(WgItem)));
     h->wg_items_cap = (int)items.size();
   }
@@ -513,13 +570,15 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   const bool prof = h->profile && (int)h->prof_events.size() + kProfEventsPerCall <= kProfMaxCalls * kProfEventsPerCall;
   if (prof) prof_mark(h, st);
   fa.w2img = h->w2_img;
+  fa.dbg = h->dbg;
   fa.scene_e = w.scene_e;
+  fa.relu_mask = w.relu_mask;
   if (h->fwd_v1) {
     k_forward<MODE_TABLE, true><<<grid, kFwdThreads, kFwdSmemBytes, st>>>(fa);
   } else {
     k_scene_fold<<<dim3((unsigned)n_seg, 2), 512, 0, st>>>(h->weff, params, h->pl, table,
                                                           (const long long*)seg_ids, w.scene_e);
-    CU(h, (launch_fwd2<MODE_TABLE, true, true>(h, fa, st)));
+    CU(h, (launch_fwd<MODE_TABLE, true, true>(h, fa, st, rows_per_seg % (2 * kTileM) == 0)));
   }
   if (prof) prof_mark(h, st);
 
@@ -594,6 +653,17 @@ extern "C" int dsdf_profile_read(dsdf_handle h, float* ms_sum, int32_t* n_calls)
   return DSDF_OK;
 }
 
+extern "C" int dsdf_debug_read(dsdf_handle h, uint64_t* out, int32_t max_words) {
+  if (!h || !out) DSDF_FAIL(h, DSDF_EINVAL, "null argument");
+  if (!h->dbg) DSDF_FAIL(h, DSDF_EINVAL, "diagnostic counters are off (set DSDF_DBG=1 before dsdf_create)");
+  int n = h->num_sms * kDbgSlots;
+  if (n > max_words) n = max_words;
+  CU(h, cudaDeviceSynchronize());
+  CU(h, cudaMemcpy(out, h->dbg, (size_t)n * 8, cudaMemcpyDeviceToHost));
+  CU(h, cudaMemset(h->dbg, 0, (size_t)h->num_sms * kDbgSlots * 8));
+  return n;
+}
+
 extern "C" int dsdf_renorm_rows(dsdf_handle h, float* table, const int64_t* seg_ids, int64_t n_seg,
                                 float max_norm, void* stream) {
   if (!h || !table || !seg_ids) DSDF_FAIL(h, DSDF_EINVAL, "null argument");
@@ -638,4 +708,54 @@ extern "C" int dsdf_selftest_gemm(int32_t kind, const void* a_img, const void* b
   e = cudaGetLastError();
   if (e != cudaSuccess) { g_err = cudaGetErrorString(e); return DSDF_ECUDA; }
   return DSDF_OK;
+}
+
+extern "C" int dsdf_selftest_mma_rate(int32_t kind, int32_t iters, int32_t n_cta, uint64_t* cycles_host) {
+  if (!cycles_host || iters <= 0 || n_cta <= 0 || n_cta > 1024) { g_err = "bad argument"; return DSDF_EINVAL; }
+  const int smem = 196608 + 64;
+  cudaError_t e = cudaFuncSetAttribute(k_mma_rate, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (e != cudaSuccess) { g_err = cudaGetErrorString(e); return DSDF_ECUDA; }
+  unsigned long long* d = nullptr;
+  if ((e = cudaMalloc(&d, (size_t)n_cta * 8)) != cudaSuccess) { g_err = cudaGetErrorString(e); return DSDF_ECUDA; }
+  if (kind & 64) {
+    cudaFuncSetAttribute(k_mma_rate2, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3((unsigned)((n_cta + 1) / 2 * 2));
+    cfg.blockDim = dim3(128);
+    cfg.dynamicSmemBytes = smem;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    e = cudaLaunchKernelEx(&cfg, k_mma_rate2, (int)(kind & 63), (int)iters, d);
+  } else {
+    k_mma_rate<<<n_cta, 128, smem>>>(kind, iters, d);
+  }
+  e = cudaDeviceSynchronize();
+  if (e == cudaSuccess) e = cudaMemcpy(cycles_host, d, (size_t)n_cta * 8, cudaMemcpyDeviceToHost);
+  cudaFree(d);
+  if (e != cudaSuccess) { g_err = cudaGetErrorString(e); return DSDF_ECUDA; }
+  return DSDF_OK;
+}
+
+// diagnostics builds (-DDSDF_HANG_TRAP): mapped host buffer the device writes deadlock reports to
+extern "C" int dsdf_debug_hang_buffer(uint32_t** host_ptr) {
+#ifdef DSDF_HANG_TRAP
+  static uint32_t* buf = nullptr;
+  if (!buf) {
+    if (cudaHostAlloc((void**)&buf, 4096, cudaHostAllocMapped) != cudaSuccess) return DSDF_ECUDA;
+    memset(buf, 0, 4096);
+    unsigned int* dptr = nullptr;
+    if (cudaHostGetDevicePointer((void**)&dptr, buf, 0) != cudaSuccess) return DSDF_ECUDA;
+    volatile unsigned int* v = dptr;
+    if (cudaMemcpyToSymbol(g_hang, &v, sizeof(v)) != cudaSuccess) return DSDF_ECUDA;
+  }
+  if (host_ptr) *host_ptr = buf;
+  return DSDF_OK;
+#else
+  (void)host_ptr;
+  g_err = "library was not built with -DDSDF_HANG_TRAP";
+  return DSDF_EUNSUPPORTED;
+#endif
 }

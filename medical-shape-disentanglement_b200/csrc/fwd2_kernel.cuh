@@ -27,6 +27,19 @@
 #include "layout.cuh"
 #include "ptx.cuh"
 
+// per-CTA cycle counters are compiled in only with -DDSDF_DBG_BUILD (tools/gpu_dbg.py builds a
+// separate library); the product build carries no instrumentation.
+#ifdef DSDF_DBG_BUILD
+#define DSDF_DBG_ON(a) ((a).dbg != nullptr)
+#else
+#define DSDF_DBG_ON(a) false
+#endif
+// timing ablations for diagnostics builds only (results are wrong): bit0 = producer skips the
+// weight copies, bit1 = MMA issuer skips the MMAs
+#ifndef DSDF_ABLATE
+#define DSDF_ABLATE 0
+#endif
+
 namespace dsdf {
 
 constexpr int kF2Stages = 11;
@@ -131,18 +144,28 @@ __global__ void __launch_bounds__(kF2Threads, 1) k_forward2(const FwdArgs a) {
 
   if (warp == 0) {
     // ===================== weight producer =====================
-    if (lane == 0) {
+    // the whole warp runs the loop (warp-uniform control flow keeps the barrier / descriptor
+    // arithmetic on the uniform datapath); one elected lane issues the copies
+    {
       uint32_t stage = 0, phase = 0;
+      long long dbg_we = 0;
       auto load = [&](const uint8_t* src, bool mc) {
+        const long long c0 = DSDF_DBG_ON(a) ? clock64() : 0;
         mbar_wait(&empty[stage], phase ^ 1);
-        mbar_arrive_expect_tx(&full[stage], kStepBytes);
-        uint8_t* dst = smem + kF2SmemRing + stage * kStepBytes;
-        if (CL > 1 && mc) {
-          constexpr uint32_t slice = kStepBytes / CL;
-          bulk_g2s_mc(dst + crank * slice, src + crank * slice, slice, &full[stage], kMask);
-        } else {
-          bulk_g2s(dst, src, kStepBytes, &full[stage]);
+        if (DSDF_DBG_ON(a)) dbg_we += clock64() - c0;
+        if (elect_one()) {
+          mbar_arrive_expect_tx(&full[stage], kStepBytes);
+          uint8_t* dst = smem + kF2SmemRing + stage * kStepBytes;
+          if (DSDF_ABLATE & 1) {
+            asm volatile("mbarrier.complete_tx.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(&full[stage])), "r"((uint32_t)kStepBytes) : "memory");
+          } else if (CL > 1 && mc) {
+            constexpr uint32_t slice = kStepBytes / CL;
+            bulk_g2s_mc(dst + crank * slice, src + crank * slice, slice, &full[stage], kMask);
+          } else {
+            bulk_g2s(dst, src, kStepBytes, &full[stage]);
+          }
         }
+        __syncwarp();
         if (++stage == kF2Stages) { stage = 0; phase ^= 1; }
       };
       for (long long it = 0; it < n_iter; ++it) {
@@ -166,46 +189,77 @@ __global__ void __launch_bounds__(kF2Threads, 1) k_forward2(const FwdArgs a) {
           }
         }
       }
+      if (DSDF_DBG_ON(a) && lane == 0) a.dbg[(size_t)blockIdx.x * kDbgSlots + 4] = dbg_we;
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
+    // warp-uniform loop; the same elected lane issues every tcgen05.mma / tcgen05.commit
+    {
       constexpr uint32_t idesc = umma_idesc_bf16(128, 256, false, false);
       uint32_t stage = 0, phase = 0, par_lo = 0, par_hi = 0;
       const uint64_t ea_desc = umma_smem_desc_ns(s_base + kF2SmemEA, 128, 256);
+      long long dbg_wf = 0, dbg_wl = 0, dbg_wh = 0;
+      const long long dbg_t0 = DSDF_DBG_ON(a) ? clock64() : 0;
       for (long long it = 0; it < n_iter; ++it) {
 #pragma unroll 1
         for (int l = 0; l < 8; ++l) {
           const int used = f2_used_ksteps<FOLD>(l);
-          mbar_wait(a_lo, par_lo);
+          {
+            const long long c0 = DSDF_DBG_ON(a) ? clock64() : 0;
+            mbar_wait(a_lo, par_lo);
+            if (DSDF_DBG_ON(a)) dbg_wl += clock64() - c0;
+          }
           par_lo ^= 1;
           tc_fence_after();
           for (int h = 0; h < w2_halves(l); ++h) {
             const uint32_t d_addr = tmem + h * 256;
             // E step: xyz (hi/lo) + bias through the ones columns; overwrites the accumulator
-            mbar_wait(&full[stage], phase);
+            {
+              const long long c0 = DSDF_DBG_ON(a) ? clock64() : 0;
+              mbar_wait(&full[stage], phase);
+              if (DSDF_DBG_ON(a)) dbg_wf += clock64() - c0;
+            }
             tc_fence_after();
-            umma_bf16(d_addr, ea_desc,
-                      umma_smem_desc_ns(s_base + kF2SmemRing + stage * kStepBytes, 128, 256), idesc, 0u);
-            if (CL > 1) umma_commit_mc(&empty[stage], kMask); else umma_commit(&empty[stage]);
+            if (elect_one()) {
+              if (!(DSDF_ABLATE & 2))
+              umma_bf16(d_addr, ea_desc,
+                        umma_smem_desc_ns(s_base + kF2SmemRing + stage * kStepBytes, 128, 256), idesc, 0u);
+              if (CL > 1) umma_commit_mc(&empty[stage], kMask); else umma_commit(&empty[stage]);
+            }
+            __syncwarp();
             if (++stage == kF2Stages) { stage = 0; phase ^= 1; }
             for (int s = 0; s < used; ++s) {
               if (h == 0 && s == 16) {   // first K-step that reads A SUB 4..7
+                const long long c0 = DSDF_DBG_ON(a) ? clock64() : 0;
                 mbar_wait(a_hi, par_hi);
+                if (DSDF_DBG_ON(a)) dbg_wh += clock64() - c0;
                 par_hi ^= 1;
                 tc_fence_after();
               }
-              mbar_wait(&full[stage], phase);
+              {
+                const long long c0 = DSDF_DBG_ON(a) ? clock64() : 0;
+                mbar_wait(&full[stage], phase);
+                if (DSDF_DBG_ON(a)) dbg_wf += clock64() - c0;
+              }
               tc_fence_after();
               const uint32_t a_addr = s_base + kF2SmemA + (s >> 2) * kSubBytes + (s & 3) * 32;
-              umma_bf16(d_addr, umma_smem_desc(a_addr, 16, 1024),
-                        umma_smem_desc_ns(s_base + kF2SmemRing + stage * kStepBytes, 128, 256), idesc, 1u);
-              if (CL > 1) umma_commit_mc(&empty[stage], kMask); else umma_commit(&empty[stage]);
+              if (elect_one()) {
+                if (!(DSDF_ABLATE & 2))
+                umma_bf16(d_addr, umma_smem_desc(a_addr, 16, 1024),
+                          umma_smem_desc_ns(s_base + kF2SmemRing + stage * kStepBytes, 128, 256), idesc, 1u);
+                if (CL > 1) umma_commit_mc(&empty[stage], kMask); else umma_commit(&empty[stage]);
+              }
+              __syncwarp();
               if (++stage == kF2Stages) { stage = 0; phase ^= 1; }
             }
-            umma_commit(&d_done[h]);
+            if (elect_one()) umma_commit(&d_done[h]);
+            __syncwarp();
           }
         }
+      }
+      if (DSDF_DBG_ON(a) && lane == 0) {
+        unsigned long long* d = a.dbg + (size_t)blockIdx.x * kDbgSlots;
+        d[0] = clock64() - dbg_t0; d[1] = dbg_wf; d[2] = dbg_wl; d[3] = dbg_wh;
       }
     }
   } else if (warp >= 4) {
@@ -217,6 +271,8 @@ __global__ void __launch_bounds__(kF2Threads, 1) k_forward2(const FwdArgs a) {
     const uint32_t tlane = (uint32_t)(q * 32) << 16;
     const uint32_t a_base = s_base + kF2SmemA;
     uint32_t par_d0 = 0, par_d1 = 0;
+    long long dbg_d0 = 0, dbg_d1 = 0;
+    const long long dbg_e0 = DSDF_DBG_ON(a) ? clock64() : 0;
     for (long long it = 0; it < n_iter; ++it) {
       long long tile = it * gridDim.x + blockIdx.x;
       const bool tile_valid = tile < n_tiles;
@@ -244,7 +300,11 @@ __global__ void __launch_bounds__(kF2Threads, 1) k_forward2(const FwdArgs a) {
         const bool has_h1 = (l != 3);
         // ---- half 0: TMEM -> ReLU -> bf16, held in registers while the MMAs still read A
         uint32_t held[64];
-        mbar_wait(&d_done[0], par_d0);
+        {
+          const long long c0 = DSDF_DBG_ON(a) ? clock64() : 0;
+          mbar_wait(&d_done[0], par_d0);
+          if (DSDF_DBG_ON(a)) dbg_d0 += clock64() - c0;
+        }
         par_d0 ^= 1;
         tc_fence_after();
 #pragma unroll
@@ -255,7 +315,9 @@ __global__ void __launch_bounds__(kF2Threads, 1) k_forward2(const FwdArgs a) {
           relu_pack32(v, held + 16 * c);
         }
         if (has_h1) {
+          const long long c0 = DSDF_DBG_ON(a) ? clock64() : 0;
           mbar_wait(&d_done[1], par_d1);    // every MMA of layer l has retired: A is free
+          if (DSDF_DBG_ON(a)) dbg_d1 += clock64() - c0;
           par_d1 ^= 1;
           tc_fence_after();
         }
@@ -385,6 +447,10 @@ __global__ void __launch_bounds__(kF2Threads, 1) k_forward2(const FwdArgs a) {
       }
     }
     if (TRAIN && t == 0) bulk_wait_all();
+    if (DSDF_DBG_ON(a) && t == 0) {
+      unsigned long long* d = a.dbg + (size_t)blockIdx.x * kDbgSlots;
+      d[5] = dbg_d0; d[6] = dbg_d1; d[7] = clock64() - dbg_e0;
+    }
   }
 
   tc_fence_before();

@@ -1,0 +1,458 @@
+// Fused 9-layer DeepSDF forward chain, v3: persistent CTAs, 128 rows per CTA tile, lean
+// single-thread issue loops, optional CTA pair (CG = 2: tcgen05 cta_group::2, M = 256 over two SMs).
+//
+//   warp 0      : weight producer (one elected lane): K-steps ([256 n x 16 k] bf16, layout.cuh)
+//                 global -> smem ring with the TMA engine.  CG = 2: each CTA of the pair copies
+//                 ITS HALF of every step (128 n rows) into its own ring and signals the LEADER's
+//                 barrier, so L2 -> SM traffic and ring writes per SM are halved.
+//   warp 1      : MMA issuer (one elected lane of the leader CTA): tcgen05.mma kind::f16,
+//                 M = 128*CG, N = 256, K = 16.  Ring stage indices, barrier addresses and operand
+//                 descriptors are compile-time constants inside fully unrolled groups of kRing
+//                 steps: the loop is a try_wait + UTCHMMA + UTCBAR per step and keeps the tensor
+//                 pipe at its 128-cycle-per-step floor (tools/gpu_mma_rate.py).
+//   warp 2      : TMEM allocator (512 columns); warp 3 idle
+//   warps 4..11 : epilogue warps, as in v2: each layer is two 256-column halves; h0's ReLU'd bf16
+//                 activations are held in registers until the layer's last MMA has retired, then
+//                 become the next layer's A tile; h1 follows straight from TMEM.
+//
+// E steps (xyz hi/lo + bias through the ones columns; in FOLD mode the per-segment bias
+// b + W[:, latent] z of lin0 / lin4) travel through their own 2-slot ring so that the W ring always
+// advances in multiples of 16 steps.
+//
+// TRAIN mode also writes, per layer, the activation stash (bf16 images, consumed by the wgrad
+// kernel) and a 1-bit/element ReLU mask (consumed by the backward chain instead of re-reading the
+// 1 KB/row activations).
+//
+// Replaces, per 128-row tile, reference networks/deep_sdf_decoder.py:74-109 (9x addmm, 2x cat,
+// 8x relu, tanh), deep_sdf/utils.py:86-97 (expand + cat) and, in TRAIN mode,
+// train_deep_sdf.py:598-606 (gather, cat, clamp, L1/N).
+#pragma once
+#include "fwd2_kernel.cuh"
+#include "fwd_kernel.cuh"
+#include "layout.cuh"
+#include "ptx.cuh"
+
+namespace dsdf {
+
+template <int CG>
+struct F3 {
+  static constexpr int kRing = 8 * CG;                   // W ring stages (per CTA)
+  static constexpr uint32_t kSlice = kStepBytes / CG;    // bytes of one K-step held by one CTA
+  static constexpr uint32_t kSmemA = 0;                  // 8 SUBs (SWIZZLE_128B)
+  static constexpr uint32_t kSmemEA = kTileBytes;        // [128 x 16] no-swizzle, 4 KB
+  static constexpr uint32_t kSmemRing = kSmemEA + 4096;
+  static constexpr uint32_t kSmemERing = kSmemRing + kRing * kSlice;   // 64 KB W ring
+  static constexpr uint32_t kSmemAux = kSmemERing + 2 * kSlice;
+  static constexpr uint32_t kAuxTmem = 512;              // after 64 barriers
+  static constexpr uint32_t kAuxPart = 528;              // 128 floats
+  static constexpr uint32_t kAuxRed = 1040;              // 16 floats
+  static constexpr uint32_t kAuxW8 = 1104;               // 512 floats
+  static constexpr uint32_t kSmemBytes = kSmemAux + kAuxW8 + 2048;
+};
+constexpr int kF3Threads = 384;
+
+// bit (31 - i) of the result = (v[i] > 0) for fp32 accumulators (sign-bit test; +0 counts as
+// positive, which only ever happens on zero-padded columns whose gradients are discarded)
+__device__ __forceinline__ uint32_t pos_mask32(const uint32_t (&v)[32]) {
+  uint32_t m = 0;
+#pragma unroll
+  for (int i = 0; i < 32; ++i) m = __funnelshift_l(v[i], m, 1);
+  return ~m;
+}
+
+template <int MODE, bool FOLD, bool TRAIN, int CG>
+__global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
+  using C = F3<CG>;
+  constexpr int kRing = C::kRing;
+  constexpr uint32_t kSlice = C::kSlice;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const uint32_t s_base = smem_u32(smem);
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::kSmemAux);
+  uint64_t* full = bars;                 // [kRing]  producer -> MMA (leader's copy is the live one)
+  uint64_t* empty = bars + 16;           // [kRing]  MMA -> producer (committed to both CTAs)
+  uint64_t* e_full = bars + 32;          // [2]
+  uint64_t* e_empty = bars + 34;         // [2]
+  uint64_t* a_lo = bars + 36;            // epilogue -> MMA: A SUB 0..3 (+E_A) ready, TMEM h0 drained
+  uint64_t* a_hi = bars + 37;            // epilogue -> MMA: A SUB 4..7 ready, TMEM h1 drained
+  uint64_t* d_done = bars + 38;          // [2] MMA -> epilogue: half h accumulated
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + C::kSmemAux + C::kAuxTmem);
+  float* part = reinterpret_cast<float*>(smem + C::kSmemAux + C::kAuxPart);
+  float* red = reinterpret_cast<float*>(smem + C::kSmemAux + C::kAuxRed);
+  float* w8s = reinterpret_cast<float*>(smem + C::kSmemAux + C::kAuxW8);
+
+  if ((s_base & 1023u) != 0) __trap();
+  const uint32_t crank = CG > 1 ? cluster_ctarank() : 0u;
+  const bool leader = crank == 0;
+
+  if (threadIdx.x == 0) {
+    // full barriers: own copy (arrive.expect_tx) + in the leader one relayed arrive per peer copy
+    for (int i = 0; i < kRing; ++i) {
+      mbar_init(&full[i], leader ? CG : 1);
+      mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&e_full[i], leader ? CG : 1);
+      mbar_init(&e_empty[i], 1);
+      mbar_init(&d_done[i], 1);
+    }
+    mbar_init(a_lo, 8 * CG);             // one elected arrive per epilogue warp of every CTA
+    mbar_init(a_hi, 8 * CG);
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    if (CG > 1) tmem_alloc2<512>(tmem_slot); else tmem_alloc<512>(tmem_slot);
+  }
+  for (int i = threadIdx.x; i < kHidden; i += blockDim.x) w8s[i] = a.w8[i];
+  tc_fence_before();
+  __syncthreads();
+  if (CG > 1) cluster_sync_all();        // the peer's barriers exist before anything is signalled
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  const long long n_tiles = (a.n_rows + kTileM - 1) / kTileM;
+  // every CTA runs the same number of iterations (a pair is lock-stepped through the MMA);
+  // iterations past the last tile recompute the last tile and write nothing.
+  const long long n_iter = (n_tiles + gridDim.x - 1) / gridDim.x;
+  // barriers the MMA issuer waits on live in the leader CTA
+  const uint32_t full_c = CG > 1 ? mapa_u32(smem_u32(full), 0) : smem_u32(full);
+  const uint32_t e_full_c = CG > 1 ? mapa_u32(smem_u32(e_full), 0) : smem_u32(e_full);
+  const uint32_t a_lo_c = CG > 1 ? mapa_u32(smem_u32(a_lo), 0) : smem_u32(a_lo);
+  const uint32_t a_hi_c = CG > 1 ? mapa_u32(smem_u32(a_hi), 0) : smem_u32(a_hi);
+
+  if (warp == 0) {
+    // ===================== weight producer =====================
+    if (elect_one()) {
+      uint32_t ph = 0, es = 0, eph = 0;
+      for (long long it = 0; it < n_iter; ++it) {
+        long long tile = it * gridDim.x + blockIdx.x;
+        tile = tile < n_tiles ? tile : n_tiles - 1;
+        const uint8_t* se = nullptr;
+        if (FOLD) {
+          const long long seg = (MODE == MODE_TABLE && a.seg_ids) ? (tile * kTileM) / a.rows_per_seg : 0;
+          se = a.scene_e + (size_t)seg * kSceneESteps * kStepBytes;
+        }
+#pragma unroll 1
+        for (int l = 0; l < 8; ++l) {
+          const int groups = f2_used_ksteps<FOLD>(l) / kRing;
+#pragma unroll 1
+          for (int h = 0; h < w2_halves(l); ++h) {
+            const uint8_t* w = a.w2img + (size_t)w2_step(l, h, 0) * kStepBytes + crank * kSlice;
+            const uint8_t* esrc = (FOLD && (l == 0 || l == kSkipLayer))
+                                      ? se + (size_t)((l == 0 ? 0 : 2) + h) * kStepBytes + crank * kSlice
+                                      : w;
+            mbar_wait(&e_empty[es], eph ^ 1);
+            mbar_arrive_expect_tx(&e_full[es], kSlice);
+            bulk_g2s(smem + C::kSmemERing + es * kSlice, esrc, kSlice, &e_full[es]);
+            es ^= 1;
+            eph ^= (es == 0);
+            w += kStepBytes;
+#pragma unroll 1
+            for (int g = 0; g < groups; ++g) {
+#pragma unroll
+              for (int u = 0; u < kRing; ++u) {
+                mbar_wait(&empty[u], ph ^ 1);
+                mbar_arrive_expect_tx(&full[u], kSlice);
+                bulk_g2s(smem + C::kSmemRing + u * kSlice, w, kSlice, &full[u]);
+                w += kStepBytes;
+              }
+              ph ^= 1;
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1 && !leader) {
+    // ===================== peer CTA: relay "my half of the step has landed" to the leader =====
+    // (a bulk copy can only signal an mbarrier of the CTA it writes to)
+    if (elect_one()) {
+      uint32_t ph = 0, es = 0, eph = 0;
+      for (long long it = 0; it < n_iter; ++it) {
+#pragma unroll 1
+        for (int l = 0; l < 8; ++l) {
+          const int groups = f2_used_ksteps<FOLD>(l) / kRing;
+#pragma unroll 1
+          for (int h = 0; h < w2_halves(l); ++h) {
+            mbar_wait(&e_full[es], eph);
+            mbar_arrive_cluster_relaxed(e_full_c + es * 8);
+            es ^= 1;
+            eph ^= (es == 0);
+#pragma unroll 1
+            for (int g = 0; g < groups; ++g) {
+#pragma unroll
+              for (int u = 0; u < kRing; ++u) {
+                mbar_wait(&full[u], ph);
+                mbar_arrive_cluster_relaxed(full_c + u * 8);
+              }
+              ph ^= 1;
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (leader CTA only) =====================
+    if (elect_one()) {
+      constexpr uint32_t idesc = umma_idesc_bf16(128 * CG, 256, false, false);
+      const uint64_t ea_desc = umma_smem_desc_ns(s_base + C::kSmemEA, 128, 256);
+      const uint64_t a_desc0 = umma_smem_desc(s_base + C::kSmemA, 16, 1024);
+      const uint64_t b_desc0 = umma_smem_desc_ns(s_base + C::kSmemRing, 128, 256);
+      const uint64_t eb_desc0 = umma_smem_desc_ns(s_base + C::kSmemERing, 128, 256);
+      uint32_t ph = 0, es = 0, eph = 0, par_lo = 0, par_hi = 0;
+      auto mma = [&](uint32_t d, uint64_t ad, uint64_t bd, uint32_t acc) {
+        if (CG > 1) umma2_bf16(d, ad, bd, idesc, acc); else umma_bf16(d, ad, bd, idesc, acc);
+      };
+      auto commit = [&](uint64_t* bar) {
+        if (CG > 1) umma2_commit_mc(bar, (uint16_t)3); else umma_commit(bar);
+      };
+      auto wait_a = [&](uint64_t* bar, uint32_t par) {
+        // plain (cta-scope acquire) wait, as CUTLASS' ClusterBarrier::wait: the operands are read by
+        // the tensor core's async proxy after tcgen05.fence::after_thread_sync, and an
+        // acquire.cluster wait costs a CCTL.IVALL per poll (measured 4x slower end to end)
+        mbar_wait(bar, par);
+      };
+      for (long long it = 0; it < n_iter; ++it) {
+#pragma unroll 1
+        for (int l = 0; l < 8; ++l) {
+          const int groups = f2_used_ksteps<FOLD>(l) / kRing;
+          wait_a(a_lo, par_lo);
+          par_lo ^= 1;
+          tc_fence_after();
+#pragma unroll 1
+          for (int h = 0; h < w2_halves(l); ++h) {
+            const uint32_t d_addr = tmem + h * 256;
+            // E step: xyz (hi/lo) + bias through the ones columns; overwrites the accumulator
+            wait_a(&e_full[es], eph);
+            tc_fence_after();
+            mma(d_addr, ea_desc, eb_desc0 + (uint64_t)(es * (kSlice >> 4)), 0u);
+            commit(&e_empty[es]);
+            es ^= 1;
+            eph ^= (es == 0);
+#pragma unroll 1
+            for (int g = 0; g < groups; ++g) {
+              if (h == 0 && g * kRing == 16) {   // first K-step that reads A SUB 4..7
+                wait_a(a_hi, par_hi);
+                par_hi ^= 1;
+                tc_fence_after();
+              }
+              // K-steps 8g*CG .. : SUB (s >> 2), 32 B per step inside the 128 B swizzle row
+              const uint64_t a_desc = a_desc0 + (uint64_t)((g * (kRing / 4) * kSubBytes) >> 4);
+#pragma unroll
+              for (int u = 0; u < kRing; ++u) {
+                wait_a(&full[u], ph);
+                tc_fence_after();
+                mma(d_addr, a_desc + (uint64_t)(((u >> 2) * kSubBytes + (u & 3) * 32) >> 4),
+                    b_desc0 + (uint64_t)((u * kSlice) >> 4), 1u);
+                commit(&empty[u]);
+              }
+              ph ^= 1;
+            }
+            commit(&d_done[h]);
+          }
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue warps =====================
+    const int t = threadIdx.x - 128;      // 0..255
+    const int q = warp & 3;               // TMEM lane quarter this warp may access
+    const int j = (warp - 4) >> 2;        // which 128 columns of a half
+    const uint32_t r = q * 32 + lane;     // row inside the tile
+    const uint32_t tlane = (uint32_t)(q * 32) << 16;
+    const uint32_t a_base = s_base + C::kSmemA;
+    uint32_t par_d0 = 0, par_d1 = 0;
+    // generic-proxy writes of this warp -> visible to the (leader's) MMA, one arrive per warp
+    // (each SM's tensor core reads its OWN A tile, so cta-scope release + the proxy fence order
+    // the data; only the arrival itself travels to the leader)
+    auto publish = [&](uint32_t bar_c) {
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        if (leader) mbar_arrive(reinterpret_cast<uint64_t*>(smem) + (bar_c - s_base) / 8);
+        else { __threadfence_block(); mbar_arrive_cluster_relaxed(bar_c); }
+      }
+    };
+    for (long long it = 0; it < n_iter; ++it) {
+      long long tile = it * gridDim.x + blockIdx.x;
+      const bool tile_valid = tile < n_tiles;
+      tile = tile_valid ? tile : n_tiles - 1;
+      const long long row0 = tile * kTileM;
+      uint32_t* mask_tile = TRAIN ? a.relu_mask + (size_t)tile * (8 * 16 * kTileM) + r : nullptr;
+      // ---- tile prologue: E_A rows (+ layer-0 latent gather when not folded)
+      if (TRAIN && !FOLD) {   // the previous tile's slot-7 stash may still be reading A
+        if (t == 0) bulk_wait_read_all();
+        named_bar_sync(1, kActThreads);
+      }
+      if (!FOLD) gather_latent<MODE>(a, row0, a_base, t);
+      float gt = 0.f;
+      if (t < kTileM) {
+        long long row = row0 + t;
+        row = row < a.n_rows ? row : a.n_rows - 1;
+        float x, y, z;
+        load_xyz<MODE>(a, row, x, y, z, gt);
+        write_e_row_ns(s_base + C::kSmemEA, t, x, y, z);
+      }
+      publish(a_lo_c);
+
+#pragma unroll 1
+      for (int l = 0; l < 7; ++l) {
+        const bool has_h1 = (l != 3);
+        // ---- half 0: TMEM -> ReLU -> bf16, held in registers while the MMAs still read A
+        uint32_t held[64];
+        mbar_wait(&d_done[0], par_d0);
+        par_d0 ^= 1;
+        tc_fence_after();
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint32_t v[32];
+          tmem_ld_32x32(tmem + tlane + (uint32_t)(j * 128 + c * 32), v);
+          tmem_ld_wait();
+          relu_pack32(v, held + 16 * c);
+          if (TRAIN && tile_valid) mask_tile[(size_t)(l * 16 + j * 4 + c) * kTileM] = pos_mask32(v);
+        }
+        if (has_h1) {
+          mbar_wait(&d_done[1], par_d1);    // every MMA of layer l has retired: A is free
+          par_d1 ^= 1;
+          tc_fence_after();
+        }
+        if (TRAIN) {                        // ... and the stash copy of A has been read out
+          if (t == 0) bulk_wait_read_all();
+          named_bar_sync(1, kActThreads);
+        }
+#pragma unroll
+        for (int c = 0; c < 4; ++c) store_chunk32(a_base, r, (uint32_t)(j * 128 + c * 32), held + 16 * c);
+        tc_fence_before();
+        publish(a_lo_c);
+        // ---- half 1: straight from TMEM into SUB 4..7
+        if (has_h1) {
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            uint32_t v[32], p[16];
+            tmem_ld_32x32(tmem + tlane + (uint32_t)(256 + j * 128 + c * 32), v);
+            tmem_ld_wait();
+            relu_pack32(v, p);
+            store_chunk32(a_base, r, (uint32_t)(256 + j * 128 + c * 32), p);
+            if (TRAIN && tile_valid) mask_tile[(size_t)(l * 16 + 8 + j * 4 + c) * kTileM] = pos_mask32(v);
+          }
+          tc_fence_before();
+          if (f2_in_hi<FOLD>(l + 1)) publish(a_hi_c); else fence_proxy_async_smem();
+        } else if (!FOLD) {
+          // skip connection: latent -> SUB 4..7 (reference cat order [x3 | latent | xyz])
+          gather_latent<MODE>(a, row0, a_base + 4 * kSubBytes, t);
+          publish(a_hi_c);
+        }
+        if (TRAIN) {
+          // stash X_{l+1} (input of lin(l+1)); for l == 3 only the x3 part (SUB 0..3) in fold mode
+          named_bar_sync(1, kActThreads);
+          if (t == 0 && tile_valid) {
+            const uint32_t bytes = (l == 3 && FOLD) ? 4 * kSubBytes : kTileBytes;
+            bulk_s2g(a.xstash + (size_t)tile * kStashTileBytes + (size_t)l * kTileBytes,
+                     smem + C::kSmemA, bytes);
+            bulk_commit();
+          }
+        }
+      }
+
+      // ---- lin7 epilogue fused with lin8 (512 -> 1), tanh, loss
+      float acc = 0.f;
+      {
+        uint32_t held[TRAIN ? 64 : 1];
+        mbar_wait(&d_done[0], par_d0);
+        par_d0 ^= 1;
+        tc_fence_after();
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint32_t v[32];
+          const uint32_t col = (uint32_t)(j * 128 + c * 32);
+          tmem_ld_32x32(tmem + tlane + col, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) acc = fmaf(fmaxf(__uint_as_float(v[i]), 0.f), w8s[col + i], acc);
+          if (TRAIN) {
+            relu_pack32(v, held + 16 * c);
+            if (tile_valid) mask_tile[(size_t)(7 * 16 + j * 4 + c) * kTileM] = pos_mask32(v);
+          }
+        }
+        mbar_wait(&d_done[1], par_d1);
+        par_d1 ^= 1;
+        tc_fence_after();
+        if (TRAIN) {
+          if (t == 0) bulk_wait_read_all();
+          named_bar_sync(1, kActThreads);
+#pragma unroll
+          for (int c = 0; c < 4; ++c) store_chunk32(a_base, r, (uint32_t)(j * 128 + c * 32), held + 16 * c);
+        }
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint32_t v[32];
+          const uint32_t col = (uint32_t)(256 + j * 128 + c * 32);
+          tmem_ld_32x32(tmem + tlane + col, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) acc = fmaf(fmaxf(__uint_as_float(v[i]), 0.f), w8s[col + i], acc);
+          if (TRAIN) {
+            uint32_t p[16];
+            relu_pack32(v, p);
+            store_chunk32(a_base, r, col, p);
+            if (tile_valid) mask_tile[(size_t)(7 * 16 + 8 + j * 4 + c) * kTileM] = pos_mask32(v);
+          }
+        }
+      }
+      tc_fence_before();
+      if (j == 1) part[r] = acc;
+      if (TRAIN) fence_proxy_async_smem();
+      named_bar_sync(1, kActThreads);
+      if (TRAIN && t == 0 && tile_valid) {
+        bulk_s2g(a.xstash + (size_t)tile * kStashTileBytes + (size_t)7 * kTileBytes,
+                 smem + C::kSmemA, kTileBytes);
+        bulk_commit();
+      }
+      if (j == 0) {
+        const long long row = row0 + r;
+        const bool valid = tile_valid && row < a.n_rows;
+        const float s = acc + part[r] + __ldg(a.b8);
+        const float th = tanhf(s);
+        if (valid) a.out[row] = th;
+        if (TRAIN && a.fused_loss) {
+          // train_deep_sdf.py:565-567,604-606: clamp both, L1(sum)/N_total.
+          const float d = a.clamp_dist;
+          const float pc = fminf(fmaxf(th, -d), d);
+          const float gc = fminf(fmaxf(gt, -d), d);
+          const float diff = pc - gc;
+          float lossr = valid ? fabsf(diff) : 0.f;
+          const float sgn = (diff > 0.f) ? 1.f : ((diff < 0.f) ? -1.f : 0.f);
+          const float inside = (th >= -d && th <= d) ? 1.f : 0.f;
+          float g = valid ? sgn * inside * (1.f - th * th) * a.inv_n_total : 0.f;
+          if (valid) a.gout[row] = g;
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) {
+            lossr += __shfl_xor_sync(0xffffffffu, lossr, o);
+            g += __shfl_xor_sync(0xffffffffu, g, o);
+          }
+          if (lane == 0) { red[q * 2] = lossr; red[q * 2 + 1] = g; }
+        }
+      }
+      if (TRAIN && a.fused_loss) {
+        named_bar_sync(1, kActThreads);
+        if (t == 0 && tile_valid) {
+          a.tile_partials[tile * 2] = (red[0] + red[2]) + (red[4] + red[6]);
+          a.tile_partials[tile * 2 + 1] = (red[1] + red[3]) + (red[5] + red[7]);
+        }
+      } else {
+        named_bar_sync(1, kActThreads);   // part[] is rewritten by the next tile
+      }
+    }
+    if (TRAIN && t == 0) bulk_wait_all();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (CG > 1) cluster_sync_all();   // no CTA exits (or frees TMEM) while the pair is still running
+  if (warp == 2) {
+    if (CG > 1) tmem_dealloc2<512>(tmem); else tmem_dealloc<512>(tmem);
+  }
+}
+
+}  // namespace dsdf

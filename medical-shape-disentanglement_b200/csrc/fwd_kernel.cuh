@@ -43,12 +43,16 @@ struct FwdArgs {
   float* out;           // [n] tanh output (un-clamped)
   // TRAIN only
   uint8_t* xstash;      // [tiles][8][128 KB]
+  uint32_t* relu_mask;  // [tiles][8 layers][16 chunks][128 rows]: bit (31-i) = column 32*chunk+i > 0
   float* gout;          // [n] dL/ds (s = pre-tanh lin8 output), fused-loss mode only
   float* tile_partials; // [tiles][2] {sum |clamp(pred)-clamp(gt)|, sum dL/ds}
   int fused_loss;       // 1: compute clamped-L1 loss + gout from sdf_data[:,3]
   float clamp_dist;
   float inv_n_total;
+  // diagnostics (nullable): per-CTA cycle counters, see dsdf_debug_read
+  unsigned long long* dbg;
 };
+constexpr int kDbgSlots = 16;
 
 constexpr int kFwdStages = 5;
 constexpr int kFwdThreads = 384;

@@ -48,8 +48,32 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+#ifdef DSDF_HANG_TRAP
+// diagnostics build: a wait that spins for ~seconds records who/where into mapped host memory
+// (dsdf_debug_hang_buffer) and traps, so a barrier deadlock becomes a readable report
+__device__ volatile unsigned int* g_hang = nullptr;
+__device__ __noinline__ void hang_report(uint32_t bar_addr, uint32_t parity) {
+  volatile unsigned int* p = g_hang;
+  if (p) {
+    const unsigned slot = atomicAdd((unsigned int*)p, 1u);
+    if (slot < 63) {
+      volatile unsigned int* q = p + 4 + slot * 4;
+      q[0] = blockIdx.x; q[1] = threadIdx.x; q[2] = bar_addr; q[3] = parity;
+    }
+    __threadfence_system();
+  }
+  for (long long t0 = clock64(); clock64() - t0 < 2000000000ll;) {}   // let the others report too
+  __trap();
+}
+#define DSDF_HANG_CHECK(n, addr, par) if (++(n) > (1u << 22)) hang_report(addr, par)
+#else
+#define DSDF_HANG_CHECK(n, addr, par)
+#endif
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  unsigned n_spin = 0;
+  (void)n_spin;
   while (!mbar_try_wait(bar, parity)) {
+    DSDF_HANG_CHECK(n_spin, smem_u32(bar), parity);
   }
 }
 
@@ -218,6 +242,83 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
 __device__ __forceinline__ void umma_commit_mc(uint64_t* bar, uint16_t cta_mask) {
   asm volatile(
       "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 "
+      "[%0], %1;" ::"r"(smem_u32(bar)),
+      "h"(cta_mask)
+      : "memory");
+}
+
+// ------------------------------------------------------------------ CTA pair (cta_group::2)
+// shared::cluster address of `smem_addr` (a shared::cta address) in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t smem_addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(rank));
+  return r;
+}
+// arrive (release at cluster scope) on an mbarrier given by its shared::cluster address
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar_cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar_cluster_addr)
+               : "memory");
+}
+// relaxed remote arrive: no cluster-scope release fence (a release.cluster arrive costs ~800 cycles
+// per call, measured).  Used where the data the consumer reads was written by the async proxy /
+// is read by the SM that wrote it (cta_group::2 operands), so only the signal crosses CTAs.
+__device__ __forceinline__ void mbar_arrive_cluster_relaxed(uint32_t bar_cluster_addr) {
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar_cluster_addr)
+               : "memory");
+}
+// wait with acquire at cluster scope (pairs with mbar_arrive_cluster from the peer CTA)
+__device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  unsigned n_spin = 0;
+  (void)n_spin;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred P;\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 P, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, P;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    if (!ok) { DSDF_HANG_CHECK(n_spin, smem_u32(bar) | 0x80000000u, parity); }
+  } while (!ok);
+}
+// global -> own shared memory, completion (complete_tx) on the mbarrier at shared::cluster
+// address `bar_cluster_addr` (the pair leader's barrier in cta_group::2 kernels)
+__device__ __forceinline__ void bulk_g2s_bar(void* smem_dst, const void* gmem_src, uint32_t bytes,
+                                             uint32_t bar_cluster_addr) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+          "r"(smem_u32(smem_dst)),
+      "l"(gmem_src), "r"(bytes), "r"(bar_cluster_addr)
+      : "memory");
+}
+template <uint32_t kCols>
+__device__ __forceinline__ void tmem_alloc2(uint32_t* smem_slot) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                   smem_u32(smem_slot)),
+               "n"(kCols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+template <uint32_t kCols>
+__device__ __forceinline__ void tmem_dealloc2(uint32_t taddr) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(kCols)
+               : "memory");
+}
+// D[tmem of both CTAs] (+)= A * B^T over the CTA pair (M = 256: 128 rows per CTA; each CTA holds
+// half of B's N rows); issued by ONE thread of the leader CTA.
+__device__ __forceinline__ void umma2_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
+                                           uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma2_commit_mc(uint64_t* bar, uint16_t cta_mask) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 "
       "[%0], %1;" ::"r"(smem_u32(bar)),
       "h"(cta_mask)
       : "memory");

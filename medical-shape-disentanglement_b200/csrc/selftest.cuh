@@ -73,3 +73,136 @@ k_selftest_gemm(int kind, const uint8_t* a_img, const uint8_t* b_img, float* d_o
 }
 
 }  // namespace dsdf
+
+namespace dsdf {
+// MMA issue-rate micro-benchmark (diagnostics): `iters` x 8 back-to-back tcgen05.mma M=128 N=256 K=16
+// on fixed (zeroed) smem operands with precomputed descriptors; out[blockIdx.x] = total cycles.
+//   kind & 7  : B layout 0 = no-swizzle K-step, 1 = SWIZZLE_128B, 4 = SWIZZLE_64B, 6 = SWIZZLE_32B
+//   kind & 8  : tcgen05.commit to a scratch barrier after every MMA
+//   kind & 16 : try_wait on an already-completed barrier before every MMA
+//   kind & 32 : commit after every 2nd MMA only
+template <int LT, bool CM, bool TW, bool CM2>
+__device__ __forceinline__ void mma_rate_loop(uint32_t s_base, uint32_t tmem, int iters, uint64_t* bar_scr,
+                                              uint64_t* bar_rdy) {
+  constexpr uint32_t idesc = umma_idesc_bf16(128, 256, false, false);
+  const uint64_t a0 = umma_smem_desc(s_base, 16, 1024);
+  uint64_t b0;
+  if (LT == 1) b0 = umma_smem_desc(s_base + 131072, 16, 1024);
+  else if (LT == 4) b0 = umma_smem_desc_ns(s_base + 131072, 16, 512) | (4ull << 61);
+  else if (LT == 6) b0 = umma_smem_desc_ns(s_base + 131072, 16, 256) | (6ull << 61);
+  else b0 = umma_smem_desc_ns(s_base + 131072, 128, 256);
+  for (int i = 0; i < iters; ++i) {
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      if (TW) mbar_wait(bar_rdy, 0);
+      const uint64_t ad = a0 + (uint64_t)(((u >> 2) * kSubBytes + (u & 3) * 32) >> 4);
+      uint64_t bd;
+      if (LT == 1) bd = b0 + (uint64_t)(((u & 3) * 32) >> 4);
+      else if (LT == 4) bd = b0 + (uint64_t)((((u >> 1) & 3) * 16384 + (u & 1) * 32) >> 4);
+      else bd = b0 + (uint64_t)((u * kStepBytes) >> 4);
+      umma_bf16(tmem + (i & 1) * 256, ad, bd, idesc, 1u);
+      if (CM || (CM2 && (u & 1))) umma_commit(bar_scr);
+    }
+  }
+}
+__global__ void __launch_bounds__(128, 1) k_mma_rate(int kind, int iters, unsigned long long* out) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  constexpr uint32_t kAux = 196608;
+  uint64_t* bar_done = reinterpret_cast<uint64_t*>(smem + kAux);
+  uint64_t* bar_scr = bar_done + 1;
+  uint64_t* bar_rdy = bar_done + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + kAux + 32);
+  const uint32_t s_base = smem_u32(smem);
+  const int warp = threadIdx.x >> 5;
+  for (uint32_t i = threadIdx.x; i < kAux / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0;
+  if (threadIdx.x == 0) {
+    mbar_init(bar_done, 1);
+    mbar_init(bar_scr, 1);
+    mbar_init(bar_rdy, 1);
+    fence_mbar_init();
+    mbar_arrive(bar_rdy);   // phase 0 complete
+  }
+  if (warp == 0) tmem_alloc<512>(tmem_slot);
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  if (warp == 1) {
+    const long long t0 = clock64();
+    if (elect_one()) {
+#define RATE_CASE(LT)                                                                           \
+      if ((kind & 7) == LT) {                                                                   \
+        if (kind & 8) mma_rate_loop<LT, true, false, false>(s_base, tmem, iters, bar_scr, bar_rdy);        \
+        else if (kind & 16) mma_rate_loop<LT, true, true, false>(s_base, tmem, iters, bar_scr, bar_rdy);   \
+        else if (kind & 32) mma_rate_loop<LT, false, false, true>(s_base, tmem, iters, bar_scr, bar_rdy);  \
+        else mma_rate_loop<LT, false, false, false>(s_base, tmem, iters, bar_scr, bar_rdy);      \
+      }
+      RATE_CASE(0) RATE_CASE(1) RATE_CASE(4) RATE_CASE(6)
+#undef RATE_CASE
+      umma_commit(bar_done);
+    }
+    __syncwarp();
+    mbar_wait(bar_done, 0);
+    if (threadIdx.x == 32) out[blockIdx.x] = (unsigned long long)(clock64() - t0);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc<512>(tmem);
+}
+}  // namespace dsdf
+
+namespace dsdf {
+// cta_group::2 variant of the issue-rate micro-benchmark (cluster of 2; the leader issues
+// M=256 N=256 K=16 MMAs).  kind & 7: B layout (0 no-swizzle, 1 SWIZZLE_128B), kind & 8: multicast
+// commit after every MMA, kind & 16: N = 128.
+__global__ void __launch_bounds__(128, 1) k_mma_rate2(int kind, int iters, unsigned long long* out) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  constexpr uint32_t kAux = 196608;
+  uint64_t* bar_done = reinterpret_cast<uint64_t*>(smem + kAux);
+  uint64_t* bar_scr = bar_done + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + kAux + 32);
+  const uint32_t s_base = smem_u32(smem);
+  const int warp = threadIdx.x >> 5;
+  const bool leader = cluster_ctarank() == 0;
+  for (uint32_t i = threadIdx.x; i < kAux / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0;
+  if (threadIdx.x == 0) {
+    mbar_init(bar_done, 1);
+    mbar_init(bar_scr, 1);
+    fence_mbar_init();
+  }
+  if (warp == 0) tmem_alloc2<512>(tmem_slot);
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  if (warp == 1) {
+    const long long t0 = clock64();
+    if (leader && elect_one()) {
+      const bool sw = kind & 1, cm = kind & 8, n128 = kind & 16;
+      const uint32_t idesc = n128 ? umma_idesc_bf16(256, 128, false, false) : umma_idesc_bf16(256, 256, false, false);
+      const uint64_t a0 = umma_smem_desc(s_base, 16, 1024);
+      const uint64_t b0 = sw ? umma_smem_desc(s_base + 131072, 16, 1024) : umma_smem_desc_ns(s_base + 131072, 128, 256);
+      for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const uint64_t ad = a0 + (uint64_t)(((u >> 2) * kSubBytes + (u & 3) * 32) >> 4);
+          const uint64_t bd = sw ? b0 + (uint64_t)(((u & 3) * 32) >> 4) : b0 + (uint64_t)((u * 4096) >> 4);
+          umma2_bf16(tmem + (i & 1) * 256, ad, bd, idesc, 1u);
+          if (cm) umma2_commit_mc(bar_scr, (uint16_t)3);
+        }
+      }
+      umma2_commit_mc(bar_done, (uint16_t)3);
+    }
+    __syncwarp();
+    mbar_wait(bar_done, 0);
+    if ((threadIdx.x & 31) == 0) out[blockIdx.x] = (unsigned long long)(clock64() - t0);
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == 0) tmem_dealloc2<512>(tmem);
+}
+}  // namespace dsdf

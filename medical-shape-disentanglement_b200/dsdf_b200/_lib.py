@@ -9,7 +9,9 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libdsdf_b200.so")
+# DSDF_LIB selects a diagnostics build of the same library (build.py DSDF_BUILD_VARIANT); it is
+# still the CUDA library -- there is no non-CUDA implementation to select.
+LIB_PATH = os.environ.get("DSDF_LIB") or os.path.join(_HERE, "libdsdf_b200.so")
 
 DSDF_NUM_LIN = 9
 
@@ -17,7 +19,7 @@ EXPORTS = [
     "dsdf_create", "dsdf_destroy", "dsdf_last_error", "dsdf_num_sms", "dsdf_set_weights",
     "dsdf_forward_dense", "dsdf_forward_segments", "dsdf_decode_grid", "dsdf_grid_coords",
     "dsdf_train_workspace_bytes", "dsdf_train_fwd_bwd", "dsdf_renorm_rows", "dsdf_clip_adam",
-    "dsdf_selftest_gemm", "dsdf_profile_enable", "dsdf_profile_read",
+    "dsdf_selftest_gemm", "dsdf_profile_enable", "dsdf_profile_read", "dsdf_debug_read", "dsdf_selftest_mma_rate", "dsdf_debug_hang_buffer",
 ]
 
 
@@ -82,6 +84,12 @@ def lib():
     L.dsdf_profile_enable.restype = C.c_int
     L.dsdf_profile_read.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_int32)]
     L.dsdf_profile_read.restype = C.c_int
+    L.dsdf_debug_read.argtypes = [vp, C.POINTER(C.c_uint64), i32]
+    L.dsdf_debug_read.restype = C.c_int
+    L.dsdf_selftest_mma_rate.argtypes = [i32, i32, i32, C.POINTER(C.c_uint64)]
+    L.dsdf_selftest_mma_rate.restype = C.c_int
+    L.dsdf_debug_hang_buffer.argtypes = [C.POINTER(C.POINTER(C.c_uint32))]
+    L.dsdf_debug_hang_buffer.restype = C.c_int
     _lib = L
     return L
 
