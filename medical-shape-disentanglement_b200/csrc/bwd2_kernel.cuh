@@ -1,0 +1,456 @@
+// Fused backward dgrad chain, v2 (scene mode): persistent CTAs, 128 rows per CTA tile, the same
+// lean issue loops / CTA pairing (tcgen05 cta_group::2) as the v3 forward chain.
+//
+//   warp 0       : weight producer: K-steps of W^T ([256 i x 16 o], layout.cuh dg2_*) -> smem ring
+//   warp 1       : MMA issuer (leader) / full-barrier relay (peer):  dX_l = dY_l W_l as two
+//                  256-column halves, M = 128*CG, N = 256, K = 16
+//   warp 2       : TMEM allocator; warp 3 idle
+//   warps 4..11  : epilogue warps: dY7 = g w8 (X8 > 0) from the forward's dL/ds and ReLU bit-mask;
+//                  per layer TMEM -> (X_l > 0) mask -> bf16; half 0 is held in registers until the
+//                  layer's last MMA has retired, then becomes the next A tile; dY stash for wgrad
+//   warps 12..15 : reducer warps (in the shadow of the MMAs): column sums of every dY tile
+//                  -> bias grads, per-tile colsums of dY0/dY4 (-> latent grads and the latent
+//                  columns of dW0/dW4 by the segmented kernels), xyz columns of dW0/dW4.
+//                  (dW8 is a wgrad item, wgrad2_kernel.cuh)
+//
+// The ReLU masks come from the forward kernel's 1-bit/element image (8 KB per layer per tile)
+// instead of re-reading the 128 KB bf16 activation tiles.
+//
+// Replaces the autograd backward of reference train_deep_sdf.py:731 for the decoder
+// (9 dgrad GEMMs, ReLU masks, tanh', bias grads).  In scene mode the latent/xyz columns of
+// dX0 and dX4 are never materialised: sum_rows dX[:, latent] = colsum(dY) * W[:, latent].
+#pragma once
+#include "bwd_kernel.cuh"
+#include "fwd3_kernel.cuh"
+#include "layout.cuh"
+#include "ptx.cuh"
+
+namespace dsdf {
+
+struct Bwd2Args {
+  long long n_rows;
+  const uint8_t* dg2img;      // dgrad K-step stream
+  const float* w8;            // [512]
+  const float* g;             // [n] dL/ds
+  const uint32_t* relu_mask;  // forward ReLU bit-masks [tiles][8][16][128]
+  uint8_t* dystash;           // out: dY_l images, slot l (1..7)
+  const float* xyz;           // xyz of row r at xyz[r * xyz_stride + 0..2]
+  long long xyz_stride;
+  float* tile_colsum;         // [tiles][2][512]: colsum(dY0), colsum(dY4)
+  float* cta_partials;        // [grid][kCtaPartialFloats]
+};
+
+template <int CG>
+struct B2 {
+  static constexpr int kRing = 8 * CG;
+  static constexpr uint32_t kSlice = kStepBytes / CG;
+  static constexpr uint32_t kSmemA = 0;
+  static constexpr uint32_t kSmemRing = kTileBytes;
+  static constexpr uint32_t kSmemAux = kSmemRing + kRing * kSlice;   // + 64 KB
+  static constexpr uint32_t kAuxTmem = 512;     // after 64 barriers
+  static constexpr uint32_t kAuxW8 = 528;       // 512 floats
+  static constexpr uint32_t kAuxG = kAuxW8 + 2048;      // 128 floats
+  static constexpr uint32_t kAuxXyz = kAuxG + 512;      // 128 x 3 floats
+  static constexpr uint32_t kSmemBytes = kSmemAux + kAuxXyz + 1536;
+};
+constexpr int kB2Threads = 512;
+
+__host__ __device__ constexpr bool b2_has_h1(int l) { return l != kSkipLayer; }   // scene mode: lin4 -> x3 part only
+__host__ __device__ constexpr bool b2_in_hi(int l) { return dg2_ksteps(l) > 16; }
+
+template <int N>
+__device__ __forceinline__ void setmaxnreg_inc() {
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N));
+}
+template <int N>
+__device__ __forceinline__ void setmaxnreg_dec() {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N));
+}
+
+// 32 fp32 dX columns -> zero where the ReLU mask bit (31 - i) is clear -> 16 packed bf16x2
+__device__ __forceinline__ void mask_pack32(const uint32_t (&v)[32], uint32_t m, uint32_t* p) {
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const float lo = (m & (0x80000000u >> (2 * i))) ? __uint_as_float(v[2 * i]) : 0.f;
+    const float hi = (m & (0x40000000u >> (2 * i))) ? __uint_as_float(v[2 * i + 1]) : 0.f;
+    p[i] = pack_bf16x2(lo, hi);
+  }
+}
+
+template <int CG>
+__global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
+  using C = B2<CG>;
+  constexpr int kRing = C::kRing;
+  constexpr uint32_t kSlice = C::kSlice;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const uint32_t s_base = smem_u32(smem);
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::kSmemAux);
+  uint64_t* full = bars;                 // [kRing]
+  uint64_t* empty = bars + 16;           // [kRing]
+  uint64_t* a_lo = bars + 32;            // epilogue -> MMA: dY columns 0..255 ready
+  uint64_t* a_hi = bars + 33;            // epilogue -> MMA: dY columns 256..511 ready
+  uint64_t* d_done = bars + 34;          // [2] MMA -> epilogue
+  uint64_t* dy_ready = bars + 36;        // epilogue -> reducers: dY tile complete in A
+  uint64_t* red_done = bars + 37;        // reducers -> epilogue: A may be overwritten
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + C::kSmemAux + C::kAuxTmem);
+  float* w8s = reinterpret_cast<float*>(smem + C::kSmemAux + C::kAuxW8);
+  float* gs = reinterpret_cast<float*>(smem + C::kSmemAux + C::kAuxG);
+  float* xyzs = reinterpret_cast<float*>(smem + C::kSmemAux + C::kAuxXyz);
+
+  if ((s_base & 1023u) != 0) __trap();
+  const uint32_t crank = CG > 1 ? cluster_ctarank() : 0u;
+  const bool leader = crank == 0;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kRing; ++i) {
+      mbar_init(&full[i], leader ? CG : 1);
+      mbar_init(&empty[i], 1);
+    }
+    mbar_init(a_lo, 8 * CG);
+    mbar_init(a_hi, 8 * CG);
+    mbar_init(&d_done[0], 1);
+    mbar_init(&d_done[1], 1);
+    mbar_init(dy_ready, 8);
+    mbar_init(red_done, 4);
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    if (CG > 1) tmem_alloc2<512>(tmem_slot); else tmem_alloc<512>(tmem_slot);
+  }
+  for (int i = threadIdx.x; i < kHidden; i += blockDim.x) w8s[i] = a.w8[i];
+  tc_fence_before();
+  __syncthreads();
+  if (CG > 1) cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  const long long n_tiles = (a.n_rows + kTileM - 1) / kTileM;
+  const long long n_iter = (n_tiles + gridDim.x - 1) / gridDim.x;
+  const uint32_t full_c = CG > 1 ? mapa_u32(smem_u32(full), 0) : smem_u32(full);
+  const uint32_t a_lo_c = CG > 1 ? mapa_u32(smem_u32(a_lo), 0) : smem_u32(a_lo);
+  const uint32_t a_hi_c = CG > 1 ? mapa_u32(smem_u32(a_hi), 0) : smem_u32(a_hi);
+
+  if (warp < 4) {
+    setmaxnreg_dec<40>();
+    if (warp == 0) {
+      // ===================== weight producer =====================
+      if (elect_one()) {
+        uint32_t ph = 0;
+        for (long long it = 0; it < n_iter; ++it) {
+#pragma unroll 1
+          for (int l = 7; l >= 1; --l) {
+            const int groups = dg2_ksteps(l) / kRing;
+            const int halves = b2_has_h1(l) ? 2 : 1;
+#pragma unroll 1
+            for (int h = 0; h < halves; ++h) {
+              const uint8_t* w = a.dg2img + (size_t)dg2_step(l, h, 0) * kStepBytes + crank * kSlice;
+#pragma unroll 1
+              for (int g = 0; g < groups; ++g) {
+#pragma unroll
+                for (int u = 0; u < kRing; ++u) {
+                  mbar_wait(&empty[u], ph ^ 1);
+                  mbar_arrive_expect_tx(&full[u], kSlice);
+                  bulk_g2s(smem + C::kSmemRing + u * kSlice, w, kSlice, &full[u]);
+                  w += kStepBytes;
+                }
+                ph ^= 1;
+              }
+            }
+          }
+        }
+      }
+    } else if (warp == 1 && !leader) {
+      // ===================== peer CTA: relay "my half of the step has landed" =====================
+      if (elect_one()) {
+        uint32_t ph = 0;
+        for (long long it = 0; it < n_iter; ++it) {
+#pragma unroll 1
+          for (int l = 7; l >= 1; --l) {
+            const int n_groups = (dg2_ksteps(l) / kRing) * (b2_has_h1(l) ? 2 : 1);
+#pragma unroll 1
+            for (int g = 0; g < n_groups; ++g) {
+#pragma unroll
+              for (int u = 0; u < kRing; ++u) {
+                mbar_wait(&full[u], ph);
+                mbar_arrive_cluster_relaxed(full_c + u * 8);
+              }
+              ph ^= 1;
+            }
+          }
+        }
+      }
+    } else if (warp == 1) {
+      // ===================== MMA issuer (leader CTA only) =====================
+      if (elect_one()) {
+        constexpr uint32_t idesc = umma_idesc_bf16(128 * CG, 256, false, false);
+        const uint64_t a_desc0 = umma_smem_desc(s_base + C::kSmemA, 16, 1024);
+        const uint64_t b_desc0 = umma_smem_desc_ns(s_base + C::kSmemRing, 128, 256);
+        uint32_t ph = 0, par_lo = 0, par_hi = 0;
+        auto mma = [&](uint32_t d, uint64_t ad, uint64_t bd, uint32_t acc) {
+          if (CG > 1) umma2_bf16(d, ad, bd, idesc, acc); else umma_bf16(d, ad, bd, idesc, acc);
+        };
+        auto commit = [&](uint64_t* bar) {
+          if (CG > 1) umma2_commit_mc(bar, (uint16_t)3); else umma_commit(bar);
+        };
+        for (long long it = 0; it < n_iter; ++it) {
+#pragma unroll 1
+          for (int l = 7; l >= 1; --l) {
+            const int groups = dg2_ksteps(l) / kRing;
+            const int halves = b2_has_h1(l) ? 2 : 1;
+            mbar_wait(a_lo, par_lo);
+            par_lo ^= 1;
+            tc_fence_after();
+#pragma unroll 1
+            for (int h = 0; h < halves; ++h) {
+              const uint32_t d_addr = tmem + h * 256;
+#pragma unroll 1
+              for (int g = 0; g < groups; ++g) {
+                if (h == 0 && g * kRing == 16) {   // first K-step that reads dY columns 256..511
+                  mbar_wait(a_hi, par_hi);
+                  par_hi ^= 1;
+                  tc_fence_after();
+                }
+                const uint64_t a_desc = a_desc0 + (uint64_t)((g * (kRing / 4) * kSubBytes) >> 4);
+#pragma unroll
+                for (int u = 0; u < kRing; ++u) {
+                  mbar_wait(&full[u], ph);
+                  tc_fence_after();
+                  mma(d_addr, a_desc + (uint64_t)(((u >> 2) * kSubBytes + (u & 3) * 32) >> 4),
+                      b_desc0 + (uint64_t)((u * kSlice) >> 4), (g > 0 || u > 0) ? 1u : 0u);
+                  commit(&empty[u]);
+                }
+                ph ^= 1;
+              }
+              commit(&d_done[h]);
+            }
+          }
+        }
+      }
+    }
+  } else if (warp < 12) {
+    // ===================== epilogue warps =====================
+    setmaxnreg_inc<176>();
+    const int t = threadIdx.x - 128;      // 0..255
+    const int q = warp & 3;               // TMEM lane quarter this warp may access
+    const int j = (warp - 4) >> 2;        // which 128 columns of a half
+    const uint32_t r = q * 32 + lane;     // row inside the tile
+    const uint32_t tlane = (uint32_t)(q * 32) << 16;
+    const uint32_t a_base = s_base + C::kSmemA;
+    uint32_t par_d0 = 0, par_d1 = 0, par_rd = 0;
+    auto publish = [&](uint64_t* bar, uint32_t bar_c) {
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        if (leader) mbar_arrive(bar);
+        else { __threadfence_block(); mbar_arrive_cluster_relaxed(bar_c); }
+      }
+    };
+    auto tell_reducers = [&]() {
+      __syncwarp();
+      if (lane == 0) mbar_arrive(dy_ready);
+    };
+    bool first = true;
+    for (long long it = 0; it < n_iter; ++it) {
+      long long tile = it * gridDim.x + blockIdx.x;
+      const bool tile_valid = tile < n_tiles;
+      tile = tile_valid ? tile : n_tiles - 1;
+      const long long row0 = tile * kTileM;
+      const long long row = row0 + r;
+      const bool valid = tile_valid && row < a.n_rows;
+      const uint32_t* mask_tile = a.relu_mask + (size_t)tile * (8 * 16 * kTileM) + r;
+      uint8_t* dy_tile = a.dystash + (size_t)tile * kStashTileBytes;
+      // previous tile: reducers done with dY0, stash stores done reading A
+      if (!first) {
+        mbar_wait(red_done, par_rd);
+        par_rd ^= 1;
+      }
+      first = false;
+      if (t == 0) bulk_wait_read_all();
+      named_bar_sync(1, 256);
+      const float gr = valid ? __ldg(a.g + row) : 0.f;
+      if (j == 0) {
+        gs[r] = gr;
+        const long long rr = row < a.n_rows ? row : a.n_rows - 1;
+        xyzs[r * 3 + 0] = __ldg(a.xyz + rr * a.xyz_stride + 0);
+        xyzs[r * 3 + 1] = __ldg(a.xyz + rr * a.xyz_stride + 1);
+        xyzs[r * 3 + 2] = __ldg(a.xyz + rr * a.xyz_stride + 2);
+      }
+      // ---- dY7[r,c] = g[r] * w8[c] * (X8[r,c] > 0)
+#pragma unroll 1
+      for (int hh = 0; hh < 2; ++hh) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          const uint32_t col = (uint32_t)(hh * 256 + j * 128 + c * 32);
+          const uint32_t m = __ldg(mask_tile + (size_t)(7 * 16 + hh * 8 + j * 4 + c) * kTileM);
+          uint32_t v[32], p[16];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(gr * w8s[col + i]);
+          mask_pack32(v, m, p);
+          store_chunk32(a_base, r, col, p);
+        }
+      }
+      publish(a_lo, a_lo_c);
+      publish(a_hi, a_hi_c);
+      named_bar_sync(1, 256);
+      if (t == 0 && tile_valid) {
+        bulk_s2g(dy_tile + (size_t)7 * kTileBytes, smem + C::kSmemA, kTileBytes);
+        bulk_commit();
+      }
+      tell_reducers();
+
+#pragma unroll 1
+      for (int l = 7; l >= 1; --l) {
+        const bool has_h1 = b2_has_h1(l);
+        const int lm = l - 1;   // X_l = ReLU output of lin(l-1): forward mask layer l-1
+        uint32_t mk[8];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          mk[c] = __ldg(mask_tile + (size_t)(lm * 16 + j * 4 + c) * kTileM);
+          mk[4 + c] = has_h1 ? __ldg(mask_tile + (size_t)(lm * 16 + 8 + j * 4 + c) * kTileM) : 0u;
+        }
+        // ---- half 0: TMEM -> mask -> bf16, held in registers while the MMAs still read A
+        uint32_t held[64];
+        mbar_wait(&d_done[0], par_d0);
+        par_d0 ^= 1;
+        tc_fence_after();
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint32_t v[32];
+          tmem_ld_32x32(tmem + tlane + (uint32_t)(j * 128 + c * 32), v);
+          tmem_ld_wait();
+          mask_pack32(v, mk[c], held + 16 * c);
+        }
+        if (has_h1) {
+          mbar_wait(&d_done[1], par_d1);    // every MMA of layer l has retired: A is free
+          par_d1 ^= 1;
+          tc_fence_after();
+        }
+        mbar_wait(red_done, par_rd);        // ... the reducers have read dY_l
+        par_rd ^= 1;
+        if (t == 0) bulk_wait_read_all();   // ... and its stash copy has been read out
+        named_bar_sync(1, 256);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) store_chunk32(a_base, r, (uint32_t)(j * 128 + c * 32), held + 16 * c);
+        tc_fence_before();
+        if (l - 1 >= 1) publish(a_lo, a_lo_c); else fence_proxy_async_smem();
+        if (has_h1) {
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            uint32_t v[32], p[16];
+            tmem_ld_32x32(tmem + tlane + (uint32_t)(256 + j * 128 + c * 32), v);
+            tmem_ld_wait();
+            mask_pack32(v, mk[4 + c], p);
+            store_chunk32(a_base, r, (uint32_t)(256 + j * 128 + c * 32), p);
+          }
+          tc_fence_before();
+          if (l - 1 >= 1 && b2_in_hi(l - 1)) publish(a_hi, a_hi_c); else fence_proxy_async_smem();
+        }
+        named_bar_sync(1, 256);
+        if (l - 1 >= 1 && t == 0 && tile_valid) {
+          bulk_s2g(dy_tile + (size_t)(l - 1) * kTileBytes, smem + C::kSmemA,
+                   has_h1 ? (uint32_t)kTileBytes : 4u * kSubBytes);
+          bulk_commit();
+        }
+        tell_reducers();
+      }
+    }
+    if (t == 0) bulk_wait_all();
+  } else {
+    // ===================== reducer warps =====================
+    setmaxnreg_dec<96>();
+    const int rt = threadIdx.x - 384;      // 0..127, columns 4rt..4rt+3
+    const uint32_t sub_o = (rt >> 4) * kSubBytes;
+    const uint32_t chk = (rt & 15) >> 1;
+    const uint32_t hb = (rt & 1) * 8;
+    float db[6][4];
+    float dw8[4];
+    float dwx[2][4][3];
+#pragma unroll
+    for (int i = 0; i < 6; ++i)
+#pragma unroll
+      for (int k = 0; k < 4; ++k) db[i][k] = 0.f;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) dw8[k] = 0.f;
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+#pragma unroll
+        for (int e = 0; e < 3; ++e) dwx[i][k][e] = 0.f;
+    uint32_t par_dy = 0;
+    for (long long it = 0; it < n_iter; ++it) {
+      long long tile = it * gridDim.x + blockIdx.x;
+      const bool tile_valid = tile < n_tiles;
+      tile = tile_valid ? tile : n_tiles - 1;
+#pragma unroll
+      for (int l = 7; l >= 0; --l) {
+        mbar_wait(dy_ready, par_dy);
+        par_dy ^= 1;
+        const bool active = (l != 3) || (rt < 64);   // dY3 has 256 columns
+        float s[4] = {0.f, 0.f, 0.f, 0.f};
+        if (active) {
+          if (false) {
+          } else if (l == 4 || l == 0) {
+            const int xi = (l == 0) ? 0 : 1;
+#pragma unroll 4
+            for (int r = 0; r < kTileM; ++r) {
+              const uint32_t off = sub_o + sub_chunk_off(r, chk) + hb;
+              uint32_t w0, w1;
+              asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(w0), "=r"(w1) : "r"(s_base + C::kSmemA + off));
+              const float d0 = bf16_lo(w0), d1 = bf16_hi(w0), d2 = bf16_lo(w1), d3 = bf16_hi(w1);
+              s[0] += d0; s[1] += d1; s[2] += d2; s[3] += d3;
+              const float x = xyzs[r * 3], y = xyzs[r * 3 + 1], z = xyzs[r * 3 + 2];
+              dwx[xi][0][0] = fmaf(d0, x, dwx[xi][0][0]); dwx[xi][0][1] = fmaf(d0, y, dwx[xi][0][1]); dwx[xi][0][2] = fmaf(d0, z, dwx[xi][0][2]);
+              dwx[xi][1][0] = fmaf(d1, x, dwx[xi][1][0]); dwx[xi][1][1] = fmaf(d1, y, dwx[xi][1][1]); dwx[xi][1][2] = fmaf(d1, z, dwx[xi][1][2]);
+              dwx[xi][2][0] = fmaf(d2, x, dwx[xi][2][0]); dwx[xi][2][1] = fmaf(d2, y, dwx[xi][2][1]); dwx[xi][2][2] = fmaf(d2, z, dwx[xi][2][2]);
+              dwx[xi][3][0] = fmaf(d3, x, dwx[xi][3][0]); dwx[xi][3][1] = fmaf(d3, y, dwx[xi][3][1]); dwx[xi][3][2] = fmaf(d3, z, dwx[xi][3][2]);
+            }
+            if (tile_valid)
+              *reinterpret_cast<float4*>(a.tile_colsum + ((size_t)tile * 2 + xi) * kHidden + 4 * rt) =
+                  make_float4(s[0], s[1], s[2], s[3]);
+          } else {
+#pragma unroll 8
+            for (int r = 0; r < kTileM; ++r) {
+              const uint32_t off = sub_o + sub_chunk_off(r, chk) + hb;
+              uint32_t w0, w1;
+              asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(w0), "=r"(w1) : "r"(s_base + C::kSmemA + off));
+              s[0] += bf16_lo(w0); s[1] += bf16_hi(w0); s[2] += bf16_lo(w1); s[3] += bf16_hi(w1);
+            }
+          }
+          if (l != 0 && l != 4) {
+            const int sl = db_slot(l);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) db[sl][k] += s[k];
+          }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(red_done);
+      }
+    }
+    float* out = a.cta_partials + (size_t)blockIdx.x * kCtaPartialFloats;
+#pragma unroll
+    for (int i = 0; i < 6; ++i)
+      *reinterpret_cast<float4*>(out + kPartDb + i * kHidden + 4 * rt) =
+          make_float4(db[i][0], db[i][1], db[i][2], db[i][3]);
+    *reinterpret_cast<float4*>(out + kPartW8 + 4 * rt) = make_float4(dw8[0], dw8[1], dw8[2], dw8[3]);
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+#pragma unroll
+        for (int e = 0; e < 3; ++e)
+          out[kPartXyz + (i * kHidden + 4 * rt + k) * 3 + e] = dwx[i][k][e];
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (CG > 1) cluster_sync_all();
+  if (warp == 2) {
+    if (CG > 1) tmem_dealloc2<512>(tmem); else tmem_dealloc<512>(tmem);
+  }
+}
+
+}  // namespace dsdf

@@ -14,6 +14,7 @@
 
 #include "../../include/dsdf.h"
 #include "bwd_kernel.cuh"
+#include "bwd2_kernel.cuh"
 #include "fold_kernels.cuh"
 #include "fwd_kernel.cuh"
 #include "fwd2_kernel.cuh"
@@ -22,6 +23,7 @@
 #include "selftest.cuh"
 #include "small_kernels.cuh"
 #include "wgrad_kernel.cuh"
+#include "wgrad2_kernel.cuh"
 
 using namespace dsdf;
 
@@ -34,6 +36,8 @@ struct dsdf_handle_s {
   uint8_t* fwd_img = nullptr;
   uint8_t* dg_img = nullptr;
   uint8_t* w2_img = nullptr;     // v2 forward K-step stream
+  uint8_t* dg2_img = nullptr;    // v2 dgrad K-step stream
+  int bwd_ver = 2;               // DSDF_BWD_VER=1: previous-generation backward kernel (A/B timing)
   uint8_t* scene_e = nullptr;    // fold-mode per-segment E steps for the inference entries
   long long scene_e_cap = 0;     // segments
   int fwd_cl = 2;                // cluster size of the v2 forward chain (DSDF_FWD_CL = 1|2|4)
@@ -49,6 +53,14 @@ struct dsdf_handle_s {
   long long wg_items_tiles = -1;
   int wg_n_items = 0;
   WgLayout wg_layout{};
+  // v2 wgrad schedule (rebuilt when the tile count changes)
+  WgSeg* wg2_segs = nullptr;
+  int* wg2_seg_begin = nullptr;
+  long long wg2_tiles = -1;
+  int wg2_pairs = 0;
+  int wg2_slots = 0;
+  Wg2Layout wg2_layout{};
+  int wg_ver = 2;                // DSDF_WG_VER=1: previous-generation wgrad kernel
   ParamLayout pl{};
   const float* params_ptr = nullptr;   // caller's flat fp32 parameters at the last dsdf_set_weights
   bool weights_set = false;
@@ -113,7 +125,10 @@ static int set_kernel_attrs(dsdf_handle h) {
   F3ATTR(MODE_TABLE, true, true)
 #undef F3ATTR
   CU(h, cudaFuncSetAttribute(k_backward, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmemBytes));
+  CU(h, cudaFuncSetAttribute(k_backward2<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, B2<1>::kSmemBytes));
+  CU(h, cudaFuncSetAttribute(k_backward2<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, B2<2>::kSmemBytes));
   CU(h, cudaFuncSetAttribute(k_wgrad, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgSmemBytes));
+  CU(h, cudaFuncSetAttribute(k_wgrad2, cudaFuncAttributeMaxDynamicSharedMemorySize, kW2SmemBytes));
   CU(h, cudaFuncSetAttribute(k_selftest_gemm, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
   h->attrs_set = true;
   return DSDF_OK;
@@ -157,6 +172,9 @@ extern "C" int dsdf_create(const dsdf_config* cfg, dsdf_handle* out) {
   if (const char* e = getenv("DSDF_FWD_V1")) h->fwd_v1 = atoi(e) != 0;
   if (const char* e = getenv("DSDF_FWD_VER")) h->fwd_ver = atoi(e) == 2 ? 2 : 3;
   if (const char* e = getenv("DSDF_FWD_CG")) h->fwd_cg = atoi(e) == 1 ? 1 : 2;
+  if (const char* e = getenv("DSDF_BWD_VER")) h->bwd_ver = atoi(e) == 1 ? 1 : 2;
+  if (const char* e = getenv("DSDF_WG_VER")) h->wg_ver = atoi(e) == 1 ? 1 : 2;
+  if (h->bwd_ver == 1) h->wg_ver = 1;   // the v1 backward computes dW8 itself
   if (const char* e = getenv("DSDF_DBG")) {
     if (atoi(e) != 0 && cudaMalloc(&h->dbg, (size_t)h->num_sms * kDbgSlots * 8) == cudaSuccess)
       cudaMemset(h->dbg, 0, (size_t)h->num_sms * kDbgSlots * 8);
@@ -164,6 +182,7 @@ extern "C" int dsdf_create(const dsdf_config* cfg, dsdf_handle* out) {
   bool ok = cudaMalloc(&h->fwd_img, (size_t)kFwdTilesTotal * kSubBytes) == cudaSuccess &&
             cudaMalloc(&h->w2_img, (size_t)kW2Steps * kStepBytes) == cudaSuccess &&
             cudaMalloc(&h->dg_img, (size_t)kDgTilesTotal * kSubBytes) == cudaSuccess &&
+            cudaMalloc(&h->dg2_img, (size_t)kDg2Steps * kStepBytes) == cudaSuccess &&
             cudaMalloc(&h->weff, (size_t)(kWeffElems + 16) * 4) == cudaSuccess &&
             cudaMalloc(&h->scale, (size_t)kScaleElems * 4) == cudaSuccess &&
             cudaMalloc(&h->inv_norm, (size_t)kScaleElems * 4) == cudaSuccess;
@@ -187,11 +206,14 @@ extern "C" int dsdf_destroy(dsdf_handle h) {
   cudaFree(h->fwd_img);
   cudaFree(h->dg_img);
   cudaFree(h->w2_img);
+  cudaFree(h->dg2_img);
   cudaFree(h->scene_e);
   cudaFree(h->weff);
   cudaFree(h->scale);
   cudaFree(h->inv_norm);
   cudaFree(h->wg_items);
+  cudaFree(h->wg2_segs);
+  cudaFree(h->wg2_seg_begin);
   cudaFree(h->dbg);
   for (cudaEvent_t e : h->prof_events) cudaEventDestroy(e);
   delete h;
@@ -221,6 +243,8 @@ extern "C" int dsdf_set_weights(dsdf_handle h, const float* params, const dsdf_p
   k_fold_fwd2<<<(unsigned)((c3 + 255) / 256), 256, 0, st>>>(h->weff, params, h->pl, h->w2_img);
   const long long c2 = (long long)kDgTilesTotal * (kSubBytes / 16);
   k_fold_dgrad<<<(unsigned)((c2 + 255) / 256), 256, 0, st>>>(h->weff, h->dg_img);
+  const long long c4 = (long long)kDg2Steps * (kStepBytes / 16);
+  k_fold_dgrad2<<<(unsigned)((c4 + 255) / 256), 256, 0, st>>>(h->weff, h->dg2_img);
   CU(h, cudaGetLastError());
   h->params_ptr = params;
   h->weights_set = true;
@@ -441,6 +465,7 @@ struct Ws {
   float* dweff;
   uint8_t* scene_e;
   uint32_t* relu_mask;
+  uint8_t* g_img;
   size_t total;
 };
 inline size_t al(size_t x) { return (x + 1023) & ~(size_t)1023; }
@@ -458,13 +483,18 @@ Ws carve(uint8_t* base, long long max_rows, long long max_seg, int num_sms) {
   w.tile_partials = (float*)take(tiles * 2 * 4);
   w.tile_colsum = (float*)take(tiles * 2 * kHidden * 4);
   w.cta_partials = (float*)take((size_t)num_sms * kCtaPartialFloats * 4);
-  w.wg_partials = (float*)take((size_t)kWgMaxItems * kTileM * kHidden * 4);
+  {
+    const size_t v1 = (size_t)kWgMaxItems * kTileM * kHidden * 4;
+    const size_t v2 = (size_t)(num_sms / 2 + 16) * 256 * kHidden * 4;
+    w.wg_partials = (float*)take(v1 > v2 ? v1 : v2);
+  }
   w.seg_sum = (float*)take((size_t)max_seg * 2 * kHidden * 4);
   w.dlat_seg = (float*)take((size_t)max_seg * kLatent * 4);
   w.seg_norm = (float*)take((size_t)max_seg * 4);
   w.dweff = (float*)take((size_t)kWeffElems * 4);
   w.scene_e = take((size_t)max_seg * kSceneESteps * kStepBytes);
   w.relu_mask = (uint32_t*)take(tiles * 8 * 16 * kTileM * 4);
+  w.g_img = take(tiles * kSubBytes);
   w.total = o;
   return w;
 }
@@ -506,6 +536,8 @@ static int build_wg_items(dsdf_handle h, long long tiles, cudaStream_t st) {
   h->wg_layout.n_split = n_split;
   if ((int)items.size() > h->wg_items_cap) {
     cudaFree(h->wg_items);
+  cudaFree(h->wg2_segs);
+  cudaFree(h->wg2_seg_begin);
   cudaFree(h->dbg);
     CU(h, cudaMalloc(&h->wg_items, items.size() * sizeof(WgItem)));
     h->wg_items_cap = (int)items.size();
@@ -517,6 +549,70 @@ static int build_wg_items(dsdf_handle h, long long tiles, cudaStream_t st) {
   h->wg_items_tiles = tiles;
   return DSDF_OK;
 }
+
+// v2 wgrad schedule: items (layer 1..8, 256-row out chunk) x tiles, cut into equal-cost contiguous
+// ranges, one per CTA pair.  Cost per tile: 2 (N = 512) or 1 (lin4's x3 part, N = 256).
+static int build_wg2_schedule(dsdf_handle h, long long tiles, cudaStream_t st) {
+  if (h->wg2_tiles == tiles) return DSDF_OK;
+  struct Item { int layer, ocp, n_sub, cost; };
+  std::vector<Item> items;
+  for (int l = 1; l <= 8; ++l) {
+    h->wg2_layout.item_base[l] = (int)items.size();
+    const int n_ocp = (l == 3 || l == 8) ? 1 : 2;
+    for (int ocp = 0; ocp < n_ocp; ++ocp) items.push_back({l, ocp, l == 4 ? 4 : 8, l == 4 ? 1 : 2});
+  }
+  h->wg2_layout.item_base[0] = 0;
+  long long total = 0;
+  for (const Item& it : items) total += (long long)it.cost * tiles;
+  int n_pairs = h->num_sms / 2;
+  if (n_pairs < 1) n_pairs = 1;
+  const long long target = (total + n_pairs - 1) / n_pairs;
+  std::vector<WgSeg> segs;
+  std::vector<int> seg_begin;
+  size_t ii = 0;
+  long long t0 = 0;   // next unassigned tile of item ii
+  for (int p = 0; p < n_pairs; ++p) {
+    seg_begin.push_back((int)segs.size());
+    long long budget = target;
+    while (ii < items.size() && budget > 0) {
+      const Item& it = items[ii];
+      long long take = (budget + it.cost - 1) / it.cost;
+      if (take > tiles - t0) take = tiles - t0;
+      WgSeg sg;
+      sg.layer = it.layer; sg.ocp = it.ocp; sg.n_sub = it.n_sub; sg.slot = (int)segs.size();
+      sg.tile_lo = t0; sg.tile_hi = t0 + take;
+      segs.push_back(sg);
+      budget -= take * it.cost;
+      t0 += take;
+      if (t0 == tiles) { ++ii; t0 = 0; }
+    }
+  }
+  seg_begin.push_back((int)segs.size());
+  if (ii != items.size()) DSDF_FAIL(h, DSDF_EINVAL, "internal: wgrad schedule did not cover all items");
+  if ((int)segs.size() > h->num_sms / 2 + 16)
+    DSDF_FAIL(h, DSDF_EINVAL, "internal: wgrad schedule has %d segments, partial buffer holds %d",
+              (int)segs.size(), h->num_sms / 2 + 16);
+  for (size_t i = 0; i < items.size(); ++i) { h->wg2_layout.slot_lo[i] = 1 << 30; h->wg2_layout.slot_hi[i] = 0; }
+  for (const WgSeg& sg : segs) {
+    const int item = h->wg2_layout.item_base[sg.layer] + sg.ocp;
+    if (sg.slot < h->wg2_layout.slot_lo[item]) h->wg2_layout.slot_lo[item] = sg.slot;
+    if (sg.slot + 1 > h->wg2_layout.slot_hi[item]) h->wg2_layout.slot_hi[item] = sg.slot + 1;
+  }
+  cudaFree(h->wg2_segs);
+  cudaFree(h->wg2_seg_begin);
+  h->wg2_segs = nullptr;
+  h->wg2_seg_begin = nullptr;
+  CU(h, cudaMalloc(&h->wg2_segs, segs.size() * sizeof(WgSeg)));
+  CU(h, cudaMalloc(&h->wg2_seg_begin, seg_begin.size() * sizeof(int)));
+  CU(h, cudaMemcpyAsync(h->wg2_segs, segs.data(), segs.size() * sizeof(WgSeg), cudaMemcpyHostToDevice, st));
+  CU(h, cudaMemcpyAsync(h->wg2_seg_begin, seg_begin.data(), seg_begin.size() * sizeof(int), cudaMemcpyHostToDevice, st));
+  CU(h, cudaStreamSynchronize(st));   // host vectors go out of scope; once per shape change
+  h->wg2_pairs = n_pairs;
+  h->wg2_slots = (int)segs.size();
+  h->wg2_tiles = tiles;
+  return DSDF_OK;
+}
+constexpr int kWg2MaxSlots = 74 + 16;
 
 extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const float* table,
                                   int64_t num_scenes, const int64_t* seg_ids, int64_t n_seg,
@@ -542,7 +638,7 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   if ((size_t)(base - (uint8_t*)workspace) + w.total > workspace_bytes)
     DSDF_FAIL(h, DSDF_ENOMEM, "workspace too small: need %zu bytes, have %zu", w.total + 1024,
               workspace_bytes);
-  int rc = build_wg_items(h, tiles, st);
+  int rc = h->wg_ver == 1 ? build_wg_items(h, tiles, st) : build_wg2_schedule(h, tiles, st);
   if (rc != DSDF_OK) return rc;
 
   const float inv_n = 1.0f / (float)n_total;
@@ -573,6 +669,7 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   fa.dbg = h->dbg;
   fa.scene_e = w.scene_e;
   fa.relu_mask = w.relu_mask;
+  fa.g_img = h->wg_ver == 2 ? w.g_img : nullptr;
   if (h->fwd_v1) {
     k_forward<MODE_TABLE, true><<<grid, kFwdThreads, kFwdSmemBytes, st>>>(fa);
   } else {
@@ -595,7 +692,42 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   ba.xyz_stride = 4;
   ba.tile_colsum = w.tile_colsum;
   ba.cta_partials = w.cta_partials;
-  k_backward<<<grid, kBwdThreads, kBwdSmemBytes, st>>>(ba);
+  unsigned bwd_grid = grid;
+  if (h->bwd_ver == 1) {
+    k_backward<<<grid, kBwdThreads, kBwdSmemBytes, st>>>(ba);
+  } else {
+    Bwd2Args b2;
+    memset(&b2, 0, sizeof(b2));
+    b2.n_rows = n;
+    b2.dg2img = h->dg2_img;
+    b2.w8 = h->weff + weff_off(8);
+    b2.g = w.g;
+    b2.relu_mask = w.relu_mask;
+    b2.dystash = w.dystash;
+    b2.xyz = sdf_data;
+    b2.xyz_stride = 4;
+    b2.tile_colsum = w.tile_colsum;
+    b2.cta_partials = w.cta_partials;
+    const int cg = (h->fwd_cg == 2 && tiles >= 2) ? 2 : 1;
+    long long g2 = tiles < h->num_sms ? tiles : h->num_sms;
+    g2 = (g2 / cg) * cg;
+    bwd_grid = (unsigned)g2;
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3(bwd_grid);
+    cfg.blockDim = dim3(kB2Threads);
+    cfg.dynamicSmemBytes = cg == 2 ? B2<2>::kSmemBytes : B2<1>::kSmemBytes;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = cg;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    if (cg == 2) CU(h, cudaLaunchKernelEx(&cfg, k_backward2<2>, b2));
+    else CU(h, cudaLaunchKernelEx(&cfg, k_backward2<1>, b2));
+  }
   if (prof) prof_mark(h, st);
 
   // ---- wgrad GEMMs (lin1..lin7) + split-K reduction
@@ -604,9 +736,35 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   wa.xstash = w.xstash;
   wa.dystash = w.dystash;
   wa.partials = w.wg_partials;
-  k_wgrad<<<h->wg_n_items, kWgThreads, kWgSmemBytes, st>>>(wa);
-  if (prof) prof_mark(h, st);
-  k_reduce_wgrad<<<dim3(kHidden, 7), kHidden, 0, st>>>(w.wg_partials, h->wg_layout, w.dweff);
+  if (h->wg_ver == 1) {
+    k_wgrad<<<h->wg_n_items, kWgThreads, kWgSmemBytes, st>>>(wa);
+    if (prof) prof_mark(h, st);
+    k_reduce_wgrad<<<dim3(kHidden, 7), kHidden, 0, st>>>(w.wg_partials, h->wg_layout, w.dweff);
+  } else {
+    Wg2Args w2;
+    w2.segs = h->wg2_segs;
+    w2.seg_begin = h->wg2_seg_begin;
+    w2.xstash = w.xstash;
+    w2.dystash = w.dystash;
+    w2.g_img = w.g_img;
+    w2.partials = w.wg_partials;
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3((unsigned)(2 * h->wg2_pairs));
+    cfg.blockDim = dim3(kW2Threads);
+    cfg.dynamicSmemBytes = kW2SmemBytes;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    CU(h, cudaLaunchKernelEx(&cfg, k_wgrad2, w2));
+    if (prof) prof_mark(h, st);
+    k_reduce_wgrad2<<<dim3(kHidden, 8), kHidden, 0, st>>>(w.wg_partials, h->wg2_layout, w.dweff);
+  }
 
   // ---- segmented (scene-contiguous) reductions: latent grads, latent columns of dW0/dW4, biases
   const float reg_coef = reg_lambda_ramp * (float)rows_per_seg * inv_n;
@@ -618,8 +776,8 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   k_lat_grad_scatter<<<1, kLatent, 0, st>>>(w.dlat_seg, (const long long*)seg_ids, (int)n_seg, lat_grad);
   k_dw_latent<<<dim3(kHidden, 2), kLatent, 0, st>>>(w.seg_sum, table, (const long long*)seg_ids,
                                                     (int)n_seg, w.dweff);
-  k_reduce_cta<<<1, kHidden, 0, st>>>(w.cta_partials, (int)grid, w.seg_sum, (int)n_seg,
-                                      w.tile_partials, tiles, h->pl, grads, w.dweff);
+  k_reduce_cta<<<1, kHidden, 0, st>>>(w.cta_partials, (int)bwd_grid, w.seg_sum, (int)n_seg,
+                                      w.tile_partials, tiles, h->pl, grads, w.dweff, h->wg_ver == 1 ? 1 : 0);
   k_param_grads<<<(kScaleElems * 32 + 255) / 256, 256, 0, st>>>(w.dweff, params, h->pl, h->scale,
                                                                 h->inv_norm, grads);
   k_loss<<<1, 1024, 0, st>>>(w.tile_partials, tiles, inv_n, w.seg_norm, (int)n_seg, reg_coef, loss_out);

@@ -223,6 +223,32 @@ __global__ void k_fold_fwd2(const float* __restrict__ weff, const float* __restr
   *reinterpret_cast<uint4*>(img + (size_t)step * kStepBytes + (size_t)within * 16) = w;
 }
 
+// v2 dgrad K-step stream (layout.cuh): one thread per 16-byte chunk
+__global__ void k_fold_dgrad2(const float* __restrict__ weff, uint8_t* __restrict__ img) {
+  const long long cidx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long total = (long long)kDg2Steps * (kStepBytes / 16);
+  if (cidx >= total) return;
+  const int step = (int)(cidx / (kStepBytes / 16));
+  const int within = (int)(cidx % (kStepBytes / 16));
+  const int n = ((within >> 4) << 3) | (within & 7);   // [n/8][k/8][n%8]
+  const int kc = (within >> 3) & 1;
+  int l = 7;
+  while (l > 0 && step >= dg2_layer_base(l - 1)) --l;
+  const int sl = step - dg2_layer_base(l);
+  const int h = sl / dg2_ksteps(l), s = sl % dg2_ksteps(l);
+  const int ic = pad_to_ref_col(l, h * 256 + n);
+  float vals[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    const int o = s * 16 + kc * 8 + e;
+    vals[e] = (ic >= 0 && o < ref_out(l)) ? weff_at(weff, l, o, ic) : 0.f;
+  }
+  uint4 w;
+  w.x = pack_bf16x2(vals[0], vals[1]); w.y = pack_bf16x2(vals[2], vals[3]);
+  w.z = pack_bf16x2(vals[4], vals[5]); w.w = pack_bf16x2(vals[6], vals[7]);
+  *reinterpret_cast<uint4*>(img + (size_t)step * kStepBytes + (size_t)within * 16) = w;
+}
+
 // Fold mode: per-segment E steps of lin0 / lin4 with bias' = b + W[:, latent] z_seg (fp32).
 // grid (n_seg, 2), 512 threads; warp w computes rows o = w, w+16, ... (coalesced over the latent).
 // seg_ids == nullptr: one segment whose latent is `table` itself.

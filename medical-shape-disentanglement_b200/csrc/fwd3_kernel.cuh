@@ -426,6 +426,16 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
           const float inside = (th >= -d && th <= d) ? 1.f : 0.f;
           float g = valid ? sgn * inside * (1.f - th * th) * a.inv_n_total : 0.f;
           if (valid) a.gout[row] = g;
+          if (tile_valid && a.g_img) {
+            const __nv_bfloat16 gh = __float2bfloat16_rn(g);
+            const __nv_bfloat16 gl = __float2bfloat16_rn(g - __bfloat162float(gh));
+            uint8_t* gi = a.g_img + (size_t)tile * kSubBytes;
+            *reinterpret_cast<uint4*>(gi + sub_chunk_off(r, 0)) = make_uint4(
+                (uint32_t)__bfloat16_as_ushort(gh) | ((uint32_t)__bfloat16_as_ushort(gl) << 16), 0u, 0u, 0u);
+#pragma unroll
+            for (int ch = 1; ch < 8; ++ch)
+              *reinterpret_cast<uint4*>(gi + sub_chunk_off(r, ch)) = make_uint4(0u, 0u, 0u, 0u);
+          }
 #pragma unroll
           for (int o = 16; o > 0; o >>= 1) {
             lossr += __shfl_xor_sync(0xffffffffu, lossr, o);

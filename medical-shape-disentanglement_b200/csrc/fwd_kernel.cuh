@@ -44,6 +44,8 @@ struct FwdArgs {
   // TRAIN only
   uint8_t* xstash;      // [tiles][8][128 KB]
   uint32_t* relu_mask;  // [tiles][8 layers][16 chunks][128 rows]: bit (31-i) = column 32*chunk+i > 0
+  uint8_t* g_img;       // [tiles][16 KB SUB]: column 0 = bf16 hi part of dL/ds, column 1 = lo part
+                        // (the wgrad kernel's "dY" operand for lin8), fused-loss mode only
   float* gout;          // [n] dL/ds (s = pre-tanh lin8 output), fused-loss mode only
   float* tile_partials; // [tiles][2] {sum |clamp(pred)-clamp(gt)|, sum dL/ds}
   int fused_loss;       // 1: compute clamped-L1 loss + gout from sdf_data[:,3]

@@ -103,6 +103,25 @@ __host__ __device__ constexpr int dg_tile_base(int l) {
 }
 constexpr int kDgTilesTotal = dg_tile_base(8);  // 32+32+16+16+32+32+32 = 192
 
+// ---- v2 dgrad weight stream ("K-step image" of W^T) -------------------------------------------
+// The v2 backward chain computes dX_l[128 x in] = dY_l[128 x out] W_l as, per output half h
+// (i in [256h, 256h+256) of the padded input order), a stream of K-steps over o:
+//     step s: [256 i x 16 o] bf16, same no-swizzle layout as the forward stream (step_off),
+//             element (n, k) = W_l[o = 16 s + k, pad_to_ref_col(l, 256 h + n)]   (0 when padded)
+// Layers in stream order 7, 6, 5, 4, 3, 2, 1, then 0 (dense-input backward only: latent part).
+// lin4's second half (latent columns) is only consumed by the dense-input backward.
+__host__ __device__ constexpr int dg2_ksteps(int l) { return l == 3 ? 16 : 32; }          // out / 16
+__host__ __device__ constexpr int dg2_halves(int l) { return l == 0 ? 1 : 2; }            // in(pad) / 256
+__host__ __device__ constexpr int dg2_layer_base(int l) {   // stream order 7..0
+  int b = 0;
+  for (int i = 7; i > l; --i) b += dg2_halves(i) * dg2_ksteps(i);
+  return b;
+}
+__host__ __device__ constexpr int dg2_step(int l, int h, int s) {
+  return dg2_layer_base(l) + h * dg2_ksteps(l) + s;
+}
+constexpr int kDg2Steps = dg2_layer_base(0) + dg2_halves(0) * dg2_ksteps(0);  // 64*6 + 32 + 32 = 448
+
 // padded K index of layer l -> reference input column (or -1 for a zero pad column)
 __host__ __device__ __forceinline__ int pad_to_ref_col(int l, int kk) {
   if (l == 0) return kk;  // kk < 256: latent

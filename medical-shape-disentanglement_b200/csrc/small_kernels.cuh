@@ -13,6 +13,7 @@
 #include "fold_kernels.cuh"
 #include "layout.cuh"
 #include "wgrad_kernel.cuh"
+#include "wgrad2_kernel.cuh"
 
 namespace dsdf {
 
@@ -124,13 +125,46 @@ __global__ void k_reduce_wgrad(const float* __restrict__ partials, WgLayout wl,
   dweff[weff_off(l) + (size_t)o * ref_in(l) + ic] = s;
 }
 
+// v2 schedule: item (layer l, out-chunk pair) -> contiguous partial slots [slot_lo, slot_hi)
+struct Wg2Layout {
+  int item_base[9];   // first item of layer l (1..8)
+  int slot_lo[16];
+  int slot_hi[16];
+};
+// grid (512 rows o, 8 layers), 512 threads (i pad).  Fixed summation order -> deterministic.
+__global__ void k_reduce_wgrad2(const float* __restrict__ partials, Wg2Layout wl,
+                                float* __restrict__ dweff) {
+  const int l = blockIdx.y + 1, o = blockIdx.x, ip = threadIdx.x;
+  if (l == 8) {
+    if (o != 0) return;
+    const int item = wl.item_base[8];
+    float s = 0.f;
+    for (int k = wl.slot_lo[item]; k < wl.slot_hi[item]; ++k) {
+      const float* p = partials + (size_t)k * 256 * kHidden + ip;
+      s += p[0] + p[kHidden];   // D row 0 = bf16-hi part of g, row 1 = lo part
+    }
+    dweff[weff_off(8) + ip] = s;
+    return;
+  }
+  if (o >= ref_out(l)) return;
+  const int npad = (l == 4) ? 256 : 512;
+  if (ip >= npad) return;
+  const int ic = pad_to_ref_col(l, ip);
+  if (ic < 0) return;
+  const int item = wl.item_base[l] + (o >> 8);
+  float s = 0.f;
+  for (int k = wl.slot_lo[item]; k < wl.slot_hi[item]; ++k)
+    s += partials[((size_t)k * 256 + (o & 255)) * kHidden + ip];
+  dweff[weff_off(l) + (size_t)o * ref_in(l) + ic] = s;
+}
+
 // ---- reducer-warp partials (per CTA) -> bias grads, dW8, xyz columns of dW0/dW4 -----------------
 // one block of 512 threads (column c)
 __global__ void k_reduce_cta(const float* __restrict__ cta_partials, int n_cta,
                              const float* __restrict__ seg_sum, int n_seg,
                              const float* __restrict__ tile_partials, long long n_tiles,
                              ParamLayout pl, float* __restrict__ grads,
-                             float* __restrict__ dweff) {
+                             float* __restrict__ dweff, int with_dw8) {
   __shared__ float sh[16];
   const int c = threadIdx.x;
   // db for l in {1,2,3,5,6,7}
@@ -140,7 +174,7 @@ __global__ void k_reduce_cta(const float* __restrict__ cta_partials, int n_cta,
     for (int k = 0; k < n_cta; ++k) s += cta_partials[(size_t)k * kCtaPartialFloats + kPartDb + i * kHidden + c];
     if (c < ref_out(ls[i])) grads[pl.b[ls[i]] + c] = s;
   }
-  {  // dW8
+  if (with_dw8) {  // dW8 (v1 backward kernel only; the v2 path gets it from the wgrad kernel)
     float s = 0.f;
     for (int k = 0; k < n_cta; ++k) s += cta_partials[(size_t)k * kCtaPartialFloats + kPartW8 + c];
     dweff[weff_off(8) + c] = s;
