@@ -95,6 +95,9 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
   uint64_t* d_done = bars + 34;          // [2] MMA -> epilogue
   uint64_t* dy_ready = bars + 36;        // epilogue -> reducers: dY tile complete in A
   uint64_t* red_done = bars + 37;        // reducers -> epilogue: A may be overwritten
+  uint64_t* s_lo = bars + 38;            // epilogue -> stash warp: dY columns 0..255 written
+  uint64_t* s_hi = bars + 39;            // epilogue -> stash warp: dY columns 256..511 written
+  uint64_t* s_done = bars + 40;          // stash warp -> epilogue: dY tile copied to HBM
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + C::kSmemAux + C::kAuxTmem);
   float* w8s = reinterpret_cast<float*>(smem + C::kSmemAux + C::kAuxW8);
   float* gs = reinterpret_cast<float*>(smem + C::kSmemAux + C::kAuxG);
@@ -115,6 +118,9 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
     mbar_init(&d_done[1], 1);
     mbar_init(dy_ready, 8);
     mbar_init(red_done, 4);
+    mbar_init(s_lo, 8);
+    mbar_init(s_hi, 8);
+    mbar_init(s_done, 1);
     fence_mbar_init();
   }
   if (warp == 2) {
@@ -134,7 +140,7 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
   const uint32_t a_hi_c = CG > 1 ? mapa_u32(smem_u32(a_hi), 0) : smem_u32(a_hi);
 
   if (warp < 4) {
-    setmaxnreg_dec<40>();
+    setmaxnreg_dec<56>();
     if (warp == 0) {
       // ===================== weight producer =====================
       if (elect_one()) {
@@ -230,6 +236,47 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
         }
       }
     }
+    if (warp == 3) {
+      // ===================== dY-stash warp =====================
+      // dY_7..dY_1 images for the wgrad kernel: byte-for-byte the smem A tile -> linear copy with
+      // coalesced 512 B warp stores (see the forward kernel's stash warp for why not TMA).
+      uint32_t par_lo = 0, par_hi = 0;
+      for (long long it = 0; it < n_iter; ++it) {
+        long long tile = it * gridDim.x + blockIdx.x;
+        const bool tile_valid = tile < n_tiles;
+        tile = tile_valid ? tile : n_tiles - 1;
+        uint8_t* dy_tile = a.dystash + (size_t)tile * kStashTileBytes;
+#pragma unroll 1
+        for (int k = 7; k >= 1; --k) {
+          uint4* dst = reinterpret_cast<uint4*>(dy_tile + (size_t)k * kTileBytes);
+          const uint32_t src = s_base + C::kSmemA;
+#pragma unroll 1
+          for (int half = 0; half < 2; ++half) {
+            if (half == 1 && k == 3) break;                   // dY3 has 256 columns
+            if (half == 0) { mbar_wait(s_lo, par_lo); par_lo ^= 1; }
+            else { mbar_wait(s_hi, par_hi); par_hi ^= 1; }
+            if (tile_valid) {
+#pragma unroll 1
+              for (int i = 0; i < 128; i += 8) {
+                uint4 v[8];
+#pragma unroll
+                for (int q8 = 0; q8 < 8; ++q8) {
+                  const uint32_t off = (uint32_t)(half * 4 * kSubBytes) + (uint32_t)((i + q8) * 32 + lane) * 16u;
+                  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                               : "=r"(v[q8].x), "=r"(v[q8].y), "=r"(v[q8].z), "=r"(v[q8].w)
+                               : "r"(src + off));
+                }
+#pragma unroll
+                for (int q8 = 0; q8 < 8; ++q8)
+                  dst[(size_t)(half * 4 * kSubBytes) / 16 + (size_t)(i + q8) * 32 + lane] = v[q8];
+              }
+            }
+          }
+          __syncwarp();
+          if (lane == 0) mbar_arrive(s_done);
+        }
+      }
+    }
   } else if (warp < 12) {
     // ===================== epilogue warps =====================
     setmaxnreg_inc<176>();
@@ -239,7 +286,10 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
     const uint32_t r = q * 32 + lane;     // row inside the tile
     const uint32_t tlane = (uint32_t)(q * 32) << 16;
     const uint32_t a_base = s_base + C::kSmemA;
-    uint32_t par_d0 = 0, par_d1 = 0, par_rd = 0;
+    uint32_t par_d0 = 0, par_d1 = 0, par_rd = 0, par_s = 0;
+    auto stash_ready = [&](uint64_t* bar) {   // after this warp's A stores (+ __syncwarp)
+      if (lane == 0) mbar_arrive(bar);
+    };
     auto publish = [&](uint64_t* bar, uint32_t bar_c) {
       fence_proxy_async_smem();
       __syncwarp();
@@ -261,15 +311,12 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
       const long long row = row0 + r;
       const bool valid = tile_valid && row < a.n_rows;
       const uint32_t* mask_tile = a.relu_mask + (size_t)tile * (8 * 16 * kTileM) + r;
-      uint8_t* dy_tile = a.dystash + (size_t)tile * kStashTileBytes;
       // previous tile: reducers done with dY0, stash stores done reading A
       if (!first) {
         mbar_wait(red_done, par_rd);
         par_rd ^= 1;
       }
       first = false;
-      if (t == 0) bulk_wait_read_all();
-      named_bar_sync(1, 256);
       const float gr = valid ? __ldg(a.g + row) : 0.f;
       if (j == 0) {
         gs[r] = gr;
@@ -294,11 +341,8 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
       }
       publish(a_lo, a_lo_c);
       publish(a_hi, a_hi_c);
-      named_bar_sync(1, 256);
-      if (t == 0 && tile_valid) {
-        bulk_s2g(dy_tile + (size_t)7 * kTileBytes, smem + C::kSmemA, kTileBytes);
-        bulk_commit();
-      }
+      stash_ready(s_lo);
+      stash_ready(s_hi);
       tell_reducers();
 
 #pragma unroll 1
@@ -330,12 +374,12 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
         }
         mbar_wait(red_done, par_rd);        // ... the reducers have read dY_l
         par_rd ^= 1;
-        if (t == 0) bulk_wait_read_all();   // ... and its stash copy has been read out
-        named_bar_sync(1, 256);
+        mbar_wait(s_done, par_s);           // ... and the stash warp has copied it
+        par_s ^= 1;
 #pragma unroll
         for (int c = 0; c < 4; ++c) store_chunk32(a_base, r, (uint32_t)(j * 128 + c * 32), held + 16 * c);
         tc_fence_before();
-        if (l - 1 >= 1) publish(a_lo, a_lo_c); else fence_proxy_async_smem();
+        if (l - 1 >= 1) { publish(a_lo, a_lo_c); stash_ready(s_lo); }
         if (has_h1) {
 #pragma unroll
           for (int c = 0; c < 4; ++c) {
@@ -346,18 +390,13 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
             store_chunk32(a_base, r, (uint32_t)(256 + j * 128 + c * 32), p);
           }
           tc_fence_before();
-          if (l - 1 >= 1 && b2_in_hi(l - 1)) publish(a_hi, a_hi_c); else fence_proxy_async_smem();
-        }
-        named_bar_sync(1, 256);
-        if (l - 1 >= 1 && t == 0 && tile_valid) {
-          bulk_s2g(dy_tile + (size_t)(l - 1) * kTileBytes, smem + C::kSmemA,
-                   has_h1 ? (uint32_t)kTileBytes : 4u * kSubBytes);
-          bulk_commit();
+          if (l - 1 >= 1 && b2_in_hi(l - 1)) publish(a_hi, a_hi_c); else __syncwarp();
+          if (l - 1 >= 1) stash_ready(s_hi);
         }
         tell_reducers();
       }
     }
-    if (t == 0) bulk_wait_all();
+
   } else {
     // ===================== reducer warps =====================
     setmaxnreg_dec<96>();

@@ -20,7 +20,7 @@
 // advances in multiples of 16 steps.
 //
 // TRAIN mode also writes, per layer, the activation stash (bf16 images, consumed by the wgrad
-// kernel) and a 1-bit/element ReLU mask (consumed by the backward chain instead of re-reading the
+// kernel; stored straight from the epilogue registers) and a 1-bit/element ReLU mask (consumed by the backward chain instead of re-reading the
 // 1 KB/row activations).
 //
 // Replaces, per 128-row tile, reference networks/deep_sdf_decoder.py:74-109 (9x addmm, 2x cat,
@@ -60,6 +60,20 @@ __device__ __forceinline__ uint32_t pos_mask32(const uint32_t (&v)[32]) {
   return ~m;
 }
 
+// 16 packed words = columns col..col+31 of row r -> activation-stash image in HBM (same
+// SWIZZLE_128B SUB layout as the smem A tile).  Straight from the epilogue registers: a 128 KB
+// bulk store per layer would sit in the SM's TMA queue in front of the 4 KB weight-ring loads and
+// starve the MMA (measured: 46 % of the issuer's time waiting on `full`).
+__device__ __forceinline__ void stash_chunk32(uint8_t* slot_base, uint32_t r, uint32_t col,
+                                              const uint32_t* p) {
+  uint8_t* sub = slot_base + (size_t)(col >> 6) * kSubBytes;
+  const uint32_t ch0 = (col & 63) >> 3;
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+    *reinterpret_cast<uint4*>(sub + sub_chunk_off(r, ch0 + i)) =
+        make_uint4(p[4 * i], p[4 * i + 1], p[4 * i + 2], p[4 * i + 3]);
+}
+
 template <int MODE, bool FOLD, bool TRAIN, int CG>
 __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
   using C = F3<CG>;
@@ -78,6 +92,9 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
   uint64_t* a_lo = bars + 36;            // epilogue -> MMA: A SUB 0..3 (+E_A) ready, TMEM h0 drained
   uint64_t* a_hi = bars + 37;            // epilogue -> MMA: A SUB 4..7 ready, TMEM h1 drained
   uint64_t* d_done = bars + 38;          // [2] MMA -> epilogue: half h accumulated
+  uint64_t* s_lo = bars + 40;            // TRAIN: epilogue -> stash warp: A SUB 0..3 written
+  uint64_t* s_hi = bars + 41;            //        epilogue -> stash warp: A SUB 4..7 written
+  uint64_t* s_done = bars + 42;          //        stash warp -> epilogue: A tile copied to HBM
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + C::kSmemAux + C::kAuxTmem);
   float* part = reinterpret_cast<float*>(smem + C::kSmemAux + C::kAuxPart);
   float* red = reinterpret_cast<float*>(smem + C::kSmemAux + C::kAuxRed);
@@ -100,6 +117,9 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
     }
     mbar_init(a_lo, 8 * CG);             // one elected arrive per epilogue warp of every CTA
     mbar_init(a_hi, 8 * CG);
+    mbar_init(s_lo, 8);
+    mbar_init(s_hi, 8);
+    mbar_init(s_done, 1);
     fence_mbar_init();
   }
   if (warp == 2) {
@@ -201,30 +221,35 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
       const uint64_t b_desc0 = umma_smem_desc_ns(s_base + C::kSmemRing, 128, 256);
       const uint64_t eb_desc0 = umma_smem_desc_ns(s_base + C::kSmemERing, 128, 256);
       uint32_t ph = 0, es = 0, eph = 0, par_lo = 0, par_hi = 0;
+      long long dbg_wf = 0, dbg_wl = 0, dbg_wh = 0, dbg_we = 0;
+      const long long dbg_t0 = DSDF_DBG_ON(a) ? clock64() : 0;
+      auto timed_wait = [&](uint64_t* bar, uint32_t par, long long& acc) {
+        if (DSDF_DBG_ON(a)) {
+          const long long c0 = clock64();
+          mbar_wait(bar, par);
+          acc += clock64() - c0;
+        } else {
+          mbar_wait(bar, par);
+        }
+      };
       auto mma = [&](uint32_t d, uint64_t ad, uint64_t bd, uint32_t acc) {
         if (CG > 1) umma2_bf16(d, ad, bd, idesc, acc); else umma_bf16(d, ad, bd, idesc, acc);
       };
       auto commit = [&](uint64_t* bar) {
         if (CG > 1) umma2_commit_mc(bar, (uint16_t)3); else umma_commit(bar);
       };
-      auto wait_a = [&](uint64_t* bar, uint32_t par) {
-        // plain (cta-scope acquire) wait, as CUTLASS' ClusterBarrier::wait: the operands are read by
-        // the tensor core's async proxy after tcgen05.fence::after_thread_sync, and an
-        // acquire.cluster wait costs a CCTL.IVALL per poll (measured 4x slower end to end)
-        mbar_wait(bar, par);
-      };
       for (long long it = 0; it < n_iter; ++it) {
 #pragma unroll 1
         for (int l = 0; l < 8; ++l) {
           const int groups = f2_used_ksteps<FOLD>(l) / kRing;
-          wait_a(a_lo, par_lo);
+          timed_wait(a_lo, par_lo, dbg_wl);
           par_lo ^= 1;
           tc_fence_after();
 #pragma unroll 1
           for (int h = 0; h < w2_halves(l); ++h) {
             const uint32_t d_addr = tmem + h * 256;
             // E step: xyz (hi/lo) + bias through the ones columns; overwrites the accumulator
-            wait_a(&e_full[es], eph);
+            timed_wait(&e_full[es], eph, dbg_we);
             tc_fence_after();
             mma(d_addr, ea_desc, eb_desc0 + (uint64_t)(es * (kSlice >> 4)), 0u);
             commit(&e_empty[es]);
@@ -233,7 +258,7 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
 #pragma unroll 1
             for (int g = 0; g < groups; ++g) {
               if (h == 0 && g * kRing == 16) {   // first K-step that reads A SUB 4..7
-                wait_a(a_hi, par_hi);
+                timed_wait(a_hi, par_hi, dbg_wh);
                 par_hi ^= 1;
                 tc_fence_after();
               }
@@ -241,7 +266,7 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
               const uint64_t a_desc = a_desc0 + (uint64_t)((g * (kRing / 4) * kSubBytes) >> 4);
 #pragma unroll
               for (int u = 0; u < kRing; ++u) {
-                wait_a(&full[u], ph);
+                timed_wait(&full[u], ph, dbg_wf);
                 tc_fence_after();
                 mma(d_addr, a_desc + (uint64_t)(((u >> 2) * kSubBytes + (u & 3) * 32) >> 4),
                     b_desc0 + (uint64_t)((u * kSlice) >> 4), 1u);
@@ -253,6 +278,54 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
           }
         }
       }
+      if (DSDF_DBG_ON(a)) {
+        unsigned long long* d = a.dbg + (size_t)blockIdx.x * kDbgSlots;
+        d[0] = clock64() - dbg_t0; d[1] = dbg_wf; d[2] = dbg_wl; d[3] = dbg_wh; d[8] = dbg_we;
+      }
+    }
+  } else if (warp == 3) {
+    // ===================== TRAIN: activation-stash warp =====================
+    // The stash image in HBM is byte-for-byte the smem A tile, so this is a linear copy with fully
+    // coalesced 512 B warp stores.  (Not a TMA bulk store: 128 KB per layer in the SM's TMA queue
+    // starves the 4 KB weight-ring loads; not per-row stores from the epilogue registers either:
+    // 16 B per 128 B line.)
+    if (TRAIN) {
+      uint32_t par_lo = 0, par_hi = 0;
+      for (long long it = 0; it < n_iter; ++it) {
+        long long tile = it * gridDim.x + blockIdx.x;
+        const bool tile_valid = tile < n_tiles;
+        tile = tile_valid ? tile : n_tiles - 1;
+        uint8_t* xs_tile = a.xstash + (size_t)tile * kStashTileBytes;
+#pragma unroll 1
+        for (int l = 0; l < 8; ++l) {
+          uint4* dst = reinterpret_cast<uint4*>(xs_tile + (size_t)l * kTileBytes);
+          const uint32_t src = s_base + C::kSmemA;
+#pragma unroll 1
+          for (int half = 0; half < 2; ++half) {
+            if (half == 1 && l == 3 && FOLD) break;          // lin3 has 256 outputs (x3 part)
+            if (half == 0) { mbar_wait(s_lo, par_lo); par_lo ^= 1; }
+            else { mbar_wait(s_hi, par_hi); par_hi ^= 1; }
+            if (tile_valid) {
+#pragma unroll 1
+              for (int i = 0; i < 128; i += 8) {              // 4 SUBs = 4096 x 16 B = 128 x (32 lanes)
+                uint4 v[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                  const uint32_t off = (uint32_t)(half * 4 * kSubBytes) + (uint32_t)((i + k) * 32 + lane) * 16u;
+                  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                               : "=r"(v[k].x), "=r"(v[k].y), "=r"(v[k].z), "=r"(v[k].w)
+                               : "r"(src + off));
+                }
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                  dst[(size_t)(half * 4 * kSubBytes) / 16 + (size_t)(i + k) * 32 + lane] = v[k];
+              }
+            }
+          }
+          __syncwarp();
+          if (lane == 0) mbar_arrive(s_done);
+        }
+      }
     }
   } else if (warp >= 4) {
     // ===================== epilogue warps =====================
@@ -262,7 +335,12 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
     const uint32_t r = q * 32 + lane;     // row inside the tile
     const uint32_t tlane = (uint32_t)(q * 32) << 16;
     const uint32_t a_base = s_base + C::kSmemA;
-    uint32_t par_d0 = 0, par_d1 = 0;
+    uint32_t par_d0 = 0, par_d1 = 0, par_s = 1;   // par_s: first wait passes (nothing copied yet)
+    auto stash_ready = [&](uint64_t* bar) {       // after publish(): this warp's A stores are done
+      if (TRAIN && lane == 0) mbar_arrive(bar);
+    };
+    long long dbg_d0 = 0, dbg_d1 = 0, dbg_rd = 0;
+    const long long dbg_e0 = DSDF_DBG_ON(a) ? clock64() : 0;
     // generic-proxy writes of this warp -> visible to the (leader's) MMA, one arrive per warp
     // (each SM's tensor core reads its OWN A tile, so cta-scope release + the proxy fence order
     // the data; only the arrival itself travels to the leader)
@@ -281,10 +359,6 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
       const long long row0 = tile * kTileM;
       uint32_t* mask_tile = TRAIN ? a.relu_mask + (size_t)tile * (8 * 16 * kTileM) + r : nullptr;
       // ---- tile prologue: E_A rows (+ layer-0 latent gather when not folded)
-      if (TRAIN && !FOLD) {   // the previous tile's slot-7 stash may still be reading A
-        if (t == 0) bulk_wait_read_all();
-        named_bar_sync(1, kActThreads);
-      }
       if (!FOLD) gather_latent<MODE>(a, row0, a_base, t);
       float gt = 0.f;
       if (t < kTileM) {
@@ -301,7 +375,11 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
         const bool has_h1 = (l != 3);
         // ---- half 0: TMEM -> ReLU -> bf16, held in registers while the MMAs still read A
         uint32_t held[64];
-        mbar_wait(&d_done[0], par_d0);
+        {
+          const long long c0 = DSDF_DBG_ON(a) ? clock64() : 0;
+          mbar_wait(&d_done[0], par_d0);
+          if (DSDF_DBG_ON(a)) dbg_d0 += clock64() - c0;
+        }
         par_d0 ^= 1;
         tc_fence_after();
 #pragma unroll
@@ -313,18 +391,23 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
           if (TRAIN && tile_valid) mask_tile[(size_t)(l * 16 + j * 4 + c) * kTileM] = pos_mask32(v);
         }
         if (has_h1) {
+          const long long c0 = DSDF_DBG_ON(a) ? clock64() : 0;
           mbar_wait(&d_done[1], par_d1);    // every MMA of layer l has retired: A is free
+          if (DSDF_DBG_ON(a)) dbg_d1 += clock64() - c0;
           par_d1 ^= 1;
           tc_fence_after();
         }
-        if (TRAIN) {                        // ... and the stash copy of A has been read out
-          if (t == 0) bulk_wait_read_all();
-          named_bar_sync(1, kActThreads);
+        if (TRAIN) {                        // ... and the stash warp has copied the old A tile
+          const long long c0 = DSDF_DBG_ON(a) ? clock64() : 0;
+          mbar_wait(s_done, par_s);
+          par_s ^= 1;
+          if (DSDF_DBG_ON(a)) dbg_rd += clock64() - c0;
         }
 #pragma unroll
         for (int c = 0; c < 4; ++c) store_chunk32(a_base, r, (uint32_t)(j * 128 + c * 32), held + 16 * c);
         tc_fence_before();
         publish(a_lo_c);
+        stash_ready(s_lo);
         // ---- half 1: straight from TMEM into SUB 4..7
         if (has_h1) {
 #pragma unroll
@@ -337,21 +420,13 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
             if (TRAIN && tile_valid) mask_tile[(size_t)(l * 16 + 8 + j * 4 + c) * kTileM] = pos_mask32(v);
           }
           tc_fence_before();
-          if (f2_in_hi<FOLD>(l + 1)) publish(a_hi_c); else fence_proxy_async_smem();
+          if (f2_in_hi<FOLD>(l + 1)) publish(a_hi_c); else __syncwarp();
+          stash_ready(s_hi);
         } else if (!FOLD) {
           // skip connection: latent -> SUB 4..7 (reference cat order [x3 | latent | xyz])
           gather_latent<MODE>(a, row0, a_base + 4 * kSubBytes, t);
           publish(a_hi_c);
-        }
-        if (TRAIN) {
-          // stash X_{l+1} (input of lin(l+1)); for l == 3 only the x3 part (SUB 0..3) in fold mode
-          named_bar_sync(1, kActThreads);
-          if (t == 0 && tile_valid) {
-            const uint32_t bytes = (l == 3 && FOLD) ? 4 * kSubBytes : kTileBytes;
-            bulk_s2g(a.xstash + (size_t)tile * kStashTileBytes + (size_t)l * kTileBytes,
-                     smem + C::kSmemA, bytes);
-            bulk_commit();
-          }
+          stash_ready(s_hi);
         }
       }
 
@@ -378,11 +453,13 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
         mbar_wait(&d_done[1], par_d1);
         par_d1 ^= 1;
         tc_fence_after();
-        if (TRAIN) {
-          if (t == 0) bulk_wait_read_all();
-          named_bar_sync(1, kActThreads);
+        if (TRAIN) {   // X8 goes through the A tile only to be stashed (wgrad of lin8, ReLU of lin7)
+          mbar_wait(s_done, par_s);
+          par_s ^= 1;
 #pragma unroll
           for (int c = 0; c < 4; ++c) store_chunk32(a_base, r, (uint32_t)(j * 128 + c * 32), held + 16 * c);
+          __syncwarp();
+          stash_ready(s_lo);
         }
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
@@ -399,16 +476,14 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
             if (tile_valid) mask_tile[(size_t)(7 * 16 + 8 + j * 4 + c) * kTileM] = pos_mask32(v);
           }
         }
+        if (TRAIN) {
+          __syncwarp();
+          stash_ready(s_hi);
+        }
       }
       tc_fence_before();
       if (j == 1) part[r] = acc;
-      if (TRAIN) fence_proxy_async_smem();
       named_bar_sync(1, kActThreads);
-      if (TRAIN && t == 0 && tile_valid) {
-        bulk_s2g(a.xstash + (size_t)tile * kStashTileBytes + (size_t)7 * kTileBytes,
-                 smem + C::kSmemA, kTileBytes);
-        bulk_commit();
-      }
       if (j == 0) {
         const long long row = row0 + r;
         const bool valid = tile_valid && row < a.n_rows;
@@ -454,7 +529,10 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
         named_bar_sync(1, kActThreads);   // part[] is rewritten by the next tile
       }
     }
-    if (TRAIN && t == 0) bulk_wait_all();
+    if (DSDF_DBG_ON(a) && t == 0) {
+      unsigned long long* d = a.dbg + (size_t)blockIdx.x * kDbgSlots;
+      d[5] = dbg_d0; d[6] = dbg_d1; d[7] = clock64() - dbg_e0; d[9] = dbg_rd;
+    }
   }
 
   tc_fence_before();

@@ -104,7 +104,7 @@ class OracleTrainer:
         self.opt.param_groups[1]["lr"] = step_lr(c.lr_latent, c.lr_interval, c.lr_factor, epoch)
 
     def forward_loss(self, sdf_data: torch.Tensor, scene_ids: torch.Tensor, epoch: int,
-                     n_total: Optional[int] = None):
+                     n_total: Optional[int] = None, pred_noise: float = 0.0):
         """Gather + forward + loss for all chunks, calling backward per chunk like the
         reference (:594-731).  sdf_data [B,P,4] (or [M,4] with P=cfg.samples_per_scene)."""
         c = self.cfg
@@ -126,6 +126,12 @@ class OracleTrainer:
             bv = self.lat_vecs(idx_c[i])
             inp = torch.cat([bv, xyz_c[i]], dim=1)
             pred = deepsdf.forward(self.params, self.spec, inp, training=True)
+            if pred_noise:
+                # test diagnostic only (not reference behaviour): uniform +-pred_noise on the SDF
+                # output, to measure how far the clamped-L1 gradient moves under an output
+                # perturbation far inside the 2e-3 parity tolerance (sign(pred-gt) is discontinuous)
+                gen = torch.Generator(device=pred.device).manual_seed(1234 + i)
+                pred = pred + pred_noise * (2 * torch.rand(pred.shape, generator=gen, device=pred.device) - 1)
             pred = torch.clamp(pred, -c.clamp_dist, c.clamp_dist)
             chunk_loss = torch.nn.functional.l1_loss(pred, gt_c[i], reduction="sum") / n_total
             sdf_loss += float(chunk_loss.item())

@@ -12,7 +12,7 @@ from dsdf_b200 import _lib, synth
 
 dev = torch.device("cuda:0")
 NAMES = ["mma_total", "mma_wait_full", "mma_wait_a_lo", "mma_wait_a_hi", "prod_wait_empty",
-         "epi_wait_d0", "epi_wait_d1", "epi_total", "s8", "s9", "s10", "s11", "s12", "s13", "s14", "s15"]
+         "epi_wait_d0", "epi_wait_d1", "epi_total", "mma_wait_e_full", "epi_wait_stash_read", "s10", "s11", "s12", "s13", "s14", "s15"]
 
 
 def read(dec, label, tiles_per_cta):
@@ -22,7 +22,7 @@ def read(dec, label, tiles_per_cta):
     buf = (C.c_uint64 * n)()
     got = L.dsdf_debug_read(h, buf, n)
     a = np.frombuffer(buf, dtype=np.uint64).reshape(-1, 16).astype(np.float64)
-    a = a[a[:, 0] > 0]
+    a = a[a[:, 7] > 0]
     print(f"== {label}: {a.shape[0]} CTAs, {tiles_per_cta:.1f} tiles/CTA")
     for i, nm in enumerate(NAMES):
         if a[:, i].max() > 0:
