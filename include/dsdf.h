@@ -130,6 +130,45 @@ int dsdf_clip_adam(dsdf_handle h, float* params, float* grads, float* exp_avg, f
                    int64_t n, float max_norm, float lr, float beta1, float beta2, float eps,
                    int64_t step, float* scratch, void* stream);
 
+/* reconstruct(decoder, num_iterations, latent_size, test_sdf, stat, clamp_dist, num_samples, lr,
+ * l2reg, code_reg_lambda, code_reg_type, code_bound, ..., dist_mean, dist_std, dist_weight,
+ * dist_type) (reconstruct.py:16-151): Adam on the latent code of a FROZEN decoder, batched over
+ * n_shapes independent shapes (each shape is exactly the reference's loop; shapes never interact).
+ * The whole num_iterations loop is enqueued on `stream` by one call: per iteration a sample-window
+ * gather (deep_sdf/data.py:112-136), the fused forward + clamped-L1(mean) + dgrad chain, the
+ * per-shape latent gradient (segmented column sums, no atomics), Adam and the optional norm bound.
+ * No wgrad, no activation stash.  lr schedule: lr * 0.1^(e // max(1, num_iterations/2)) (:35-44). */
+typedef struct {
+  int64_t num_iterations;
+  int64_t num_samples;      /* rows per iteration and shape; even (half pos, half neg) */
+  float clamp_dist;
+  float lr;
+  int32_t reg_kind;         /* 0 none; 1 lambda*mean(z^2) (l2reg / "l2_sq"); 2 lambda*||z|| ("l2_norm") */
+  float reg_lambda;
+  float code_bound;         /* <= 0: none; else z *= min(1, bound/(||z||+1e-12)) after every step */
+  int32_t dist_kind;        /* 0 none; 1 mean(diff^2) ("zscore_l2"); 2 mean(|diff|) ("l1") */
+  float dist_weight;
+  const float* dist_mean;   /* device [256] or NULL */
+  const float* dist_std;    /* device [256] (clamped >= 1e-8 by the caller) or NULL */
+} dsdf_reconstruct_cfg;
+
+size_t dsdf_reconstruct_workspace_bytes(dsdf_handle h, int64_t n_shapes, int64_t num_samples);
+
+/*   samples     [total_rows, 4] (x,y,z,sdf): every shape's `pos` rows and `neg` rows (data.py:83-110)
+ *   shape_base  [n_shapes, 2] int64 device: first row of the shape's pos block, of its neg block
+ *   windows     [num_iterations, n_shapes, 2] int64 device: window starts inside pos / neg
+ *               (the reference draws them with random.randint per iteration, data.py:118-131;
+ *               the host side draws the same sequence and uploads it)
+ *   latents     [n_shapes, 256] in/out; exp_avg / exp_avg_sq [n_shapes, 256] Adam state (zeroed by
+ *               the caller for a fresh run); loss_hist [num_iterations, n_shapes] device (nullable);
+ *   first_step  1-based Adam step / iteration index of the first iteration run by this call
+ *               (1 for a fresh run; lets a caller split the loop into several calls). */
+int dsdf_reconstruct(dsdf_handle h, const float* params, const dsdf_reconstruct_cfg* cfg,
+                     int64_t n_shapes, const float* samples, const int64_t* shape_base,
+                     const int64_t* windows, int64_t first_step, int64_t n_steps, float* latents,
+                     float* exp_avg, float* exp_avg_sq, void* workspace, size_t workspace_bytes,
+                     float* loss_hist, void* stream);
+
 /* Per-kernel timing of dsdf_train_fwd_bwd with CUDA events recorded on the caller's stream
  * (the stream the kernels are launched on).  After enable(1) every call records 5 events;
  * read() synchronises on them and returns, summed over the n_calls recorded calls, the

@@ -255,7 +255,7 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
             if (half == 1 && k == 3) break;                   // dY3 has 256 columns
             if (half == 0) { mbar_wait(s_lo, par_lo); par_lo ^= 1; }
             else { mbar_wait(s_hi, par_hi); par_hi ^= 1; }
-            if (tile_valid) {
+            if (tile_valid && a.dystash) {    // frozen-decoder callers pass no stash (no wgrad)
 #pragma unroll 1
               for (int i = 0; i < 128; i += 8) {
                 uint4 v[8];

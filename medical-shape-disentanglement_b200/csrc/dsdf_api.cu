@@ -20,6 +20,7 @@
 #include "fwd2_kernel.cuh"
 #include "fwd3_kernel.cuh"
 #include "layout.cuh"
+#include "recon_kernels.cuh"
 #include "selftest.cuh"
 #include "small_kernels.cuh"
 #include "wgrad_kernel.cuh"
@@ -536,9 +537,7 @@ static int build_wg_items(dsdf_handle h, long long tiles, cudaStream_t st) {
   h->wg_layout.n_split = n_split;
   if ((int)items.size() > h->wg_items_cap) {
     cudaFree(h->wg_items);
-  cudaFree(h->wg2_segs);
-  cudaFree(h->wg2_seg_begin);
-  cudaFree(h->dbg);
+    h->wg_items = nullptr;
     CU(h, cudaMalloc(&h->wg_items, items.size() * sizeof(WgItem)));
     h->wg_items_cap = (int)items.size();
   }
@@ -613,6 +612,31 @@ static int build_wg2_schedule(dsdf_handle h, long long tiles, cudaStream_t st) {
   return DSDF_OK;
 }
 constexpr int kWg2MaxSlots = 74 + 16;
+
+// persistent dgrad chain launch (CTA pairs when there are at least two tiles)
+static int launch_backward2(dsdf_handle h, const Bwd2Args& b2, long long tiles, cudaStream_t st,
+                            unsigned* grid_out) {
+  const int cg = (h->fwd_cg == 2 && tiles >= 2) ? 2 : 1;
+  long long g2 = tiles < h->num_sms ? tiles : h->num_sms;
+  g2 = (g2 / cg) * cg;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3((unsigned)g2);
+  cfg.blockDim = dim3(kB2Threads);
+  cfg.dynamicSmemBytes = cg == 2 ? B2<2>::kSmemBytes : B2<1>::kSmemBytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = cg;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  if (cg == 2) CU(h, cudaLaunchKernelEx(&cfg, k_backward2<2>, b2));
+  else CU(h, cudaLaunchKernelEx(&cfg, k_backward2<1>, b2));
+  if (grid_out) *grid_out = (unsigned)g2;
+  return DSDF_OK;
+}
 
 extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const float* table,
                                   int64_t num_scenes, const int64_t* seg_ids, int64_t n_seg,
@@ -708,25 +732,8 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
     b2.xyz_stride = 4;
     b2.tile_colsum = w.tile_colsum;
     b2.cta_partials = w.cta_partials;
-    const int cg = (h->fwd_cg == 2 && tiles >= 2) ? 2 : 1;
-    long long g2 = tiles < h->num_sms ? tiles : h->num_sms;
-    g2 = (g2 / cg) * cg;
-    bwd_grid = (unsigned)g2;
-    cudaLaunchConfig_t cfg;
-    memset(&cfg, 0, sizeof(cfg));
-    cfg.gridDim = dim3(bwd_grid);
-    cfg.blockDim = dim3(kB2Threads);
-    cfg.dynamicSmemBytes = cg == 2 ? B2<2>::kSmemBytes : B2<1>::kSmemBytes;
-    cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = cg;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    if (cg == 2) CU(h, cudaLaunchKernelEx(&cfg, k_backward2<2>, b2));
-    else CU(h, cudaLaunchKernelEx(&cfg, k_backward2<1>, b2));
+    int rc2 = launch_backward2(h, b2, tiles, st, &bwd_grid);
+    if (rc2 != DSDF_OK) return rc2;
   }
   if (prof) prof_mark(h, st);
 
@@ -782,6 +789,164 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
                                                                 h->inv_norm, grads);
   k_loss<<<1, 1024, 0, st>>>(w.tile_partials, tiles, inv_n, w.seg_norm, (int)n_seg, reg_coef, loss_out);
   if (prof) prof_mark(h, st);
+  CU(h, cudaGetLastError());
+  return DSDF_OK;
+}
+
+// ------------------------------------------------------------------------------- reconstruct
+namespace {
+struct RWs {
+  float* sdf;            // [n_shapes][rows_pad][4]
+  long long* ids;        // [n_shapes] identity segment ids
+  float* g;
+  float* pred;
+  float* tile_partials;
+  float* tile_colsum;
+  float* cta_partials;
+  float* seg_sum;
+  uint8_t* scene_e;
+  uint32_t* relu_mask;
+  float* loss_sink;      // [n_shapes] when the caller wants no loss history
+  size_t total;
+};
+inline long long recon_rows_pad(long long num_samples) {
+  return (num_samples + 2 * kTileM - 1) / (2 * kTileM) * (2 * kTileM);   // whole CTA pairs
+}
+RWs recon_carve(uint8_t* base, long long n_shapes, long long num_samples, int num_sms) {
+  const long long rows_pad = recon_rows_pad(num_samples);
+  const size_t rows = (size_t)(n_shapes * rows_pad);
+  const size_t tiles = rows / kTileM;
+  RWs w;
+  size_t o = 0;
+  auto take = [&](size_t bytes) { uint8_t* p = base ? base + o : nullptr; o += al(bytes); return p; };
+  w.sdf = (float*)take(rows * 16);
+  w.ids = (long long*)take((size_t)n_shapes * 8);
+  w.g = (float*)take(rows * 4);
+  w.pred = (float*)take(rows * 4);
+  w.tile_partials = (float*)take(tiles * 2 * 4);
+  w.tile_colsum = (float*)take(tiles * 2 * kHidden * 4);
+  w.cta_partials = (float*)take((size_t)num_sms * kCtaPartialFloats * 4);
+  w.seg_sum = (float*)take((size_t)n_shapes * 2 * kHidden * 4);
+  w.scene_e = take((size_t)n_shapes * kSceneESteps * kStepBytes);
+  w.relu_mask = (uint32_t*)take(tiles * 8 * 16 * kTileM * 4);
+  w.loss_sink = (float*)take((size_t)n_shapes * 4);
+  w.total = o;
+  return w;
+}
+}  // namespace
+
+extern "C" size_t dsdf_reconstruct_workspace_bytes(dsdf_handle h, int64_t n_shapes, int64_t num_samples) {
+  if (!h || n_shapes <= 0 || num_samples <= 0) return 0;
+  return recon_carve(nullptr, n_shapes, num_samples, h->num_sms).total + 1024;
+}
+
+extern "C" int dsdf_reconstruct(dsdf_handle h, const float* params, const dsdf_reconstruct_cfg* cfg,
+                                int64_t n_shapes, const float* samples, const int64_t* shape_base,
+                                const int64_t* windows, int64_t first_step, int64_t n_steps,
+                                float* latents, float* exp_avg, float* exp_avg_sq, void* workspace,
+                                size_t workspace_bytes, float* loss_hist, void* stream) {
+  if (!h || !params || !cfg || !samples || !shape_base || !windows || !latents || !exp_avg ||
+      !exp_avg_sq || !workspace)
+    DSDF_FAIL(h, DSDF_EINVAL, "null argument");
+  if (!h->weights_set) DSDF_FAIL(h, DSDF_EINVAL, "dsdf_set_weights has not been called");
+  if (n_shapes <= 0 || cfg->num_samples < 2 || (cfg->num_samples & 1))
+    DSDF_FAIL(h, DSDF_EINVAL, "num_samples must be even and >= 2 (half pos, half neg; got %lld)",
+              (long long)cfg->num_samples);
+  if (first_step < 1 || n_steps < 0 || first_step - 1 + n_steps > cfg->num_iterations)
+    DSDF_FAIL(h, DSDF_EINVAL, "iterations [%lld, %lld) outside 1..num_iterations",
+              (long long)first_step, (long long)(first_step + n_steps));
+  if (cfg->reg_kind < 0 || cfg->reg_kind > 2 || cfg->dist_kind < 0 || cfg->dist_kind > 2)
+    DSDF_FAIL(h, DSDF_EINVAL, "unknown regulariser kind");
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long num = cfg->num_samples;
+  const long long rows_pad = recon_rows_pad(num);
+  const long long n = n_shapes * rows_pad;
+  const long long tiles = n / kTileM;
+  const int tiles_per_seg = (int)(rows_pad / kTileM);
+  uint8_t* base = (uint8_t*)(((uintptr_t)workspace + 1023) & ~(uintptr_t)1023);
+  RWs w = recon_carve(base, n_shapes, num, h->num_sms);
+  if ((size_t)(base - (uint8_t*)workspace) + w.total > workspace_bytes)
+    DSDF_FAIL(h, DSDF_ENOMEM, "workspace too small: need %zu bytes, have %zu", w.total + 1024,
+              workspace_bytes);
+
+  FwdArgs fa;
+  memset(&fa, 0, sizeof(fa));
+  fa.wimg = h->fwd_img;
+  fa.w8 = h->weff + weff_off(8);
+  fa.b8 = h->weff + kWeffElems;
+  fa.n_rows = n;
+  fa.table = latents;
+  fa.seg_ids = w.ids;
+  fa.rows_per_seg = rows_pad;
+  fa.valid_per_seg = num;
+  fa.xyzs = w.sdf;
+  fa.xyz_stride = 4;
+  fa.out = w.pred;
+  fa.gout = w.g;
+  fa.tile_partials = w.tile_partials;
+  fa.fused_loss = 1;
+  fa.clamp_dist = cfg->clamp_dist;
+  fa.inv_n_total = 1.0f / (float)num;          // L1Loss() = mean over num_samples (reconstruct.py:102)
+  fa.w2img = h->w2_img;
+  fa.dbg = h->dbg;
+  fa.scene_e = w.scene_e;
+  fa.relu_mask = w.relu_mask;                   // xstash / g_img stay null: frozen decoder, no wgrad
+
+  Bwd2Args b2;
+  memset(&b2, 0, sizeof(b2));
+  b2.n_rows = n;
+  b2.dg2img = h->dg2_img;
+  b2.w8 = h->weff + weff_off(8);
+  b2.g = w.g;
+  b2.relu_mask = w.relu_mask;
+  b2.xyz = w.sdf;
+  b2.xyz_stride = 4;
+  b2.tile_colsum = w.tile_colsum;
+  b2.cta_partials = w.cta_partials;
+
+  ReconUpdateArgs ua;
+  memset(&ua, 0, sizeof(ua));
+  ua.seg_sum = w.seg_sum;
+  ua.weff = h->weff;
+  ua.tile_partials = w.tile_partials;
+  ua.tiles_per_seg = tiles_per_seg;
+  ua.inv_n = 1.0f / (float)num;
+  ua.reg_kind = cfg->reg_lambda > 0.f ? cfg->reg_kind : 0;
+  ua.reg_lambda = cfg->reg_lambda;
+  ua.dist_kind = (cfg->dist_weight > 0.f && cfg->dist_mean) ? cfg->dist_kind : 0;
+  ua.dist_weight = cfg->dist_weight;
+  ua.dist_mean = cfg->dist_mean;
+  ua.dist_std = cfg->dist_std;
+  ua.b1 = 0.9f;
+  ua.b2 = 0.999f;
+  ua.eps = 1e-8f;
+  ua.code_bound = cfg->code_bound;
+  ua.latents = latents;
+  ua.exp_avg = exp_avg;
+  ua.exp_avg_sq = exp_avg_sq;
+
+  long long adjust_every = cfg->num_iterations / 2;
+  if (adjust_every < 1) adjust_every = 1;
+  const dim3 ggrid((unsigned)((rows_pad + 255) / 256), (unsigned)n_shapes);
+  for (long long i = 0; i < n_steps; ++i) {
+    const long long e = first_step - 1 + i;     // 0-based iteration (reconstruct.py:76)
+    k_recon_gather<<<ggrid, 256, 0, st>>>((const float4*)samples, (const long long*)shape_base,
+                                          (const long long*)windows + e * n_shapes * 2, num / 2, rows_pad,
+                                          (float4*)w.sdf, w.ids);
+    k_scene_fold<<<dim3((unsigned)n_shapes, 2), 512, 0, st>>>(h->weff, params, h->pl, latents, w.ids,
+                                                             w.scene_e);
+    CU(h, (launch_fwd<MODE_TABLE, true, true>(h, fa, st, true)));
+    int rc = launch_backward2(h, b2, tiles, st, nullptr);
+    if (rc != DSDF_OK) return rc;
+    k_seg_colsum<<<dim3((unsigned)n_shapes, 2), kHidden, 0, st>>>(w.tile_colsum, tiles_per_seg, w.seg_sum);
+    const double lr = (double)cfg->lr * pow(0.1, (double)(e / adjust_every));
+    const double bc1 = 1.0 - pow(0.9, (double)(e + 1));
+    const double bc2 = 1.0 - pow(0.999, (double)(e + 1));
+    ua.step_size = (float)(lr / bc1);
+    ua.bc2_sqrt = (float)sqrt(bc2);
+    ua.loss_out = loss_hist ? loss_hist + e * n_shapes : w.loss_sink;
+    k_recon_update<<<(unsigned)n_shapes, 1024, 0, st>>>(ua);
+  }
   CU(h, cudaGetLastError());
   return DSDF_OK;
 }

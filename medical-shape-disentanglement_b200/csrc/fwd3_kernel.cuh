@@ -305,7 +305,7 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
             if (half == 1 && l == 3 && FOLD) break;          // lin3 has 256 outputs (x3 part)
             if (half == 0) { mbar_wait(s_lo, par_lo); par_lo ^= 1; }
             else { mbar_wait(s_hi, par_hi); par_hi ^= 1; }
-            if (tile_valid) {
+            if (tile_valid && a.xstash) {     // frozen-decoder callers pass no stash (no wgrad)
 #pragma unroll 1
               for (int i = 0; i < 128; i += 8) {              // 4 SUBs = 4096 x 16 B = 128 x (32 lanes)
                 uint4 v[8];
@@ -486,10 +486,11 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
       named_bar_sync(1, kActThreads);
       if (j == 0) {
         const long long row = row0 + r;
-        const bool valid = tile_valid && row < a.n_rows;
+        const bool in_range = tile_valid && row < a.n_rows;
+        const bool valid = in_range && (a.valid_per_seg == 0 || (row % a.rows_per_seg) < a.valid_per_seg);
         const float s = acc + part[r] + __ldg(a.b8);
         const float th = tanhf(s);
-        if (valid) a.out[row] = th;
+        if (in_range) a.out[row] = th;
         if (TRAIN && a.fused_loss) {
           // train_deep_sdf.py:565-567,604-606: clamp both, L1(sum)/N_total.
           const float d = a.clamp_dist;
@@ -500,7 +501,7 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
           const float sgn = (diff > 0.f) ? 1.f : ((diff < 0.f) ? -1.f : 0.f);
           const float inside = (th >= -d && th <= d) ? 1.f : 0.f;
           float g = valid ? sgn * inside * (1.f - th * th) * a.inv_n_total : 0.f;
-          if (valid) a.gout[row] = g;
+          if (in_range) a.gout[row] = g;
           if (tile_valid && a.g_img) {
             const __nv_bfloat16 gh = __float2bfloat16_rn(g);
             const __nv_bfloat16 gl = __float2bfloat16_rn(g - __bfloat162float(gh));

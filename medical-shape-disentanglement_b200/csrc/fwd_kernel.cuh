@@ -51,6 +51,10 @@ struct FwdArgs {
   int fused_loss;       // 1: compute clamped-L1 loss + gout from sdf_data[:,3]
   float clamp_dist;
   float inv_n_total;
+  // v3 fused-loss mode: rows r with (r % rows_per_seg) >= valid_per_seg are padding (zero loss,
+  // zero dL/ds); 0 = every row is a sample.  Used by the latent-only optimisation whose
+  // num_samples (reconstruct.py:22, 8000 on the CLI) is not a multiple of the 128-row tile.
+  long long valid_per_seg;
   // diagnostics (nullable): per-CTA cycle counters, see dsdf_debug_read
   unsigned long long* dbg;
 };

@@ -9,3 +9,4 @@ from ._lib import DsdfError, LIB_PATH  # noqa: F401
 from .decoder import Decoder  # noqa: F401
 from .trainer import FusedTrainer, StepConfig  # noqa: F401
 from .mesh import create_mesh_sdf, decode_grid_sharded  # noqa: F401
+from .reconstruct import reconstruct, reconstruct_batch, draw_windows  # noqa: F401

@@ -2,8 +2,7 @@
 
 Follows /root/reference/reconstruct.py:16-151 (frozen decoder, Adam on one latent) and the
 sample window draw of /root/reference/deep_sdf/data.py:112-136.  The optional
-`code_reg_lambda` / `dist_*` regularisers of the reference default to off and are restated
-for `l2_sq` / `l2_norm` only.
+`code_reg_lambda` (`l2_sq` / `l2_norm`) and `dist_*` regularisers of the reference default to off.
 
 Window offsets come from Python's `random.randint` in the reference; here they are drawn
 up front (`draw_windows`) so the CUDA path can replay the identical sequence.
@@ -40,13 +39,20 @@ def reconstruct(params, spec: deepsdf.DecoderSpec, num_iterations: int, pos: tor
                 neg: torch.Tensor, windows, latent_init: torch.Tensor, clamp_dist: float,
                 num_samples: int = 8000, lr: float = 5e-3, l2reg: bool = True,
                 code_reg_lambda: Optional[float] = None, code_reg_type: str = "l2_sq",
-                code_bound: Optional[float] = None, device: str = "cpu"):
+                code_bound: Optional[float] = None, device: str = "cpu",
+                dist_mean: Optional[torch.Tensor] = None, dist_std: Optional[torch.Tensor] = None,
+                dist_weight: float = 0.0, dist_type: str = "zscore_l2", return_first_grad: bool = False):
     decreased_by = 10
     adjust_lr_every = max(1, int(num_iterations / 2))                    # :43-44
     params = {k: v.to(device) for k, v in params.items()}
     latent = latent_init.clone().to(device).requires_grad_(True)         # :49-54
     opt = torch.optim.Adam([latent], lr=lr)                              # :56
     losses = []
+    first_grad = None
+    if dist_mean is not None:                                            # :58-70
+        dist_mean = dist_mean.to(device)
+    if dist_std is not None:
+        dist_std = torch.clamp(dist_std.to(device), min=1e-8)
     for e in range(num_iterations):
         sdf_data = window(pos, neg, num_samples, windows[e]).to(device)  # :80
         xyz = sdf_data[:, 0:3]
@@ -66,11 +72,21 @@ def reconstruct(params, spec: deepsdf.DecoderSpec, num_iterations: int, pos: tor
                 loss = loss + float(code_reg_lambda) * torch.mean(latent.pow(2))
         elif l2reg:
             loss = loss + 1e-4 * torch.mean(latent.pow(2))               # :114-116
+        if dist_weight > 0.0 and dist_mean is not None:                  # :117-129
+            diff = (latent - dist_mean) / dist_std if dist_std is not None else latent - dist_mean
+            if dist_type in ("zscore_l2", "diag_gaussian", "gaussian", "l2", "mse"):
+                loss = loss + dist_weight * torch.mean(diff.pow(2))
+            else:
+                loss = loss + dist_weight * torch.mean(diff.abs())
         loss.backward()                                                  # :130
+        if e == 0:
+            first_grad = latent.grad.detach().clone().cpu()
         opt.step()                                                       # :131
         if code_bound is not None and float(code_bound) > 0:             # :134-140
             with torch.no_grad():
                 n = latent.norm(dim=1, keepdim=True)
                 latent.mul_(torch.clamp(float(code_bound) / (n + 1e-12), max=1.0))
         losses.append(float(loss.detach().cpu()))
+    if return_first_grad:
+        return losses, latent.detach().cpu(), first_grad
     return losses, latent.detach().cpu()
