@@ -130,6 +130,20 @@ int dsdf_clip_adam(dsdf_handle h, float* params, float* grads, float* exp_avg, f
                    int64_t n, float max_norm, float lr, float beta1, float beta2, float eps,
                    int64_t step, float* scratch, void* stream);
 
+/* Training-mode dropout of the hidden layers (networks/deep_sdf_decoder.py:24,103-104:
+ * F.dropout(x, p=dropout_prob, training=self.training) after the ReLU of every layer in `dropout`),
+ * fused into the forward epilogues of dsdf_train_fwd_bwd: layer_mask bit l <=> l in NetworkSpecs.dropout,
+ * prob = dropout_prob.  Keep/drop of element (row, layer, column) is Philox4x32-10 keyed by `seed`
+ * and counted by (row_base + row, layer, column block, offset): deterministic, order-independent;
+ * pass a new `offset` (the step count) every step.  layer_mask 0 or prob 0 switches dropout off
+ * (the default; eval mode).  Takes effect for subsequent dsdf_train_fwd_bwd calls on this handle. */
+int dsdf_set_dropout(dsdf_handle h, uint32_t layer_mask, float prob, uint64_t seed, uint64_t offset,
+                     int64_t row_base);
+/* Bookkeeping view of that stream: keep_out[n_rows][512] (1 = kept) for rows [row_lo, row_lo+n_rows)
+ * after lin `layer` under the current dsdf_set_dropout settings. */
+int dsdf_dropout_keep(dsdf_handle h, int32_t layer, int64_t row_lo, int64_t n_rows, uint8_t* keep_out,
+                      void* stream);
+
 /* reconstruct(decoder, num_iterations, latent_size, test_sdf, stat, clamp_dist, num_samples, lr,
  * l2reg, code_reg_lambda, code_reg_type, code_bound, ..., dist_mean, dist_std, dist_weight,
  * dist_type) (reconstruct.py:16-151): Adam on the latent code of a FROZEN decoder, batched over

@@ -38,6 +38,8 @@ struct Bwd2Args {
   long long xyz_stride;
   float* tile_colsum;         // [tiles][2][512]: colsum(dY0), colsum(dY4)
   float* cta_partials;        // [grid][kCtaPartialFloats]
+  DropoutArgs drop;           // DROP: layers + scale (the keep bits already sit in relu_mask)
+  int stash_dy0;              // dense-input backward: also stash dY0 (slot 0) for the dInput / dW0 kernels
 };
 
 template <int CG>
@@ -77,7 +79,7 @@ __device__ __forceinline__ void mask_pack32(const uint32_t (&v)[32], uint32_t m,
   }
 }
 
-template <int CG>
+template <int CG, bool DROP = false>
 __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
   using C = B2<CG>;
   constexpr int kRing = C::kRing;
@@ -247,7 +249,7 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
         tile = tile_valid ? tile : n_tiles - 1;
         uint8_t* dy_tile = a.dystash + (size_t)tile * kStashTileBytes;
 #pragma unroll 1
-        for (int k = 7; k >= 1; --k) {
+        for (int k = 7; k >= (a.stash_dy0 ? 0 : 1); --k) {
           uint4* dst = reinterpret_cast<uint4*>(dy_tile + (size_t)k * kTileBytes);
           const uint32_t src = s_base + C::kSmemA;
 #pragma unroll 1
@@ -315,9 +317,14 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
       if (!first) {
         mbar_wait(red_done, par_rd);
         par_rd ^= 1;
+        if (a.stash_dy0) {                  // ... and the stash warp has copied the previous tile's dY0
+          mbar_wait(s_done, par_s);
+          par_s ^= 1;
+        }
       }
       first = false;
-      const float gr = valid ? __ldg(a.g + row) : 0.f;
+      float gr = valid ? __ldg(a.g + row) : 0.f;
+      if (DROP && ((a.drop.layers >> 7) & 1u)) gr *= a.drop.scale;   // dropout after lin7's ReLU
       if (j == 0) {
         gs[r] = gr;
         const long long rr = row < a.n_rows ? row : a.n_rows - 1;
@@ -365,7 +372,8 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
           uint32_t v[32];
           tmem_ld_32x32(tmem + tlane + (uint32_t)(j * 128 + c * 32), v);
           tmem_ld_wait();
-          mask_pack32(v, mk[c], held + 16 * c);
+          if (DROP && ((a.drop.layers >> lm) & 1u)) mask_scale_pack32(v, mk[c], a.drop.scale, held + 16 * c);
+          else mask_pack32(v, mk[c], held + 16 * c);
         }
         if (has_h1) {
           mbar_wait(&d_done[1], par_d1);    // every MMA of layer l has retired: A is free
@@ -380,18 +388,20 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
         for (int c = 0; c < 4; ++c) store_chunk32(a_base, r, (uint32_t)(j * 128 + c * 32), held + 16 * c);
         tc_fence_before();
         if (l - 1 >= 1) { publish(a_lo, a_lo_c); stash_ready(s_lo); }
+        else if (a.stash_dy0) { __syncwarp(); stash_ready(s_lo); }
         if (has_h1) {
 #pragma unroll
           for (int c = 0; c < 4; ++c) {
             uint32_t v[32], p[16];
             tmem_ld_32x32(tmem + tlane + (uint32_t)(256 + j * 128 + c * 32), v);
             tmem_ld_wait();
-            mask_pack32(v, mk[4 + c], p);
+            if (DROP && ((a.drop.layers >> lm) & 1u)) mask_scale_pack32(v, mk[4 + c], a.drop.scale, p);
+            else mask_pack32(v, mk[4 + c], p);
             store_chunk32(a_base, r, (uint32_t)(256 + j * 128 + c * 32), p);
           }
           tc_fence_before();
           if (l - 1 >= 1 && b2_in_hi(l - 1)) publish(a_hi, a_hi_c); else __syncwarp();
-          if (l - 1 >= 1) stash_ready(s_hi);
+          if (l - 1 >= 1 || a.stash_dy0) stash_ready(s_hi);
         }
         tell_reducers();
       }

@@ -66,6 +66,7 @@ struct dsdf_handle_s {
   const float* params_ptr = nullptr;   // caller's flat fp32 parameters at the last dsdf_set_weights
   bool weights_set = false;
   bool attrs_set = false;
+  DropoutArgs drop{};                  // dsdf_set_dropout; layers == 0: no dropout
   // optional per-kernel timing (CUDA events on the caller's stream), see dsdf_profile_*
   bool profile = false;
   std::vector<cudaEvent_t> prof_events;   // 5 per dsdf_train_fwd_bwd call
@@ -125,6 +126,10 @@ static int set_kernel_attrs(dsdf_handle h) {
   F3ATTR(MODE_GRID, true, false)
   F3ATTR(MODE_TABLE, true, true)
 #undef F3ATTR
+  CU(h, cudaFuncSetAttribute(k_forward3<MODE_TABLE, true, true, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, F3<1>::kSmemBytes));
+  CU(h, cudaFuncSetAttribute(k_forward3<MODE_TABLE, true, true, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, F3<2>::kSmemBytes));
+  CU(h, cudaFuncSetAttribute(k_backward2<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, B2<1>::kSmemBytes));
+  CU(h, cudaFuncSetAttribute(k_backward2<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, B2<2>::kSmemBytes));
   CU(h, cudaFuncSetAttribute(k_backward, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmemBytes));
   CU(h, cudaFuncSetAttribute(k_backward2<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, B2<1>::kSmemBytes));
   CU(h, cudaFuncSetAttribute(k_backward2<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, B2<2>::kSmemBytes));
@@ -289,7 +294,7 @@ static cudaError_t launch_fwd2(dsdf_handle h, const FwdArgs& a, cudaStream_t st)
   return launch_fwd2_cl<MODE, FOLD, TRAIN, 1>(h, a, st);
 }
 // ---- v3 forward launcher: persistent grid, CTA pairs (cta_group::2) when `pair_ok` -------------
-template <int MODE, bool FOLD, bool TRAIN, int CG>
+template <int MODE, bool FOLD, bool TRAIN, int CG, bool DROP = false>
 static cudaError_t launch_fwd3_cg(dsdf_handle h, const FwdArgs& a, cudaStream_t st) {
   const long long tiles = (a.n_rows + kTileM - 1) / kTileM;
   long long g = tiles < h->num_sms ? tiles : h->num_sms;
@@ -308,16 +313,16 @@ static cudaError_t launch_fwd3_cg(dsdf_handle h, const FwdArgs& a, cudaStream_t 
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  return cudaLaunchKernelEx(&cfg, k_forward3<MODE, FOLD, TRAIN, CG>, a);
+  return cudaLaunchKernelEx(&cfg, k_forward3<MODE, FOLD, TRAIN, CG, DROP>, a);
 }
 // pair_ok: both tiles of a pair may share the B operand (always true unless FOLD segments are
 // shorter than 256 rows-aligned, see callers)
-template <int MODE, bool FOLD, bool TRAIN>
+template <int MODE, bool FOLD, bool TRAIN, bool DROP = false>
 static cudaError_t launch_fwd(dsdf_handle h, const FwdArgs& a, cudaStream_t st, bool pair_ok) {
-  if (h->fwd_ver == 2) return launch_fwd2<MODE, FOLD, TRAIN>(h, a, st);
+  if (h->fwd_ver == 2 && !DROP) return launch_fwd2<MODE, FOLD, TRAIN>(h, a, st);
   const long long tiles = (a.n_rows + kTileM - 1) / kTileM;
-  if (pair_ok && h->fwd_cg == 2 && tiles >= 2) return launch_fwd3_cg<MODE, FOLD, TRAIN, 2>(h, a, st);
-  return launch_fwd3_cg<MODE, FOLD, TRAIN, 1>(h, a, st);
+  if (pair_ok && h->fwd_cg == 2 && tiles >= 2) return launch_fwd3_cg<MODE, FOLD, TRAIN, 2, DROP>(h, a, st);
+  return launch_fwd3_cg<MODE, FOLD, TRAIN, 1, DROP>(h, a, st);
 }
 // per-segment E steps for the fold-mode inference entries (handle-owned, grown on demand)
 static int ensure_scene_e(dsdf_handle h, long long n_seg) {
@@ -632,8 +637,13 @@ static int launch_backward2(dsdf_handle h, const Bwd2Args& b2, long long tiles, 
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  if (cg == 2) CU(h, cudaLaunchKernelEx(&cfg, k_backward2<2>, b2));
-  else CU(h, cudaLaunchKernelEx(&cfg, k_backward2<1>, b2));
+  if (b2.drop.layers != 0) {
+    if (cg == 2) CU(h, (cudaLaunchKernelEx(&cfg, k_backward2<2, true>, b2)));
+    else CU(h, (cudaLaunchKernelEx(&cfg, k_backward2<1, true>, b2)));
+  } else {
+    if (cg == 2) CU(h, (cudaLaunchKernelEx(&cfg, k_backward2<2>, b2)));
+    else CU(h, (cudaLaunchKernelEx(&cfg, k_backward2<1>, b2)));
+  }
   if (grid_out) *grid_out = (unsigned)g2;
   return DSDF_OK;
 }
@@ -653,6 +663,8 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
               "fused step needs scene-contiguous segments with SamplesPerScene %% 128 == 0 (got %lld)",
               (long long)rows_per_seg);
   if (n_total <= 0) DSDF_FAIL(h, DSDF_EINVAL, "n_total must be positive");
+  if (h->drop.layers != 0 && (h->fwd_v1 || h->bwd_ver == 1))
+    DSDF_FAIL(h, DSDF_EUNSUPPORTED, "dropout needs the v3 forward / v2 backward kernels");
   cudaStream_t st = (cudaStream_t)stream;
   const long long n = n_seg * rows_per_seg;
   const long long tiles = n / kTileM;
@@ -699,7 +711,11 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   } else {
     k_scene_fold<<<dim3((unsigned)n_seg, 2), 512, 0, st>>>(h->weff, params, h->pl, table,
                                                           (const long long*)seg_ids, w.scene_e);
-    CU(h, (launch_fwd<MODE_TABLE, true, true>(h, fa, st, rows_per_seg % (2 * kTileM) == 0)));
+    fa.drop = h->drop;
+    if (h->drop.layers != 0)
+      CU(h, (launch_fwd<MODE_TABLE, true, true, true>(h, fa, st, rows_per_seg % (2 * kTileM) == 0)));
+    else
+      CU(h, (launch_fwd<MODE_TABLE, true, true>(h, fa, st, rows_per_seg % (2 * kTileM) == 0)));
   }
   if (prof) prof_mark(h, st);
 
@@ -732,6 +748,7 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
     b2.xyz_stride = 4;
     b2.tile_colsum = w.tile_colsum;
     b2.cta_partials = w.cta_partials;
+    b2.drop = h->drop;
     int rc2 = launch_backward2(h, b2, tiles, st, &bwd_grid);
     if (rc2 != DSDF_OK) return rc2;
   }
@@ -789,6 +806,44 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
                                                                 h->inv_norm, grads);
   k_loss<<<1, 1024, 0, st>>>(w.tile_partials, tiles, inv_n, w.seg_norm, (int)n_seg, reg_coef, loss_out);
   if (prof) prof_mark(h, st);
+  CU(h, cudaGetLastError());
+  return DSDF_OK;
+}
+
+// ------------------------------------------------------------------------------- dropout
+extern "C" int dsdf_set_dropout(dsdf_handle h, uint32_t layer_mask, float prob, uint64_t seed,
+                                uint64_t offset, int64_t row_base) {
+  if (!h) return DSDF_EINVAL;
+  if (layer_mask & ~0xFFu) DSDF_FAIL(h, DSDF_EINVAL, "dropout layers must be hidden layers 0..7");
+  if (!(prob >= 0.f) || prob >= 1.f) DSDF_FAIL(h, DSDF_EINVAL, "dropout_prob must be in [0, 1)");
+  memset(&h->drop, 0, sizeof(h->drop));
+  if (layer_mask == 0 || prob == 0.f) return DSDF_OK;
+  h->drop.layers = layer_mask;
+  h->drop.thresh16 = (uint32_t)lrint((double)prob * 65536.0);
+  h->drop.scale = 1.0f / (1.0f - prob);
+  h->drop.seed_lo = (uint32_t)seed;
+  h->drop.seed_hi = (uint32_t)(seed >> 32);
+  h->drop.offset = (uint32_t)offset;
+  h->drop.row_base = row_base;
+  return DSDF_OK;
+}
+
+__global__ void k_dropout_keep(DropoutArgs d, int layer, long long row_lo, long long n_rows, uint8_t* out) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;   // (row, chunk32)
+  if (i >= n_rows * 16) return;
+  const long long r = i >> 4;
+  const int ch = (int)(i & 15);
+  const uint32_t m = dropout_keep32(d, d.row_base + row_lo + r, layer, ch);
+  for (int k = 0; k < 32; ++k) out[r * kHidden + ch * 32 + k] = (m >> (31 - k)) & 1u;
+}
+
+extern "C" int dsdf_dropout_keep(dsdf_handle h, int32_t layer, int64_t row_lo, int64_t n_rows,
+                                 uint8_t* keep_out, void* stream) {
+  if (!h || !keep_out || layer < 0 || layer > 7 || n_rows < 0) DSDF_FAIL(h, DSDF_EINVAL, "bad argument");
+  if (n_rows == 0) return DSDF_OK;
+  DropoutArgs d = h->drop;
+  if (!((d.layers >> layer) & 1u)) d.thresh16 = 0;   // layer without dropout: everything kept
+  k_dropout_keep<<<(unsigned)((n_rows * 16 + 255) / 256), 256, 0, (cudaStream_t)stream>>>(d, layer, row_lo, n_rows, keep_out);
   CU(h, cudaGetLastError());
   return DSDF_OK;
 }

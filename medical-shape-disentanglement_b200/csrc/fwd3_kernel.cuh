@@ -74,8 +74,21 @@ __device__ __forceinline__ void stash_chunk32(uint8_t* slot_base, uint32_t r, ui
         make_uint4(p[4 * i], p[4 * i + 1], p[4 * i + 2], p[4 * i + 3]);
 }
 
-template <int MODE, bool FOLD, bool TRAIN, int CG>
+// 32 fp32 columns -> zero where mask bit (31 - i) is clear, else x * scale -> 16 packed bf16x2
+// (ReLU and dropout in one select: the mask is (x > 0) & keep)
+__device__ __forceinline__ void mask_scale_pack32(const uint32_t (&v)[32], uint32_t m, float scale,
+                                                  uint32_t* p) {
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const float lo = (m & (0x80000000u >> (2 * i))) ? __uint_as_float(v[2 * i]) * scale : 0.f;
+    const float hi = (m & (0x40000000u >> (2 * i))) ? __uint_as_float(v[2 * i + 1]) * scale : 0.f;
+    p[i] = pack_bf16x2(lo, hi);
+  }
+}
+
+template <int MODE, bool FOLD, bool TRAIN, int CG, bool DROP = false>
 __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
+  static_assert(!DROP || TRAIN, "dropout exists in training mode only");
   using C = F3<CG>;
   constexpr int kRing = C::kRing;
   constexpr uint32_t kSlice = C::kSlice;
@@ -358,6 +371,16 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
       tile = tile_valid ? tile : n_tiles - 1;
       const long long row0 = tile * kTileM;
       uint32_t* mask_tile = TRAIN ? a.relu_mask + (size_t)tile * (8 * 16 * kTileM) + r : nullptr;
+      // ReLU (+ dropout) of 32 accumulator columns -> packed bf16; returns the stored mask word
+      auto act_pack32 = [&](const uint32_t (&v)[32], int l, uint32_t col, uint32_t* p) -> uint32_t {
+        if (DROP && ((a.drop.layers >> l) & 1u)) {
+          const uint32_t m = pos_mask32(v) & dropout_keep32(a.drop, a.drop.row_base + row0 + r, l, (int)(col >> 5));
+          mask_scale_pack32(v, m, a.drop.scale, p);
+          return m;
+        }
+        relu_pack32(v, p);
+        return TRAIN ? pos_mask32(v) : 0u;
+      };
       // ---- tile prologue: E_A rows (+ layer-0 latent gather when not folded)
       if (!FOLD) gather_latent<MODE>(a, row0, a_base, t);
       float gt = 0.f;
@@ -387,8 +410,8 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
           uint32_t v[32];
           tmem_ld_32x32(tmem + tlane + (uint32_t)(j * 128 + c * 32), v);
           tmem_ld_wait();
-          relu_pack32(v, held + 16 * c);
-          if (TRAIN && tile_valid) mask_tile[(size_t)(l * 16 + j * 4 + c) * kTileM] = pos_mask32(v);
+          const uint32_t mw = act_pack32(v, l, (uint32_t)(j * 128 + c * 32), held + 16 * c);
+          if (TRAIN && tile_valid) mask_tile[(size_t)(l * 16 + j * 4 + c) * kTileM] = mw;
         }
         if (has_h1) {
           const long long c0 = DSDF_DBG_ON(a) ? clock64() : 0;
@@ -415,9 +438,9 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
             uint32_t v[32], p[16];
             tmem_ld_32x32(tmem + tlane + (uint32_t)(256 + j * 128 + c * 32), v);
             tmem_ld_wait();
-            relu_pack32(v, p);
+            const uint32_t mw = act_pack32(v, l, (uint32_t)(256 + j * 128 + c * 32), p);
             store_chunk32(a_base, r, (uint32_t)(256 + j * 128 + c * 32), p);
-            if (TRAIN && tile_valid) mask_tile[(size_t)(l * 16 + 8 + j * 4 + c) * kTileM] = pos_mask32(v);
+            if (TRAIN && tile_valid) mask_tile[(size_t)(l * 16 + 8 + j * 4 + c) * kTileM] = mw;
           }
           tc_fence_before();
           if (f2_in_hi<FOLD>(l + 1)) publish(a_hi_c); else __syncwarp();
@@ -443,11 +466,19 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
           const uint32_t col = (uint32_t)(j * 128 + c * 32);
           tmem_ld_32x32(tmem + tlane + col, v);
           tmem_ld_wait();
+          if (DROP && ((a.drop.layers >> 7) & 1u)) {
+            const uint32_t mw = act_pack32(v, 7, col, held + 16 * c);
 #pragma unroll
-          for (int i = 0; i < 32; ++i) acc = fmaf(fmaxf(__uint_as_float(v[i]), 0.f), w8s[col + i], acc);
-          if (TRAIN) {
-            relu_pack32(v, held + 16 * c);
-            if (tile_valid) mask_tile[(size_t)(7 * 16 + j * 4 + c) * kTileM] = pos_mask32(v);
+            for (int i = 0; i < 32; ++i)
+              acc = fmaf((mw & (0x80000000u >> i)) ? __uint_as_float(v[i]) * a.drop.scale : 0.f, w8s[col + i], acc);
+            if (tile_valid) mask_tile[(size_t)(7 * 16 + j * 4 + c) * kTileM] = mw;
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) acc = fmaf(fmaxf(__uint_as_float(v[i]), 0.f), w8s[col + i], acc);
+            if (TRAIN) {
+              relu_pack32(v, held + 16 * c);
+              if (tile_valid) mask_tile[(size_t)(7 * 16 + j * 4 + c) * kTileM] = pos_mask32(v);
+            }
           }
         }
         mbar_wait(&d_done[1], par_d1);
@@ -467,13 +498,23 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
           const uint32_t col = (uint32_t)(256 + j * 128 + c * 32);
           tmem_ld_32x32(tmem + tlane + col, v);
           tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 32; ++i) acc = fmaf(fmaxf(__uint_as_float(v[i]), 0.f), w8s[col + i], acc);
-          if (TRAIN) {
+          if (DROP && ((a.drop.layers >> 7) & 1u)) {
             uint32_t p[16];
-            relu_pack32(v, p);
+            const uint32_t mw = act_pack32(v, 7, col, p);
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              acc = fmaf((mw & (0x80000000u >> i)) ? __uint_as_float(v[i]) * a.drop.scale : 0.f, w8s[col + i], acc);
             store_chunk32(a_base, r, col, p);
-            if (tile_valid) mask_tile[(size_t)(7 * 16 + 8 + j * 4 + c) * kTileM] = pos_mask32(v);
+            if (tile_valid) mask_tile[(size_t)(7 * 16 + 8 + j * 4 + c) * kTileM] = mw;
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) acc = fmaf(fmaxf(__uint_as_float(v[i]), 0.f), w8s[col + i], acc);
+            if (TRAIN) {
+              uint32_t p[16];
+              relu_pack32(v, p);
+              store_chunk32(a_base, r, col, p);
+              if (tile_valid) mask_tile[(size_t)(7 * 16 + 8 + j * 4 + c) * kTileM] = pos_mask32(v);
+            }
           }
         }
         if (TRAIN) {

@@ -12,6 +12,7 @@
 // train_deep_sdf.py:598-606 (gather, cat, clamp, L1/N).
 #pragma once
 #include "layout.cuh"
+#include "philox.cuh"
 #include "ptx.cuh"
 
 namespace dsdf {
@@ -55,6 +56,8 @@ struct FwdArgs {
   // zero dL/ds); 0 = every row is a sample.  Used by the latent-only optimisation whose
   // num_samples (reconstruct.py:22, 8000 on the CLI) is not a multiple of the 128-row tile.
   long long valid_per_seg;
+  // v3 TRAIN + DROP: training-mode dropout after the ReLUs (deep_sdf_decoder.py:103-104), philox.cuh
+  DropoutArgs drop;
   // diagnostics (nullable): per-CTA cycle counters, see dsdf_debug_read
   unsigned long long* dbg;
 };

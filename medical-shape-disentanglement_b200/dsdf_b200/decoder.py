@@ -53,6 +53,8 @@ class Decoder(nn.Module):
             raise NotImplementedError("NetworkSpecs.norm_layers without weight_norm (LayerNorm) is not supported")
         if any(l not in range(8) for l in norm_layers):
             raise NotImplementedError(f"NetworkSpecs.norm_layers={norm_layers}: only hidden layers 0..7")
+        if dropout is not None and any(int(l) not in range(8) for l in dropout):
+            raise NotImplementedError(f"NetworkSpecs.dropout={list(dropout)}: only hidden layers 0..7")
 
         widths = [latent_size + 3] + dims + [1]
         self.num_layers = len(widths)
@@ -179,8 +181,10 @@ class Decoder(nn.Module):
     def forward(self, input):
         if input.dim() != 2 or input.shape[1] != LATENT + 3:
             raise ValueError(f"expected input [N, {LATENT + 3}], got {tuple(input.shape)}")
-        if self.training and self.dropout:
-            raise NotImplementedError("NetworkSpecs.dropout in training mode is not supported yet")
+        if self.training and self.dropout and self.dropout_prob > 0:
+            raise NotImplementedError(
+                "training-mode dropout runs inside the fused step (dsdf_b200.FusedTrainer, Philox stream "
+                "fused into the forward epilogues); Decoder.forward serves eval mode -- call .eval() first")
         if not input.is_cuda:
             raise DsdfError("dsdf_b200.Decoder has no CPU path; pass CUDA tensors")
         need_grad = torch.is_grad_enabled() and (

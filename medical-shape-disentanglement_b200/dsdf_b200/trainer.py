@@ -43,6 +43,7 @@ class StepConfig:
     lr_factor: float = 0.5
     betas: tuple = (0.9, 0.999)
     eps: float = 1e-8
+    dropout_seed: int = 0                   # key of the Philox dropout stream (NetworkSpecs.dropout)
 
     @staticmethod
     def from_specs(specs: dict) -> "StepConfig":
@@ -94,6 +95,7 @@ class FusedTrainer:
         self._ws = None
         self._ws_key = None
         self._pred = None
+        self.dropout_row_base = 0               # global index of this rank's first row (sharded runs)
 
     # ---------------------------------------------------------------- helpers
     def lr(self, which: int, epoch: int) -> float:
@@ -136,6 +138,14 @@ class FusedTrainer:
         st = _stream_ptr(self.device)
         table = self.lat_vecs.weight.data
         with torch.cuda.device(self.device):
+            # decoder.train() + NetworkSpecs.dropout: F.dropout after the listed ReLUs
+            # (deep_sdf_decoder.py:103-104), fused into the forward epilogues; a new mask per step
+            drop_layers = 0
+            if dec.training and dec.dropout and dec.dropout_prob > 0:
+                for l in dec.dropout:
+                    drop_layers |= 1 << int(l)
+            _lib.check(L.dsdf_set_dropout(h, drop_layers, float(dec.dropout_prob), int(c.dropout_seed),
+                                          self.step_count, int(self.dropout_row_base)), h)
             if c.code_bound is not None:
                 _lib.check(L.dsdf_renorm_rows(h, table.data_ptr(), ids.data_ptr(), n_seg,
                                               float(c.code_bound), st), h)

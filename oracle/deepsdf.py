@@ -124,8 +124,12 @@ def effective_weight(p: Dict[str, torch.Tensor], spec: DecoderSpec, l: int) -> t
 
 
 def forward(p: Dict[str, torch.Tensor], spec: DecoderSpec, inp: torch.Tensor,
-            training: bool = False) -> torch.Tensor:
-    """input [N, L+3] -> [N, 1]; deep_sdf_decoder.py:74-109."""
+            training: bool = False, dropout_keep: Dict[int, torch.Tensor] | None = None) -> torch.Tensor:
+    """input [N, L+3] -> [N, 1]; deep_sdf_decoder.py:74-109.
+
+    `dropout_keep[l]` ([N, out] bool/0-1), when given, replaces the RNG draw of F.dropout for layer l
+    by an explicit keep mask (y = x * keep / (1 - p), the same arithmetic F.dropout applies), so a
+    counter-based dropout stream can be checked against this oracle element by element."""
     n_lin = len(spec.dims) + 1
     xyz = inp[:, -3:]
     if inp.shape[1] > 3 and spec.latent_dropout:
@@ -146,7 +150,10 @@ def forward(p: Dict[str, torch.Tensor], spec: DecoderSpec, inp: torch.Tensor,
                 x = F.layer_norm(x, (x.shape[1],), p[f"bn{l}.weight"], p[f"bn{l}.bias"])
             x = torch.relu(x)
             if spec.dropout is not None and l in spec.dropout:
-                x = F.dropout(x, p=spec.dropout_prob, training=training)
+                if dropout_keep is not None and training:
+                    x = x * dropout_keep[l].to(x.dtype) * (1.0 / (1.0 - spec.dropout_prob))
+                else:
+                    x = F.dropout(x, p=spec.dropout_prob, training=training)
     return torch.tanh(x)  # `self.th` is always present (:71,106-107)
 
 

@@ -104,7 +104,7 @@ class OracleTrainer:
         self.opt.param_groups[1]["lr"] = step_lr(c.lr_latent, c.lr_interval, c.lr_factor, epoch)
 
     def forward_loss(self, sdf_data: torch.Tensor, scene_ids: torch.Tensor, epoch: int,
-                     n_total: Optional[int] = None, pred_noise: float = 0.0):
+                     n_total: Optional[int] = None, pred_noise: float = 0.0, dropout_keep=None):
         """Gather + forward + loss for all chunks, calling backward per chunk like the
         reference (:594-731).  sdf_data [B,P,4] (or [M,4] with P=cfg.samples_per_scene)."""
         c = self.cfg
@@ -125,7 +125,8 @@ class OracleTrainer:
         for i in range(c.batch_split):
             bv = self.lat_vecs(idx_c[i])
             inp = torch.cat([bv, xyz_c[i]], dim=1)
-            pred = deepsdf.forward(self.params, self.spec, inp, training=True)
+            assert dropout_keep is None or c.batch_split == 1
+            pred = deepsdf.forward(self.params, self.spec, inp, training=True, dropout_keep=dropout_keep)
             if pred_noise:
                 # test diagnostic only (not reference behaviour): uniform +-pred_noise on the SDF
                 # output, to measure how far the clamped-L1 gradient moves under an output

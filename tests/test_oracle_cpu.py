@@ -147,3 +147,39 @@ def test_oracle_equals_live_reference(wn):
     assert torch.equal(ref(x), deepsdf.forward(p, spec, x))
     ref.train()
     assert torch.equal(ref(x), deepsdf.forward(p, spec, x, training=True))
+
+
+def test_philox4x32_10_known_answer_vectors():
+    """Random123's published KATs for philox4x32-10 pin the oracle of the dropout stream."""
+    from oracle import philox
+    kat = [((0, 0, 0, 0), (0, 0), (0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8)),
+           ((0xffffffff,) * 4, (0xffffffff,) * 2, (0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd)),
+           ((0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344), (0xa4093822, 0x299f31d0),
+            (0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1))]
+    for c, k, want in kat:
+        got = philox.philox4x32_10(np.array(c, dtype=np.uint32), np.array(k, dtype=np.uint32))
+        assert got.tolist() == list(want)
+    keep = philox.dropout_keep(seed=7, offset=3, layer=2, row_lo=1000, n_rows=512, prob=0.2)
+    assert keep.shape == (512, 512) and abs(keep.mean() - 0.8) < 5e-3
+    assert np.array_equal(keep[10:20], philox.dropout_keep(7, 3, 2, 1010, 10, 0.2))   # pure function of the row
+    assert not np.array_equal(keep, philox.dropout_keep(7, 4, 2, 1000, 512, 0.2))
+
+
+def test_oracle_dropout_with_explicit_mask_equals_f_dropout_arithmetic():
+    spec = deepsdf.DecoderSpec(norm_layers=tuple(range(8)), weight_norm=True, dropout=(0, 3, 7), dropout_prob=0.2)
+    p = deepsdf.init_params(spec, seed=0)
+    x = torch.randn(64, 259, generator=torch.Generator().manual_seed(1)) * 0.3
+    ones = {l: torch.ones(64, 253 if l == 3 else 512) for l in (0, 3, 7)}
+    a = deepsdf.forward(p, spec, x, training=True, dropout_keep=ones)
+    spec_scaled = deepsdf.DecoderSpec(norm_layers=tuple(range(8)), weight_norm=True)
+    # all-kept mask = plain network with activations of layers 0,3,7 scaled by 1/(1-p)
+    h = x
+    for l in range(9):
+        if l == 4:
+            h = torch.cat([h, x], 1)
+        h = torch.nn.functional.linear(h, deepsdf.effective_weight(p, spec_scaled, l), p[f"lin{l}.bias"])
+        if l < 8:
+            h = torch.relu(h)
+            if l in (0, 3, 7):
+                h = h * (1.0 / (1.0 - 0.2))
+    np.testing.assert_allclose(a.numpy(), torch.tanh(h).numpy(), atol=1e-6)
