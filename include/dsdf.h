@@ -130,6 +130,20 @@ int dsdf_clip_adam(dsdf_handle h, float* params, float* grads, float* exp_avg, f
                    int64_t n, float max_norm, float lr, float beta1, float beta2, float eps,
                    int64_t step, float* scratch, void* stream);
 
+/* Decoder.forward(input[N, L+3]) under autograd (networks/deep_sdf_decoder.py:74-109 called with
+ * grad enabled, e.g. reconstruct.py:90-94,130): arbitrary per-row latents, differentiable w.r.t. the
+ * parameters AND the input.  forward_train = dsdf_forward_dense that also keeps the activation
+ * stash + ReLU bit-masks in `workspace` (dsdf_dense_workspace_bytes(max_rows), ~2 MiB per 128 rows);
+ * backward consumes that workspace with dOut[N] and writes grads (flat, dsdf_param_layout addressing,
+ * OVERWRITTEN) and, if non-NULL, dInput[N, 259].  Tensor-core chain shared with the fused step;
+ * the latent products that only exist for dense input run as fp32 tile GEMMs (dense_kernels.cuh). */
+size_t dsdf_dense_workspace_bytes(dsdf_handle h, int64_t max_rows);
+int dsdf_dense_forward_train(dsdf_handle h, const float* input, int64_t n, float* out, void* workspace,
+                             size_t workspace_bytes, void* stream);
+int dsdf_dense_backward(dsdf_handle h, const float* params, const float* input, int64_t n,
+                        const float* out, const float* dout, void* workspace, size_t workspace_bytes,
+                        float* grads, float* dinput, void* stream);
+
 /* Training-mode dropout of the hidden layers (networks/deep_sdf_decoder.py:24,103-104:
  * F.dropout(x, p=dropout_prob, training=self.training) after the ReLU of every layer in `dropout`),
  * fused into the forward epilogues of dsdf_train_fwd_bwd: layer_mask bit l <=> l in NetworkSpecs.dropout,

@@ -15,6 +15,7 @@
 #include "../../include/dsdf.h"
 #include "bwd_kernel.cuh"
 #include "bwd2_kernel.cuh"
+#include "dense_kernels.cuh"
 #include "fold_kernels.cuh"
 #include "fwd_kernel.cuh"
 #include "fwd2_kernel.cuh"
@@ -125,6 +126,7 @@ static int set_kernel_attrs(dsdf_handle h) {
   F3ATTR(MODE_TABLE, true, false)
   F3ATTR(MODE_GRID, true, false)
   F3ATTR(MODE_TABLE, true, true)
+  F3ATTR(MODE_DENSE, false, true)
 #undef F3ATTR
   CU(h, cudaFuncSetAttribute(k_forward3<MODE_TABLE, true, true, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, F3<1>::kSmemBytes));
   CU(h, cudaFuncSetAttribute(k_forward3<MODE_TABLE, true, true, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, F3<2>::kSmemBytes));
@@ -806,6 +808,114 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
                                                                 h->inv_norm, grads);
   k_loss<<<1, 1024, 0, st>>>(w.tile_partials, tiles, inv_n, w.seg_norm, (int)n_seg, reg_coef, loss_out);
   if (prof) prof_mark(h, st);
+  CU(h, cudaGetLastError());
+  return DSDF_OK;
+}
+
+// ------------------------------------------------------------------------------- dense autograd
+extern "C" size_t dsdf_dense_workspace_bytes(dsdf_handle h, int64_t max_rows) {
+  if (!h || max_rows <= 0) return 0;
+  return carve(nullptr, max_rows, 64, h->num_sms).total + 1024;
+}
+
+// Decoder.forward(input[N,259]) in a grad-enabled context: same forward chain, additionally keeping
+// the activation stash + ReLU masks in `workspace` for dsdf_dense_backward.
+extern "C" int dsdf_dense_forward_train(dsdf_handle h, const float* input, int64_t n, float* out,
+                                        void* workspace, size_t workspace_bytes, void* stream) {
+  if (!h || !input || !out || !workspace) DSDF_FAIL(h, DSDF_EINVAL, "null argument");
+  if (!h->weights_set) DSDF_FAIL(h, DSDF_EINVAL, "dsdf_set_weights has not been called");
+  if (n <= 0) return DSDF_OK;
+  uint8_t* base = (uint8_t*)(((uintptr_t)workspace + 1023) & ~(uintptr_t)1023);
+  Ws w = carve(base, n, 64, h->num_sms);
+  if ((size_t)(base - (uint8_t*)workspace) + w.total > workspace_bytes)
+    DSDF_FAIL(h, DSDF_ENOMEM, "workspace too small: need %zu bytes, have %zu", w.total + 1024, workspace_bytes);
+  FwdArgs a;
+  memset(&a, 0, sizeof(a));
+  a.wimg = h->fwd_img;
+  a.w8 = h->weff + weff_off(8);
+  a.b8 = h->weff + kWeffElems;
+  a.n_rows = n;
+  a.input = input;
+  a.out = out;
+  a.w2img = h->w2_img;
+  a.dbg = h->dbg;
+  a.xstash = w.xstash;
+  a.relu_mask = w.relu_mask;
+  const long long tiles = (n + kTileM - 1) / kTileM;
+  if (h->fwd_cg == 2 && tiles >= 2) CU(h, (launch_fwd3_cg<MODE_DENSE, false, true, 2>(h, a, (cudaStream_t)stream)));
+  else CU(h, (launch_fwd3_cg<MODE_DENSE, false, true, 1>(h, a, (cudaStream_t)stream)));
+  CU(h, cudaGetLastError());
+  return DSDF_OK;
+}
+
+// autograd backward of Decoder.forward: given dOut[N] returns the parameter gradients (flat,
+// dsdf_param_layout addressing, OVERWRITTEN) and, when dinput != NULL, dInput[N,259].
+extern "C" int dsdf_dense_backward(dsdf_handle h, const float* params, const float* input, int64_t n,
+                                   const float* out, const float* dout, void* workspace,
+                                   size_t workspace_bytes, float* grads, float* dinput, void* stream) {
+  if (!h || !params || !input || !out || !dout || !workspace || !grads) DSDF_FAIL(h, DSDF_EINVAL, "null argument");
+  if (!h->weights_set) DSDF_FAIL(h, DSDF_EINVAL, "dsdf_set_weights has not been called");
+  if (h->bwd_ver == 1 || h->wg_ver == 1) DSDF_FAIL(h, DSDF_EUNSUPPORTED, "dense backward needs the v2 kernels");
+  if (n <= 0) return DSDF_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  uint8_t* base = (uint8_t*)(((uintptr_t)workspace + 1023) & ~(uintptr_t)1023);
+  Ws w = carve(base, n, 64, h->num_sms);
+  if ((size_t)(base - (uint8_t*)workspace) + w.total > workspace_bytes)
+    DSDF_FAIL(h, DSDF_ENOMEM, "workspace too small: need %zu bytes, have %zu", w.total + 1024, workspace_bytes);
+  const long long tiles = (n + kTileM - 1) / kTileM;
+  int rc = build_wg2_schedule(h, tiles, st);
+  if (rc != DSDF_OK) return rc;
+  k_dense_g<<<(unsigned)tiles, kTileM, 0, st>>>(dout, out, n, w.g, w.g_img, w.tile_partials);
+  Bwd2Args b2;
+  memset(&b2, 0, sizeof(b2));
+  b2.n_rows = n;
+  b2.dg2img = h->dg2_img;
+  b2.w8 = h->weff + weff_off(8);
+  b2.g = w.g;
+  b2.relu_mask = w.relu_mask;
+  b2.dystash = w.dystash;
+  b2.xyz = input + kLatent;
+  b2.xyz_stride = kIn0;
+  b2.tile_colsum = w.tile_colsum;
+  b2.cta_partials = w.cta_partials;
+  b2.stash_dy0 = 1;
+  unsigned bwd_grid = 0;
+  rc = launch_backward2(h, b2, tiles, st, &bwd_grid);
+  if (rc != DSDF_OK) return rc;
+  {
+    Wg2Args w2;
+    w2.segs = h->wg2_segs;
+    w2.seg_begin = h->wg2_seg_begin;
+    w2.xstash = w.xstash;
+    w2.dystash = w.dystash;
+    w2.g_img = w.g_img;
+    w2.partials = w.wg_partials;
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3((unsigned)(2 * h->wg2_pairs));
+    cfg.blockDim = dim3(kW2Threads);
+    cfg.dynamicSmemBytes = kW2SmemBytes;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    CU(h, cudaLaunchKernelEx(&cfg, k_wgrad2, w2));
+    k_reduce_wgrad2<<<dim3(kHidden, 8), kHidden, 0, st>>>(w.wg_partials, h->wg2_layout, w.dweff);
+  }
+  // latent columns of dW0 / dW4 (wg_partials is free again: stream order)
+  int n_split = (int)(tiles < 16 ? tiles : 16);
+  k_dense_dw_latent<<<dim3(16, 2, (unsigned)n_split), 256, 0, st>>>(w.dystash, input, n, tiles, w.wg_partials);
+  k_dense_dw_reduce<<<dim3(kHidden, 2), kLatent, 0, st>>>(w.wg_partials, n_split, w.dweff);
+  if (dinput) k_dense_dinput<<<dim3((unsigned)tiles, 5), 256, 0, st>>>(w.dystash, h->weff, n, dinput);
+  const int n_chunks = (int)(tiles < 64 ? tiles : 64);
+  k_colsum_chunks<<<dim3((unsigned)n_chunks, 2), kHidden, 0, st>>>(w.tile_colsum, tiles, w.seg_sum);
+  k_reduce_cta<<<1, kHidden, 0, st>>>(w.cta_partials, (int)bwd_grid, w.seg_sum, n_chunks, w.tile_partials, tiles,
+                                      h->pl, grads, w.dweff, 0);
+  k_param_grads<<<(kScaleElems * 32 + 255) / 256, 256, 0, st>>>(w.dweff, params, h->pl, h->scale, h->inv_norm, grads);
   CU(h, cudaGetLastError());
   return DSDF_OK;
 }

@@ -19,6 +19,7 @@ EXPORTS = [
     "dsdf_create", "dsdf_destroy", "dsdf_last_error", "dsdf_num_sms", "dsdf_set_weights",
     "dsdf_forward_dense", "dsdf_forward_segments", "dsdf_decode_grid", "dsdf_grid_coords",
     "dsdf_train_workspace_bytes", "dsdf_train_fwd_bwd", "dsdf_renorm_rows", "dsdf_clip_adam",
+    "dsdf_dense_workspace_bytes", "dsdf_dense_forward_train", "dsdf_dense_backward",
     "dsdf_set_dropout", "dsdf_dropout_keep", "dsdf_reconstruct_workspace_bytes", "dsdf_reconstruct",
     "dsdf_selftest_gemm", "dsdf_profile_enable", "dsdf_profile_read", "dsdf_debug_read", "dsdf_selftest_mma_rate", "dsdf_debug_hang_buffer",
 ]
@@ -79,6 +80,12 @@ def lib():
     L.dsdf_renorm_rows.restype = C.c_int
     L.dsdf_clip_adam.argtypes = [vp, vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, i64, vp, vp]
     L.dsdf_clip_adam.restype = C.c_int
+    L.dsdf_dense_workspace_bytes.argtypes = [vp, i64]
+    L.dsdf_dense_workspace_bytes.restype = sz
+    L.dsdf_dense_forward_train.argtypes = [vp, vp, i64, vp, vp, sz, vp]
+    L.dsdf_dense_forward_train.restype = C.c_int
+    L.dsdf_dense_backward.argtypes = [vp, vp, vp, i64, vp, vp, vp, sz, vp, vp, vp]
+    L.dsdf_dense_backward.restype = C.c_int
     L.dsdf_set_dropout.argtypes = [vp, C.c_uint32, f32, C.c_uint64, C.c_uint64, i64]
     L.dsdf_set_dropout.restype = C.c_int
     L.dsdf_dropout_keep.argtypes = [vp, i32, i64, i64, vp, vp]

@@ -1,0 +1,67 @@
+"""torch.autograd bridge of `Decoder.forward` (reference networks/deep_sdf_decoder.py:74-109 when
+called with grad enabled): forward = dsdf_dense_forward_train (the fused tcgen05 chain, keeping the
+activation stash + ReLU masks in a workspace), backward = dsdf_dense_backward (dgrad chain, wgrad,
+weight-norm backward, dInput).  Gradients flow to every decoder parameter and to `input`
+(latent and xyz columns), which is what reconstruct.py:90-94,130 and Stage-2 callers rely on.
+
+Python only owns the tensors; all arithmetic is in libdsdf_b200.so.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+from .decoder import _stream_ptr
+
+
+class _DecoderFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, dec, inp, *params):
+        L = _lib.lib()
+        h = dec.sync_weights()
+        x = inp.detach().contiguous().float()
+        n = x.shape[0]
+        dev = x.device
+        out = torch.empty(n, dtype=torch.float32, device=dev)
+        ws = torch.empty(L.dsdf_dense_workspace_bytes(h, max(n, 1)), dtype=torch.uint8, device=dev)
+        if n > 0:
+            with torch.cuda.device(dev):
+                _lib.check(L.dsdf_dense_forward_train(h, x.data_ptr(), n, out.data_ptr(), ws.data_ptr(),
+                                                      ws.numel(), _stream_ptr(dev)), h)
+        ctx.dec, ctx.ws, ctx.x, ctx.out = dec, ws, x, out
+        ctx.param_shapes = [p.shape for p in params]
+        ctx.weights_key = dec._folded_key
+        return out.view(n, 1)
+
+    @staticmethod
+    def backward(ctx, dout):
+        dec, x, out = ctx.dec, ctx.x, ctx.out
+        L = _lib.lib()
+        n = x.shape[0]
+        dev = x.device
+        if dec._folded_key != ctx.weights_key:
+            raise RuntimeError("decoder parameters were modified between forward and backward")
+        h = dec.handle()
+        flat = dec.flat_params()
+        grads = torch.zeros_like(flat)
+        need_dx = ctx.needs_input_grad[1]
+        dx = torch.empty(n, x.shape[1], dtype=torch.float32, device=dev) if need_dx else None
+        if n > 0:
+            d = dout.detach().reshape(-1).contiguous().float()
+            with torch.cuda.device(dev):
+                _lib.check(L.dsdf_dense_backward(h, flat.data_ptr(), x.data_ptr(), n, out.data_ptr(), d.data_ptr(),
+                                                 ctx.ws.data_ptr(), ctx.ws.numel(), grads.data_ptr(),
+                                                 dx.data_ptr() if need_dx else None, _stream_ptr(dev)), h)
+        ctx.ws = None
+        pg, off = [], 0
+        for i, shp in enumerate(ctx.param_shapes):
+            k = 1
+            for s in shp:
+                k *= s
+            pg.append(grads[off:off + k].view(shp) if ctx.needs_input_grad[2 + i] else None)
+            off += k
+        return (None, dx) + tuple(pg)
+
+
+def decoder_apply(dec, inp: torch.Tensor) -> torch.Tensor:
+    return _DecoderFn.apply(dec, inp, *list(dec.parameters()))
