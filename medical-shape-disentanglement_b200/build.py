@@ -39,18 +39,37 @@ def needs_build() -> bool:
     return any(os.path.getmtime(s) > t for s in deps)
 
 
-def build_lib(force: bool = False, verbose: bool = False) -> str:
-    if not force and not needs_build():
-        return OUT
-    cmd = [NVCC] + FLAGS + EXTRA + ["-o", OUT, os.path.join(CSRC, "dsdf_api.cu")]
+# the same source tree builds one library per network family (layout.cuh: geometry + activation are
+# compile-time constants): libdsdf_b200.so = networks/deep_sdf_decoder, libdsdf_b200_siren.so =
+# networks/siren_decoder (-DDSDF_ARCH_SIREN).  Same C ABI (include/dsdf.h); dsdf_arch() tells which.
+OUT_SIREN = OUT[:-3] + "_siren.so"
+
+
+def _compile(out: str, defs, report: str | None, verbose: bool) -> None:
+    cmd = [NVCC] + FLAGS + EXTRA + list(defs) + ["-o", out, os.path.join(CSRC, "dsdf_api.cu")]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if verbose or r.returncode != 0:
         sys.stderr.write(r.stdout + r.stderr)
     if r.returncode != 0:
-        raise RuntimeError("nvcc failed building libdsdf_b200.so")
-    if not VARIANT:
-        with open(os.path.join(HERE, "dsdf_b200", "ptxas_report.txt"), "w") as f:
+        raise RuntimeError("nvcc failed building " + os.path.basename(out))
+    if report and not VARIANT:
+        with open(os.path.join(HERE, "dsdf_b200", report), "w") as f:
             f.write(r.stdout + r.stderr)
+
+
+def _stale(out: str) -> bool:
+    if not os.path.exists(out):
+        return True
+    t = os.path.getmtime(out)
+    deps = sources() + [os.path.join(HERE, "..", "include", "dsdf.h")]
+    return any(os.path.getmtime(s) > t for s in deps)
+
+
+def build_lib(force: bool = False, verbose: bool = False) -> str:
+    if force or _stale(OUT):
+        _compile(OUT, [], "ptxas_report.txt", verbose)
+    if force or _stale(OUT_SIREN):
+        _compile(OUT_SIREN, ["-DDSDF_ARCH_SIREN"], "ptxas_report_siren.txt", verbose)
     return OUT
 
 

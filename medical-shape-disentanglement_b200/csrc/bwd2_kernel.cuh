@@ -79,6 +79,16 @@ __device__ __forceinline__ void mask_pack32(const uint32_t (&v)[32], uint32_t m,
   }
 }
 
+#ifdef DSDF_ARCH_SIREN
+// 32 fp32 dX columns * stashed activation derivative 30 cos(30 x) (16 packed bf16x2) -> 16 packed bf16x2
+__device__ __forceinline__ void deriv_mul_pack32(const uint32_t (&v)[32], const uint32_t* d, uint32_t* p) {
+#pragma unroll
+  for (int i = 0; i < 16; ++i)
+    p[i] = pack_bf16x2(__uint_as_float(v[2 * i]) * __uint_as_float(d[i] << 16),
+                       __uint_as_float(v[2 * i + 1]) * __uint_as_float(d[i] & 0xFFFF0000u));
+}
+#endif
+
 template <int CG, bool DROP = false>
 __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
   using C = B2<CG>;
@@ -312,7 +322,11 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
       const long long row0 = tile * kTileM;
       const long long row = row0 + r;
       const bool valid = tile_valid && row < a.n_rows;
+#ifdef DSDF_ARCH_SIREN
+      const uint8_t* aux_tile = reinterpret_cast<const uint8_t*>(a.relu_mask) + (size_t)tile * kActAuxTileBytes;
+#else
       const uint32_t* mask_tile = a.relu_mask + (size_t)tile * (8 * 16 * kTileM) + r;
+#endif
       // previous tile: reducers done with dY0, stash stores done reading A
       if (!first) {
         mbar_wait(red_done, par_rd);
@@ -338,11 +352,17 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           const uint32_t col = (uint32_t)(hh * 256 + j * 128 + c * 32);
-          const uint32_t m = __ldg(mask_tile + (size_t)(7 * 16 + hh * 8 + j * 4 + c) * kTileM);
           uint32_t v[32], p[16];
 #pragma unroll
           for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(gr * w8s[col + i]);
+#ifdef DSDF_ARCH_SIREN
+          uint32_t d[16];
+          deriv_load(aux_tile, 7, hh * 8 + j * 4 + c, r, d);
+          deriv_mul_pack32(v, d, p);
+#else
+          const uint32_t m = __ldg(mask_tile + (size_t)(7 * 16 + hh * 8 + j * 4 + c) * kTileM);
           mask_pack32(v, m, p);
+#endif
           store_chunk32(a_base, r, col, p);
         }
       }
@@ -356,12 +376,14 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
       for (int l = 7; l >= 1; --l) {
         const bool has_h1 = b2_has_h1(l);
         const int lm = l - 1;   // X_l = ReLU output of lin(l-1): forward mask layer l-1
+#ifndef DSDF_ARCH_SIREN
         uint32_t mk[8];
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           mk[c] = __ldg(mask_tile + (size_t)(lm * 16 + j * 4 + c) * kTileM);
           mk[4 + c] = has_h1 ? __ldg(mask_tile + (size_t)(lm * 16 + 8 + j * 4 + c) * kTileM) : 0u;
         }
+#endif
         // ---- half 0: TMEM -> mask -> bf16, held in registers while the MMAs still read A
         uint32_t held[64];
         mbar_wait(&d_done[0], par_d0);
@@ -372,8 +394,14 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
           uint32_t v[32];
           tmem_ld_32x32(tmem + tlane + (uint32_t)(j * 128 + c * 32), v);
           tmem_ld_wait();
+#ifdef DSDF_ARCH_SIREN
+          uint32_t d[16];
+          deriv_load(aux_tile, lm, j * 4 + c, r, d);
+          deriv_mul_pack32(v, d, held + 16 * c);
+#else
           if (DROP && ((a.drop.layers >> lm) & 1u)) mask_scale_pack32(v, mk[c], a.drop.scale, held + 16 * c);
           else mask_pack32(v, mk[c], held + 16 * c);
+#endif
         }
         if (has_h1) {
           mbar_wait(&d_done[1], par_d1);    // every MMA of layer l has retired: A is free
@@ -395,8 +423,14 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
             uint32_t v[32], p[16];
             tmem_ld_32x32(tmem + tlane + (uint32_t)(256 + j * 128 + c * 32), v);
             tmem_ld_wait();
+#ifdef DSDF_ARCH_SIREN
+            uint32_t d[16];
+            deriv_load(aux_tile, lm, 8 + j * 4 + c, r, d);
+            deriv_mul_pack32(v, d, p);
+#else
             if (DROP && ((a.drop.layers >> lm) & 1u)) mask_scale_pack32(v, mk[4 + c], a.drop.scale, p);
             else mask_pack32(v, mk[4 + c], p);
+#endif
             store_chunk32(a_base, r, (uint32_t)(256 + j * 128 + c * 32), p);
           }
           tc_fence_before();

@@ -75,7 +75,8 @@ __global__ void __launch_bounds__(256) k_dense_dinput(const uint8_t* __restrict_
       for (int q = 0; q < 16; ++q) {          // 64 k x 64 n
         const int id = t + 256 * q, k = id >> 6, n = id & 63;
         const int j = n0 + n;
-        Bs[k][n] = j < kIn0 ? __ldg(w + (size_t)(sub * 64 + k) * ld + coff + j) : 0.f;
+        const bool has = j < kIn0 && (which == 0 || kXyzAtSkip || j < kLatent);   // SIREN: no xyz into lin4
+        Bs[k][n] = has ? __ldg(w + (size_t)(sub * 64 + k) * ld + coff + j) : 0.f;
       }
       __syncthreads();
       dense_mac64(As, Bs, tm, tn, acc);
@@ -159,7 +160,12 @@ __global__ void k_dense_g(const float* __restrict__ dout, const float* __restric
   float gv = 0.f;
   if (row < n_rows) {
     const float o = out[row];
-    gv = dout[row] * (1.f - o * o);
+#ifdef DSDF_ARCH_SIREN
+    gv = dout[row];                       // no output nonlinearity
+    (void)o;
+#else
+    gv = dout[row] * (1.f - o * o);       // through self.th
+#endif
     g[row] = gv;
   }
   const __nv_bfloat16 gh = __float2bfloat16_rn(gv);

@@ -183,6 +183,10 @@ extern "C" int dsdf_create(const dsdf_config* cfg, dsdf_handle* out) {
   if (const char* e = getenv("DSDF_BWD_VER")) h->bwd_ver = atoi(e) == 1 ? 1 : 2;
   if (const char* e = getenv("DSDF_WG_VER")) h->wg_ver = atoi(e) == 1 ? 1 : 2;
   if (h->bwd_ver == 1) h->wg_ver = 1;   // the v1 backward computes dW8 itself
+#ifdef DSDF_ARCH_SIREN
+  // the sine epilogues exist in the current-generation kernels only
+  h->fwd_v1 = false; h->fwd_ver = 3; h->bwd_ver = 2; h->wg_ver = 2;
+#endif
   if (const char* e = getenv("DSDF_DBG")) {
     if (atoi(e) != 0 && cudaMalloc(&h->dbg, (size_t)h->num_sms * kDbgSlots * 8) == cudaSuccess)
       cudaMemset(h->dbg, 0, (size_t)h->num_sms * kDbgSlots * 8);
@@ -226,6 +230,15 @@ extern "C" int dsdf_destroy(dsdf_handle h) {
   for (cudaEvent_t e : h->prof_events) cudaEventDestroy(e);
   delete h;
   return DSDF_OK;
+}
+
+// which network family this build of the library implements (one source tree, two builds)
+extern "C" const char* dsdf_arch(void) {
+#ifdef DSDF_ARCH_SIREN
+  return "siren_decoder";
+#else
+  return "deep_sdf_decoder";
+#endif
 }
 
 extern "C" const char* dsdf_last_error(dsdf_handle h) { return h ? h->err.c_str() : g_err.c_str(); }
@@ -501,7 +514,7 @@ Ws carve(uint8_t* base, long long max_rows, long long max_seg, int num_sms) {
   w.seg_norm = (float*)take((size_t)max_seg * 4);
   w.dweff = (float*)take((size_t)kWeffElems * 4);
   w.scene_e = take((size_t)max_seg * kSceneESteps * kStepBytes);
-  w.relu_mask = (uint32_t*)take(tiles * 8 * 16 * kTileM * 4);
+  w.relu_mask = (uint32_t*)take(tiles * kActAuxTileBytes);
   w.g_img = take(tiles * kSubBytes);
   w.total = o;
   return w;
@@ -925,6 +938,9 @@ extern "C" int dsdf_set_dropout(dsdf_handle h, uint32_t layer_mask, float prob, 
                                 uint64_t offset, int64_t row_base) {
   if (!h) return DSDF_EINVAL;
   if (layer_mask & ~0xFFu) DSDF_FAIL(h, DSDF_EINVAL, "dropout layers must be hidden layers 0..7");
+#ifdef DSDF_ARCH_SIREN
+  if (layer_mask != 0 && prob > 0.f) DSDF_FAIL(h, DSDF_EUNSUPPORTED, "dropout is not built for the SIREN decoder");
+#endif
   if (!(prob >= 0.f) || prob >= 1.f) DSDF_FAIL(h, DSDF_EINVAL, "dropout_prob must be in [0, 1)");
   memset(&h->drop, 0, sizeof(h->drop));
   if (layer_mask == 0 || prob == 0.f) return DSDF_OK;
@@ -993,7 +1009,7 @@ RWs recon_carve(uint8_t* base, long long n_shapes, long long num_samples, int nu
   w.cta_partials = (float*)take((size_t)num_sms * kCtaPartialFloats * 4);
   w.seg_sum = (float*)take((size_t)n_shapes * 2 * kHidden * 4);
   w.scene_e = take((size_t)n_shapes * kSceneESteps * kStepBytes);
-  w.relu_mask = (uint32_t*)take(tiles * 8 * 16 * kTileM * 4);
+  w.relu_mask = (uint32_t*)take(tiles * kActAuxTileBytes);
   w.loss_sink = (float*)take((size_t)n_shapes * 4);
   w.total = o;
   return w;

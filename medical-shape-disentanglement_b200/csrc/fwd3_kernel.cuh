@@ -86,6 +86,38 @@ __device__ __forceinline__ void mask_scale_pack32(const uint32_t (&v)[32], uint3
   }
 }
 
+#ifdef DSDF_ARCH_SIREN
+// networks/modules.py:4-14 Sine: 32 fp32 pre-activations -> sin(30 x) (16 packed bf16x2 in p) and the
+// derivative 30 cos(30 x) (16 packed bf16x2 in d); returns sum_i sin(30 x_i) w[i] when w != nullptr.
+__device__ __forceinline__ float sine_pack32(const uint32_t (&v)[32], uint32_t* p, uint32_t* d, const float* w) {
+  float acc = 0.f;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    float s0, c0, s1, c1;
+    __sincosf(30.f * __uint_as_float(v[2 * i]), &s0, &c0);
+    __sincosf(30.f * __uint_as_float(v[2 * i + 1]), &s1, &c1);
+    p[i] = pack_bf16x2(s0, s1);
+    d[i] = pack_bf16x2(30.f * c0, 30.f * c1);
+    if (w) acc = fmaf(s1, w[2 * i + 1], fmaf(s0, w[2 * i], acc));
+  }
+  return acc;
+}
+__device__ __forceinline__ void deriv_store(uint8_t* aux_tile, int l, int chunk, uint32_t r, const uint32_t* d) {
+  uint8_t* b = aux_tile + (size_t)(l * 16 + chunk) * (4 * kTileM * 16) + (size_t)r * 16;
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+    *reinterpret_cast<uint4*>(b + (size_t)i * kTileM * 16) = make_uint4(d[4 * i], d[4 * i + 1], d[4 * i + 2], d[4 * i + 3]);
+}
+__device__ __forceinline__ void deriv_load(const uint8_t* aux_tile, int l, int chunk, uint32_t r, uint32_t* d) {
+  const uint8_t* b = aux_tile + (size_t)(l * 16 + chunk) * (4 * kTileM * 16) + (size_t)r * 16;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const uint4 q = __ldg(reinterpret_cast<const uint4*>(b + (size_t)i * kTileM * 16));
+    d[4 * i] = q.x; d[4 * i + 1] = q.y; d[4 * i + 2] = q.z; d[4 * i + 3] = q.w;
+  }
+}
+#endif
+
 template <int MODE, bool FOLD, bool TRAIN, int CG, bool DROP = false>
 __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
   static_assert(!DROP || TRAIN, "dropout exists in training mode only");
@@ -370,17 +402,31 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
       const bool tile_valid = tile < n_tiles;
       tile = tile_valid ? tile : n_tiles - 1;
       const long long row0 = tile * kTileM;
-      uint32_t* mask_tile = TRAIN ? a.relu_mask + (size_t)tile * (8 * 16 * kTileM) + r : nullptr;
-      // ReLU (+ dropout) of 32 accumulator columns -> packed bf16; returns the stored mask word
+#ifdef DSDF_ARCH_SIREN
+      uint8_t* aux_tile = TRAIN ? reinterpret_cast<uint8_t*>(a.relu_mask) + (size_t)tile * kActAuxTileBytes : nullptr;
+      // sin(30 x) of 32 accumulator columns -> packed bf16 (+ derivative stash for the backward chain)
       auto act_pack32 = [&](const uint32_t (&v)[32], int l, uint32_t col, uint32_t* p) -> uint32_t {
-        if (DROP && ((a.drop.layers >> l) & 1u)) {
-          const uint32_t m = pos_mask32(v) & dropout_keep32(a.drop, a.drop.row_base + row0 + r, l, (int)(col >> 5));
-          mask_scale_pack32(v, m, a.drop.scale, p);
-          return m;
-        }
-        relu_pack32(v, p);
-        return TRAIN ? pos_mask32(v) : 0u;
+        uint32_t d[16];
+        sine_pack32(v, p, d, nullptr);
+        if (TRAIN && tile_valid) deriv_store(aux_tile, l, (int)(col >> 5), r, d);
+        return 0u;
       };
+#else
+      uint32_t* mask_tile = TRAIN ? a.relu_mask + (size_t)tile * (8 * 16 * kTileM) + r : nullptr;
+      // ReLU (+ dropout) of 32 accumulator columns -> packed bf16; stores and returns the mask word
+      auto act_pack32 = [&](const uint32_t (&v)[32], int l, uint32_t col, uint32_t* p) -> uint32_t {
+        uint32_t m;
+        if (DROP && ((a.drop.layers >> l) & 1u)) {
+          m = pos_mask32(v) & dropout_keep32(a.drop, a.drop.row_base + row0 + r, l, (int)(col >> 5));
+          mask_scale_pack32(v, m, a.drop.scale, p);
+        } else {
+          relu_pack32(v, p);
+          m = TRAIN ? pos_mask32(v) : 0u;
+        }
+        if (TRAIN && tile_valid) mask_tile[(size_t)(l * 16 + (col >> 5)) * kTileM] = m;
+        return m;
+      };
+#endif
       // ---- tile prologue: E_A rows (+ layer-0 latent gather when not folded)
       if (!FOLD) gather_latent<MODE>(a, row0, a_base, t);
       float gt = 0.f;
@@ -410,8 +456,7 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
           uint32_t v[32];
           tmem_ld_32x32(tmem + tlane + (uint32_t)(j * 128 + c * 32), v);
           tmem_ld_wait();
-          const uint32_t mw = act_pack32(v, l, (uint32_t)(j * 128 + c * 32), held + 16 * c);
-          if (TRAIN && tile_valid) mask_tile[(size_t)(l * 16 + j * 4 + c) * kTileM] = mw;
+          act_pack32(v, l, (uint32_t)(j * 128 + c * 32), held + 16 * c);
         }
         if (has_h1) {
           const long long c0 = DSDF_DBG_ON(a) ? clock64() : 0;
@@ -438,9 +483,8 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
             uint32_t v[32], p[16];
             tmem_ld_32x32(tmem + tlane + (uint32_t)(256 + j * 128 + c * 32), v);
             tmem_ld_wait();
-            const uint32_t mw = act_pack32(v, l, (uint32_t)(256 + j * 128 + c * 32), p);
+            act_pack32(v, l, (uint32_t)(256 + j * 128 + c * 32), p);
             store_chunk32(a_base, r, (uint32_t)(256 + j * 128 + c * 32), p);
-            if (TRAIN && tile_valid) mask_tile[(size_t)(l * 16 + 8 + j * 4 + c) * kTileM] = mw;
           }
           tc_fence_before();
           if (f2_in_hi<FOLD>(l + 1)) publish(a_hi_c); else __syncwarp();
@@ -466,20 +510,28 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
           const uint32_t col = (uint32_t)(j * 128 + c * 32);
           tmem_ld_32x32(tmem + tlane + col, v);
           tmem_ld_wait();
+#ifdef DSDF_ARCH_SIREN
+          {
+            uint32_t pp[16], d[16];
+            acc += sine_pack32(v, pp, d, w8s + col);
+            if (TRAIN) {
+#pragma unroll
+              for (int i = 0; i < 16; ++i) held[16 * c + i] = pp[i];
+              if (tile_valid) deriv_store(aux_tile, 7, (int)(col >> 5), r, d);
+            }
+          }
+#else
           if (DROP && ((a.drop.layers >> 7) & 1u)) {
             const uint32_t mw = act_pack32(v, 7, col, held + 16 * c);
 #pragma unroll
             for (int i = 0; i < 32; ++i)
               acc = fmaf((mw & (0x80000000u >> i)) ? __uint_as_float(v[i]) * a.drop.scale : 0.f, w8s[col + i], acc);
-            if (tile_valid) mask_tile[(size_t)(7 * 16 + j * 4 + c) * kTileM] = mw;
           } else {
 #pragma unroll
             for (int i = 0; i < 32; ++i) acc = fmaf(fmaxf(__uint_as_float(v[i]), 0.f), w8s[col + i], acc);
-            if (TRAIN) {
-              relu_pack32(v, held + 16 * c);
-              if (tile_valid) mask_tile[(size_t)(7 * 16 + j * 4 + c) * kTileM] = pos_mask32(v);
-            }
+            if (TRAIN) act_pack32(v, 7, col, held + 16 * c);
           }
+#endif
         }
         mbar_wait(&d_done[1], par_d1);
         par_d1 ^= 1;
@@ -498,6 +550,16 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
           const uint32_t col = (uint32_t)(256 + j * 128 + c * 32);
           tmem_ld_32x32(tmem + tlane + col, v);
           tmem_ld_wait();
+#ifdef DSDF_ARCH_SIREN
+          {
+            uint32_t pp[16], d[16];
+            acc += sine_pack32(v, pp, d, w8s + col);
+            if (TRAIN) {
+              store_chunk32(a_base, r, col, pp);
+              if (tile_valid) deriv_store(aux_tile, 7, (int)(col >> 5), r, d);
+            }
+          }
+#else
           if (DROP && ((a.drop.layers >> 7) & 1u)) {
             uint32_t p[16];
             const uint32_t mw = act_pack32(v, 7, col, p);
@@ -505,17 +567,16 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
             for (int i = 0; i < 32; ++i)
               acc = fmaf((mw & (0x80000000u >> i)) ? __uint_as_float(v[i]) * a.drop.scale : 0.f, w8s[col + i], acc);
             store_chunk32(a_base, r, col, p);
-            if (tile_valid) mask_tile[(size_t)(7 * 16 + 8 + j * 4 + c) * kTileM] = mw;
           } else {
 #pragma unroll
             for (int i = 0; i < 32; ++i) acc = fmaf(fmaxf(__uint_as_float(v[i]), 0.f), w8s[col + i], acc);
             if (TRAIN) {
               uint32_t p[16];
-              relu_pack32(v, p);
+              act_pack32(v, 7, col, p);
               store_chunk32(a_base, r, col, p);
-              if (tile_valid) mask_tile[(size_t)(7 * 16 + 8 + j * 4 + c) * kTileM] = pos_mask32(v);
             }
           }
+#endif
         }
         if (TRAIN) {
           __syncwarp();
@@ -530,7 +591,13 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
         const bool in_range = tile_valid && row < a.n_rows;
         const bool valid = in_range && (a.valid_per_seg == 0 || (row % a.rows_per_seg) < a.valid_per_seg);
         const float s = acc + part[r] + __ldg(a.b8);
-        const float th = tanhf(s);
+#ifdef DSDF_ARCH_SIREN
+        const float th = s;                 // use_tanh=False: no output nonlinearity (siren_decoder.py:233-237)
+        const float dth = 1.f;
+#else
+        const float th = tanhf(s);          // self.th, always (deep_sdf_decoder.py:71,106-107)
+        const float dth = 1.f - th * th;
+#endif
         if (in_range) a.out[row] = th;
         if (TRAIN && a.fused_loss) {
           // train_deep_sdf.py:565-567,604-606: clamp both, L1(sum)/N_total.
@@ -541,7 +608,7 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
           float lossr = valid ? fabsf(diff) : 0.f;
           const float sgn = (diff > 0.f) ? 1.f : ((diff < 0.f) ? -1.f : 0.f);
           const float inside = (th >= -d && th <= d) ? 1.f : 0.f;
-          float g = valid ? sgn * inside * (1.f - th * th) * a.inv_n_total : 0.f;
+          float g = valid ? sgn * inside * dth * a.inv_n_total : 0.f;
           if (in_range) a.gout[row] = g;
           if (tile_valid && a.g_img) {
             const __nv_bfloat16 gh = __float2bfloat16_rn(g);

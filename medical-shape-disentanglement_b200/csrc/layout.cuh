@@ -29,7 +29,15 @@ constexpr int kLatent = 256;
 constexpr int kHidden = 512;
 constexpr int kNumLin = 9;       // lin0..lin8
 constexpr int kSkipLayer = 4;    // latent_in = [4]
+#ifdef DSDF_ARCH_SIREN
+// networks/siren_decoder.py (8x512, latent_in=[4], no xyz_in): lin3 512->256, lin4 [x3(256) | latent(256)],
+// sin(30 x) activations, no final tanh (SirenDecoder.__init__/forward :98-237).  Same padded geometry.
+constexpr int kX3 = 256;         // out features of lin3
+constexpr bool kXyzAtSkip = false;
+#else
 constexpr int kX3 = 253;         // out features of lin3
+constexpr bool kXyzAtSkip = true;
+#endif
 constexpr int kIn0 = 259;
 
 constexpr int kTileM = 128;      // rows per tile (= TMEM lanes)
@@ -135,7 +143,7 @@ __host__ __device__ constexpr int ref_in(int l) { return l == 0 ? kIn0 : kHidden
 __host__ __device__ constexpr int ref_out(int l) { return l == 3 ? kX3 : (l == 8 ? 1 : kHidden); }
 // reference column of xyz component e (0..2) for layers with an xyz input, else -1
 __host__ __device__ constexpr int xyz_col(int l, int e) {
-  return l == 0 ? 256 + e : (l == kSkipLayer ? 509 + e : -1);
+  return l == 0 ? 256 + e : ((l == kSkipLayer && kXyzAtSkip) ? kX3 + 256 + e : -1);
 }
 
 // ---- activation stash in HBM ---------------------------------------------------------------
@@ -144,5 +152,15 @@ __host__ __device__ constexpr int xyz_col(int l, int e) {
 // dY stash: [tile][slot 0..7][8 SUB]  slot l = gradient w.r.t. the pre-activation of lin l
 //           (l = 1..7 used in scene mode; lin3 has 4 SUBs).
 constexpr size_t kStashTileBytes = 8 * (size_t)kTileBytes;  // 1 MiB per 128-row tile
+// ---- activation-derivative side channel forward -> backward, per 128-row tile ----------------------
+// ReLU nets : 1 bit / element: [8 layers][16 chunks of 32 columns][128 rows] words, bit (31-i) = column
+//             32*chunk+i active (and kept by dropout)
+// SIREN     : bf16 30*cos(30 x) / element: [8 layers][16 chunks][4][128 rows][16 B] (a warp's 32 rows
+//             write 512 contiguous bytes per store instruction)
+#ifdef DSDF_ARCH_SIREN
+constexpr size_t kActAuxTileBytes = 8 * 16 * (size_t)kTileM * 64;   // 1 MiB
+#else
+constexpr size_t kActAuxTileBytes = 8 * 16 * (size_t)kTileM * 4;    // 64 KB
+#endif
 
 }  // namespace dsdf

@@ -185,7 +185,7 @@ __global__ void k_reduce_cta(const float* __restrict__ cta_partials, int n_cta,
       for (int k = 0; k < n_cta; ++k)
         s += cta_partials[(size_t)k * kCtaPartialFloats + kPartXyz + (i * kHidden + c) * 3 + e];
       const int l = i == 0 ? 0 : 4;
-      dweff[weff_off(l) + (size_t)c * ref_in(l) + xyz_col(l, e)] = s;
+      if (xyz_col(l, e) >= 0) dweff[weff_off(l) + (size_t)c * ref_in(l) + xyz_col(l, e)] = s;
     }
   }
   for (int i = 0; i < 2; ++i) {  // db0, db4 from the segment colsums

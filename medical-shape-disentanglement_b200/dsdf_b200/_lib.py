@@ -16,7 +16,7 @@ LIB_PATH = os.environ.get("DSDF_LIB") or os.path.join(_HERE, "libdsdf_b200.so")
 DSDF_NUM_LIN = 9
 
 EXPORTS = [
-    "dsdf_create", "dsdf_destroy", "dsdf_last_error", "dsdf_num_sms", "dsdf_set_weights",
+    "dsdf_arch", "dsdf_create", "dsdf_destroy", "dsdf_last_error", "dsdf_num_sms", "dsdf_set_weights",
     "dsdf_forward_dense", "dsdf_forward_segments", "dsdf_decode_grid", "dsdf_grid_coords",
     "dsdf_train_workspace_bytes", "dsdf_train_fwd_bwd", "dsdf_renorm_rows", "dsdf_clip_adam",
     "dsdf_dense_workspace_bytes", "dsdf_dense_forward_train", "dsdf_dense_backward",
@@ -39,19 +39,27 @@ class DsdfError(RuntimeError):
     pass
 
 
-_lib = None
+_libs = {}
+SIREN_LIB_PATH = os.environ.get("DSDF_LIB_SIREN") or LIB_PATH[:-3] + "_siren.so"
 
 
-def lib():
-    """Load (once) and return the C library with argtypes set."""
-    global _lib
-    if _lib is not None:
-        return _lib
-    if not os.path.exists(LIB_PATH):
+def lib(arch: str = "deep_sdf_decoder"):
+    """Load (once) and return the C library of network family `arch` with argtypes set.
+    One source tree, one build per family (build.py); both export the same C ABI."""
+    if arch in _libs:
+        return _libs[arch]
+    if arch not in ("deep_sdf_decoder", "siren_decoder"):
+        raise DsdfError(f"no library for NetworkArch {arch!r}")
+    path = LIB_PATH if arch == "deep_sdf_decoder" else SIREN_LIB_PATH
+    if not os.path.exists(path):
         raise DsdfError(
-            f"{LIB_PATH} not found: build it with `python medical-shape-disentanglement_b200/build.py` "
+            f"{path} not found: build it with `python medical-shape-disentanglement_b200/build.py` "
             "(there is no CPU / PyTorch fallback for this path)")
-    L = C.CDLL(LIB_PATH)
+    L = C.CDLL(path)
+    L.dsdf_arch.argtypes = []
+    L.dsdf_arch.restype = C.c_char_p
+    if L.dsdf_arch().decode() != arch:
+        raise DsdfError(f"{path} implements {L.dsdf_arch().decode()}, expected {arch}")
     vp, i64, i32, f32, sz = C.c_void_p, C.c_int64, C.c_int32, C.c_float, C.c_size_t
     L.dsdf_create.argtypes = [C.POINTER(DsdfConfig), C.POINTER(vp)]
     L.dsdf_create.restype = C.c_int
@@ -106,11 +114,11 @@ def lib():
     L.dsdf_selftest_mma_rate.restype = C.c_int
     L.dsdf_debug_hang_buffer.argtypes = [C.POINTER(C.POINTER(C.c_uint32))]
     L.dsdf_debug_hang_buffer.restype = C.c_int
-    _lib = L
+    _libs[arch] = L
     return L
 
 
-def check(rc: int, handle=None) -> None:
+def check(rc: int, handle=None, L=None) -> None:
     if rc != 0:
-        msg = lib().dsdf_last_error(handle)
+        msg = (L or lib()).dsdf_last_error(handle)
         raise DsdfError(f"libdsdf_b200 error {rc}: {msg.decode() if msg else '?'}")

@@ -17,7 +17,7 @@ from .decoder import _stream_ptr
 class _DecoderFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, dec, inp, *params):
-        L = _lib.lib()
+        L = dec.L
         h = dec.sync_weights()
         x = inp.detach().contiguous().float()
         n = x.shape[0]
@@ -27,7 +27,7 @@ class _DecoderFn(torch.autograd.Function):
         if n > 0:
             with torch.cuda.device(dev):
                 _lib.check(L.dsdf_dense_forward_train(h, x.data_ptr(), n, out.data_ptr(), ws.data_ptr(),
-                                                      ws.numel(), _stream_ptr(dev)), h)
+                                                      ws.numel(), _stream_ptr(dev)), h, L)
         ctx.dec, ctx.ws, ctx.x, ctx.out = dec, ws, x, out
         ctx.param_shapes = [p.shape for p in params]
         ctx.weights_key = dec._folded_key
@@ -36,7 +36,7 @@ class _DecoderFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dout):
         dec, x, out = ctx.dec, ctx.x, ctx.out
-        L = _lib.lib()
+        L = dec.L
         n = x.shape[0]
         dev = x.device
         if dec._folded_key != ctx.weights_key:
@@ -51,7 +51,7 @@ class _DecoderFn(torch.autograd.Function):
             with torch.cuda.device(dev):
                 _lib.check(L.dsdf_dense_backward(h, flat.data_ptr(), x.data_ptr(), n, out.data_ptr(), d.data_ptr(),
                                                  ctx.ws.data_ptr(), ctx.ws.numel(), grads.data_ptr(),
-                                                 dx.data_ptr() if need_dx else None, _stream_ptr(dev)), h)
+                                                 dx.data_ptr() if need_dx else None, _stream_ptr(dev)), h, L)
         ctx.ws = None
         pg, off = [], 0
         for i, shp in enumerate(ctx.param_shapes):

@@ -29,56 +29,18 @@ def _stream_ptr(device) -> int:
     return torch.cuda.current_stream(device).cuda_stream
 
 
-class Decoder(nn.Module):
-    def __init__(self, latent_size, dims, dropout=None, dropout_prob=0.0, norm_layers=(),
-                 latent_in=(), weight_norm=False, xyz_in_all=None, use_tanh=False,
-                 latent_dropout=False):
-        super().__init__()
-        dims = list(dims)
-        # ---- supported matrix; anything else raises, naming the key
-        if latent_size != LATENT:
-            raise NotImplementedError(f"CodeLength={latent_size}: fused path supports 256")
-        if dims != [HIDDEN] * 8:
-            raise NotImplementedError(f"NetworkSpecs.dims={dims}: fused path supports [512]*8")
-        if list(latent_in) != [4]:
-            raise NotImplementedError(f"NetworkSpecs.latent_in={list(latent_in)}: fused path supports [4]")
-        if xyz_in_all:
-            raise NotImplementedError("NetworkSpecs.xyz_in_all=true is not supported by the fused path")
-        if use_tanh:
-            raise NotImplementedError("NetworkSpecs.use_tanh=true (double tanh) is not supported")
-        if latent_dropout:
-            raise NotImplementedError("NetworkSpecs.latent_dropout=true is not supported")
-        norm_layers = list(norm_layers or [])
-        if norm_layers and not weight_norm:
-            raise NotImplementedError("NetworkSpecs.norm_layers without weight_norm (LayerNorm) is not supported")
-        if any(l not in range(8) for l in norm_layers):
-            raise NotImplementedError(f"NetworkSpecs.norm_layers={norm_layers}: only hidden layers 0..7")
-        if dropout is not None and any(int(l) not in range(8) for l in dropout):
-            raise NotImplementedError(f"NetworkSpecs.dropout={list(dropout)}: only hidden layers 0..7")
+class _FusedDecoderBase(nn.Module):
+    """Runtime machinery shared by the decoder families (deep_sdf_decoder, siren_decoder): flat fp32
+    parameter buffer, C handle, weight folding, forward / decode entry points.  A subclass builds the
+    nn.Linear layers with the reference's names in its constructor, sets `_wn_mask`, `dropout`,
+    `dropout_prob`, calls `_init_runtime()`, and names its library with `_arch`."""
+    _arch = "deep_sdf_decoder"
 
-        widths = [latent_size + 3] + dims + [1]
-        self.num_layers = len(widths)
-        self.norm_layers = norm_layers
-        self.latent_in = list(latent_in)
-        self.latent_dropout = latent_dropout
-        self.xyz_in_all = xyz_in_all
-        self.weight_norm = weight_norm
-        self.use_tanh = use_tanh
-        self.dropout_prob = dropout_prob
-        self.dropout = list(dropout) if dropout is not None else None
-        self._wn_mask = 0
-        # identical construction order / RNG stream to the reference ctor (:39-55)
-        for layer in range(self.num_layers - 1):
-            out_dim = widths[layer + 1] - widths[0] if (layer + 1) in self.latent_in else widths[layer + 1]
-            lin = nn.Linear(widths[layer], out_dim)
-            if weight_norm and layer in norm_layers:
-                with warnings.catch_warnings():
-                    warnings.simplefilter("ignore")
-                    lin = nn.utils.weight_norm(lin)
-                self._wn_mask |= 1 << layer
-            setattr(self, "lin" + str(layer), lin)
-        self.relu = nn.ReLU()
-        self.th = nn.Tanh()
+    @property
+    def L(self):
+        return _lib.lib(self._arch)
+
+    def _init_runtime(self):
         # runtime state (not part of state_dict)
         self._handle = None
         self._handle_device = None
@@ -86,9 +48,12 @@ class Decoder(nn.Module):
         self._layout: Optional[DsdfParamLayout] = None
         self._folded_key = None
 
+    def _lin(self, l: int):
+        return getattr(self, "lin" + str(l))
+
     # ------------------------------------------------------------------ parameter plumbing
     def _lin_params(self, l: int):
-        lin = getattr(self, "lin" + str(l))
+        lin = self._lin(l)
         if (self._wn_mask >> l) & 1:
             return lin.weight_v, lin.weight_g, lin.bias
         return lin.weight, None, lin.bias
@@ -144,7 +109,7 @@ class Decoder(nn.Module):
         self._release()
         cfg = DsdfConfig(LATENT, HIDDEN, 8, 4, self._wn_mask, dev.index or 0)
         h = C.c_void_p()
-        _lib.check(_lib.lib().dsdf_create(C.byref(cfg), C.byref(h)))
+        _lib.check(self.L.dsdf_create(C.byref(cfg), C.byref(h)))
         self._handle, self._handle_device = h, dev
         self._folded_key = None
         return h
@@ -154,7 +119,7 @@ class Decoder(nn.Module):
         if h is not None:
             self.__dict__["_handle"] = None      # plain dict write: safe during interpreter teardown
             try:
-                _lib.lib().dsdf_destroy(h)
+                self.L.dsdf_destroy(h)
             except Exception:
                 pass
 
@@ -172,8 +137,8 @@ class Decoder(nn.Module):
         if force or key != self._folded_key:
             dev = flat.device
             with torch.cuda.device(dev):
-                _lib.check(_lib.lib().dsdf_set_weights(h, flat.data_ptr(), C.byref(self._layout),
-                                                       _stream_ptr(dev)), h)
+                _lib.check(self.L.dsdf_set_weights(h, flat.data_ptr(), C.byref(self._layout),
+                                                       _stream_ptr(dev)), h, self.L)
             self._folded_key = key
         return h
 
@@ -203,8 +168,8 @@ class Decoder(nn.Module):
         if n == 0:
             return out.view(0, 1)
         with torch.cuda.device(x.device):
-            _lib.check(_lib.lib().dsdf_forward_dense(h, x.data_ptr(), n, out.data_ptr(),
-                                                     _stream_ptr(x.device)), h)
+            _lib.check(self.L.dsdf_forward_dense(h, x.data_ptr(), n, out.data_ptr(),
+                                                     _stream_ptr(x.device)), h, self.L)
         return out.view(n, 1)
 
     @torch.no_grad()
@@ -220,9 +185,9 @@ class Decoder(nn.Module):
         if n == 0:
             return out.view(0, 1)
         with torch.cuda.device(q.device):
-            _lib.check(_lib.lib().dsdf_forward_segments(h, lat.data_ptr(), None, 1, n, q.data_ptr(),
+            _lib.check(self.L.dsdf_forward_segments(h, lat.data_ptr(), None, 1, n, q.data_ptr(),
                                                         q.shape[1], n, out.data_ptr(),
-                                                        _stream_ptr(q.device)), h)
+                                                        _stream_ptr(q.device)), h, self.L)
         return out.view(n, 1)
 
     @torch.no_grad()
@@ -236,6 +201,62 @@ class Decoder(nn.Module):
         if out is None:
             out = torch.empty(hi - lo, dtype=torch.float32, device=dev)
         with torch.cuda.device(dev):
-            _lib.check(_lib.lib().dsdf_decode_grid(h, lat.data_ptr(), N, lo, hi, out.data_ptr(),
-                                                   _stream_ptr(dev)), h)
+            _lib.check(self.L.dsdf_decode_grid(h, lat.data_ptr(), N, lo, hi, out.data_ptr(),
+                                                   _stream_ptr(dev)), h, self.L)
         return out
+
+
+class Decoder(_FusedDecoderBase):
+    """networks/deep_sdf_decoder.Decoder (reference networks/deep_sdf_decoder.py:10-109)."""
+    _arch = "deep_sdf_decoder"
+
+    def __init__(self, latent_size, dims, dropout=None, dropout_prob=0.0, norm_layers=(),
+                 latent_in=(), weight_norm=False, xyz_in_all=None, use_tanh=False,
+                 latent_dropout=False):
+        super().__init__()
+        dims = list(dims)
+        # ---- supported matrix (SURVEY.md 8(b)); anything else raises, naming the key
+        if latent_size != LATENT:
+            raise NotImplementedError(f"CodeLength={latent_size}: fused path supports 256")
+        if dims != [HIDDEN] * 8:
+            raise NotImplementedError(f"NetworkSpecs.dims={dims}: fused path supports [512]*8")
+        if list(latent_in) != [4]:
+            raise NotImplementedError(f"NetworkSpecs.latent_in={list(latent_in)}: fused path supports [4]")
+        if xyz_in_all:
+            raise NotImplementedError("NetworkSpecs.xyz_in_all=true is not supported by the fused path")
+        if use_tanh:
+            raise NotImplementedError("NetworkSpecs.use_tanh=true (double tanh) is not supported")
+        if latent_dropout:
+            raise NotImplementedError("NetworkSpecs.latent_dropout=true is not supported")
+        norm_layers = list(norm_layers or [])
+        if norm_layers and not weight_norm:
+            raise NotImplementedError("NetworkSpecs.norm_layers without weight_norm (LayerNorm) is not supported")
+        if any(l not in range(8) for l in norm_layers):
+            raise NotImplementedError(f"NetworkSpecs.norm_layers={norm_layers}: only hidden layers 0..7")
+        if dropout is not None and any(int(l) not in range(8) for l in dropout):
+            raise NotImplementedError(f"NetworkSpecs.dropout={list(dropout)}: only hidden layers 0..7")
+
+        widths = [latent_size + 3] + dims + [1]
+        self.num_layers = len(widths)
+        self.norm_layers = norm_layers
+        self.latent_in = list(latent_in)
+        self.latent_dropout = latent_dropout
+        self.xyz_in_all = xyz_in_all
+        self.weight_norm = weight_norm
+        self.use_tanh = use_tanh
+        self.dropout_prob = dropout_prob
+        self.dropout = list(dropout) if dropout is not None else None
+        self._wn_mask = 0
+        # identical construction order / RNG stream to the reference ctor (:39-55)
+        for layer in range(self.num_layers - 1):
+            out_dim = widths[layer + 1] - widths[0] if (layer + 1) in self.latent_in else widths[layer + 1]
+            lin = nn.Linear(widths[layer], out_dim)
+            if weight_norm and layer in norm_layers:
+                with warnings.catch_warnings():
+                    warnings.simplefilter("ignore")
+                    lin = nn.utils.weight_norm(lin)
+                self._wn_mask |= 1 << layer
+            setattr(self, "lin" + str(layer), lin)
+        self.relu = nn.ReLU()
+        self.th = nn.Tanh()
+        self._init_runtime()

@@ -80,7 +80,7 @@ def reconstruct_batch(decoder: Decoder, num_iterations: int, shapes: Sequence[Tu
     dev = next(decoder.parameters()).device
     if dev.type != "cuda":
         raise _lib.DsdfError("reconstruct needs the decoder on a CUDA device (no CPU path)")
-    L = _lib.lib()
+    L = decoder.L
     n_shapes = len(shapes)
     if latents.shape != (n_shapes, LATENT):
         raise ValueError(f"latents must be [{n_shapes}, {LATENT}], got {tuple(latents.shape)}")
@@ -123,7 +123,7 @@ def reconstruct_batch(decoder: Decoder, num_iterations: int, shapes: Sequence[Tu
         _lib.check(L.dsdf_reconstruct(h, flat.data_ptr(), C.byref(cfg), n_shapes, samples.data_ptr(),
                                       shape_base.data_ptr(), win.data_ptr(), 1, num_iterations,
                                       lat.data_ptr(), m.data_ptr(), v.data_ptr(), ws.data_ptr(), ws.numel(),
-                                      hist.data_ptr(), _stream_ptr(dev)), h)
+                                      hist.data_ptr(), _stream_ptr(dev)), h, L)
     # keep every buffer the enqueued kernels use alive until they have run
     torch.cuda.current_stream(dev).synchronize()
     if return_state:

@@ -106,7 +106,7 @@ class FusedTrainer:
     def _workspace(self, h, rows: int, segs: int):
         key = (rows, segs)
         if self._ws_key != key:
-            nbytes = _lib.lib().dsdf_train_workspace_bytes(h, rows, segs)
+            nbytes = self.decoder.L.dsdf_train_workspace_bytes(h, rows, segs)
             self._ws = None
             self._ws = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
             self._pred = torch.empty(rows, dtype=torch.float32, device=self.device)
@@ -117,9 +117,9 @@ class FusedTrainer:
     def forward_backward(self, sdf_data: torch.Tensor, indices: torch.Tensor, epoch: int,
                          n_total: Optional[int] = None):
         """gather + forward + loss + backward; fills self.grads / self.lat_grad (no optimiser)."""
-        L = _lib.lib()
         c = self.cfg
         dec = self.decoder
+        L = dec.L
         h = dec.sync_weights()
         flat = dec.flat_params()
         if self.grads.data_ptr() == 0 or self.grads.numel() != flat.numel():
@@ -145,22 +145,22 @@ class FusedTrainer:
                 for l in dec.dropout:
                     drop_layers |= 1 << int(l)
             _lib.check(L.dsdf_set_dropout(h, drop_layers, float(dec.dropout_prob), int(c.dropout_seed),
-                                          self.step_count, int(self.dropout_row_base)), h)
+                                          self.step_count, int(self.dropout_row_base)), h, L)
             if c.code_bound is not None:
                 _lib.check(L.dsdf_renorm_rows(h, table.data_ptr(), ids.data_ptr(), n_seg,
-                                              float(c.code_bound), st), h)
+                                              float(c.code_bound), st), h, L)
             ramp = c.code_reg_lambda * min(1, epoch / 100) if c.code_reg else 0.0
             _lib.check(L.dsdf_train_fwd_bwd(
                 h, flat.data_ptr(), table.data_ptr(), self.num_scenes, ids.data_ptr(), n_seg, p,
                 sdf.data_ptr(), int(n_total), float(c.clamp_dist), float(ramp), ws.data_ptr(),
                 ws.numel(), self.grads.data_ptr(), self.lat_grad.data_ptr(),
-                self._pred.data_ptr(), self.loss_buf.data_ptr(), st), h)
+                self._pred.data_ptr(), self.loss_buf.data_ptr(), st), h, L)
         return self._pred
 
     def step(self, sdf_data: torch.Tensor, indices: torch.Tensor, epoch: int,
              n_total: Optional[int] = None, lr_decoder: Optional[float] = None,
              lr_latent: Optional[float] = None) -> Dict[str, torch.Tensor]:
-        L = _lib.lib()
+        L = self.decoder.L
         c = self.cfg
         self.forward_backward(sdf_data, indices, epoch, n_total)
         if self.pg is not None and torch.distributed.get_world_size(self.pg) > 1:
@@ -178,12 +178,12 @@ class FusedTrainer:
                 h, flat.data_ptr(), self.grads.data_ptr(), self.exp_avg.data_ptr(),
                 self.exp_avg_sq.data_ptr(), flat.numel(),
                 float(c.grad_clip) if c.grad_clip is not None else 0.0, float(lr0), b1, b2, c.eps,
-                self.step_count, self.scratch.data_ptr(), st), h)
+                self.step_count, self.scratch.data_ptr(), st), h, L)
             table = self.lat_vecs.weight.data
             _lib.check(L.dsdf_clip_adam(
                 h, table.data_ptr(), self.lat_grad.data_ptr(), self.lat_exp_avg.data_ptr(),
                 self.lat_exp_avg_sq.data_ptr(), table.numel(), 0.0, float(lr1), b1, b2, c.eps,
-                self.step_count, self.scratch_lat.data_ptr(), st), h)
+                self.step_count, self.scratch_lat.data_ptr(), st), h, L)
         self.decoder.sync_weights(force=True)
         # device scalars, no host sync: [0] L1 term, [1] regulariser term (this rank's share)
         return {"sdf_loss": self.loss_buf[0], "reg_loss": self.loss_buf[1],

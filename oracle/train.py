@@ -24,7 +24,7 @@ from typing import Dict, List, Optional
 
 import torch
 
-from . import deepsdf
+from . import deepsdf, siren
 
 
 @dataclass
@@ -79,10 +79,12 @@ class OracleTrainer:
     """The reference's training state + step, single process, any device."""
 
     def __init__(self, spec: deepsdf.DecoderSpec, cfg: TrainConfig, num_scenes: int,
-                 seed: int = 0, device: str = "cpu", params=None, latents=None):
-        self.spec, self.cfg, self.device = spec, cfg, torch.device(device)
+                 seed: int = 0, device: str = "cpu", params=None, latents=None,
+                 arch: str = "deep_sdf_decoder"):
+        # arch selects the decoder the step loop wraps (specs["NetworkArch"], train_deep_sdf.py:225,348)
+        self.spec, self.cfg, self.device, self.arch = spec, cfg, torch.device(device), arch
         if params is None:
-            params = deepsdf.init_params(spec, seed)
+            params = deepsdf.init_params(spec, seed) if arch == "deep_sdf_decoder" else siren.init_params(seed)
         self.params = {k: torch.nn.Parameter(v.clone().to(self.device)) for k, v in params.items()}
         # train_deep_sdf.py:429-435
         self.lat_vecs = torch.nn.Embedding(num_scenes, spec.latent_size, max_norm=cfg.code_bound)
@@ -126,7 +128,10 @@ class OracleTrainer:
             bv = self.lat_vecs(idx_c[i])
             inp = torch.cat([bv, xyz_c[i]], dim=1)
             assert dropout_keep is None or c.batch_split == 1
-            pred = deepsdf.forward(self.params, self.spec, inp, training=True, dropout_keep=dropout_keep)
+            if self.arch == "siren_decoder":
+                pred = siren.forward(self.params, inp)
+            else:
+                pred = deepsdf.forward(self.params, self.spec, inp, training=True, dropout_keep=dropout_keep)
             if pred_noise:
                 # test diagnostic only (not reference behaviour): uniform +-pred_noise on the SDF
                 # output, to measure how far the clamped-L1 gradient moves under an output

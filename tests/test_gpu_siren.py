@@ -1,0 +1,114 @@
+"""GPU parity of the SIREN decoder variant (BASELINE config 5): dsdf_b200.siren.Decoder
+through the C ABI of libdsdf_b200_siren.so against the oracle (bit-equal to the live reference on CPU) and
+the golden fixture generated from the reference.  Tolerances: outputs <= 2e-3, gradient cosine >= 0.999."""
+import numpy as np
+import pytest
+import torch
+
+import dsdf_b200
+import dsdf_b200.siren as S
+from common import check_checksums, cos, golden
+from dsdf_b200 import synth
+from oracle import deepsdf, siren
+from oracle import train as otrain
+
+pytestmark = pytest.mark.gpu
+
+
+def make(seed=0):
+    torch.manual_seed(seed)
+    dec = S.Decoder(256, **siren.network_specs())
+    params = {k: v.detach().clone() for k, v in dec.state_dict().items()}
+    return dec.cuda(), params
+
+
+def test_siren_library_is_the_siren_build():
+    dec, _ = make()
+    assert dec.L.dsdf_arch().decode() == "siren_decoder"
+    assert "libdsdf_b200_siren.so" in open("/proc/self/maps").read()
+
+
+def test_forward_matches_reference_golden_and_oracle():
+    dec, params = make()
+    g = golden("decoder_siren.npz")
+    check_checksums(params, g)
+    x = torch.from_numpy(g["input"]).cuda()
+    with torch.no_grad():
+        y = dec(x)
+    assert np.abs(y.cpu().numpy() - g["output"]).max() <= 2e-3
+    # livelier inputs + the fold-mode entries (one latent for all rows; grid decode)
+    gen = torch.Generator().manual_seed(3)
+    lat = (torch.randn(1, 256, generator=gen) * 0.5).cuda()
+    q = (torch.rand(1000, 3, generator=gen) * 2 - 1).cuda()
+    p = {k: v.cuda() for k, v in params.items()}
+    ref = siren.forward(p, torch.cat([lat.expand(1000, -1), q], 1))
+    with torch.no_grad():
+        a = dec(torch.cat([lat.expand(1000, -1), q], 1))
+        b = dec.decode_sdf(lat, q)
+    assert (a - ref).abs().max().item() <= 2e-3
+    assert (b - ref).abs().max().item() <= 2e-3
+    sdf = dsdf_b200.create_mesh_sdf(dec, lat, 16, to_cpu=False)
+    from oracle import mesh_grid
+    coords = torch.from_numpy(mesh_grid.grid_coords_closed_form(16)).cuda()
+    ref_grid = siren.forward(p, torch.cat([lat.expand(16 ** 3, -1), coords], 1)).view(16, 16, 16)
+    assert (sdf - ref_grid).abs().max().item() <= 2e-3
+
+
+@pytest.mark.parametrize("n", [1000, 256])
+def test_autograd_matches_oracle(n):
+    dec, params = make()
+    gen = torch.Generator().manual_seed(4)
+    xyz = (torch.rand(n, 3, generator=gen) * 2 - 1).cuda()
+    gt = (xyz.norm(dim=1, keepdim=True) - 0.5).clamp(-0.1, 0.1)
+    lat = (torch.randn(1, 256, generator=gen) * 0.3).cuda()
+    x = torch.cat([lat.expand(n, -1), xyz], 1)
+    # SIREN's init gives outputs ~1e-2: use a wider clamp so the loss gradient is not zeroed out
+    loss = lambda o: torch.nn.functional.l1_loss(torch.clamp(o, -0.5, 0.5), gt, reduction="sum") / n
+    p_ref = {k: v.clone().cuda().requires_grad_(True) for k, v in params.items()}
+    x_ref = x.clone().requires_grad_(True)
+    out_ref = siren.forward(p_ref, x_ref)
+    loss(out_ref).backward()
+    x1 = x.clone().requires_grad_(True)
+    out = dec(x1)
+    loss(out).backward()
+    assert (out - out_ref).abs().max().item() <= 2e-3
+    flat_ref = torch.cat([p_ref[k].grad.flatten() for k, _ in dec.named_parameters()])
+    flat = torch.cat([p.grad.flatten() for _, p in dec.named_parameters()])
+    cs = {"params": cos(flat, flat_ref), "lat_sum": cos(x1.grad[:, :256].sum(0), x_ref.grad[:, :256].sum(0)),
+          "xyz_rows": cos(x1.grad[:, 256:], x_ref.grad[:, 256:]),
+          "worst_param": min(cos(p.grad, p_ref[k].grad) for k, p in dec.named_parameters())}
+    print("siren autograd:", cs)
+    assert cs["params"] >= 0.999 and cs["lat_sum"] >= 0.999 and cs["xyz_rows"] >= 0.995, cs
+
+
+def test_fused_train_step_matches_oracle():
+    dec, params = make()
+    S_, B, P = 6, 3, 256
+    # SIREN weights are ~4e-3 in magnitude (sine_init): Adam's first steps move every weight by +-lr, so the
+    # reference's DeepSDF learning rate (5e-4) would change them by 14 % per step in the direction sign(g),
+    # which amplifies any rounding difference; a SIREN-scale rate keeps the comparison meaningful
+    cfg = otrain.TrainConfig(samples_per_scene=P, scenes_per_batch=B, code_bound=1.0, grad_clip=1.0, clamp_dist=0.5,
+                             lr_decoder=1e-5, lr_latent=1e-4)
+    spec = deepsdf.DecoderSpec()
+    orc = otrain.OracleTrainer(spec, cfg, S_, seed=0, device="cuda", params=params, arch="siren_decoder")
+    tr = dsdf_b200.FusedTrainer(dec, S_, dsdf_b200.StepConfig(code_bound=1.0, grad_clip=1.0, clamp_dist=0.5, lr_decoder=1e-5, lr_latent=1e-4),
+                                latents=orc.lat_vecs.weight.data.clone())
+    data = synth.scene_samples(S_, P, seed=2).cuda()
+    ids = torch.tensor([5, 1, 2])
+    orc.opt.zero_grad()
+    sl, rl, pred_ref = orc.forward_loss(data[ids], ids, 50)
+    pred = tr.forward_backward(data[ids], ids.cuda(), 50)
+    torch.cuda.synchronize()
+    assert (pred.clamp(-0.5, 0.5)[:, None] - pred_ref).abs().max().item() <= 2e-3
+    ref_flat = torch.cat([orc.params[k].grad.flatten() for k, _ in dec.named_parameters()])
+    assert cos(tr.grads, ref_flat) >= 0.999
+    assert cos(tr.lat_grad, orc.latent_grad()) >= 0.999
+    assert float(tr.loss_buf[0]) == pytest.approx(sl, rel=1e-2)
+    # bookkeeping: exactly the batch rows receive latent gradient
+    nz = (tr.lat_grad.abs().sum(1) != 0).cpu()
+    assert nz.tolist() == [False, True, True, False, False, True]
+    # a few full steps stay locked to the oracle's losses
+    for it in range(5):
+        st_ref = orc.step(data[ids], ids, 50)
+        st = tr.step(data[ids], ids.cuda(), 50)
+        assert float(st["sdf_loss"]) == pytest.approx(st_ref["sdf_loss"], rel=1e-2)

@@ -183,3 +183,45 @@ def test_oracle_dropout_with_explicit_mask_equals_f_dropout_arithmetic():
             if l in (0, 3, 7):
                 h = h * (1.0 / (1.0 - 0.2))
     np.testing.assert_allclose(a.numpy(), torch.tanh(h).numpy(), atol=1e-6)
+
+
+def test_siren_oracle_matches_golden_from_the_live_reference():
+    from oracle import siren
+    g = golden("decoder_siren.npz")
+    p = siren.init_params(seed=0)
+    check_checksums(p, g)
+    assert sum(v.numel() for v in p.values()) == 1_840_897 and siren.macs_per_row() == 1_837_056
+    x = torch.from_numpy(g["input"]).requires_grad_(True)
+    pr = {k: v.clone().requires_grad_(True) for k, v in p.items()}
+    y = siren.forward(pr, x)
+    (y * torch.from_numpy(g["w"])).sum().backward()
+    np.testing.assert_allclose(y.detach().numpy(), g["output"], atol=1e-6)
+    np.testing.assert_allclose(x.grad.numpy(), g["dinput"], atol=1e-6, rtol=1e-4)
+    for k in ("decoder.lin8.weight", "decoder.lin4.bias", "decoder.lin0.bias"):
+        np.testing.assert_allclose(pr[k].grad.numpy(), g["grad/" + k], atol=1e-6, rtol=1e-4)
+    for k, v in pr.items():
+        assert float(v.grad.norm()) == pytest.approx(float(g["gradnorm/" + k]), rel=1e-4)
+
+
+@pytest.mark.skipif(not have_ref, reason="reference tree not mounted")
+def test_siren_oracle_and_host_decoder_equal_live_reference():
+    sys.path.insert(0, REF_DIR)
+    from networks.siren_decoder import Decoder as RefSiren
+    from oracle import siren
+    import dsdf_b200.siren as S
+    torch.manual_seed(0)
+    ref = RefSiren(256, **siren.network_specs())
+    p = siren.init_params(seed=0)
+    sd = ref.state_dict()
+    assert list(sd.keys()) == list(p.keys()) and all(torch.equal(sd[k], p[k]) for k in sd)
+    x = torch.randn(200, 259, generator=torch.Generator().manual_seed(2)) * 0.3
+    assert torch.equal(ref(x), siren.forward(p, x))
+    torch.manual_seed(0)
+    mine = S.Decoder(256, **siren.network_specs())
+    sd2 = mine.state_dict()
+    assert list(sd2.keys()) == list(sd.keys()) and all(torch.equal(sd2[k], sd[k]) for k in sd)
+    mine.load_state_dict(sd)            # reference checkpoints load unchanged
+    for kw in (dict(nonlinearity="relu"), dict(xyz_in=[2]), dict(encoding_features=8), dict(use_tanh=True)):
+        spec = dict(siren.network_specs()); spec.update(kw)
+        with pytest.raises(NotImplementedError):
+            S.Decoder(256, **spec)
