@@ -88,10 +88,10 @@ def test_fused_train_step_matches_oracle():
     # reference's DeepSDF learning rate (5e-4) would change them by 14 % per step in the direction sign(g),
     # which amplifies any rounding difference; a SIREN-scale rate keeps the comparison meaningful
     cfg = otrain.TrainConfig(samples_per_scene=P, scenes_per_batch=B, code_bound=1.0, grad_clip=1.0, clamp_dist=0.5,
-                             lr_decoder=1e-5, lr_latent=1e-4)
+                             lr_decoder=2e-6, lr_latent=1e-4)
     spec = deepsdf.DecoderSpec()
     orc = otrain.OracleTrainer(spec, cfg, S_, seed=0, device="cuda", params=params, arch="siren_decoder")
-    tr = dsdf_b200.FusedTrainer(dec, S_, dsdf_b200.StepConfig(code_bound=1.0, grad_clip=1.0, clamp_dist=0.5, lr_decoder=1e-5, lr_latent=1e-4),
+    tr = dsdf_b200.FusedTrainer(dec, S_, dsdf_b200.StepConfig(code_bound=1.0, grad_clip=1.0, clamp_dist=0.5, lr_decoder=2e-6, lr_latent=1e-4),
                                 latents=orc.lat_vecs.weight.data.clone())
     data = synth.scene_samples(S_, P, seed=2).cuda()
     ids = torch.tensor([5, 1, 2])
