@@ -61,7 +61,7 @@ class ClockSampler(threading.Thread):
              "clocks_event_reasons.sw_power_cap")
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             for line in self.proc.stdout:
                 if self._stop.is_set():
@@ -119,6 +119,83 @@ def cpu_reference_run(steps: int, warmup: int, scenes_per_step: int = 4):
             "sample": f"{len(times)} steps of {scenes_per_step} scenes x {P} rows ({rows} rows/step) of the same workload, fp32 torch CPU, after {warmup} warm-up"}
 
 
+def _time_ms(fn, reps):
+    import torch
+    fn()
+    torch.cuda.synchronize()
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps
+
+
+def run_extras(dec, dev, pk):
+    """Side measurements of the other rows of the path (not the headline metric): BASELINE.json's second
+    metric (grid pts/s decode, configs[3]), the latent-only optimisation of reconstruct.py (configs[3]) and
+    the SIREN variant's fused step (configs[4]).  CUDA events on the launching stream, inputs resident."""
+    import random
+    import torch
+    import dsdf_b200
+    import dsdf_b200.siren as siren_mod
+    from dsdf_b200 import synth
+    out = {}
+    burst = float(pk["bf16_tflops"])
+    # ---- create_mesh grid decode, N = 256 (deep_sdf/mesh.py:32-71), one latent
+    dec.eval()
+    lat = torch.randn(1, 256, device=dev) * 0.05
+    buf = torch.empty(256 ** 3, device=dev)
+    ms = _time_ms(lambda: dec.decode_grid(lat, 256, out=buf), 5)
+    out["grid_decode_256"] = {"ms": ms, "pts_per_s": 256 ** 3 / (ms * 1e-3), "unit": "grid pts/s",
+                              "frac_of_burst_bf16_peak": 256 ** 3 * FWD_FLOP / (ms * 1e-3) / 1e12 / burst,
+                              "note": "coordinates generated in-kernel; output 4 B/pt stays on the device"}
+    t0 = time.perf_counter()
+    sdf_host = dsdf_b200.create_mesh_sdf(dec, lat, 256)          # incl. the one 67 MB D2H (pageable)
+    out["grid_decode_256"]["create_mesh_sdf_wall_ms_incl_d2h"] = (time.perf_counter() - t0) * 1e3
+    del sdf_host
+    # ---- reconstruct.py: 800 Adam iterations x 8000 samples, frozen decoder (CLI defaults :262-263,345-356)
+    shapes = []
+    for s_ in range(64):
+        d = synth.fast_scene_samples(1, 500000, seed=100 + s_, device=str(dev))[0]
+        shapes.append((d[:250000].contiguous(), d[250000:].contiguous()))
+    rng = random.Random(0)
+    for n_shapes in (1, 64):
+        wins = torch.tensor([[dsdf_b200.draw_windows(250000, 250000, 8000, 1, rng)[0] for _ in range(n_shapes)]
+                             for _ in range(800)], dtype=torch.int64)
+        lat0 = torch.randn(n_shapes, 256) * 0.01
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        hist, lat_out = dsdf_b200.reconstruct_batch(dec, 800, shapes[:n_shapes], lat0, wins, 0.1, num_samples=8000,
+                                                    lr=5e-3, l2reg=True)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        out[f"reconstruct_800it_8000samples_x{n_shapes}"] = {
+            "wall_s": dt, "s_per_shape": dt / n_shapes, "shapes_per_s": n_shapes / dt,
+            "loss_first": float(hist[0].mean()), "loss_last": float(hist[-1].mean()),
+            "note": "whole Adam loop enqueued by one C call, incl. sample upload; FLOP/sample = fwd + dgrad"}
+    del shapes
+    # ---- SIREN 8x512 fused step (configs[4]), same rows/step as the headline
+    torch.manual_seed(0)
+    sd = siren_mod.Decoder(256, dims=[512] * 8, latent_in=[4], nonlinearity="sine").to(dev)
+    str_ = dsdf_b200.FusedTrainer(sd, SCENES, dsdf_b200.StepConfig(clamp_dist=0.1, code_bound=1.0, grad_clip=1.0,
+                                                                    lr_decoder=1e-5, lr_latent=1e-4))
+    data = synth.fast_scene_samples(B_PER_GPU, P, seed=5, device=str(dev))
+    ids = torch.arange(B_PER_GPU, device=dev)
+    for _ in range(3):
+        str_.step(data, ids, epoch=10)
+    ms = _time_ms(lambda: str_.step(data, ids, epoch=10), 8)
+    rows = B_PER_GPU * P
+    flop = 3 * 2 * 1_837_056
+    out["siren_train_step"] = {"ms_per_step": ms, "samples_per_s": rows / (ms * 1e-3), "flop_per_sample": flop,
+                               "frac_of_burst_bf16_peak": rows * flop / (ms * 1e-3) / 1e12 / burst,
+                               "loss": float(str_.loss_buf[0])}
+    del str_, sd, data
+    torch.cuda.empty_cache()
+    return out
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -144,6 +221,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the decode / reconstruct / SIREN side measurements")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -225,7 +303,6 @@ def main():
     ms_sum = (C.c_float * 4)(); ncalls = C.c_int32()
     _lib.check(L.dsdf_profile_read(h, ms_sum, C.byref(ncalls)), h)
     L.dsdf_profile_enable(h, 0)
-    clocks = sampler.summary(t0, t1)
     t = torch.tensor([ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -279,6 +356,7 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_ms = float(t.item())
     e2e_value = rows * world * K / (e2e_ms * 1e-3)
+    clocks = sampler.summary(t0, time.time())      # both timed regions (device-resident arm + e2e arm)
     sampler.stop()
 
     # ---------------- roofline of the dominant kernel + CPU baseline (rank 0) ----------------
@@ -301,6 +379,9 @@ def main():
                 "kernels_ms": {names[i]: per[i] for i in range(4)},
                 "step_tflops_algorithmic": rows * STEP_FLOP / (ms / K * 1e-3) / 1e12,
                 "step_frac_of_burst_peak": rows * STEP_FLOP / (ms / K * 1e-3) / 1e12 / float(pk["bf16_tflops"])}
+    extras = None
+    if rank == 0 and world == 1 and not args.no_extras:
+        extras = run_extras(dec, dev, pk)
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         r = cpu_reference_run(3, 1)
@@ -318,7 +399,7 @@ def main():
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": rows * 16 + B_PER_GPU * 8,
                     "d2h_bytes_per_step": 8, "ms_per_step": e2e_ms / K},
             "gpu_launches": launches_per_step * K,
-            "roofline": roofline, "cpu_baseline": cpu_baseline, "clocks": clocks,
+            "roofline": roofline, "cpu_baseline": cpu_baseline, "clocks": clocks, "extras": extras,
             "loss": float(st["sdf_loss"].item()),
         }
         print(json.dumps(line), flush=True)

@@ -59,6 +59,13 @@ typedef struct {
   int64_t total;             /* elements in the flat buffer */
 } dsdf_param_layout;
 
+/* Which specs["NetworkArch"] (train_deep_sdf.py:225) this build of the library implements: the one
+ * source tree is built once per decoder family -- "deep_sdf_decoder" (libdsdf_b200.so,
+ * networks/deep_sdf_decoder.py) and "siren_decoder" (libdsdf_b200_siren.so, -DDSDF_ARCH_SIREN,
+ * networks/siren_decoder.py: sin(30x) activations, lin3 512->256, lin4 = [x3 | latent], no output
+ * tanh).  Every entry below has the same signature and meaning in both. */
+const char* dsdf_arch(void);
+
 /* arch.Decoder(latent_size, **NetworkSpecs)  (train_deep_sdf.py:348) */
 int dsdf_create(const dsdf_config* cfg, dsdf_handle* out);
 int dsdf_destroy(dsdf_handle h);

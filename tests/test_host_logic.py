@@ -71,9 +71,11 @@ def test_library_loads_and_exports_every_declared_symbol():
     hdr = open(os.path.join(ROOT, "include", "dsdf.h")).read()
     declared = sorted(set(re.findall(r"\b(dsdf_[a-z_0-9]+)\s*\(", hdr)))
     assert len(declared) >= 16
-    L = _lib.lib()
-    for name in declared:
-        assert hasattr(L, name), name
+    for arch in ("deep_sdf_decoder", "siren_decoder"):     # one source tree, one build per family
+        L = _lib.lib(arch)
+        for name in declared:
+            assert hasattr(L, name), (arch, name)
+        assert L.dsdf_arch().decode() == arch
     assert sorted(_lib.EXPORTS) == declared
     assert C.sizeof(_lib.DsdfConfig) == 24 and C.sizeof(_lib.DsdfParamLayout) == 8 * 28
 
