@@ -63,6 +63,7 @@ struct dsdf_handle_s {
   int wg2_slots = 0;
   Wg2Layout wg2_layout{};
   int wg_ver = 2;                // DSDF_WG_VER=1: previous-generation wgrad kernel
+  int wg_quad = 1;               // DSDF_WG_QUAD=0: item-major schedule (every out-chunk pair re-reads X from HBM)
   ParamLayout pl{};
   const float* params_ptr = nullptr;   // caller's flat fp32 parameters at the last dsdf_set_weights
   bool weights_set = false;
@@ -182,6 +183,7 @@ extern "C" int dsdf_create(const dsdf_config* cfg, dsdf_handle* out) {
   if (const char* e = getenv("DSDF_FWD_CG")) h->fwd_cg = atoi(e) == 1 ? 1 : 2;
   if (const char* e = getenv("DSDF_BWD_VER")) h->bwd_ver = atoi(e) == 1 ? 1 : 2;
   if (const char* e = getenv("DSDF_WG_VER")) h->wg_ver = atoi(e) == 1 ? 1 : 2;
+  if (const char* e = getenv("DSDF_WG_QUAD")) h->wg_quad = atoi(e) != 0;
   if (h->bwd_ver == 1) h->wg_ver = 1;   // the v1 backward computes dW8 itself
 #ifdef DSDF_ARCH_SIREN
   // the sine epilogues exist in the current-generation kernels only
@@ -471,6 +473,9 @@ extern "C" int dsdf_grid_coords(dsdf_handle h, int32_t grid_n, int64_t lo, int64
 }
 
 // ------------------------------------------------------------------------------------ training
+// partial-sum slots of the v2 wgrad schedule (one per (CTA pair, work segment))
+static inline int wg2_max_slots(int num_sms) { return 3 * (num_sms / 2) + 32; }
+
 namespace {
 struct Ws {
   uint8_t* xstash;
@@ -506,7 +511,7 @@ Ws carve(uint8_t* base, long long max_rows, long long max_seg, int num_sms) {
   w.cta_partials = (float*)take((size_t)num_sms * kCtaPartialFloats * 4);
   {
     const size_t v1 = (size_t)kWgMaxItems * kTileM * kHidden * 4;
-    const size_t v2 = (size_t)(num_sms / 2 + 16) * 256 * kHidden * 4;
+    const size_t v2 = (size_t)wg2_max_slots(num_sms) * 256 * kHidden * 4;
     w.wg_partials = (float*)take(v1 > v2 ? v1 : v2);
   }
   w.seg_sum = (float*)take((size_t)max_seg * 2 * kHidden * 4);
@@ -581,13 +586,65 @@ static int build_wg2_schedule(dsdf_handle h, long long tiles, cudaStream_t st) {
     for (int ocp = 0; ocp < n_ocp; ++ocp) items.push_back({l, ocp, l == 4 ? 4 : 8, l == 4 ? 1 : 2});
   }
   h->wg2_layout.item_base[0] = 0;
-  long long total = 0;
-  for (const Item& it : items) total += (long long)it.cost * tiles;
   int n_pairs = h->num_sms / 2;
   if (n_pairs < 1) n_pairs = 1;
-  const long long target = (total + n_pairs - 1) / n_pairs;
   std::vector<WgSeg> segs;
   std::vector<int> seg_begin;
+  if (h->wg_quad && n_pairs >= 2) {
+    // "quad" schedule: two CTA pairs walk the SAME tile range of a layer side by side, one per
+    // 256-row out chunk, so the X tiles the second pair needs are L2 hits behind the first pair's
+    // HBM reads (the item-major schedule read X twice from HBM: 21.0 GB instead of 14.7 GB per step at
+    // 1 M rows, ncu profiles/r01_ncu_full_v4_benchsize.txt, which made the kernel HBM-bound).
+    // Layers with a single out chunk (lin3, lin8) split the tile range between the two pairs.
+    const int n_quads = n_pairs / 2;
+    auto quad_cost = [](int l) { return (l == 4 || l == 3 || l == 8) ? 1 : 2; };   // quad-time per tile
+    long long total = 0;
+    for (int l = 1; l <= 8; ++l) total += (long long)quad_cost(l) * tiles;
+    const long long target = (total + n_quads - 1) / n_quads;
+    std::vector<std::vector<WgSeg>> per_pair(n_pairs);
+    int l = 1;
+    long long t0 = 0;
+    for (int q = 0; q < n_quads && l <= 8; ++q) {
+      long long budget = target;
+      while (l <= 8 && budget > 0) {
+        const int c = quad_cost(l);
+        long long take = (budget + c - 1) / c;
+        if (take > tiles - t0) take = tiles - t0;
+        const int n_sub = l == 4 ? 4 : 8;
+        const bool two = !(l == 3 || l == 8);
+        WgSeg a;
+        a.layer = l; a.n_sub = n_sub; a.slot = 0;
+        if (two) {
+          a.ocp = 0; a.tile_lo = t0; a.tile_hi = t0 + take; per_pair[2 * q].push_back(a);
+          a.ocp = 1; per_pair[2 * q + 1].push_back(a);
+        } else {
+          const long long mid = t0 + (take + 1) / 2;
+          a.ocp = 0; a.tile_lo = t0; a.tile_hi = mid; per_pair[2 * q].push_back(a);
+          if (mid < t0 + take) { a.tile_lo = mid; a.tile_hi = t0 + take; per_pair[2 * q + 1].push_back(a); }
+        }
+        budget -= take * c;
+        t0 += take;
+        if (t0 == tiles) { ++l; t0 = 0; }
+      }
+    }
+    if (l <= 8) DSDF_FAIL(h, DSDF_EINVAL, "internal: wgrad schedule did not cover all layers");
+    // slots: contiguous per item (layer, ocp), in item order
+    std::vector<int> next_slot(items.size(), 0), base_slot(items.size(), 0), cnt(items.size(), 0);
+    for (auto& v : per_pair) for (WgSeg& sg : v) ++cnt[h->wg2_layout.item_base[sg.layer] + sg.ocp];
+    for (size_t i = 1; i < items.size(); ++i) base_slot[i] = base_slot[i - 1] + cnt[i - 1];
+    for (int p = 0; p < n_pairs; ++p) {
+      seg_begin.push_back((int)segs.size());
+      for (WgSeg& sg : per_pair[p]) {
+        const int item = h->wg2_layout.item_base[sg.layer] + sg.ocp;
+        sg.slot = base_slot[item] + next_slot[item]++;
+        segs.push_back(sg);
+      }
+    }
+    seg_begin.push_back((int)segs.size());
+  } else {
+  long long total = 0;
+  for (const Item& it : items) total += (long long)it.cost * tiles;
+  const long long target = (total + n_pairs - 1) / n_pairs;
   size_t ii = 0;
   long long t0 = 0;   // next unassigned tile of item ii
   for (int p = 0; p < n_pairs; ++p) {
@@ -608,9 +665,10 @@ static int build_wg2_schedule(dsdf_handle h, long long tiles, cudaStream_t st) {
   }
   seg_begin.push_back((int)segs.size());
   if (ii != items.size()) DSDF_FAIL(h, DSDF_EINVAL, "internal: wgrad schedule did not cover all items");
-  if ((int)segs.size() > h->num_sms / 2 + 16)
+  }
+  if ((int)segs.size() > wg2_max_slots(h->num_sms))
     DSDF_FAIL(h, DSDF_EINVAL, "internal: wgrad schedule has %d segments, partial buffer holds %d",
-              (int)segs.size(), h->num_sms / 2 + 16);
+              (int)segs.size(), wg2_max_slots(h->num_sms));
   for (size_t i = 0; i < items.size(); ++i) { h->wg2_layout.slot_lo[i] = 1 << 30; h->wg2_layout.slot_hi[i] = 0; }
   for (const WgSeg& sg : segs) {
     const int item = h->wg2_layout.item_base[sg.layer] + sg.ocp;
@@ -631,7 +689,6 @@ static int build_wg2_schedule(dsdf_handle h, long long tiles, cudaStream_t st) {
   h->wg2_tiles = tiles;
   return DSDF_OK;
 }
-constexpr int kWg2MaxSlots = 74 + 16;
 
 // persistent dgrad chain launch (CTA pairs when there are at least two tiles)
 static int launch_backward2(dsdf_handle h, const Bwd2Args& b2, long long tiles, cudaStream_t st,
