@@ -865,14 +865,14 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   // ---- segmented (scene-contiguous) reductions: latent grads, latent columns of dW0/dW4, biases
   const float reg_coef = reg_lambda_ramp * (float)rows_per_seg * inv_n;
   k_seg_colsum<<<dim3((unsigned)n_seg, 2), kHidden, 0, st>>>(w.tile_colsum, tiles_per_seg, w.seg_sum);
-  k_lat_grad_seg<<<(unsigned)n_seg, kLatent, 0, st>>>(w.seg_sum, h->weff, table,
+  k_lat_grad_seg<<<(unsigned)n_seg, 1024, 0, st>>>(w.seg_sum, h->weff, table,
                                                       (const long long*)seg_ids, reg_coef,
                                                       w.dlat_seg, w.seg_norm);
   CU(h, cudaMemsetAsync(lat_grad, 0, (size_t)num_scenes * kLatent * 4, st));
   k_lat_grad_scatter<<<1, kLatent, 0, st>>>(w.dlat_seg, (const long long*)seg_ids, (int)n_seg, lat_grad);
   k_dw_latent<<<dim3(kHidden, 2), kLatent, 0, st>>>(w.seg_sum, table, (const long long*)seg_ids,
                                                     (int)n_seg, w.dweff);
-  k_reduce_cta<<<1, kHidden, 0, st>>>(w.cta_partials, (int)bwd_grid, w.seg_sum, (int)n_seg,
+  k_reduce_cta<<<16, kHidden, 0, st>>>(w.cta_partials, (int)bwd_grid, w.seg_sum, (int)n_seg,
                                       w.tile_partials, tiles, h->pl, grads, w.dweff, h->wg_ver == 1 ? 1 : 0);
   k_param_grads<<<(kScaleElems * 32 + 255) / 256, 256, 0, st>>>(w.dweff, params, h->pl, h->scale,
                                                                 h->inv_norm, grads);
@@ -983,7 +983,7 @@ extern "C" int dsdf_dense_backward(dsdf_handle h, const float* params, const flo
   if (dinput) k_dense_dinput<<<dim3((unsigned)tiles, 5), 256, 0, st>>>(w.dystash, h->weff, n, dinput);
   const int n_chunks = (int)(tiles < 64 ? tiles : 64);
   k_colsum_chunks<<<dim3((unsigned)n_chunks, 2), kHidden, 0, st>>>(w.tile_colsum, tiles, w.seg_sum);
-  k_reduce_cta<<<1, kHidden, 0, st>>>(w.cta_partials, (int)bwd_grid, w.seg_sum, n_chunks, w.tile_partials, tiles,
+  k_reduce_cta<<<16, kHidden, 0, st>>>(w.cta_partials, (int)bwd_grid, w.seg_sum, n_chunks, w.tile_partials, tiles,
                                       h->pl, grads, w.dweff, 0);
   k_param_grads<<<(kScaleElems * 32 + 255) / 256, 256, 0, st>>>(w.dweff, params, h->pl, h->scale, h->inv_norm, grads);
   CU(h, cudaGetLastError());

@@ -12,6 +12,7 @@
 #include "bwd_kernel.cuh"
 #include "fold_kernels.cuh"
 #include "layout.cuh"
+#include "ptx.cuh"
 #include "wgrad_kernel.cuh"
 #include "wgrad2_kernel.cuh"
 
@@ -55,28 +56,42 @@ __global__ void k_seg_colsum(const float* __restrict__ tile_colsum, int tiles_pe
 }
 
 // ---- latent gradient per segment ---------------------------------------------------------------
-// dlat[b][j] = sum_c S0[b][c] W0[c][j] + sum_c S4[b][c] W4[c][253+j] + reg_coef * z[j]/||z||
-// grid n_seg, 256 threads
-__global__ void k_lat_grad_seg(const float* __restrict__ seg_sum, const float* __restrict__ weff,
-                               const float* __restrict__ table,
-                               const long long* __restrict__ seg_ids, float reg_coef,
-                               float* __restrict__ dlat_seg, float* __restrict__ seg_norm) {
-  __shared__ float s0[kHidden], s4[kHidden], sh[8];
-  const int b = blockIdx.x, j = threadIdx.x;
-  for (int c = j; c < kHidden; c += 256) {
-    s0[c] = seg_sum[((size_t)b * 2 + 0) * kHidden + c];
-    s4[c] = seg_sum[((size_t)b * 2 + 1) * kHidden + c];
+// dlat[b][j] = sum_c S0[b][c] W0[c][j] + sum_c S4[b][c] W4[c][kX3+j] + reg_coef * z[j]/||z||
+// grid n_seg, 1024 threads: thread (part = t / 256, j = t % 256) sums a quarter of c; fixed-order combine
+__global__ void __launch_bounds__(1024) k_lat_grad_seg(const float* __restrict__ seg_sum,
+                                                       const float* __restrict__ weff,
+                                                       const float* __restrict__ table,
+                                                       const long long* __restrict__ seg_ids, float reg_coef,
+                                                       float* __restrict__ dlat_seg, float* __restrict__ seg_norm) {
+  __shared__ float s0[kHidden], s4[kHidden], accs[4][kLatent], sh[8];
+  const int b = blockIdx.x, t = threadIdx.x, j = t & 255, part = t >> 8;
+  for (int c = t; c < 2 * kHidden; c += 1024) {
+    const float v = seg_sum[(size_t)b * 2 * kHidden + c];
+    if (c < kHidden) s0[c] = v; else s4[c - kHidden] = v;
   }
   __syncthreads();
   const float* w0 = weff + weff_off(0) + j;             // [512][259]
   const float* w4 = weff + weff_off(4) + kX3 + j;       // [512][512]
-  float acc = 0.f;
-  for (int c = 0; c < kHidden; ++c) {
-    acc = fmaf(s0[c], w0[(size_t)c * kIn0], acc);
-    acc = fmaf(s4[c], w4[(size_t)c * kHidden], acc);
+  float a0 = 0.f, a4 = 0.f;
+  const int c0 = part * (kHidden / 4);
+#pragma unroll 8
+  for (int c = c0; c < c0 + kHidden / 4; ++c) {
+    a0 = fmaf(s0[c], __ldg(w0 + (size_t)c * kIn0), a0);
+    a4 = fmaf(s4[c], __ldg(w4 + (size_t)c * kHidden), a4);
   }
+  accs[part][j] = a0 + a4;
+  __syncthreads();
+  if (t >= 256) return;
+  float acc = (accs[0][j] + accs[1][j]) + (accs[2][j] + accs[3][j]);
   const float z = table[seg_ids[b] * kLatent + j];
-  const float nrm = sqrtf(block_sum_256(z * z, sh));
+  float v = z * z;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if ((t & 31) == 0) sh[t >> 5] = v;
+  named_bar_sync(2, 256);
+  float zz = 0.f;
+  for (int i = 0; i < 8; ++i) zz += sh[i];
+  const float nrm = sqrtf(zz);
   if (reg_coef != 0.f && nrm > 0.f) acc += reg_coef * z / nrm;
   dlat_seg[(size_t)b * kLatent + j] = acc;
   if (j == 0) seg_norm[b] = nrm;
@@ -159,51 +174,52 @@ __global__ void k_reduce_wgrad2(const float* __restrict__ partials, Wg2Layout wl
 }
 
 // ---- reducer-warp partials (per CTA) -> bias grads, dW8, xyz columns of dW0/dW4 -----------------
-// one block of 512 threads (column c)
+// grid 16 jobs x 512 threads (column c); every job sums its partials in a fixed order (deterministic):
+//   0..5   db of lin {1,2,3,5,6,7}        6..11  xyz column e of dW{0,4}   (job - 6 = 3 i + e)
+//   12,13  db0 / db4 from the segment column sums      14  db8 = sum_rows g      15  dW8 (v1 backward only)
 __global__ void k_reduce_cta(const float* __restrict__ cta_partials, int n_cta,
                              const float* __restrict__ seg_sum, int n_seg,
                              const float* __restrict__ tile_partials, long long n_tiles,
                              ParamLayout pl, float* __restrict__ grads,
                              float* __restrict__ dweff, int with_dw8) {
   __shared__ float sh[16];
-  const int c = threadIdx.x;
-  // db for l in {1,2,3,5,6,7}
-  const int ls[6] = {1, 2, 3, 5, 6, 7};
-  for (int i = 0; i < 6; ++i) {
+  const int c = threadIdx.x, job = blockIdx.x;
+  if (job < 6) {
+    const int ls[6] = {1, 2, 3, 5, 6, 7};
     float s = 0.f;
-    for (int k = 0; k < n_cta; ++k) s += cta_partials[(size_t)k * kCtaPartialFloats + kPartDb + i * kHidden + c];
-    if (c < ref_out(ls[i])) grads[pl.b[ls[i]] + c] = s;
-  }
-  if (with_dw8) {  // dW8 (v1 backward kernel only; the v2 path gets it from the wgrad kernel)
+#pragma unroll 4
+    for (int k = 0; k < n_cta; ++k) s += cta_partials[(size_t)k * kCtaPartialFloats + kPartDb + job * kHidden + c];
+    if (c < ref_out(ls[job])) grads[pl.b[ls[job]] + c] = s;
+  } else if (job < 12) {
+    const int i = (job - 6) / 3, e = (job - 6) % 3, l = i == 0 ? 0 : 4;
+    if (xyz_col(l, e) < 0) return;
+    float s = 0.f;
+#pragma unroll 4
+    for (int k = 0; k < n_cta; ++k)
+      s += cta_partials[(size_t)k * kCtaPartialFloats + kPartXyz + (i * kHidden + c) * 3 + e];
+    dweff[weff_off(l) + (size_t)c * ref_in(l) + xyz_col(l, e)] = s;
+  } else if (job < 14) {
+    const int i = job - 12;
+    float s = 0.f;
+#pragma unroll 4
+    for (int b = 0; b < n_seg; ++b) s += seg_sum[((size_t)b * 2 + i) * kHidden + c];
+    grads[pl.b[i == 0 ? 0 : 4] + c] = s;
+  } else if (job == 14) {
+    float s = 0.f;
+    for (long long t = c; t < n_tiles; t += blockDim.x) s += tile_partials[t * 2 + 1];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if ((c & 31) == 0) sh[c >> 5] = s;
+    __syncthreads();
+    if (c == 0) {
+      float t = 0.f;
+      for (int i = 0; i < 16; ++i) t += sh[i];
+      grads[pl.b[8]] = t;
+    }
+  } else if (with_dw8) {   // dW8 (v1 backward kernel only; the v2 path gets it from the wgrad kernel)
     float s = 0.f;
     for (int k = 0; k < n_cta; ++k) s += cta_partials[(size_t)k * kCtaPartialFloats + kPartW8 + c];
     dweff[weff_off(8) + c] = s;
-  }
-  for (int i = 0; i < 2; ++i) {  // xyz columns
-    for (int e = 0; e < 3; ++e) {
-      float s = 0.f;
-      for (int k = 0; k < n_cta; ++k)
-        s += cta_partials[(size_t)k * kCtaPartialFloats + kPartXyz + (i * kHidden + c) * 3 + e];
-      const int l = i == 0 ? 0 : 4;
-      if (xyz_col(l, e) >= 0) dweff[weff_off(l) + (size_t)c * ref_in(l) + xyz_col(l, e)] = s;
-    }
-  }
-  for (int i = 0; i < 2; ++i) {  // db0, db4 from the segment colsums
-    float s = 0.f;
-    for (int b = 0; b < n_seg; ++b) s += seg_sum[((size_t)b * 2 + i) * kHidden + c];
-    grads[pl.b[i == 0 ? 0 : 4] + c] = s;
-  }
-  // db8 = sum_rows g
-  float s = 0.f;
-  for (long long t = c; t < n_tiles; t += blockDim.x) s += tile_partials[t * 2 + 1];
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-  if ((c & 31) == 0) sh[c >> 5] = s;
-  __syncthreads();
-  if (c == 0) {
-    float t = 0.f;
-    for (int i = 0; i < 16; ++i) t += sh[i];
-    grads[pl.b[8]] = t;
   }
 }
 

@@ -23,6 +23,9 @@ def read(dec, label, tiles_per_cta):
     got = L.dsdf_debug_read(h, buf, n)
     a = np.frombuffer(buf, dtype=np.uint64).reshape(-1, 16).astype(np.float64)
     a = a[a[:, 7] > 0]
+    if a.shape[0] == 0:
+        print(f"== {label}: no counters (build with DSDF_BUILD_VARIANT=dbg DSDF_BUILD_DEFS=-DDSDF_DBG_BUILD and set DSDF_LIB)")
+        return
     print(f"== {label}: {a.shape[0]} CTAs, {tiles_per_cta:.1f} tiles/CTA")
     for i, nm in enumerate(NAMES):
         if a[:, i].max() > 0:
