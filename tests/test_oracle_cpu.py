@@ -225,3 +225,40 @@ def test_siren_oracle_and_host_decoder_equal_live_reference():
         spec = dict(siren.network_specs()); spec.update(kw)
         with pytest.raises(NotImplementedError):
             S.Decoder(256, **spec)
+
+
+def _callers_setup():
+    """Decoder parameters, shape and RNG replay of tests/golden/make_golden_callers.py."""
+    import random
+    from dsdf_b200 import synth
+    g = golden("callers_ref.npz")
+    spec = spec_for(True)
+    p = deepsdf.init_params(spec, seed=0)
+    for l in range(8):
+        p[f"lin{l}.weight_g"] = p[f"lin{l}.weight_g"] * 1.5
+    check_checksums(p, g)
+    d = synth.scene_samples(1, 4096, seed=9)[0]
+    return g, spec, p, d[:2048].contiguous(), d[2048:].contiguous(), random
+
+
+def test_oracle_callers_match_the_executed_reference():
+    """callers_ref.npz was produced by RUNNING the reference's reconstruct.reconstruct, data.unpack_sdf_samples_from_ram
+    and mesh.create_mesh (sampling loop) on CPU: the oracle restatements must reproduce them."""
+    g, spec, p, pos, neg, random = _callers_setup()
+    # sampler (deep_sdf/data.py:112-136): same random.randint stream -> identical rows
+    random.seed(3)
+    w = orec.draw_windows(2048, 2048, 800, 1, random)[0]
+    np.testing.assert_array_equal(orec.window(pos, neg, 800, w).numpy(), g["window_sample"])
+    # reconstruct (reconstruct.py:16-151): initial latent from torch's RNG, then two randints per iteration
+    for name, kw in (("a", dict(l2reg=True)), ("b", dict(l2reg=False, code_reg_lambda=1e-2, code_reg_type="l2_norm", code_bound=0.2))):
+        random.seed(0); torch.manual_seed(0)
+        lat0 = torch.ones(1, 256).normal_(mean=0, std=0.01)
+        wins = orec.draw_windows(2048, 2048, 800, 30, random)
+        losses, lat = orec.reconstruct(p, spec, 30, pos, neg, wins, lat0, 0.1, num_samples=800, lr=5e-3, **kw)
+        np.testing.assert_allclose(np.array(losses), g[f"recon_{name}/losses"], rtol=2e-5, atol=1e-7)
+        np.testing.assert_allclose(lat.numpy(), g[f"recon_{name}/latent"], atol=2e-5)
+    # create_mesh sampling (mesh.py:32-71): closed-form grid + decode_sdf
+    lat = torch.from_numpy(g["recon_a/latent"])
+    coords = torch.from_numpy(mesh_grid.grid_coords_closed_form(24))
+    sdf = deepsdf.forward(p, spec, torch.cat([lat.expand(24 ** 3, -1), coords], 1)).reshape(24, 24, 24)
+    np.testing.assert_allclose(sdf.numpy(), g["mesh/sdf24"], atol=2e-6)
