@@ -131,7 +131,8 @@ int dsdf_renorm_rows(dsdf_handle h, float* table, const int64_t* seg_ids, int64_
 
 /* torch.nn.utils.clip_grad_norm_(params, max_norm) + torch.optim.Adam step
  * (train_deep_sdf.py:780-784, 445-454) over one flat buffer.  max_norm <= 0: no clipping.
- * scratch: >= 8 KiB device scratch; scratch[0] = grad norm, scratch[1] = clip coef on return.
+ * scratch: >= 8 KiB device scratch; with max_norm > 0, scratch[0] = grad norm, scratch[1] = clip coef on
+ * return (the norm is not computed when nothing is clipped).
  * `step` is the 1-based Adam step count. */
 int dsdf_clip_adam(dsdf_handle h, float* params, float* grads, float* exp_avg, float* exp_avg_sq,
                    int64_t n, float max_norm, float lr, float beta1, float beta2, float eps,

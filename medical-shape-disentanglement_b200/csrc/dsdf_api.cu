@@ -261,11 +261,12 @@ extern "C" int dsdf_set_weights(dsdf_handle h, const float* params, const dsdf_p
   k_rowscale<<<(kScaleElems * 32 + 255) / 256, 256, 0, st>>>(params, h->pl, h->scale, h->inv_norm);
   k_weff<<<(unsigned)((kWeffElems + 255) / 256), 256, 0, st>>>(params, h->pl, h->scale, h->weff);
   const long long c1 = (long long)kFwdTilesTotal * (kSubBytes / 16);
-  k_fold_fwd<<<(unsigned)((c1 + 255) / 256), 256, 0, st>>>(h->weff, params, h->pl, h->fwd_img);
+  // the first-generation images are only read by the A/B kernels (DSDF_FWD_V1 / DSDF_BWD_VER=1)
+  if (h->fwd_v1) k_fold_fwd<<<(unsigned)((c1 + 255) / 256), 256, 0, st>>>(h->weff, params, h->pl, h->fwd_img);
   const long long c3 = (long long)kW2Steps * (kStepBytes / 16);
   k_fold_fwd2<<<(unsigned)((c3 + 255) / 256), 256, 0, st>>>(h->weff, params, h->pl, h->w2_img);
   const long long c2 = (long long)kDgTilesTotal * (kSubBytes / 16);
-  k_fold_dgrad<<<(unsigned)((c2 + 255) / 256), 256, 0, st>>>(h->weff, h->dg_img);
+  if (h->bwd_ver == 1) k_fold_dgrad<<<(unsigned)((c2 + 255) / 256), 256, 0, st>>>(h->weff, h->dg_img);
   const long long c4 = (long long)kDg2Steps * (kStepBytes / 16);
   k_fold_dgrad2<<<(unsigned)((c4 + 255) / 256), 256, 0, st>>>(h->weff, h->dg2_img);
   CU(h, cudaGetLastError());
@@ -1243,14 +1244,16 @@ extern "C" int dsdf_clip_adam(dsdf_handle h, float* params, float* grads, float*
   cudaStream_t st = (cudaStream_t)stream;
   const int nb = 1024;
   float* part = scratch + 16;
-  k_sqnorm_partial<<<nb, 256, 0, st>>>(grads, n, part);
-  k_clip_coef<<<1, 256, 0, st>>>(part, nb, max_norm, scratch);
+  if (max_norm > 0.f) {   // the reference computes the norm only when it clips (train_deep_sdf.py:780-782)
+    k_sqnorm_partial<<<nb, 256, 0, st>>>(grads, n, part);
+    k_clip_coef<<<1, 256, 0, st>>>(part, nb, max_norm, scratch);
+  }
   const double bc1 = 1.0 - pow((double)beta1, (double)step);
   const double bc2 = 1.0 - pow((double)beta2, (double)step);
   const float step_size = (float)((double)lr / bc1);
   const float bc2_sqrt = (float)sqrt(bc2);
   const unsigned blocks = (unsigned)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
-  k_adam<<<blocks, 256, 0, st>>>(params, grads, exp_avg, exp_avg_sq, n, scratch, step_size,
+  k_adam<<<blocks, 256, 0, st>>>(params, grads, exp_avg, exp_avg_sq, n, max_norm > 0.f ? scratch : nullptr, step_size,
                                  bc2_sqrt, beta1, beta2, eps, max_norm > 0.f ? 1 : 0);
   CU(h, cudaGetLastError());
   return DSDF_OK;

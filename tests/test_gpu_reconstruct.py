@@ -116,3 +116,37 @@ def test_error_paths():
     with pytest.raises(ValueError):
         dsdf_b200.reconstruct_batch(dec, 1, [(pos, neg)], torch.zeros(1, 256), torch.zeros(1, 1, 2), 0.1, num_samples=256,
                                     code_reg_lambda=1.0, code_reg_type="bogus")
+
+
+def test_reconstruct_and_create_mesh_match_the_executed_reference_golden():
+    """tests/golden/callers_ref.npz holds outputs of the reference's own reconstruct.reconstruct and
+    mesh.create_mesh (sampling loop) executed on CPU; the CUDA drop-ins, seeded identically, must follow them:
+    loss history within 1 %, latent update direction, SDF grid <= 2e-3."""
+    from common import check_checksums, golden
+    g = golden("callers_ref.npz")
+    torch.manual_seed(0)
+    dec = dsdf_b200.Decoder(256, norm_layers=list(range(8)), **KW)
+    sd = dec.state_dict()
+    for l in range(8):
+        sd[f"lin{l}.weight_g"] = sd[f"lin{l}.weight_g"] * 1.5
+    dec.load_state_dict(sd)
+    check_checksums({k: v for k, v in dec.state_dict().items()}, g)
+    dec = dec.cuda()
+    d = synth.scene_samples(1, 4096, seed=9)[0]
+    pos, neg = d[:2048].contiguous(), d[2048:].contiguous()
+    for name, kw in (("a", dict(l2reg=True)), ("b", dict(code_reg_lambda=1e-2, code_reg_type="l2_norm", code_bound=0.2))):
+        random.seed(0); torch.manual_seed(0)
+        lat0 = torch.ones(1, 256).normal_(mean=0, std=0.01)          # what the reference drew on CPU
+        random.seed(0); torch.manual_seed(0)
+        # the drop-in draws its initial latent on the decoder's device (as the reference does, :47-50), which is
+        # a different torch stream on CUDA: feed the CPU-drawn latent through the batched entry instead
+        wins = dsdf_b200.draw_windows(2048, 2048, 800, 30, random)
+        hist, lat = dsdf_b200.reconstruct_batch(dec, 30, [(pos, neg)], lat0, torch.tensor(wins).view(30, 1, 2), 0.1,
+                                                num_samples=800, lr=5e-3, **kw)
+        np.testing.assert_allclose(hist[:, 0].cpu().numpy(), g[f"recon_{name}/losses"], rtol=1e-2)
+        ref_lat = torch.from_numpy(g[f"recon_{name}/latent"])
+        assert cos(lat.cpu() - lat0, ref_lat - lat0) >= 0.98
+    lat = torch.from_numpy(g["recon_a/latent"])
+    sdf = dsdf_b200.create_mesh_sdf(dec, lat, N=24)
+    assert sdf.shape == (24, 24, 24)
+    assert np.abs(sdf.numpy() - g["mesh/sdf24"]).max() <= 2e-3

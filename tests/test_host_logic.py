@@ -3,6 +3,7 @@ parameter addressing, the C-ABI library's exports (no compute calls without a GP
 import ctypes as C
 import os
 import re
+import sys
 
 import pytest
 import torch
@@ -112,3 +113,44 @@ def test_scene_partition_is_a_partition():
         assert seen == list(range(S))
     assert sum(dist.local_batch(64, r, 8) for r in range(8)) == 64
     assert sum(dist.local_batch(24, r, 8) for r in range(8)) == 24
+
+
+def test_sample_file_contract_matches_reference_data_module(tmp_path):
+    """dsdf_b200.data restates deep_sdf/data.py:76-136,196-206: same rows for the same RNG streams as the golden
+    drawn by the executed reference (tests/golden/callers_ref.npz) and, when the reference tree is mounted, as the
+    live functions."""
+    import random
+    import numpy as np
+    from common import golden
+    from dsdf_b200 import data as D, synth
+    d = synth.scene_samples(1, 4096, seed=9)[0]
+    pos, neg = d[:2048].contiguous(), d[2048:].contiguous()
+    random.seed(3)
+    got = D.unpack_sdf_samples_from_ram([pos, neg], 800)
+    np.testing.assert_array_equal(got.numpy(), golden("callers_ref.npz")["window_sample"])
+    # file round trip incl. NaN rows (dropped, data.py:76-78) and the load-time shuffle
+    pos_n = pos.clone(); pos_n[5, 3] = float("nan")
+    f = str(tmp_path / "shape.npz")
+    D.write_sdf_samples(f, pos_n, neg)
+    p2, n2 = D.read_sdf_samples_into_ram(f)
+    assert torch.equal(n2, neg) and torch.isnan(p2[5, 3])
+    torch.manual_seed(1); random.seed(1)
+    ds = D.SDFSamples([f], 512)
+    item, idx = ds[0]
+    assert item.shape == (512, 4) and idx == 0 and not torch.isnan(item).any()
+    assert ds.loaded_data[0][0].shape[0] == 2047 and (item[:256, 3] > 0).all() and (item[256:, 3] <= 0).all()
+    torch.manual_seed(2)
+    a = D.unpack_sdf_samples(f, 100)
+    assert a.shape == (100, 4) and not torch.isnan(a).any()
+    if os.path.isdir("/root/reference/deep_sdf"):
+        sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+        import make_golden_callers as mk
+        mk.install_stubs()
+        import deep_sdf.data as R
+        random.seed(7); ref = R.unpack_sdf_samples_from_ram([pos, neg], 600)
+        random.seed(7); mine = D.unpack_sdf_samples_from_ram([pos, neg], 600)
+        assert torch.equal(ref, mine)
+        torch.manual_seed(5); ref = R.unpack_sdf_samples(f, 64)
+        torch.manual_seed(5); mine = D.unpack_sdf_samples(f, 64)
+        assert torch.equal(ref, mine)
+        assert torch.equal(R.remove_nans(pos_n), D.remove_nans(pos_n))
