@@ -152,6 +152,20 @@ int dsdf_dense_backward(dsdf_handle h, const float* params, const float* input, 
                         const float* out, const float* dout, void* workspace, size_t workspace_bytes,
                         float* grads, float* dinput, void* stream);
 
+/* Stage-2 style call (train_MLP_VAE_deep_sdf.py:3097-3133: z_hat[B,256] produced by another network,
+ * repeated over each shape's P samples, concatenated with xyz and decoded; gradients flow back into z_hat
+ * and, if trainable, the decoder): the scene-structured form of the autograd path.  Row r of segment b uses
+ * latents[b]; forward_train keeps stash + masks in `workspace` (dsdf_train_workspace_bytes(h, n, n_seg)),
+ * backward turns dOut[n] into grads (flat, OVERWRITTEN) and dlatents[n_seg,256] (OVERWRITTEN) with the
+ * deterministic segmented reduction.  rows_per_seg %% 128 == 0. */
+int dsdf_segments_forward_train(dsdf_handle h, const float* params, const float* latents, int64_t n_seg,
+                                int64_t rows_per_seg, const float* xyz, int64_t xyz_stride, float* out,
+                                void* workspace, size_t workspace_bytes, void* stream);
+int dsdf_segments_backward(dsdf_handle h, const float* params, const float* latents, int64_t n_seg,
+                           int64_t rows_per_seg, const float* xyz, int64_t xyz_stride, const float* out,
+                           const float* dout, void* workspace, size_t workspace_bytes, float* grads,
+                           float* dlatents, void* stream);
+
 /* Training-mode dropout of the hidden layers (networks/deep_sdf_decoder.py:24,103-104:
  * F.dropout(x, p=dropout_prob, training=self.training) after the ReLU of every layer in `dropout`),
  * fused into the forward epilogues of dsdf_train_fwd_bwd: layer_mask bit l <=> l in NetworkSpecs.dropout,

@@ -489,6 +489,7 @@ struct Ws {
   float* seg_sum;
   float* dlat_seg;
   float* seg_norm;
+  long long* ids;        // identity segment ids (segments autograd entry)
   float* dweff;
   uint8_t* scene_e;
   uint32_t* relu_mask;
@@ -518,6 +519,7 @@ Ws carve(uint8_t* base, long long max_rows, long long max_seg, int num_sms) {
   w.seg_sum = (float*)take((size_t)max_seg * 2 * kHidden * 4);
   w.dlat_seg = (float*)take((size_t)max_seg * kLatent * 4);
   w.seg_norm = (float*)take((size_t)max_seg * 4);
+  w.ids = (long long*)take((size_t)max_seg * 8);
   w.dweff = (float*)take((size_t)kWeffElems * 4);
   w.scene_e = take((size_t)max_seg * kSceneESteps * kStepBytes);
   w.relu_mask = (uint32_t*)take(tiles * kActAuxTileBytes);
@@ -688,6 +690,34 @@ static int build_wg2_schedule(dsdf_handle h, long long tiles, cudaStream_t st) {
   h->wg2_pairs = n_pairs;
   h->wg2_slots = (int)segs.size();
   h->wg2_tiles = tiles;
+  return DSDF_OK;
+}
+
+// wgrad GEMMs (lin1..lin8) over the stashed images + ordered split-K reduction into dweff
+static int launch_wgrad2(dsdf_handle h, const uint8_t* xstash, const uint8_t* dystash, const uint8_t* g_img,
+                         float* partials, float* dweff, cudaStream_t st) {
+  Wg2Args w2;
+  w2.segs = h->wg2_segs;
+  w2.seg_begin = h->wg2_seg_begin;
+  w2.xstash = xstash;
+  w2.dystash = dystash;
+  w2.g_img = g_img;
+  w2.partials = partials;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3((unsigned)(2 * h->wg2_pairs));
+  cfg.blockDim = dim3(kW2Threads);
+  cfg.dynamicSmemBytes = kW2SmemBytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  CU(h, cudaLaunchKernelEx(&cfg, k_wgrad2, w2));
+  k_reduce_wgrad2<<<dim3(kHidden, 8), kHidden, 0, st>>>(partials, h->wg2_layout, dweff);
   return DSDF_OK;
 }
 
@@ -986,6 +1016,102 @@ extern "C" int dsdf_dense_backward(dsdf_handle h, const float* params, const flo
   k_colsum_chunks<<<dim3((unsigned)n_chunks, 2), kHidden, 0, st>>>(w.tile_colsum, tiles, w.seg_sum);
   k_reduce_cta<<<16, kHidden, 0, st>>>(w.cta_partials, (int)bwd_grid, w.seg_sum, n_chunks, w.tile_partials, tiles,
                                       h->pl, grads, w.dweff, 0);
+  k_param_grads<<<(kScaleElems * 32 + 255) / 256, 256, 0, st>>>(w.dweff, params, h->pl, h->scale, h->inv_norm, grads);
+  CU(h, cudaGetLastError());
+  return DSDF_OK;
+}
+
+// ------------------------------------------------------------------------------- segments autograd
+__global__ void k_iota(long long* ids, long long n) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) ids[i] = i;
+}
+
+// decoder(cat([latents[b].expand(P), xyz[b]])) for b < n_seg in a grad-enabled context: the fold-mode
+// forward (per-scene latent product in the bias) keeping stash + masks in `workspace`.
+extern "C" int dsdf_segments_forward_train(dsdf_handle h, const float* params, const float* latents,
+                                           int64_t n_seg, int64_t rows_per_seg, const float* xyz,
+                                           int64_t xyz_stride, float* out, void* workspace,
+                                           size_t workspace_bytes, void* stream) {
+  if (!h || !params || !latents || !xyz || !out || !workspace) DSDF_FAIL(h, DSDF_EINVAL, "null argument");
+  if (!h->weights_set) DSDF_FAIL(h, DSDF_EINVAL, "dsdf_set_weights has not been called");
+  if (n_seg <= 0 || rows_per_seg <= 0 || rows_per_seg % kTileM != 0 || xyz_stride < 3)
+    DSDF_FAIL(h, DSDF_EUNSUPPORTED, "segments need rows_per_seg %% 128 == 0 (got %lld) and xyz_stride >= 3",
+              (long long)rows_per_seg);
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long n = n_seg * rows_per_seg;
+  uint8_t* base = (uint8_t*)(((uintptr_t)workspace + 1023) & ~(uintptr_t)1023);
+  Ws w = carve(base, n, n_seg, h->num_sms);
+  if ((size_t)(base - (uint8_t*)workspace) + w.total > workspace_bytes)
+    DSDF_FAIL(h, DSDF_ENOMEM, "workspace too small: need %zu bytes, have %zu", w.total + 1024, workspace_bytes);
+  FwdArgs fa;
+  memset(&fa, 0, sizeof(fa));
+  fa.wimg = h->fwd_img;
+  fa.w8 = h->weff + weff_off(8);
+  fa.b8 = h->weff + kWeffElems;
+  fa.n_rows = n;
+  fa.table = latents;
+  fa.seg_ids = w.ids;
+  fa.rows_per_seg = rows_per_seg;
+  fa.xyzs = xyz;
+  fa.xyz_stride = xyz_stride;
+  fa.out = out;
+  fa.xstash = w.xstash;
+  fa.relu_mask = w.relu_mask;
+  fa.w2img = h->w2_img;
+  fa.dbg = h->dbg;
+  fa.scene_e = w.scene_e;
+  k_iota<<<(unsigned)((n_seg + 255) / 256), 256, 0, st>>>(w.ids, n_seg);
+  k_scene_fold<<<dim3((unsigned)n_seg, 2), 512, 0, st>>>(h->weff, params, h->pl, latents, w.ids, w.scene_e);
+  CU(h, (launch_fwd<MODE_TABLE, true, true>(h, fa, st, rows_per_seg % (2 * kTileM) == 0)));
+  CU(h, cudaGetLastError());
+  return DSDF_OK;
+}
+
+// backward of the above: dOut[n] -> grads (flat, OVERWRITTEN) and dlatents[n_seg, 256] (OVERWRITTEN).
+extern "C" int dsdf_segments_backward(dsdf_handle h, const float* params, const float* latents,
+                                      int64_t n_seg, int64_t rows_per_seg, const float* xyz,
+                                      int64_t xyz_stride, const float* out, const float* dout,
+                                      void* workspace, size_t workspace_bytes, float* grads,
+                                      float* dlatents, void* stream) {
+  if (!h || !params || !latents || !xyz || !out || !dout || !workspace || !grads || !dlatents)
+    DSDF_FAIL(h, DSDF_EINVAL, "null argument");
+  if (h->bwd_ver == 1 || h->wg_ver == 1) DSDF_FAIL(h, DSDF_EUNSUPPORTED, "needs the v2 kernels");
+  if (n_seg <= 0 || rows_per_seg <= 0 || rows_per_seg % kTileM != 0)
+    DSDF_FAIL(h, DSDF_EUNSUPPORTED, "segments need rows_per_seg %% 128 == 0");
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long n = n_seg * rows_per_seg;
+  const long long tiles = n / kTileM;
+  const int tiles_per_seg = (int)(rows_per_seg / kTileM);
+  uint8_t* base = (uint8_t*)(((uintptr_t)workspace + 1023) & ~(uintptr_t)1023);
+  Ws w = carve(base, n, n_seg, h->num_sms);
+  if ((size_t)(base - (uint8_t*)workspace) + w.total > workspace_bytes)
+    DSDF_FAIL(h, DSDF_ENOMEM, "workspace too small: need %zu bytes, have %zu", w.total + 1024, workspace_bytes);
+  int rc = build_wg2_schedule(h, tiles, st);
+  if (rc != DSDF_OK) return rc;
+  k_dense_g<<<(unsigned)tiles, kTileM, 0, st>>>(dout, out, n, w.g, w.g_img, w.tile_partials);
+  Bwd2Args b2;
+  memset(&b2, 0, sizeof(b2));
+  b2.n_rows = n;
+  b2.dg2img = h->dg2_img;
+  b2.w8 = h->weff + weff_off(8);
+  b2.g = w.g;
+  b2.relu_mask = w.relu_mask;
+  b2.dystash = w.dystash;
+  b2.xyz = xyz;
+  b2.xyz_stride = xyz_stride;
+  b2.tile_colsum = w.tile_colsum;
+  b2.cta_partials = w.cta_partials;
+  unsigned bwd_grid = 0;
+  rc = launch_backward2(h, b2, tiles, st, &bwd_grid);
+  if (rc != DSDF_OK) return rc;
+  rc = launch_wgrad2(h, w.xstash, w.dystash, w.g_img, w.wg_partials, w.dweff, st);
+  if (rc != DSDF_OK) return rc;
+  k_seg_colsum<<<dim3((unsigned)n_seg, 2), kHidden, 0, st>>>(w.tile_colsum, tiles_per_seg, w.seg_sum);
+  k_lat_grad_seg<<<(unsigned)n_seg, 1024, 0, st>>>(w.seg_sum, h->weff, latents, w.ids, 0.f, dlatents, w.seg_norm);
+  k_dw_latent<<<dim3(kHidden, 2), kLatent, 0, st>>>(w.seg_sum, latents, w.ids, (int)n_seg, w.dweff);
+  k_reduce_cta<<<16, kHidden, 0, st>>>(w.cta_partials, (int)bwd_grid, w.seg_sum, (int)n_seg, w.tile_partials, tiles,
+                                       h->pl, grads, w.dweff, 0);
   k_param_grads<<<(kScaleElems * 32 + 255) / 256, 256, 0, st>>>(w.dweff, params, h->pl, h->scale, h->inv_norm, grads);
   CU(h, cudaGetLastError());
   return DSDF_OK;

@@ -20,7 +20,7 @@ EXPORTS = [
     "dsdf_forward_dense", "dsdf_forward_segments", "dsdf_decode_grid", "dsdf_grid_coords",
     "dsdf_train_workspace_bytes", "dsdf_train_fwd_bwd", "dsdf_renorm_rows", "dsdf_clip_adam",
     "dsdf_dense_workspace_bytes", "dsdf_dense_forward_train", "dsdf_dense_backward",
-    "dsdf_set_dropout", "dsdf_dropout_keep", "dsdf_reconstruct_workspace_bytes", "dsdf_reconstruct",
+    "dsdf_segments_forward_train", "dsdf_segments_backward", "dsdf_set_dropout", "dsdf_dropout_keep", "dsdf_reconstruct_workspace_bytes", "dsdf_reconstruct",
     "dsdf_selftest_gemm", "dsdf_profile_enable", "dsdf_profile_read", "dsdf_debug_read", "dsdf_selftest_mma_rate", "dsdf_debug_hang_buffer",
 ]
 
@@ -94,6 +94,10 @@ def lib(arch: str = "deep_sdf_decoder"):
     L.dsdf_dense_forward_train.restype = C.c_int
     L.dsdf_dense_backward.argtypes = [vp, vp, vp, i64, vp, vp, vp, sz, vp, vp, vp]
     L.dsdf_dense_backward.restype = C.c_int
+    L.dsdf_segments_forward_train.argtypes = [vp, vp, vp, i64, i64, vp, i64, vp, vp, sz, vp]
+    L.dsdf_segments_forward_train.restype = C.c_int
+    L.dsdf_segments_backward.argtypes = [vp, vp, vp, i64, i64, vp, i64, vp, vp, vp, sz, vp, vp, vp]
+    L.dsdf_segments_backward.restype = C.c_int
     L.dsdf_set_dropout.argtypes = [vp, C.c_uint32, f32, C.c_uint64, C.c_uint64, i64]
     L.dsdf_set_dropout.restype = C.c_int
     L.dsdf_dropout_keep.argtypes = [vp, i32, i64, i64, vp, vp]

@@ -127,3 +127,38 @@ def test_no_grad_and_frozen_paths():
     c.sum().backward()
     assert x2.grad is not None and all(p.grad is None for p in dec.parameters())
     assert (c - a).abs().max().item() <= 1e-5
+
+
+@pytest.mark.parametrize("wn", [True, False])
+def test_decode_segments_stage2_style_call(wn):
+    """train_MLP_VAE_deep_sdf.py:3097-3133 shape of call: per-shape latents produced upstream (here a linear map
+    standing in for the VAE), repeated over P samples, decoded; gradients must reach the upstream weights and the
+    decoder.  Compared with the oracle on the materialised [B*P, 259] input."""
+    dec, spec, params = make(wn)
+    B, P = 3, 256
+    g = torch.Generator().manual_seed(8)
+    xyz = (torch.rand(B, P, 3, generator=g) * 2 - 1).cuda()
+    gt = (xyz.norm(dim=2).reshape(-1, 1) - 0.5).clamp(-0.1, 0.1)
+    enc_w = (torch.randn(16, 256, generator=g) * 0.02).cuda()
+    codes = torch.randn(B, 16, generator=g).cuda()
+    loss = lambda o: torch.nn.functional.l1_loss(torch.clamp(o, -0.1, 0.1), gt, reduction="sum") / (B * P)
+    # oracle
+    p_ref = {k: v.clone().cuda().requires_grad_(True) for k, v in params.items()}
+    w_ref = enc_w.clone().requires_grad_(True)
+    z = codes @ w_ref
+    inp = torch.cat([z.repeat_interleave(P, 0), xyz.reshape(-1, 3)], 1)
+    out_ref = deepsdf.forward(p_ref, spec, inp)
+    loss(out_ref).backward()
+    # CUDA
+    w1 = enc_w.clone().requires_grad_(True)
+    for p in dec.parameters():
+        p.grad = None
+    out = dsdf_b200.decode_segments(dec, codes @ w1, xyz)
+    loss(out).backward()
+    assert (out - out_ref).abs().max().item() <= 2e-3
+    assert cos(w1.grad, w_ref.grad) >= 0.999
+    flat_ref = torch.cat([p_ref[k].grad.flatten() for k, _ in dec.named_parameters()])
+    flat = torch.cat([p.grad.flatten() for _, p in dec.named_parameters()])
+    assert cos(flat, flat_ref) >= 0.999
+    with pytest.raises(ValueError):
+        dsdf_b200.decode_segments(dec, codes @ w1, xyz[:, :100])
