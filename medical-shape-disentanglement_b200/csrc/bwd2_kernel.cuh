@@ -518,7 +518,7 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
     for (int i = 0; i < 6; ++i)
       *reinterpret_cast<float4*>(out + kPartDb + i * kHidden + 4 * rt) =
           make_float4(db[i][0], db[i][1], db[i][2], db[i][3]);
-    *reinterpret_cast<float4*>(out + kPartW8 + 4 * rt) = make_float4(dw8[0], dw8[1], dw8[2], dw8[3]);
+    // (the kPartW8 slot is written by the forward kernel: dW8 is accumulated there)
 #pragma unroll
     for (int i = 0; i < 2; ++i)
 #pragma unroll

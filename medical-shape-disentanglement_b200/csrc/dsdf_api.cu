@@ -59,10 +59,12 @@ struct dsdf_handle_s {
   WgSeg* wg2_segs = nullptr;
   int* wg2_seg_begin = nullptr;
   long long wg2_tiles = -1;
+  int wg2_with_l8 = -1;          // schedule currently holds a lin8 item (autograd entries) or not (fused step)
   int wg2_pairs = 0;
   int wg2_slots = 0;
   Wg2Layout wg2_layout{};
   int wg_ver = 2;                // DSDF_WG_VER=1: previous-generation wgrad kernel
+  int dw8_wgrad = 0;             // DSDF_DW8_WGRAD=1: dW8 as a wgrad item (previous split), for A/B timing
   int wg_quad = 1;               // DSDF_WG_QUAD=0: item-major schedule (every out-chunk pair re-reads X from HBM)
   ParamLayout pl{};
   const float* params_ptr = nullptr;   // caller's flat fp32 parameters at the last dsdf_set_weights
@@ -184,6 +186,7 @@ extern "C" int dsdf_create(const dsdf_config* cfg, dsdf_handle* out) {
   if (const char* e = getenv("DSDF_BWD_VER")) h->bwd_ver = atoi(e) == 1 ? 1 : 2;
   if (const char* e = getenv("DSDF_WG_VER")) h->wg_ver = atoi(e) == 1 ? 1 : 2;
   if (const char* e = getenv("DSDF_WG_QUAD")) h->wg_quad = atoi(e) != 0;
+  if (const char* e = getenv("DSDF_DW8_WGRAD")) h->dw8_wgrad = atoi(e) != 0;
   if (h->bwd_ver == 1) h->wg_ver = 1;   // the v1 backward computes dW8 itself
 #ifdef DSDF_ARCH_SIREN
   // the sine epilogues exist in the current-generation kernels only
@@ -579,11 +582,12 @@ static int build_wg_items(dsdf_handle h, long long tiles, cudaStream_t st) {
 
 // v2 wgrad schedule: items (layer 1..8, 256-row out chunk) x tiles, cut into equal-cost contiguous
 // ranges, one per CTA pair.  Cost per tile: 2 (N = 512) or 1 (lin4's x3 part, N = 256).
-static int build_wg2_schedule(dsdf_handle h, long long tiles, cudaStream_t st) {
-  if (h->wg2_tiles == tiles) return DSDF_OK;
+static int build_wg2_schedule(dsdf_handle h, long long tiles, cudaStream_t st, bool with_l8 = true) {
+  if (h->wg2_tiles == tiles && h->wg2_with_l8 == (int)with_l8) return DSDF_OK;
+  const int l_last = with_l8 ? 8 : 7;    // fused step: the forward epilogue accumulates dW8 itself
   struct Item { int layer, ocp, n_sub, cost; };
   std::vector<Item> items;
-  for (int l = 1; l <= 8; ++l) {
+  for (int l = 1; l <= l_last; ++l) {
     h->wg2_layout.item_base[l] = (int)items.size();
     const int n_ocp = (l == 3 || l == 8) ? 1 : 2;
     for (int ocp = 0; ocp < n_ocp; ++ocp) items.push_back({l, ocp, l == 4 ? 4 : 8, l == 4 ? 1 : 2});
@@ -602,14 +606,14 @@ static int build_wg2_schedule(dsdf_handle h, long long tiles, cudaStream_t st) {
     const int n_quads = n_pairs / 2;
     auto quad_cost = [](int l) { return (l == 4 || l == 3 || l == 8) ? 1 : 2; };   // quad-time per tile
     long long total = 0;
-    for (int l = 1; l <= 8; ++l) total += (long long)quad_cost(l) * tiles;
+    for (int l = 1; l <= l_last; ++l) total += (long long)quad_cost(l) * tiles;
     const long long target = (total + n_quads - 1) / n_quads;
     std::vector<std::vector<WgSeg>> per_pair(n_pairs);
     int l = 1;
     long long t0 = 0;
-    for (int q = 0; q < n_quads && l <= 8; ++q) {
+    for (int q = 0; q < n_quads && l <= l_last; ++q) {
       long long budget = target;
-      while (l <= 8 && budget > 0) {
+      while (l <= l_last && budget > 0) {
         const int c = quad_cost(l);
         long long take = (budget + c - 1) / c;
         if (take > tiles - t0) take = tiles - t0;
@@ -630,7 +634,7 @@ static int build_wg2_schedule(dsdf_handle h, long long tiles, cudaStream_t st) {
         if (t0 == tiles) { ++l; t0 = 0; }
       }
     }
-    if (l <= 8) DSDF_FAIL(h, DSDF_EINVAL, "internal: wgrad schedule did not cover all layers");
+    if (l <= l_last) DSDF_FAIL(h, DSDF_EINVAL, "internal: wgrad schedule did not cover all layers");
     // slots: contiguous per item (layer, ocp), in item order
     std::vector<int> next_slot(items.size(), 0), base_slot(items.size(), 0), cnt(items.size(), 0);
     for (auto& v : per_pair) for (WgSeg& sg : v) ++cnt[h->wg2_layout.item_base[sg.layer] + sg.ocp];
@@ -690,6 +694,7 @@ static int build_wg2_schedule(dsdf_handle h, long long tiles, cudaStream_t st) {
   h->wg2_pairs = n_pairs;
   h->wg2_slots = (int)segs.size();
   h->wg2_tiles = tiles;
+  h->wg2_with_l8 = (int)with_l8;
   return DSDF_OK;
 }
 
@@ -717,7 +722,7 @@ static int launch_wgrad2(dsdf_handle h, const uint8_t* xstash, const uint8_t* dy
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   CU(h, cudaLaunchKernelEx(&cfg, k_wgrad2, w2));
-  k_reduce_wgrad2<<<dim3(kHidden, 8), kHidden, 0, st>>>(partials, h->wg2_layout, dweff);
+  k_reduce_wgrad2<<<dim3(kHidden, h->wg2_with_l8 ? 8 : 7), kHidden, 0, st>>>(partials, h->wg2_layout, dweff);
   return DSDF_OK;
 }
 
@@ -777,7 +782,10 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   if ((size_t)(base - (uint8_t*)workspace) + w.total > workspace_bytes)
     DSDF_FAIL(h, DSDF_ENOMEM, "workspace too small: need %zu bytes, have %zu", w.total + 1024,
               workspace_bytes);
-  int rc = h->wg_ver == 1 ? build_wg_items(h, tiles, st) : build_wg2_schedule(h, tiles, st);
+  // current-generation kernels: the forward epilogue accumulates dW8 = g^T X8 itself (no X8 stash, no lin8
+  // wgrad item); DSDF_DW8_WGRAD=1 keeps the previous split for A/B timing
+  const bool dw8_fwd = h->wg_ver == 2 && !h->fwd_v1 && h->fwd_ver == 3 && !h->dw8_wgrad;
+  int rc = h->wg_ver == 1 ? build_wg_items(h, tiles, st) : build_wg2_schedule(h, tiles, st, !dw8_fwd);
   if (rc != DSDF_OK) return rc;
 
   const float inv_n = 1.0f / (float)n_total;
@@ -808,7 +816,21 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   fa.dbg = h->dbg;
   fa.scene_e = w.scene_e;
   fa.relu_mask = w.relu_mask;
-  fa.g_img = h->wg_ver == 2 ? w.g_img : nullptr;
+  fa.g_img = (h->wg_ver == 2 && !dw8_fwd) ? w.g_img : nullptr;
+  if (dw8_fwd) {
+    fa.dw8_partials = w.cta_partials + kPartW8;
+    fa.dw8_stride = kCtaPartialFloats;
+  }
+  const bool pair_ok = rows_per_seg % (2 * kTileM) == 0;
+  // CTAs of the forward launch (launch_fwd3_cg): one dW8 partial each
+  int fwd_ctas = 0;
+  {
+    const int cg = (pair_ok && h->fwd_cg == 2 && tiles >= 2) ? 2 : 1;
+    long long g = tiles < h->num_sms ? tiles : h->num_sms;
+    g = (g / cg) * cg;
+    if (g < cg) g = cg;
+    fwd_ctas = (int)g;
+  }
   if (h->fwd_v1) {
     k_forward<MODE_TABLE, true><<<grid, kFwdThreads, kFwdSmemBytes, st>>>(fa);
   } else {
@@ -816,9 +838,9 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
                                                           (const long long*)seg_ids, w.scene_e);
     fa.drop = h->drop;
     if (h->drop.layers != 0)
-      CU(h, (launch_fwd<MODE_TABLE, true, true, true>(h, fa, st, rows_per_seg % (2 * kTileM) == 0)));
+      CU(h, (launch_fwd<MODE_TABLE, true, true, true>(h, fa, st, pair_ok)));
     else
-      CU(h, (launch_fwd<MODE_TABLE, true, true>(h, fa, st, rows_per_seg % (2 * kTileM) == 0)));
+      CU(h, (launch_fwd<MODE_TABLE, true, true>(h, fa, st, pair_ok)));
   }
   if (prof) prof_mark(h, st);
 
@@ -890,7 +912,7 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
     cfg.numAttrs = 1;
     CU(h, cudaLaunchKernelEx(&cfg, k_wgrad2, w2));
     if (prof) prof_mark(h, st);
-    k_reduce_wgrad2<<<dim3(kHidden, 8), kHidden, 0, st>>>(w.wg_partials, h->wg2_layout, w.dweff);
+    k_reduce_wgrad2<<<dim3(kHidden, h->wg2_with_l8 ? 8 : 7), kHidden, 0, st>>>(w.wg_partials, h->wg2_layout, w.dweff);
   }
 
   // ---- segmented (scene-contiguous) reductions: latent grads, latent columns of dW0/dW4, biases
@@ -904,7 +926,8 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   k_dw_latent<<<dim3(kHidden, 2), kLatent, 0, st>>>(w.seg_sum, table, (const long long*)seg_ids,
                                                     (int)n_seg, w.dweff);
   k_reduce_cta<<<16, kHidden, 0, st>>>(w.cta_partials, (int)bwd_grid, w.seg_sum, (int)n_seg,
-                                      w.tile_partials, tiles, h->pl, grads, w.dweff, h->wg_ver == 1 ? 1 : 0);
+                                      w.tile_partials, tiles, h->pl, grads, w.dweff,
+                                      h->wg_ver == 1 ? (int)bwd_grid : (dw8_fwd ? fwd_ctas : 0));
   k_param_grads<<<(kScaleElems * 32 + 255) / 256, 256, 0, st>>>(w.dweff, params, h->pl, h->scale,
                                                                 h->inv_norm, grads);
   k_loss<<<1, 1024, 0, st>>>(w.tile_partials, tiles, inv_n, w.seg_norm, (int)n_seg, reg_coef, loss_out);

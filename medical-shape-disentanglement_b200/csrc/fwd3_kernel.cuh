@@ -47,7 +47,8 @@ struct F3 {
   static constexpr uint32_t kAuxPart = 528;              // 128 floats
   static constexpr uint32_t kAuxRed = 1040;              // 16 floats
   static constexpr uint32_t kAuxW8 = 1104;               // 512 floats
-  static constexpr uint32_t kSmemBytes = kSmemAux + kAuxW8 + 2048;
+  static constexpr uint32_t kAuxG = kAuxW8 + 2048;       // 128 floats: dL/ds of the tile's rows
+  static constexpr uint32_t kSmemBytes = kSmemAux + kAuxG + 512;
 };
 constexpr int kF3Threads = 384;
 
@@ -144,6 +145,7 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
   float* part = reinterpret_cast<float*>(smem + C::kSmemAux + C::kAuxPart);
   float* red = reinterpret_cast<float*>(smem + C::kSmemAux + C::kAuxRed);
   float* w8s = reinterpret_cast<float*>(smem + C::kSmemAux + C::kAuxW8);
+  float* gsm = reinterpret_cast<float*>(smem + C::kSmemAux + C::kAuxG);
 
   if ((s_base & 1023u) != 0) __trap();
   const uint32_t crank = CG > 1 ? cluster_ctarank() : 0u;
@@ -350,7 +352,9 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
             if (half == 1 && l == 3 && FOLD) break;          // lin3 has 256 outputs (x3 part)
             if (half == 0) { mbar_wait(s_lo, par_lo); par_lo ^= 1; }
             else { mbar_wait(s_hi, par_hi); par_hi ^= 1; }
-            if (tile_valid && a.xstash) {     // frozen-decoder callers pass no stash (no wgrad)
+            // frozen-decoder callers pass no stash (no wgrad); X8 (slot 7) is consumed on-chip when the
+            // epilogue accumulates dW8 itself
+            if (tile_valid && a.xstash && !(l == 7 && a.dw8_partials)) {
 #pragma unroll 1
               for (int i = 0; i < 128; i += 8) {              // 4 SUBs = 4096 x 16 B = 128 x (32 lanes)
                 uint4 v[8];
@@ -385,6 +389,7 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
       if (TRAIN && lane == 0) mbar_arrive(bar);
     };
     long long dbg_d0 = 0, dbg_d1 = 0, dbg_rd = 0;
+    float dw8a = 0.f, dw8b = 0.f;           // dW8 columns 2t, 2t+1 (fused-loss TRAIN)
     const long long dbg_e0 = DSDF_DBG_ON(a) ? clock64() : 0;
     // generic-proxy writes of this warp -> visible to the (leader's) MMA, one arrive per warp
     // (each SM's tensor core reads its OWN A tile, so cta-scope release + the proxy fence order
@@ -610,6 +615,7 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
           const float inside = (th >= -d && th <= d) ? 1.f : 0.f;
           float g = valid ? sgn * inside * dth * a.inv_n_total : 0.f;
           if (in_range) a.gout[row] = g;
+          gsm[r] = g;
           if (tile_valid && a.g_img) {
             const __nv_bfloat16 gh = __float2bfloat16_rn(g);
             const __nv_bfloat16 gl = __float2bfloat16_rn(g - __bfloat162float(gh));
@@ -634,9 +640,31 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
           a.tile_partials[tile * 2] = (red[0] + red[2]) + (red[4] + red[6]);
           a.tile_partials[tile * 2 + 1] = (red[1] + red[3]) + (red[5] + red[7]);
         }
+        if (a.dw8_partials) {
+          // dW8[c] += sum_r g[r] X8[r, c] straight from the A tile (train_deep_sdf.py:731 for lin8.weight):
+          // thread t owns columns 2t, 2t+1; a warp reads one 128-byte swizzled row per step (conflict-free)
+          const uint32_t c0 = (uint32_t)(2 * t) & 63u;
+          const uint32_t sub = a_base + (uint32_t)(t >> 5) * kSubBytes;
+          if (tile_valid) {
+#pragma unroll 8
+            for (uint32_t rr = 0; rr < (uint32_t)kTileM; ++rr) {
+              uint32_t wv;
+              asm volatile("ld.shared.b32 %0, [%1];" : "=r"(wv) : "r"(sub + sub_off(rr, c0)));
+              const float gr = gsm[rr];
+              dw8a = fmaf(gr, __uint_as_float(wv << 16), dw8a);
+              dw8b = fmaf(gr, __uint_as_float(wv & 0xFFFF0000u), dw8b);
+            }
+          }
+          named_bar_sync(1, kActThreads);   // the next tile rewrites gsm and the A tile
+        }
       } else {
         named_bar_sync(1, kActThreads);   // part[] is rewritten by the next tile
       }
+    }
+    if (TRAIN && a.fused_loss && a.dw8_partials) {
+      float* o = a.dw8_partials + (size_t)blockIdx.x * a.dw8_stride;
+      o[2 * t] = dw8a;
+      o[2 * t + 1] = dw8b;
     }
     if (DSDF_DBG_ON(a) && t == 0) {
       unsigned long long* d = a.dbg + (size_t)blockIdx.x * kDbgSlots;

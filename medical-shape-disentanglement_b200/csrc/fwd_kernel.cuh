@@ -58,6 +58,11 @@ struct FwdArgs {
   long long valid_per_seg;
   // v3 TRAIN + DROP: training-mode dropout after the ReLUs (deep_sdf_decoder.py:103-104), philox.cuh
   DropoutArgs drop;
+  // v3 TRAIN + fused loss: dW8 = sum_r g_r X8[r,:] accumulated by the forward epilogue itself (X8 is in the
+  // smem A tile, g is known there), one 512-float partial per CTA at dw8_partials[blockIdx.x * dw8_stride];
+  // non-null => X8 is not stashed and the wgrad kernel has no lin8 item.
+  float* dw8_partials;
+  long long dw8_stride;
   // diagnostics (nullable): per-CTA cycle counters, see dsdf_debug_read
   unsigned long long* dbg;
 };

@@ -146,7 +146,8 @@ struct Wg2Layout {
   int slot_lo[16];
   int slot_hi[16];
 };
-// grid (512 rows o, 8 layers), 512 threads (i pad).  Fixed summation order -> deterministic.
+// grid (512 rows o, 8 layers; 7 when dW8 comes from the forward kernel), 512 threads (i pad).
+// Fixed summation order -> deterministic.
 __global__ void k_reduce_wgrad2(const float* __restrict__ partials, Wg2Layout wl,
                                 float* __restrict__ dweff) {
   const int l = blockIdx.y + 1, o = blockIdx.x, ip = threadIdx.x;
@@ -176,12 +177,12 @@ __global__ void k_reduce_wgrad2(const float* __restrict__ partials, Wg2Layout wl
 // ---- reducer-warp partials (per CTA) -> bias grads, dW8, xyz columns of dW0/dW4 -----------------
 // grid 16 jobs x 512 threads (column c); every job sums its partials in a fixed order (deterministic):
 //   0..5   db of lin {1,2,3,5,6,7}        6..11  xyz column e of dW{0,4}   (job - 6 = 3 i + e)
-//   12,13  db0 / db4 from the segment column sums      14  db8 = sum_rows g      15  dW8 (v1 backward only)
+//   12,13  db0 / db4 from the segment column sums      14  db8 = sum_rows g      15  dW8 (forward partials)
 __global__ void k_reduce_cta(const float* __restrict__ cta_partials, int n_cta,
                              const float* __restrict__ seg_sum, int n_seg,
                              const float* __restrict__ tile_partials, long long n_tiles,
                              ParamLayout pl, float* __restrict__ grads,
-                             float* __restrict__ dweff, int with_dw8) {
+                             float* __restrict__ dweff, int n_cta_dw8) {
   __shared__ float sh[16];
   const int c = threadIdx.x, job = blockIdx.x;
   if (job < 6) {
@@ -216,9 +217,10 @@ __global__ void k_reduce_cta(const float* __restrict__ cta_partials, int n_cta,
       for (int i = 0; i < 16; ++i) t += sh[i];
       grads[pl.b[8]] = t;
     }
-  } else if (with_dw8) {   // dW8 (v1 backward kernel only; the v2 path gets it from the wgrad kernel)
-    float s = 0.f;
-    for (int k = 0; k < n_cta; ++k) s += cta_partials[(size_t)k * kCtaPartialFloats + kPartW8 + c];
+  } else if (n_cta_dw8 > 0) {   // dW8 partials of the forward kernel's epilogue (or the v1 backward kernel);
+    float s = 0.f;              // 0: the wgrad kernel produced dW8 (autograd entries: g unknown in the forward)
+#pragma unroll 4
+    for (int k = 0; k < n_cta_dw8; ++k) s += cta_partials[(size_t)k * kCtaPartialFloats + kPartW8 + c];
     dweff[weff_off(8) + c] = s;
   }
 }
