@@ -190,8 +190,11 @@ class FusedTrainer:
                 "grad_norm": self.scratch[0]}
 
     # ---------------------------------------------------------------- checkpoint interchange
-    def optimizer_state_dict(self) -> dict:
-        """torch.optim.Adam-format state (param order: decoder.parameters(), then lat_vecs)."""
+    def optimizer_state_dict(self, epoch: int = 0) -> dict:
+        """torch.optim.Adam-format state (param order: decoder.parameters(), then lat_vecs), what the reference's
+        save_optimizer writes (train_deep_sdf.py:42-49); loads into a torch.optim.Adam built the reference's way
+        (:454-466) and back through load_optimizer_state_dict."""
+        c = self.cfg
         state = {}
         off = 0
         plist = list(self.decoder.parameters())
@@ -204,5 +207,39 @@ class FusedTrainer:
         state[len(plist)] = {"step": torch.tensor(float(self.step_count)),
                              "exp_avg": self.lat_exp_avg.clone(),
                              "exp_avg_sq": self.lat_exp_avg_sq.clone()}
-        groups = [{"params": list(range(len(plist)))}, {"params": [len(plist)]}]
+        common = {"betas": tuple(c.betas), "eps": c.eps, "weight_decay": 0, "amsgrad": False, "maximize": False,
+                  "foreach": None, "capturable": False, "differentiable": False, "fused": None,
+                  "decoupled_weight_decay": False}
+        groups = [dict(common, lr=self.lr(0, epoch), params=list(range(len(plist)))),
+                  dict(common, lr=self.lr(1, epoch), params=[len(plist)])]
         return {"state": state, "param_groups": groups}
+
+    def load_optimizer_state_dict(self, sd: dict) -> None:
+        """Resume (`--continue`, train_deep_sdf.py:469-493 -> load_optimizer :52-61): take the Adam moments and
+        step count from a torch.optim.Adam state_dict (ours or one the reference saved)."""
+        plist = list(self.decoder.parameters())
+        st = sd["state"]
+        if len(st) == 0:
+            self.exp_avg.zero_(); self.exp_avg_sq.zero_()
+            self.lat_exp_avg.zero_(); self.lat_exp_avg_sq.zero_()
+            self.step_count = 0
+            return
+        if len(st) != len(plist) + 1:
+            raise ValueError(f"optimizer state has {len(st)} entries, this decoder + lat_vecs need {len(plist) + 1}")
+        off = 0
+        for i, p in enumerate(plist):
+            n = p.numel()
+            if tuple(st[i]["exp_avg"].shape) != tuple(p.shape):
+                raise ValueError(f"optimizer state entry {i} has shape {tuple(st[i]['exp_avg'].shape)}, "
+                                 f"parameter has {tuple(p.shape)}")
+            self.exp_avg[off:off + n].copy_(st[i]["exp_avg"].reshape(-1))
+            self.exp_avg_sq[off:off + n].copy_(st[i]["exp_avg_sq"].reshape(-1))
+            off += n
+        lat = st[len(plist)]
+        if tuple(lat["exp_avg"].shape) != tuple(self.lat_exp_avg.shape):
+            raise ValueError("latent-code optimizer state does not match lat_vecs")
+        self.lat_exp_avg.copy_(lat["exp_avg"]); self.lat_exp_avg_sq.copy_(lat["exp_avg_sq"])
+        steps = {int(float(v["step"])) for v in st.values()}
+        if len(steps) != 1:
+            raise ValueError(f"per-parameter step counts differ ({sorted(steps)}): one shared count is supported")
+        self.step_count = steps.pop()

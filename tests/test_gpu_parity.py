@@ -355,3 +355,96 @@ def test_error_paths_through_the_c_abi():
         tr.forward_backward(data, torch.tensor([0, 1]).cuda(), 1)
     with pytest.raises(dsdf_b200.DsdfError):
         dec.decode_grid(torch.zeros(256, device="cuda"), 1)
+
+
+def _fresh_trainer(S, seed=0):
+    dec, _, _ = make(True, seed=seed)
+    lat = torch.randn(S, 256, generator=torch.Generator().manual_seed(5)) * 0.05
+    return dec, dsdf_b200.FusedTrainer(dec, S, dsdf_b200.StepConfig(code_bound=1.0, grad_clip=1.0), latents=lat)
+
+
+def test_checkpoint_resume_is_bit_exact():
+    """save_model / save_latent_vectors / save_optimizer then `--continue` (train_deep_sdf.py:32-79, 469-493):
+    3 steps + checkpoint + 3 steps in a NEW trainer must equal 6 uninterrupted steps bit for bit (the step has no
+    float atomics, so the run is deterministic and a resume cannot drift)."""
+    S, B, P = 8, 4, 256
+    data = synth.scene_samples(S, P, seed=2).cuda()
+    batches = [torch.randperm(S, generator=torch.Generator().manual_seed(i))[:B] for i in range(6)]
+    dec_a, tr_a = _fresh_trainer(S)
+    for ids in batches:
+        tr_a.step(data[ids], ids.cuda(), 7)
+    dec_b, tr_b = _fresh_trainer(S)
+    for ids in batches[:3]:
+        tr_b.step(data[ids], ids.cuda(), 7)
+    ckpt = {"model": {k: v.cpu().clone() for k, v in dec_b.state_dict().items()},
+            "latents": {k: v.cpu().clone() for k, v in tr_b.lat_vecs.state_dict().items()},
+            "optimizer": tr_b.optimizer_state_dict(epoch=7)}
+    ckpt["optimizer"]["state"] = {k: {n: t.cpu() for n, t in v.items()} for k, v in ckpt["optimizer"]["state"].items()}
+    dec_c, tr_c = _fresh_trainer(S, seed=123)                   # different init: everything must come from ckpt
+    dec_c.load_state_dict(ckpt["model"])
+    tr_c.lat_vecs.load_state_dict(ckpt["latents"])
+    tr_c.load_optimizer_state_dict(ckpt["optimizer"])
+    assert tr_c.step_count == 3
+    for ids in batches[3:]:
+        tr_c.step(data[ids], ids.cuda(), 7)
+    torch.cuda.synchronize()
+    for (k, a), (_, c) in zip(dec_a.state_dict().items(), dec_c.state_dict().items()):
+        assert torch.equal(a, c), k
+    assert torch.equal(tr_a.lat_vecs.weight.data, tr_c.lat_vecs.weight.data)
+    assert torch.equal(tr_a.exp_avg_sq, tr_c.exp_avg_sq)
+    with pytest.raises(ValueError):
+        bad = tr_b.optimizer_state_dict()
+        bad["state"].pop(0)
+        tr_c.load_optimizer_state_dict(bad)
+
+
+def test_optimizer_state_loads_into_torch_adam_and_steps_alike():
+    """The state we save is a torch.optim.Adam state_dict for the reference's optimizer_all (train_deep_sdf.py:454-466):
+    torch's Adam, loaded with it and fed our gradients, must make the same next step as dsdf_clip_adam."""
+    S, B, P = 6, 3, 128
+    data = synth.scene_samples(S, P, seed=4).cuda()
+    dec, tr = _fresh_trainer(S)
+    tr.cfg.grad_clip = None
+    ids = torch.tensor([0, 2, 5])
+    tr.step(data[ids], ids.cuda(), 3)
+    tr.step(data[ids], ids.cuda(), 3)
+    sd = tr.optimizer_state_dict(epoch=3)
+    twin = [p.detach().clone().requires_grad_(True) for p in dec.parameters()]
+    twin_lat = tr.lat_vecs.weight.detach().clone().requires_grad_(True)
+    opt = torch.optim.Adam([{"params": twin, "lr": 1.0}, {"params": [twin_lat], "lr": 1.0}])
+    opt.load_state_dict(sd)
+    assert opt.param_groups[0]["lr"] == tr.lr(0, 3) and opt.param_groups[1]["lr"] == tr.lr(1, 3)
+    ids2 = torch.tensor([1, 2, 4])
+    tr.forward_backward(data[ids2], ids2.cuda(), 3)            # fills tr.grads / tr.lat_grad at the current weights
+    off = 0
+    for p in twin:
+        p.grad = tr.grads[off:off + p.numel()].view(p.shape).clone()
+        off += p.numel()
+    twin_lat.grad = tr.lat_grad.clone()
+    opt.step()
+    tr.step(data[ids2], ids2.cuda(), 3)                        # same gradients again (deterministic), then our Adam
+    torch.cuda.synchronize()
+    for p, q in zip(dec.parameters(), twin):
+        torch.testing.assert_close(p.detach(), q.detach(), rtol=1e-5, atol=1e-7)
+    torch.testing.assert_close(tr.lat_vecs.weight.detach(), twin_lat.detach(), rtol=1e-5, atol=1e-7)
+
+
+def test_dataparallel_wrapper_is_a_pass_through():
+    """The reference wraps the decoder in nn.DataParallel and unwraps `.module` for checkpoints
+    (train_deep_sdf.py:352, 36; reconstruct.py:231-240: saved keys carry the `module.` prefix)."""
+    dec, spec, params = make(True, scale=1.5)
+    dp = torch.nn.DataParallel(dec, device_ids=[0])
+    x = torch.cat([torch.randn(300, 256) * 0.05, torch.rand(300, 3) * 2 - 1], 1).cuda()
+    dp.eval()
+    with torch.no_grad():
+        a = dp(x)
+        b = dec(x)
+    assert torch.equal(a, b)
+    sd = dp.state_dict()
+    assert all(k.startswith("module.lin") for k in sd)
+    dec2, _, _ = make(True, seed=9)
+    dp2 = torch.nn.DataParallel(dec2, device_ids=[0])
+    dp2.load_state_dict(sd)                                     # the reference's load path (reconstruct.py:238)
+    dp2.eval()
+    with torch.no_grad():
+        assert torch.equal(dp2(x), a)
