@@ -1,8 +1,8 @@
 """Grid decode of deep_sdf/mesh.create_mesh (reference deep_sdf/mesh.py:21-71) on the fused
 forward kernel: coordinates are generated in-kernel (bit-exact with the reference's fp32 torch
 expressions, including the true-division shear of mesh.py:46-47), the latent is read once per
-tile instead of expand+cat per chunk, and there is one D2H of N^3 floats at the end instead
-of one H2D + one D2H per 2^18-point chunk.
+tile instead of expand+cat per chunk, and the N^3 floats drain to pinned host memory slab by slab
+under the kernel instead of one H2D + one D2H per 2^18-point chunk.
 
 Marching cubes / PLY writing (mesh.py:96-165) stay on the host in the reference's own code
 (skimage / plyfile are not available in this image): `create_mesh_sdf` returns exactly the
@@ -28,9 +28,40 @@ def create_mesh_sdf(decoder: Decoder, latent_vec: torch.Tensor, N: int = 256,
     decoder.eval()
     dev = next(decoder.parameters()).device
     lat = latent_vec.to(dev)
-    out = decoder.decode_grid(lat, N)
-    out = out.view(N, N, N)
-    return out.cpu() if to_cpu else out
+    total = N ** 3
+    if not to_cpu:
+        return decoder.decode_grid(lat, N).view(N, N, N)
+    # Host result: decode in slabs and drain each finished slab to pinned host memory on a copy stream while the
+    # next slab computes, so the N^3 x 4 B read-back (67 MB at N = 256) hides under the kernel instead of
+    # following it.  The pinned block comes from torch's caching host allocator (no cudaHostAlloc after the first
+    # call) and is returned as an ordinary CPU tensor.
+    host = torch.empty(total, dtype=torch.float32, pin_memory=True)
+    buf = torch.empty(total, dtype=torch.float32, device=dev)
+    n_slabs = max(1, min(_GRID_SLABS, total // (1 << 20)))
+    cuts = [(total * i // n_slabs) // 128 * 128 for i in range(n_slabs)] + [total]
+    main = torch.cuda.current_stream(dev)
+    copy = _copy_stream(dev)
+    for lo, hi in zip(cuts[:-1], cuts[1:]):
+        decoder.decode_grid(lat, N, lo, hi, out=buf[lo:hi])
+        ready = torch.cuda.Event()
+        ready.record(main)
+        copy.wait_event(ready)
+        with torch.cuda.stream(copy):
+            host[lo:hi].copy_(buf[lo:hi], non_blocking=True)
+    buf.record_stream(copy)
+    copy.synchronize()
+    return host.view(N, N, N)
+
+
+_GRID_SLABS = 8
+_copy_streams = {}
+
+
+def _copy_stream(dev) -> "torch.cuda.Stream":
+    key = torch.device(dev).index if torch.device(dev).index is not None else torch.cuda.current_device()
+    if key not in _copy_streams:
+        _copy_streams[key] = torch.cuda.Stream(device=dev)
+    return _copy_streams[key]
 
 
 @torch.no_grad()
