@@ -9,6 +9,6 @@ from ._lib import DsdfError, LIB_PATH  # noqa: F401
 from .decoder import Decoder  # noqa: F401
 from .trainer import FusedTrainer, StepConfig  # noqa: F401
 from .mesh import create_mesh_sdf, decode_grid_sharded  # noqa: F401
-from .reconstruct import reconstruct, reconstruct_batch, draw_windows  # noqa: F401
+from .reconstruct import reconstruct, reconstruct_batch, draw_windows, plan_samples  # noqa: F401
 from . import data, siren  # noqa: F401,E402  (sample-file contract; SIREN decoder family)
 from .autograd_fn import decode_segments  # noqa: F401,E402

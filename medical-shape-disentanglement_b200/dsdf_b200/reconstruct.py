@@ -44,7 +44,7 @@ def draw_windows(pos_size: int, neg_size: int, num_samples: int, num_iterations:
     if neg_size <= half:
         raise NotImplementedError(
             f"shape has {neg_size} negative samples <= num_samples/2 = {half}: the reference falls back to "
-            "random index_select (data.py:123-125), which the fused window gather does not restate")
+            "random index_select (data.py:123-125); use plan_samples(), which lays the selected rows out as windows")
     if pos_size < half:
         raise ValueError(f"shape has {pos_size} positive samples < num_samples/2 = {half}")
     out = []
@@ -53,6 +53,30 @@ def draw_windows(pos_size: int, neg_size: int, num_samples: int, num_iterations:
         ns = rng.randint(0, neg_size - half)
         out.append((ps, ns))
     return out
+
+
+def plan_samples(pos: torch.Tensor, neg: torch.Tensor, num_samples: int, num_iterations: int, rng=random):
+    """Every iteration's sample of unpack_sdf_samples_from_ram (deep_sdf/data.py:112-134) as (neg_pool, windows)
+    for the window gather, consuming `rng` and torch's global CPU generator exactly as the reference loop does.
+    Usual case (neg_size > half): neg_pool is `neg` and both starts are random.randint draws.  Small-shape case
+    (:123-125, neg_size <= half): the reference draws `(torch.rand(half) * neg_size).long()` and index_selects;
+    the selected rows of all iterations are laid end to end (num_iterations * half * 16 B) so iteration e's
+    negatives are again a window, starting at e * half."""
+    half = int(num_samples / 2)
+    if neg.shape[0] > half:
+        return neg, draw_windows(pos.shape[0], neg.shape[0], num_samples, num_iterations, rng)
+    if pos.shape[0] < half:
+        raise ValueError(f"shape has {pos.shape[0]} positive samples < num_samples/2 = {half}")
+    if neg.shape[0] == 0:
+        raise ValueError("shape has no negative samples")
+    src = neg.detach().cpu()
+    wins, picked = [], []
+    for e in range(num_iterations):
+        ps = rng.randint(0, pos.shape[0] - half)
+        picked.append(torch.index_select(src, 0, (torch.rand(half) * src.shape[0]).long()))
+        wins.append((ps, e * half))
+    pool = torch.cat(picked, 0) if picked else src[:0]
+    return pool, wins
 
 
 def _reg_args(l2reg, code_reg_lambda, code_reg_type):
@@ -145,7 +169,7 @@ def reconstruct(decoder, num_iterations, latent_size, test_sdf, stat, clamp_dist
     else:
         latent = torch.normal(stat[0].detach(), stat[1].detach()).to(device)
     pos, neg = test_sdf[0], test_sdf[1]
-    wins = draw_windows(pos.shape[0], neg.shape[0], num_samples, num_iterations, random)
+    neg, wins = plan_samples(pos, neg, num_samples, num_iterations, random)
     hist, lat = reconstruct_batch(
         decoder, num_iterations, [(pos, neg)], latent.reshape(1, latent_size),
         torch.tensor(wins, dtype=torch.int64).reshape(num_iterations, 1, 2), clamp_dist,

@@ -30,6 +30,23 @@ def draw_windows(pos_size: int, neg_size: int, num_samples: int, iters: int,
     return out
 
 
+def draw_plan(pos: torch.Tensor, neg: torch.Tensor, num_samples: int, iters: int, rng=random):
+    """data.py:112-134 including the small-shape branch (:123-125): when neg_size <= half the reference draws
+    `(torch.rand(half) * neg_size).long()` from torch's global CPU generator and index_selects.  Returns
+    (neg_pool, windows) such that window(pos, neg_pool, num_samples, windows[e]) is iteration e's sample: in the
+    small-shape branch neg_pool is the concatenation of every iteration's selected rows."""
+    half = int(num_samples / 2)
+    if neg.shape[0] > half:
+        return neg, draw_windows(pos.shape[0], neg.shape[0], num_samples, iters, rng)
+    wins, picked = [], []
+    for e in range(iters):
+        ps = rng.randint(0, pos.shape[0] - half)                         # :120
+        random_neg = (torch.rand(half) * neg.shape[0]).long()            # :124
+        picked.append(torch.index_select(neg, 0, random_neg))            # :125
+        wins.append((ps, e * half))
+    return torch.cat(picked, 0), wins
+
+
 def window(pos: torch.Tensor, neg: torch.Tensor, num_samples: int, w: Tuple[int, int]):
     half = int(num_samples / 2)
     return torch.cat([pos[w[0]:w[0] + half], neg[w[1]:w[1] + half]], 0)

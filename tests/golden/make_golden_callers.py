@@ -109,5 +109,34 @@ def main():
     print("losses a:", out["recon_a/losses"][:3], "...", out["recon_a/losses"][-1])
 
 
+def main_fallback():
+    """The sampler's small-shape branch (data.py:123-125: neg_size <= half -> torch.rand + index_select) and a
+    reconstruct() run that takes it every iteration; written to callers_fallback_ref.npz."""
+    install_stubs()
+    import reconstruct as ref_reconstruct
+    import deep_sdf.data as ref_data
+    from dsdf_b200 import synth
+    dec = make_decoder()
+    out = {}
+    d = synth.scene_samples(1, 4096, seed=9)[0]
+    pos, neg = d[:2048].contiguous(), d[2048:2348].contiguous()          # 300 negatives < half = 400
+    random.seed(3)
+    torch.manual_seed(3)
+    for k in range(3):
+        out[f"sample_{k}"] = ref_data.unpack_sdf_samples_from_ram([pos, neg], 800).numpy()
+    random.seed(0)
+    torch.manual_seed(0)
+    losses, latent = ref_reconstruct.reconstruct(dec, 20, 256, [pos, neg], 0.01, 0.1, num_samples=800, lr=5e-3,
+                                                 return_loss_hist=True, l2reg=True)
+    out["recon_c/losses"] = np.array([float(x) for x in losses], dtype=np.float64)
+    out["recon_c/latent"] = latent.detach().numpy()
+    np.savez_compressed(os.path.join(HERE, "callers_fallback_ref.npz"), **out)
+    print({k: v.shape for k, v in out.items()})
+    print("losses c:", out["recon_c/losses"][:3], "...", out["recon_c/losses"][-1])
+
+
 if __name__ == "__main__":
-    main()
+    if "--fallback" in sys.argv:
+        main_fallback()
+    else:
+        main()

@@ -109,7 +109,7 @@ def test_reference_signature_consumes_the_same_random_streams():
 def test_error_paths():
     dec, _, _ = make()
     pos, neg = shape(1, n=1024)
-    with pytest.raises(NotImplementedError):       # neg_size <= half: reference falls back to index_select
+    with pytest.raises(NotImplementedError):       # neg_size <= half is plan_samples' business, not draw_windows'
         dsdf_b200.draw_windows(512, 256, 512, 1)
     with pytest.raises(ValueError):
         dsdf_b200.reconstruct_batch(dec, 1, [(pos, neg)], torch.zeros(1, 256), torch.zeros(1, 1, 2), 0.1, num_samples=301)
@@ -150,3 +150,32 @@ def test_reconstruct_and_create_mesh_match_the_executed_reference_golden():
     sdf = dsdf_b200.create_mesh_sdf(dec, lat, N=24)
     assert sdf.shape == (24, 24, 24)
     assert np.abs(sdf.numpy() - g["mesh/sdf24"]).max() <= 2e-3
+
+
+def test_small_shape_sampler_branch_follows_the_executed_reference():
+    """A shape with 300 negatives < num_samples/2: the reference index_selects random negatives every iteration
+    (data.py:123-125).  plan_samples lays them out as windows; losses must follow the executed reference run
+    (tests/golden/callers_fallback_ref.npz) within 1 %."""
+    from common import golden
+    g = golden("callers_fallback_ref.npz")
+    torch.manual_seed(0)
+    dec = dsdf_b200.Decoder(256, norm_layers=list(range(8)), **KW)
+    sd = dec.state_dict()
+    for l in range(8):
+        sd[f"lin{l}.weight_g"] = sd[f"lin{l}.weight_g"] * 1.5
+    dec.load_state_dict(sd)
+    dec = dec.cuda()
+    d = synth.scene_samples(1, 4096, seed=9)[0]
+    pos, neg = d[:2048].contiguous(), d[2048:2348].contiguous()
+    random.seed(0); torch.manual_seed(0)
+    lat0 = torch.ones(1, 256).normal_(mean=0, std=0.01)
+    pool, wins = dsdf_b200.plan_samples(pos, neg, 800, 20, random)
+    hist, lat = dsdf_b200.reconstruct_batch(dec, 20, [(pos, pool)], lat0, torch.tensor(wins).view(20, 1, 2), 0.1,
+                                            num_samples=800, lr=5e-3, l2reg=True)
+    np.testing.assert_allclose(hist[:, 0].cpu().numpy(), g["recon_c/losses"], rtol=1e-2)
+    assert cos(lat.cpu() - lat0, torch.from_numpy(g["recon_c/latent"]) - lat0) >= 0.98
+    # and through the reference-signature entry (draws its own latent on the device): runs, finite, optimises
+    random.seed(0); torch.manual_seed(0)
+    losses, latent = dsdf_b200.reconstruct(dec, 20, 256, [pos, neg], 0.01, 0.1, num_samples=800, lr=5e-3, l2reg=True,
+                                           return_loss_hist=True)
+    assert len(losses) == 20 and np.isfinite(losses).all() and losses[-1] < losses[0]

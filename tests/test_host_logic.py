@@ -154,3 +154,31 @@ def test_sample_file_contract_matches_reference_data_module(tmp_path):
         torch.manual_seed(5); mine = D.unpack_sdf_samples(f, 64)
         assert torch.equal(ref, mine)
         assert torch.equal(R.remove_nans(pos_n), D.remove_nans(pos_n))
+
+
+def test_small_shape_sampler_branch_is_laid_out_as_windows():
+    """plan_samples (host side of dsdf_reconstruct) and data.unpack_sdf_samples_from_ram on a shape with fewer
+    negatives than num_samples/2: bit-equal rows to the executed reference (callers_fallback_ref.npz)."""
+    import random
+    import numpy as np
+    import torch
+    from common import golden
+    import dsdf_b200
+    from dsdf_b200 import data as D, synth
+    g = golden("callers_fallback_ref.npz")
+    d = synth.scene_samples(1, 4096, seed=9)[0]
+    pos, neg = d[:2048].contiguous(), d[2048:2348].contiguous()
+    random.seed(3); torch.manual_seed(3)
+    for k in range(3):
+        np.testing.assert_array_equal(D.unpack_sdf_samples_from_ram([pos, neg], 800).numpy(), g[f"sample_{k}"])
+    random.seed(3); torch.manual_seed(3)
+    pool, wins = dsdf_b200.plan_samples(pos, neg, 800, 3, random)
+    assert pool.shape == (1200, 4) and [w[1] for w in wins] == [0, 400, 800]
+    for k in range(3):
+        got = torch.cat([pos[wins[k][0]:wins[k][0] + 400], pool[wins[k][1]:wins[k][1] + 400]], 0)
+        np.testing.assert_array_equal(got.numpy(), g[f"sample_{k}"])
+    # usual case: the pool is the shape's own negatives and the draws are draw_windows'
+    random.seed(5)
+    pool2, wins2 = dsdf_b200.plan_samples(pos, d[2048:], 800, 4, random)
+    random.seed(5)
+    assert pool2 is not neg and pool2.shape[0] == 2048 and wins2 == dsdf_b200.draw_windows(2048, 2048, 800, 4, random)

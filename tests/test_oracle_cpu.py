@@ -262,3 +262,22 @@ def test_oracle_callers_match_the_executed_reference():
     coords = torch.from_numpy(mesh_grid.grid_coords_closed_form(24))
     sdf = deepsdf.forward(p, spec, torch.cat([lat.expand(24 ** 3, -1), coords], 1)).reshape(24, 24, 24)
     np.testing.assert_allclose(sdf.numpy(), g["mesh/sdf24"], atol=2e-6)
+
+
+def test_oracle_small_shape_sampler_branch_matches_the_executed_reference():
+    """callers_fallback_ref.npz: the reference's unpack_sdf_samples_from_ram / reconstruct.reconstruct RUN on a shape
+    with 300 negatives < num_samples/2 = 400 (data.py:123-125: torch.rand + index_select every iteration)."""
+    _, spec, p, pos, neg, random = _callers_setup()
+    g = golden("callers_fallback_ref.npz")
+    neg = neg[:300].contiguous()
+    random.seed(3); torch.manual_seed(3)
+    pool, wins = orec.draw_plan(pos, neg, 800, 3, random)
+    assert pool.shape == (1200, 4)
+    for k in range(3):
+        np.testing.assert_array_equal(orec.window(pos, pool, 800, wins[k]).numpy(), g[f"sample_{k}"])
+    random.seed(0); torch.manual_seed(0)
+    lat0 = torch.ones(1, 256).normal_(mean=0, std=0.01)
+    pool, wins = orec.draw_plan(pos, neg, 800, 20, random)
+    losses, lat = orec.reconstruct(p, spec, 20, pos, pool, wins, lat0, 0.1, num_samples=800, lr=5e-3, l2reg=True)
+    np.testing.assert_allclose(np.array(losses), g["recon_c/losses"], rtol=2e-5, atol=1e-7)
+    np.testing.assert_allclose(lat.numpy(), g["recon_c/latent"], atol=2e-5)
