@@ -448,3 +448,36 @@ def test_dataparallel_wrapper_is_a_pass_through():
     dp2.eval()
     with torch.no_grad():
         assert torch.equal(dp2(x), a)
+
+
+@pytest.mark.parametrize("env", [
+    {"DSDF_DW8_WGRAD": "1"},            # dW8 as a wgrad item instead of the forward epilogue
+    {"DSDF_WG_QUAD": "0"},              # wgrad: one CTA pair per range instead of the side-by-side quad walk
+    {"DSDF_FWD_CG": "1"},               # forward without CTA pairs
+    {"DSDF_FWD_VER": "2"},              # previous-generation forward
+    {"DSDF_WG_VER": "1"},               # previous-generation wgrad
+    {"DSDF_BWD_VER": "1"},              # previous-generation backward (+ wgrad)
+    {"DSDF_FWD_V1": "1"},               # first-generation forward
+])
+def test_ab_kernel_generations_agree_with_the_shipping_path(env, monkeypatch):
+    """The library keeps earlier kernel generations selectable by environment variable (read at dsdf_create) for A/B
+    timing; each must compute the same step as the default path (different summation orders, so not bit-equal)."""
+    S, B, P = 6, 4, 512
+    data = synth.scene_samples(S, P, seed=3).cuda()
+    ids = torch.tensor([0, 2, 3, 5])
+
+    def run():
+        dec, tr = _fresh_trainer(S)
+        pred = tr.forward_backward(data[ids], ids.cuda(), 40).clone()
+        torch.cuda.synchronize()
+        return pred, tr.grads.clone(), tr.lat_grad.clone(), tr.loss_buf[:2].clone()
+
+    p0, g0, l0, s0 = run()
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    p1, g1, l1, s1 = run()
+    assert (p0 - p1).abs().max().item() <= 2e-4          # a tenth of the SDF tolerance (v1 has no hi/lo xyz split)
+    torch.testing.assert_close(s1, s0, rtol=1e-4, atol=1e-9)
+    assert cos(g1, g0) >= 0.9999
+    assert cos(l1, l0) >= 0.9999
+    assert torch.equal(l1 != 0, l0 != 0)
