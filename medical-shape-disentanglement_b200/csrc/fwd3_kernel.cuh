@@ -141,6 +141,9 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
   uint64_t* s_lo = bars + 40;            // TRAIN: epilogue -> stash warp: A SUB 0..3 written
   uint64_t* s_hi = bars + 41;            //        epilogue -> stash warp: A SUB 4..7 written
   uint64_t* s_done = bars + 42;          //        stash warp -> epilogue: A tile copied to HBM
+  uint64_t* a_sub = bars + 44;           // [3] epilogue -> MMA at a layer boundary: A SUB 1 / 2 / 3 written
+                                         // (a_lo then only means SUB 0: the MMAs of the next layer start
+                                         //  after 16 KB of A stores instead of 64 KB)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + C::kSmemAux + C::kAuxTmem);
   float* part = reinterpret_cast<float*>(smem + C::kSmemAux + C::kAuxPart);
   float* red = reinterpret_cast<float*>(smem + C::kSmemAux + C::kAuxRed);
@@ -164,6 +167,7 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
     }
     mbar_init(a_lo, 8 * CG);             // one elected arrive per epilogue warp of every CTA
     mbar_init(a_hi, 8 * CG);
+    for (int i = 0; i < 3; ++i) mbar_init(&a_sub[i], 4 * CG);   // the 4 warps that own the SUB's columns
     mbar_init(s_lo, 8);
     mbar_init(s_hi, 8);
     mbar_init(s_done, 1);
@@ -188,6 +192,7 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
   const uint32_t e_full_c = CG > 1 ? mapa_u32(smem_u32(e_full), 0) : smem_u32(e_full);
   const uint32_t a_lo_c = CG > 1 ? mapa_u32(smem_u32(a_lo), 0) : smem_u32(a_lo);
   const uint32_t a_hi_c = CG > 1 ? mapa_u32(smem_u32(a_hi), 0) : smem_u32(a_hi);
+  const uint32_t a_sub_c = CG > 1 ? mapa_u32(smem_u32(a_sub), 0) : smem_u32(a_sub);
 
   if (warp == 0) {
     // ===================== weight producer =====================
@@ -267,8 +272,8 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
       const uint64_t a_desc0 = umma_smem_desc(s_base + C::kSmemA, 16, 1024);
       const uint64_t b_desc0 = umma_smem_desc_ns(s_base + C::kSmemRing, 128, 256);
       const uint64_t eb_desc0 = umma_smem_desc_ns(s_base + C::kSmemERing, 128, 256);
-      uint32_t ph = 0, es = 0, eph = 0, par_lo = 0, par_hi = 0;
-      long long dbg_wf = 0, dbg_wl = 0, dbg_wh = 0, dbg_we = 0;
+      uint32_t ph = 0, es = 0, eph = 0, par_lo = 0, par_hi = 0, par_sub = 0;
+      long long dbg_wf = 0, dbg_wl = 0, dbg_wh = 0, dbg_we = 0, dbg_first = 0;
       const long long dbg_t0 = DSDF_DBG_ON(a) ? clock64() : 0;
       auto timed_wait = [&](uint64_t* bar, uint32_t par, long long& acc) {
         if (DSDF_DBG_ON(a)) {
@@ -299,6 +304,7 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
             timed_wait(&e_full[es], eph, dbg_we);
             tc_fence_after();
             mma(d_addr, ea_desc, eb_desc0 + (uint64_t)(es * (kSlice >> 4)), 0u);
+            if (DSDF_DBG_ON(a) && h == 0 && l >= 1) dbg_first += clock64();   // first MMA of layer l issued
             commit(&e_empty[es]);
             es ^= 1;
             eph ^= (es == 0);
@@ -313,6 +319,14 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
               const uint64_t a_desc = a_desc0 + (uint64_t)((g * (kRing / 4) * kSubBytes) >> 4);
 #pragma unroll
               for (int u = 0; u < kRing; ++u) {
+                if ((u & 3) == 0 && h == 0 && l >= 1) {
+                  // first K-step of an A SUB the epilogue wrote at the layer boundary (SUB 0 = a_lo)
+                  const int sub = g * (kRing / 4) + (u >> 2);
+                  if (sub >= 1 && sub <= 3) {
+                    timed_wait(&a_sub[sub - 1], par_sub, dbg_wl);
+                    tc_fence_after();
+                  }
+                }
                 timed_wait(&full[u], ph, dbg_wf);
                 tc_fence_after();
                 mma(d_addr, a_desc + (uint64_t)(((u >> 2) * kSubBytes + (u & 3) * 32) >> 4),
@@ -323,11 +337,12 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
             }
             commit(&d_done[h]);
           }
+          if (l >= 1) par_sub ^= 1;
         }
       }
       if (DSDF_DBG_ON(a)) {
         unsigned long long* d = a.dbg + (size_t)blockIdx.x * kDbgSlots;
-        d[0] = clock64() - dbg_t0; d[1] = dbg_wf; d[2] = dbg_wl; d[3] = dbg_wh; d[8] = dbg_we;
+        d[0] = clock64() - dbg_t0; d[1] = dbg_wf; d[2] = dbg_wl; d[3] = dbg_wh; d[8] = dbg_we; d[11] = dbg_first;
       }
     }
   } else if (warp == 3) {
@@ -388,7 +403,7 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
     auto stash_ready = [&](uint64_t* bar) {       // after publish(): this warp's A stores are done
       if (TRAIN && lane == 0) mbar_arrive(bar);
     };
-    long long dbg_d0 = 0, dbg_d1 = 0, dbg_rd = 0;
+    long long dbg_d0 = 0, dbg_d1 = 0, dbg_rd = 0, dbg_free = 0, dbg_st = 0, dbg_h1 = 0;
     float dw8a = 0.f, dw8b = 0.f;           // dW8 columns 2t, 2t+1 (fused-loss TRAIN)
     const long long dbg_e0 = DSDF_DBG_ON(a) ? clock64() : 0;
     // generic-proxy writes of this warp -> visible to the (leader's) MMA, one arrive per warp
@@ -470,17 +485,36 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
           par_d1 ^= 1;
           tc_fence_after();
         }
+        const long long c_free = DSDF_DBG_ON(a) ? clock64() : 0;   // tensor pipe idle from here (layer l retired)
+        if (DSDF_DBG_ON(a)) dbg_free += c_free;
         if (TRAIN) {                        // ... and the stash warp has copied the old A tile
           const long long c0 = DSDF_DBG_ON(a) ? clock64() : 0;
           mbar_wait(s_done, par_s);
           par_s ^= 1;
           if (DSDF_DBG_ON(a)) dbg_rd += clock64() - c0;
         }
-#pragma unroll
-        for (int c = 0; c < 4; ++c) store_chunk32(a_base, r, (uint32_t)(j * 128 + c * 32), held + 16 * c);
+        // SUB by SUB, so the next layer's first K-steps start after the first 16 KB are in place;
+        // warps 4..7 own SUB 0,1 (columns 0..127), warps 8..11 own SUB 2,3
         tc_fence_before();
-        publish(a_lo_c);
+        if (j == 0) {
+          store_chunk32(a_base, r, 0u, held);
+          store_chunk32(a_base, r, 32u, held + 16);
+          publish(a_lo_c);
+          store_chunk32(a_base, r, 64u, held + 32);
+          store_chunk32(a_base, r, 96u, held + 48);
+          publish(a_sub_c);
+        } else {
+          publish(a_lo_c);                  // this warp's h0 columns left TMEM long ago; SUB 0 is not its business
+          store_chunk32(a_base, r, 128u, held);
+          store_chunk32(a_base, r, 160u, held + 16);
+          publish(a_sub_c + 8);
+          store_chunk32(a_base, r, 192u, held + 32);
+          store_chunk32(a_base, r, 224u, held + 48);
+          publish(a_sub_c + 16);
+        }
         stash_ready(s_lo);
+        const long long c_pub = DSDF_DBG_ON(a) ? clock64() : 0;
+        if (DSDF_DBG_ON(a)) dbg_st += c_pub - c_free;
         // ---- half 1: straight from TMEM into SUB 4..7
         if (has_h1) {
 #pragma unroll
@@ -494,6 +528,7 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
           tc_fence_before();
           if (f2_in_hi<FOLD>(l + 1)) publish(a_hi_c); else __syncwarp();
           stash_ready(s_hi);
+          if (DSDF_DBG_ON(a)) dbg_h1 += clock64() - c_pub;
         } else if (!FOLD) {
           // skip connection: latent -> SUB 4..7 (reference cat order [x3 | latent | xyz])
           gather_latent<MODE>(a, row0, a_base + 4 * kSubBytes, t);
@@ -669,6 +704,7 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
     if (DSDF_DBG_ON(a) && t == 0) {
       unsigned long long* d = a.dbg + (size_t)blockIdx.x * kDbgSlots;
       d[5] = dbg_d0; d[6] = dbg_d1; d[7] = clock64() - dbg_e0; d[9] = dbg_rd;
+      d[10] = dbg_free; d[12] = dbg_st; d[13] = dbg_h1;
     }
   }
 

@@ -12,7 +12,7 @@ from dsdf_b200 import _lib, synth
 
 dev = torch.device("cuda:0")
 NAMES = ["mma_total", "mma_wait_full", "mma_wait_a_lo", "mma_wait_a_hi", "prod_wait_empty",
-         "epi_wait_d0", "epi_wait_d1", "epi_total", "mma_wait_e_full", "epi_wait_stash_read", "s10", "s11", "s12", "s13", "s14", "s15"]
+         "epi_wait_d0", "epi_wait_d1", "epi_total", "mma_wait_e_full", "epi_wait_stash_read", "epi_sum_t_free", "mma_sum_t_first", "epi_free_to_publish_lo", "epi_half1", "s14", "s15"]
 
 
 def read(dec, label, tiles_per_cta):
@@ -27,7 +27,13 @@ def read(dec, label, tiles_per_cta):
         print(f"== {label}: no counters (build with DSDF_BUILD_VARIANT=dbg DSDF_BUILD_DEFS=-DDSDF_DBG_BUILD and set DSDF_LIB)")
         return
     print(f"== {label}: {a.shape[0]} CTAs, {tiles_per_cta:.1f} tiles/CTA")
+    lead = a[a[:, 11] > 0]
+    if lead.shape[0]:
+        bub = (lead[:, 11] - lead[:, 10]) / (7 * tiles_per_cta)
+        print(f"  layer-boundary bubble (layer l retired -> first MMA of l+1 issued): mean {bub.mean():8.0f} cyc/layer  min {bub.min():8.0f} max {bub.max():8.0f}")
     for i, nm in enumerate(NAMES):
+        if i in (10, 11):
+            continue
         if a[:, i].max() > 0:
             print(f"  {nm:18s} mean {a[:, i].mean():12.0f} cyc  ({a[:, i].mean() / tiles_per_cta:9.0f} /tile)  min {a[:, i].min():12.0f} max {a[:, i].max():12.0f}")
 
