@@ -36,17 +36,17 @@ namespace dsdf {
 
 template <int CG>
 struct F3 {
-  static constexpr int kRing = 8 * CG;                   // W ring stages (per CTA)
+  static constexpr int kRing = CG == 2 ? DSDF_FWD_RING : 8;   // W ring stages (per CTA), any depth <= 32
   static constexpr uint32_t kSlice = kStepBytes / CG;    // bytes of one K-step held by one CTA
   static constexpr uint32_t kSmemA = 0;                  // 8 SUBs (SWIZZLE_128B)
   static constexpr uint32_t kSmemEA = kTileBytes;        // [128 x 16] no-swizzle, 4 KB
   static constexpr uint32_t kSmemRing = kSmemEA + 4096;
   static constexpr uint32_t kSmemERing = kSmemRing + kRing * kSlice;   // 64 KB W ring
   static constexpr uint32_t kSmemAux = kSmemERing + 2 * kSlice;
-  static constexpr uint32_t kAuxTmem = 512;              // after 64 barriers
-  static constexpr uint32_t kAuxPart = 528;              // 128 floats
-  static constexpr uint32_t kAuxRed = 1040;              // 16 floats
-  static constexpr uint32_t kAuxW8 = 1104;               // 512 floats
+  static constexpr uint32_t kAuxTmem = 1024;             // after 128 barrier slots
+  static constexpr uint32_t kAuxPart = 1040;             // 128 floats
+  static constexpr uint32_t kAuxRed = 1552;              // 16 floats
+  static constexpr uint32_t kAuxW8 = 1616;               // 512 floats
   static constexpr uint32_t kAuxG = kAuxW8 + 2048;       // 128 floats: dL/ds of the tile's rows
   static constexpr uint32_t kSmemBytes = kSmemAux + kAuxG + 512;
 };
@@ -131,17 +131,18 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
   const int lane = threadIdx.x & 31;
 
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::kSmemAux);
+  static_assert(kRing <= 32, "barrier layout holds 32 ring stages");
   uint64_t* full = bars;                 // [kRing]  producer -> MMA (leader's copy is the live one)
-  uint64_t* empty = bars + 16;           // [kRing]  MMA -> producer (committed to both CTAs)
-  uint64_t* e_full = bars + 32;          // [2]
-  uint64_t* e_empty = bars + 34;         // [2]
-  uint64_t* a_lo = bars + 36;            // epilogue -> MMA: A SUB 0..3 (+E_A) ready, TMEM h0 drained
-  uint64_t* a_hi = bars + 37;            // epilogue -> MMA: A SUB 4..7 ready, TMEM h1 drained
-  uint64_t* d_done = bars + 38;          // [2] MMA -> epilogue: half h accumulated
-  uint64_t* s_lo = bars + 40;            // TRAIN: epilogue -> stash warp: A SUB 0..3 written
-  uint64_t* s_hi = bars + 41;            //        epilogue -> stash warp: A SUB 4..7 written
-  uint64_t* s_done = bars + 42;          //        stash warp -> epilogue: A tile copied to HBM
-  uint64_t* a_sub = bars + 44;           // [3] epilogue -> MMA at a layer boundary: A SUB 1 / 2 / 3 written
+  uint64_t* empty = bars + 32;           // [kRing]  MMA -> producer (committed to both CTAs)
+  uint64_t* e_full = bars + 64;          // [2]
+  uint64_t* e_empty = bars + 66;         // [2]
+  uint64_t* a_lo = bars + 68;            // epilogue -> MMA: A SUB 0..3 (+E_A) ready, TMEM h0 drained
+  uint64_t* a_hi = bars + 69;            // epilogue -> MMA: A SUB 4..7 ready, TMEM h1 drained
+  uint64_t* d_done = bars + 70;          // [2] MMA -> epilogue: half h accumulated
+  uint64_t* s_lo = bars + 72;            // TRAIN: epilogue -> stash warp: A SUB 0..3 written
+  uint64_t* s_hi = bars + 73;            //        epilogue -> stash warp: A SUB 4..7 written
+  uint64_t* s_done = bars + 74;          //        stash warp -> epilogue: A tile copied to HBM
+  uint64_t* a_sub = bars + 76;           // [3] epilogue -> MMA at a layer boundary: A SUB 1 / 2 / 3 written
                                          // (a_lo then only means SUB 0: the MMAs of the next layer start
                                          //  after 16 KB of A stores instead of 64 KB)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + C::kSmemAux + C::kAuxTmem);
@@ -197,7 +198,7 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
   if (warp == 0) {
     // ===================== weight producer =====================
     if (elect_one()) {
-      uint32_t ph = 0, es = 0, eph = 0;
+      uint32_t ph = 0, st = 0, es = 0, eph = 0;   // st/ph: ring stage and its phase, running through layers and tiles
       for (long long it = 0; it < n_iter; ++it) {
         long long tile = it * gridDim.x + blockIdx.x;
         tile = tile < n_tiles ? tile : n_tiles - 1;
@@ -208,7 +209,7 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
         }
 #pragma unroll 1
         for (int l = 0; l < 8; ++l) {
-          const int groups = f2_used_ksteps<FOLD>(l) / kRing;
+          const int ksteps = f2_used_ksteps<FOLD>(l);
 #pragma unroll 1
           for (int h = 0; h < w2_halves(l); ++h) {
             const uint8_t* w = a.w2img + (size_t)w2_step(l, h, 0) * kStepBytes + crank * kSlice;
@@ -221,16 +222,13 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
             es ^= 1;
             eph ^= (es == 0);
             w += kStepBytes;
-#pragma unroll 1
-            for (int g = 0; g < groups; ++g) {
-#pragma unroll
-              for (int u = 0; u < kRing; ++u) {
-                mbar_wait(&empty[u], ph ^ 1);
-                mbar_arrive_expect_tx(&full[u], kSlice);
-                bulk_g2s(smem + C::kSmemRing + u * kSlice, w, kSlice, &full[u]);
-                w += kStepBytes;
-              }
-              ph ^= 1;
+#pragma unroll 4
+            for (int k = 0; k < ksteps; ++k) {
+              mbar_wait(&empty[st], ph ^ 1);
+              mbar_arrive_expect_tx(&full[st], kSlice);
+              bulk_g2s(smem + C::kSmemRing + st * kSlice, w, kSlice, &full[st]);
+              w += kStepBytes;
+              if (++st == (uint32_t)kRing) { st = 0; ph ^= 1; }
             }
           }
         }
@@ -240,25 +238,22 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
     // ===================== peer CTA: relay "my half of the step has landed" to the leader =====
     // (a bulk copy can only signal an mbarrier of the CTA it writes to)
     if (elect_one()) {
-      uint32_t ph = 0, es = 0, eph = 0;
+      uint32_t ph = 0, st = 0, es = 0, eph = 0;
       for (long long it = 0; it < n_iter; ++it) {
 #pragma unroll 1
         for (int l = 0; l < 8; ++l) {
-          const int groups = f2_used_ksteps<FOLD>(l) / kRing;
+          const int ksteps = f2_used_ksteps<FOLD>(l);
 #pragma unroll 1
           for (int h = 0; h < w2_halves(l); ++h) {
             mbar_wait(&e_full[es], eph);
             mbar_arrive_cluster_relaxed(e_full_c + es * 8);
             es ^= 1;
             eph ^= (es == 0);
-#pragma unroll 1
-            for (int g = 0; g < groups; ++g) {
-#pragma unroll
-              for (int u = 0; u < kRing; ++u) {
-                mbar_wait(&full[u], ph);
-                mbar_arrive_cluster_relaxed(full_c + u * 8);
-              }
-              ph ^= 1;
+#pragma unroll 4
+            for (int k = 0; k < ksteps; ++k) {
+              mbar_wait(&full[st], ph);
+              mbar_arrive_cluster_relaxed(full_c + st * 8);
+              if (++st == (uint32_t)kRing) { st = 0; ph ^= 1; }
             }
           }
         }
@@ -272,7 +267,7 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
       const uint64_t a_desc0 = umma_smem_desc(s_base + C::kSmemA, 16, 1024);
       const uint64_t b_desc0 = umma_smem_desc_ns(s_base + C::kSmemRing, 128, 256);
       const uint64_t eb_desc0 = umma_smem_desc_ns(s_base + C::kSmemERing, 128, 256);
-      uint32_t ph = 0, es = 0, eph = 0, par_lo = 0, par_hi = 0, par_sub = 0;
+      uint32_t ph = 0, st = 0, es = 0, eph = 0, par_lo = 0, par_hi = 0, par_sub = 0;
       long long dbg_wf = 0, dbg_wl = 0, dbg_wh = 0, dbg_we = 0, dbg_first = 0;
       const long long dbg_t0 = DSDF_DBG_ON(a) ? clock64() : 0;
       auto timed_wait = [&](uint64_t* bar, uint32_t par, long long& acc) {
@@ -293,7 +288,7 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
       for (long long it = 0; it < n_iter; ++it) {
 #pragma unroll 1
         for (int l = 0; l < 8; ++l) {
-          const int groups = f2_used_ksteps<FOLD>(l) / kRing;
+          const int ksteps = f2_used_ksteps<FOLD>(l);
           timed_wait(a_lo, par_lo, dbg_wl);
           par_lo ^= 1;
           tc_fence_after();
@@ -309,31 +304,26 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
             es ^= 1;
             eph ^= (es == 0);
 #pragma unroll 1
-            for (int g = 0; g < groups; ++g) {
-              if (h == 0 && g * kRing == 16) {   // first K-step that reads A SUB 4..7
+            for (int sub = 0; sub < (ksteps >> 2); ++sub) {   // one A SUB = 64 K = 4 K-steps
+              if (h == 0 && sub == 4) {          // first K-step that reads A SUB 4..7
                 timed_wait(a_hi, par_hi, dbg_wh);
                 par_hi ^= 1;
                 tc_fence_after();
               }
-              // K-steps 8g*CG .. : SUB (s >> 2), 32 B per step inside the 128 B swizzle row
-              const uint64_t a_desc = a_desc0 + (uint64_t)((g * (kRing / 4) * kSubBytes) >> 4);
-#pragma unroll
-              for (int u = 0; u < kRing; ++u) {
-                if ((u & 3) == 0 && h == 0 && l >= 1) {
-                  // first K-step of an A SUB the epilogue wrote at the layer boundary (SUB 0 = a_lo)
-                  const int sub = g * (kRing / 4) + (u >> 2);
-                  if (sub >= 1 && sub <= 3) {
-                    timed_wait(&a_sub[sub - 1], par_sub, dbg_wl);
-                    tc_fence_after();
-                  }
-                }
-                timed_wait(&full[u], ph, dbg_wf);
+              if (h == 0 && l >= 1 && sub >= 1 && sub <= 3) {
+                // an A SUB the epilogue wrote at the layer boundary (SUB 0 = a_lo)
+                timed_wait(&a_sub[sub - 1], par_sub, dbg_wl);
                 tc_fence_after();
-                mma(d_addr, a_desc + (uint64_t)(((u >> 2) * kSubBytes + (u & 3) * 32) >> 4),
-                    b_desc0 + (uint64_t)((u * kSlice) >> 4), 1u);
-                commit(&empty[u]);
               }
-              ph ^= 1;
+              const uint64_t a_desc = a_desc0 + (uint64_t)((sub * kSubBytes) >> 4);
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                timed_wait(&full[st], ph, dbg_wf);
+                tc_fence_after();
+                mma(d_addr, a_desc + (uint64_t)((k * 32) >> 4), b_desc0 + (uint64_t)((st * kSlice) >> 4), 1u);
+                commit(&empty[st]);
+                if (++st == (uint32_t)kRing) { st = 0; ph ^= 1; }
+              }
             }
             commit(&d_done[h]);
           }

@@ -23,6 +23,14 @@
 #pragma once
 #include <stdint.h>
 
+// forward weight-ring depth (4 KB stages per CTA of a pair).  Measured on B200: 8 stages cost 24 % of the chain
+// kernels, 16 -> 20 gains 1-3 % (the knee of the latency curve); 20 is what shared memory allows.  The backward
+// kernel keeps its 16-stage ring with compile-time stage descriptors (a running stage index measured 1.5 % slower
+// there: its MMA issuer lives under a 56-register setmaxnreg budget).
+#ifndef DSDF_FWD_RING
+#define DSDF_FWD_RING 20
+#endif
+
 namespace dsdf {
 
 constexpr int kLatent = 256;
