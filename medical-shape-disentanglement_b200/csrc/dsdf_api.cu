@@ -922,7 +922,7 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
                                                       (const long long*)seg_ids, reg_coef,
                                                       w.dlat_seg, w.seg_norm);
   CU(h, cudaMemsetAsync(lat_grad, 0, (size_t)num_scenes * kLatent * 4, st));
-  k_lat_grad_scatter<<<1, kLatent, 0, st>>>(w.dlat_seg, (const long long*)seg_ids, (int)n_seg, lat_grad);
+  k_lat_grad_scatter<<<(unsigned)n_seg, kLatent, 0, st>>>(w.dlat_seg, (const long long*)seg_ids, (int)n_seg, lat_grad);
   k_dw_latent<<<dim3(kHidden, 2), kLatent, 0, st>>>(w.seg_sum, table, (const long long*)seg_ids,
                                                     (int)n_seg, w.dweff);
   k_reduce_cta<<<16, kHidden, 0, st>>>(w.cta_partials, (int)bwd_grid, w.seg_sum, (int)n_seg,
@@ -1379,7 +1379,7 @@ extern "C" int dsdf_renorm_rows(dsdf_handle h, float* table, const int64_t* seg_
                                 float max_norm, void* stream) {
   if (!h || !table || !seg_ids) DSDF_FAIL(h, DSDF_EINVAL, "null argument");
   if (n_seg <= 0) return DSDF_OK;
-  k_renorm_rows<<<1, kLatent, 0, (cudaStream_t)stream>>>(table, (const long long*)seg_ids, (int)n_seg, max_norm);
+  k_renorm_rows<<<(unsigned)n_seg, kLatent, 0, (cudaStream_t)stream>>>(table, (const long long*)seg_ids, (int)n_seg, max_norm);
   CU(h, cudaGetLastError());
   return DSDF_OK;
 }

@@ -31,17 +31,25 @@ __device__ __forceinline__ float block_sum_256(float v, float* sh) {
   return t;
 }
 
-// ---- embedding max_norm (one block of 256 threads, segments processed in order) ----------
+// ---- embedding max_norm: grid n_seg, 256 threads.  A scene that appears more than once in the batch is
+// handled by the block of its FIRST occurrence only (renorm is idempotent -- torch renorms the unique ids --
+// and two blocks rescaling one row concurrently would mix old and new elements in the norm).
+__device__ __forceinline__ bool first_occurrence(const long long* __restrict__ seg_ids, int b) {
+  const long long id = seg_ids[b];
+  for (int k = 0; k < b; ++k)
+    if (seg_ids[k] == id) return false;
+  return true;
+}
+
 __global__ void k_renorm_rows(float* __restrict__ table, const long long* __restrict__ seg_ids,
                               int n_seg, float max_norm) {
   __shared__ float sh[8];
-  for (int b = 0; b < n_seg; ++b) {
-    float* row = table + seg_ids[b] * kLatent;
-    const float x = row[threadIdx.x];
-    const float nrm = sqrtf(block_sum_256(x * x, sh));
-    if (nrm > max_norm) row[threadIdx.x] = x * (max_norm / (nrm + 1e-7f));
-    __syncthreads();
-  }
+  const int b = blockIdx.x;
+  if (b >= n_seg || !first_occurrence(seg_ids, b)) return;      // block-uniform
+  float* row = table + seg_ids[b] * kLatent;
+  const float x = row[threadIdx.x];
+  const float nrm = sqrtf(block_sum_256(x * x, sh));
+  if (nrm > max_norm) row[threadIdx.x] = x * (max_norm / (nrm + 1e-7f));
 }
 
 // ---- per-segment column sums of dY0 / dY4: seg_sum[b][which][c] -----------------------------
@@ -97,13 +105,18 @@ __global__ void __launch_bounds__(1024) k_lat_grad_seg(const float* __restrict__
   if (j == 0) seg_norm[b] = nrm;
 }
 
-// dense latent grad rows += per-segment grads, segments in order (duplicate ids are summed
-// deterministically).  one block, 256 threads.  lat_grad must be zeroed by the caller.
+// dense latent grad rows = per-segment grads; duplicate ids are summed in segment order by the block of the
+// id's first occurrence (deterministic).  grid n_seg, 256 threads.  lat_grad must be zeroed by the caller.
 __global__ void k_lat_grad_scatter(const float* __restrict__ dlat_seg,
                                    const long long* __restrict__ seg_ids, int n_seg,
                                    float* __restrict__ lat_grad) {
-  for (int b = 0; b < n_seg; ++b)
-    lat_grad[seg_ids[b] * kLatent + threadIdx.x] += dlat_seg[(size_t)b * kLatent + threadIdx.x];
+  const int b = blockIdx.x;
+  if (b >= n_seg || !first_occurrence(seg_ids, b)) return;      // block-uniform
+  const long long id = seg_ids[b];
+  float acc = dlat_seg[(size_t)b * kLatent + threadIdx.x];
+  for (int k = b + 1; k < n_seg; ++k)
+    if (seg_ids[k] == id) acc += dlat_seg[(size_t)k * kLatent + threadIdx.x];
+  lat_grad[id * kLatent + threadIdx.x] = acc;
 }
 
 // ---- latent columns of dW0 / dW4: outer products of segment colsums and latents ---------------

@@ -481,3 +481,32 @@ def test_ab_kernel_generations_agree_with_the_shipping_path(env, monkeypatch):
     assert cos(g1, g0) >= 0.9999
     assert cos(l1, l0) >= 0.9999
     assert torch.equal(l1 != 0, l0 != 0)
+
+
+def test_duplicate_scene_ids_in_one_batch():
+    """The same scene twice in a batch (possible with a sampler that draws with replacement): the latent row is
+    renormed once (torch renorms the unique ids) and its gradient is the ordered sum of both segments."""
+    S, B, P = 6, 4, 256
+    lat0 = torch.randn(S, 256, generator=torch.Generator().manual_seed(4)) / 16.0
+    lat0[1] *= 30.0                                   # exceeds CodeBound, appears twice below
+    dec, orc, tr = _paired(True, S, B, P, lat0)
+    data = synth.scene_samples(S, P, seed=1).cuda()
+    ids = torch.tensor([1, 3, 1, 2])
+    batch = data[ids].clone()
+    batch[2] = data[4]                                # second visit of scene 1 sees different samples
+    orc.set_epoch_lr(50); orc.opt.zero_grad()
+    sl, rl, pred_ref = orc.forward_loss(batch, ids, 50)
+    pred = tr.forward_backward(batch, ids.cuda(), 50)
+    torch.cuda.synchronize()
+    assert abs(tr.loss_buf[0].item() - sl) <= 1e-2 * abs(sl)
+    assert (pred.clamp(-0.1, 0.1)[:, None] - pred_ref).abs().max().item() <= SDF_TOL
+    lg = orc.lat_vecs.weight.grad
+    assert cos(tr.lat_grad, lg) >= COS_TOL
+    assert cos(tr.lat_grad[1], lg[1]) >= COS_TOL      # the doubled row on its own
+    assert torch.equal(tr.lat_grad != 0, lg != 0)
+    torch.testing.assert_close(tr.lat_vecs.weight.data, orc.lat_vecs.weight.data, rtol=1e-6, atol=1e-7)
+    # deterministic: the same call again gives the same bits
+    g1 = tr.lat_grad.clone()
+    tr.forward_backward(batch, ids.cuda(), 50)
+    torch.cuda.synchronize()
+    assert torch.equal(g1, tr.lat_grad)
