@@ -411,7 +411,7 @@ extern "C" int dsdf_forward_segments(dsdf_handle h, const float* table, const in
     int rc = ensure_scene_e(h, ns);
     if (rc != DSDF_OK) return rc;
     a.scene_e = h->scene_e;
-    k_scene_fold<<<dim3((unsigned)ns, 2), 512, 0, (cudaStream_t)stream>>>(
+    k_scene_fold<<<dim3((unsigned)ns, 2, kFoldSplit), 512, 0, (cudaStream_t)stream>>>(
         h->weff, h->params_ptr, h->pl, table, (const long long*)seg_ids, h->scene_e);
     CU(h, (launch_fwd<MODE_TABLE, true, false>(h, a, (cudaStream_t)stream, !seg_ids || rows_per_seg % (2 * kTileM) == 0)));
   } else {
@@ -447,7 +447,7 @@ extern "C" int dsdf_decode_grid(dsdf_handle h, const float* latent, int32_t grid
     int rc = ensure_scene_e(h, 1);
     if (rc != DSDF_OK) return rc;
     a.scene_e = h->scene_e;
-    k_scene_fold<<<dim3(1, 2), 512, 0, (cudaStream_t)stream>>>(h->weff, h->params_ptr, h->pl, latent,
+    k_scene_fold<<<dim3(1, 2, kFoldSplit), 512, 0, (cudaStream_t)stream>>>(h->weff, h->params_ptr, h->pl, latent,
                                                                nullptr, h->scene_e);
     CU(h, (launch_fwd<MODE_GRID, true, false>(h, a, (cudaStream_t)stream, true)));
   }
@@ -834,7 +834,7 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   if (h->fwd_v1) {
     k_forward<MODE_TABLE, true><<<grid, kFwdThreads, kFwdSmemBytes, st>>>(fa);
   } else {
-    k_scene_fold<<<dim3((unsigned)n_seg, 2), 512, 0, st>>>(h->weff, params, h->pl, table,
+    k_scene_fold<<<dim3((unsigned)n_seg, 2, kFoldSplit), 512, 0, st>>>(h->weff, params, h->pl, table,
                                                           (const long long*)seg_ids, w.scene_e);
     fa.drop = h->drop;
     if (h->drop.layers != 0)
@@ -1085,7 +1085,7 @@ extern "C" int dsdf_segments_forward_train(dsdf_handle h, const float* params, c
   fa.dbg = h->dbg;
   fa.scene_e = w.scene_e;
   k_iota<<<(unsigned)((n_seg + 255) / 256), 256, 0, st>>>(w.ids, n_seg);
-  k_scene_fold<<<dim3((unsigned)n_seg, 2), 512, 0, st>>>(h->weff, params, h->pl, latents, w.ids, w.scene_e);
+  k_scene_fold<<<dim3((unsigned)n_seg, 2, kFoldSplit), 512, 0, st>>>(h->weff, params, h->pl, latents, w.ids, w.scene_e);
   CU(h, (launch_fwd<MODE_TABLE, true, true>(h, fa, st, rows_per_seg % (2 * kTileM) == 0)));
   CU(h, cudaGetLastError());
   return DSDF_OK;
@@ -1214,7 +1214,7 @@ RWs recon_carve(uint8_t* base, long long n_shapes, long long num_samples, int nu
   w.tile_partials = (float*)take(tiles * 2 * 4);
   w.tile_colsum = (float*)take(tiles * 2 * kHidden * 4);
   w.cta_partials = (float*)take((size_t)num_sms * kCtaPartialFloats * 4);
-  w.seg_sum = (float*)take((size_t)n_shapes * 2 * kHidden * 4);
+  w.seg_sum = (float*)take((size_t)n_shapes * kReconParts * kLatent * 4);   // latent-gradient partials
   w.scene_e = take((size_t)n_shapes * kSceneESteps * kStepBytes);
   w.relu_mask = (uint32_t*)take(tiles * kActAuxTileBytes);
   w.loss_sink = (float*)take((size_t)n_shapes * 4);
@@ -1294,8 +1294,7 @@ extern "C" int dsdf_reconstruct(dsdf_handle h, const float* params, const dsdf_r
 
   ReconUpdateArgs ua;
   memset(&ua, 0, sizeof(ua));
-  ua.seg_sum = w.seg_sum;
-  ua.weff = h->weff;
+  ua.dlat_part = w.seg_sum;
   ua.tile_partials = w.tile_partials;
   ua.tiles_per_seg = tiles_per_seg;
   ua.inv_n = 1.0f / (float)num;
@@ -1321,19 +1320,20 @@ extern "C" int dsdf_reconstruct(dsdf_handle h, const float* params, const dsdf_r
     k_recon_gather<<<ggrid, 256, 0, st>>>((const float4*)samples, (const long long*)shape_base,
                                           (const long long*)windows + e * n_shapes * 2, num / 2, rows_pad,
                                           (float4*)w.sdf, w.ids);
-    k_scene_fold<<<dim3((unsigned)n_shapes, 2), 512, 0, st>>>(h->weff, params, h->pl, latents, w.ids,
+    k_scene_fold<<<dim3((unsigned)n_shapes, 2, kFoldSplit), 512, 0, st>>>(h->weff, params, h->pl, latents, w.ids,
                                                              w.scene_e);
     CU(h, (launch_fwd<MODE_TABLE, true, true>(h, fa, st, true)));
     int rc = launch_backward2(h, b2, tiles, st, nullptr);
     if (rc != DSDF_OK) return rc;
-    k_seg_colsum<<<dim3((unsigned)n_shapes, 2), kHidden, 0, st>>>(w.tile_colsum, tiles_per_seg, w.seg_sum);
+    k_recon_dlat_partial<<<dim3((unsigned)n_shapes, kReconParts), 256, 0, st>>>(w.tile_colsum, tiles_per_seg,
+                                                                             h->weff, w.seg_sum);
     const double lr = (double)cfg->lr * pow(0.1, (double)(e / adjust_every));
     const double bc1 = 1.0 - pow(0.9, (double)(e + 1));
     const double bc2 = 1.0 - pow(0.999, (double)(e + 1));
     ua.step_size = (float)(lr / bc1);
     ua.bc2_sqrt = (float)sqrt(bc2);
     ua.loss_out = loss_hist ? loss_hist + e * n_shapes : w.loss_sink;
-    k_recon_update<<<(unsigned)n_shapes, 1024, 0, st>>>(ua);
+    k_recon_update<<<(unsigned)n_shapes, 256, 0, st>>>(ua);
   }
   CU(h, cudaGetLastError());
   return DSDF_OK;

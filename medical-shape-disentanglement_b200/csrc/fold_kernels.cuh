@@ -250,35 +250,40 @@ __global__ void k_fold_dgrad2(const float* __restrict__ weff, uint8_t* __restric
 }
 
 // Fold mode: per-segment E steps of lin0 / lin4 with bias' = b + W[:, latent] z_seg (fp32).
-// grid (n_seg, 2), 512 threads; warp w computes rows o = w, w+16, ... (coalesced over the latent).
-// seg_ids == nullptr: one segment whose latent is `table` itself.
+// grid (n_seg, 2, kFoldSplit), 512 threads: block z owns 512 / kFoldSplit output rows (so a single segment --
+// reconstruct, grid decode -- still spreads over 8 SMs); warp w computes rows w, w+16, ... of its slice
+// (coalesced over the latent).  seg_ids == nullptr: one segment whose latent is `table` itself.
+constexpr int kFoldSplit = 4;
+constexpr int kFoldRows = kHidden / kFoldSplit;
 __global__ void __launch_bounds__(512) k_scene_fold(const float* __restrict__ weff,
                                                     const float* __restrict__ params, ParamLayout pl,
                                                     const float* __restrict__ table,
                                                     const long long* __restrict__ seg_ids,
                                                     uint8_t* __restrict__ scene_e) {
   __shared__ float z[kLatent];
-  __shared__ float bias[kHidden];
-  const int b = blockIdx.x, which = blockIdx.y;
+  __shared__ float bias[kFoldRows];
+  const int b = blockIdx.x, which = blockIdx.y, o0 = blockIdx.z * kFoldRows;
   const int l = which == 0 ? 0 : kSkipLayer;
   const int lat0 = which == 0 ? 0 : kX3;   // first latent column in the reference weight
   const float* zr = table + (seg_ids ? seg_ids[b] * kLatent : 0);
   if (threadIdx.x < kLatent) z[threadIdx.x] = zr[threadIdx.x];
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int o = warp; o < kHidden; o += 16) {
+  for (int r = warp; r < kFoldRows; r += 16) {
+    const int o = o0 + r;
     const float* wr = weff + weff_off(l) + (size_t)o * ref_in(l) + lat0;
     float acc = 0.f;
 #pragma unroll
     for (int k = 0; k < kLatent / 32; ++k) acc = fmaf(wr[lane + 32 * k], z[lane + 32 * k], acc);
 #pragma unroll
     for (int s = 16; s > 0; s >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, s);
-    if (lane == 0) bias[o] = acc + params[pl.b[l] + o];
+    if (lane == 0) bias[r] = acc + params[pl.b[l] + o];
   }
   __syncthreads();
-  const int o = threadIdx.x, h = o >> 8, n = o & 255;
+  if (threadIdx.x >= kFoldRows) return;
+  const int o = o0 + threadIdx.x, h = o >> 8, n = o & 255;
   uint4 c0, c1;
-  e_step_row(weff, l, o, true, bias[o], c0, c1);
+  e_step_row(weff, l, o, true, bias[threadIdx.x], c0, c1);
   uint8_t* dst = scene_e + ((size_t)b * kSceneESteps + which * 2 + h) * kStepBytes +
                  (size_t)(n >> 3) * 256 + (size_t)(n & 7) * 16;
   *reinterpret_cast<uint4*>(dst) = c0;

@@ -3,6 +3,10 @@
 //   k_recon_gather  deep_sdf/data.py:112-136 (unpack_sdf_samples_from_ram): the per-iteration sample
 //                   window cat(pos[ps:ps+half], neg[ns:ns+half]) of every shape, written into the
 //                   tile-padded [shape][rows_pad][4] buffer the forward chain reads
+//   k_recon_dlat_partial  the shape's latent gradient sum_rows dX[:, latent] = colsum(dY0) W0[:, lat] +
+//                   colsum(dY4) W4[:, lat], cut into kReconParts slices of the 512 hidden channels so that one
+//                   shape keeps 8 SMs busy instead of one (the loop is latency-bound: a single shape is the
+//                   reference's use case)
 //   k_recon_update  reconstruct.py:102-140: loss value, regulariser gradients, torch.optim.Adam
 //                   step on the latent and the optional hard norm bound, one block per shape
 #pragma once
@@ -32,9 +36,39 @@ __global__ void k_recon_gather(const float4* __restrict__ samples,
   out[(long long)s * rows_pad + r] = __ldg(samples + src);
 }
 
+constexpr int kReconParts = 8;                      // slices of the hidden dimension
+constexpr int kReconPartC = kHidden / kReconParts;  // 64 channels each
+
+// grid (n_shapes, kReconParts), 256 threads.  Phase 1: column sums of dY0 / dY4 over the shape's tiles (in tile
+// order) for this slice's channels; phase 2: their product with the latent columns of W0 / W4 (thread = latent j).
+__global__ void __launch_bounds__(256) k_recon_dlat_partial(const float* __restrict__ tile_colsum, int tiles_per_seg,
+                                                            const float* __restrict__ weff,
+                                                            float* __restrict__ dlat_part) {
+  __shared__ float sc[2][kReconPartC];
+  const int b = blockIdx.x, part = blockIdx.y, t = threadIdx.x;
+  const int cbase = part * kReconPartC;
+  if (t < 2 * kReconPartC) {
+    const int which = t / kReconPartC, c = cbase + t % kReconPartC;
+    const float* src = tile_colsum + ((size_t)b * tiles_per_seg * 2 + which) * kHidden + c;
+    float s = 0.f;
+#pragma unroll 8
+    for (int tt = 0; tt < tiles_per_seg; ++tt) s += src[(size_t)tt * 2 * kHidden];
+    sc[which][t % kReconPartC] = s;
+  }
+  __syncthreads();
+  const float* w0 = weff + weff_off(0) + (size_t)cbase * kIn0 + t;                  // [512][259], latent cols 0..255
+  const float* w4 = weff + weff_off(4) + (size_t)cbase * kHidden + kX3 + t;         // [512][512], latent cols 253..508
+  float acc0 = 0.f, acc4 = 0.f;
+#pragma unroll 16
+  for (int c = 0; c < kReconPartC; ++c) {
+    acc0 = fmaf(sc[0][c], __ldg(w0 + (size_t)c * kIn0), acc0);
+    acc4 = fmaf(sc[1][c], __ldg(w4 + (size_t)c * kHidden), acc4);
+  }
+  dlat_part[((size_t)b * kReconParts + part) * kLatent + t] = acc0 + acc4;
+}
+
 struct ReconUpdateArgs {
-  const float* seg_sum;        // [n_shapes][2][512] column sums of dY0 / dY4
-  const float* weff;           // effective fp32 weights
+  const float* dlat_part;      // [n_shapes][kReconParts][256] from k_recon_dlat_partial
   const float* tile_partials;  // [tiles][2]
   int tiles_per_seg;
   float inv_n;                 // 1 / num_samples (the L1 partial sums are unscaled)
@@ -53,40 +87,22 @@ struct ReconUpdateArgs {
   float* grad_out;             // [n_shapes][256] (nullable) dL/dz of this iteration
 };
 
-// grid n_shapes, 1024 threads: thread (part = t / 256, j = t % 256)
-__global__ void __launch_bounds__(1024) k_recon_update(const ReconUpdateArgs a) {
-  __shared__ float s0[kHidden], s4[kHidden], accs[4][kLatent], sh[8];
-  const int b = blockIdx.x, t = threadIdx.x, j = t & 255, part = t >> 8;
-  for (int c = t; c < 2 * kHidden; c += 1024) {
-    const float v = a.seg_sum[(size_t)b * 2 * kHidden + c];
-    if (c < kHidden) s0[c] = v; else s4[c - kHidden] = v;
-  }
-  __syncthreads();
-  {
-    const float* w0 = a.weff + weff_off(0) + j;                 // [512][259], latent columns 0..255
-    const float* w4 = a.weff + weff_off(4) + kX3 + j;           // [512][512], latent columns 253..508
-    float acc0 = 0.f, acc4 = 0.f;
-    const int c0 = part * (kHidden / 4);
-#pragma unroll 8
-    for (int c = c0; c < c0 + kHidden / 4; ++c) {
-      acc0 = fmaf(s0[c], __ldg(w0 + (size_t)c * kIn0), acc0);
-      acc4 = fmaf(s4[c], __ldg(w4 + (size_t)c * kHidden), acc4);
-    }
-    accs[part][j] = acc0 + acc4;
-  }
-  __syncthreads();
-  if (t >= 256) return;   // the rest is one thread per latent element (no block-wide barrier below
-                          // other than block_sum_256-style reductions over these 256 threads)
-  float g = (accs[0][j] + accs[1][j]) + (accs[2][j] + accs[3][j]);
+// grid n_shapes, 256 threads: thread = latent element j
+__global__ void __launch_bounds__(256) k_recon_update(const ReconUpdateArgs a) {
+  __shared__ float sh[8];
+  const int b = blockIdx.x, t = threadIdx.x, j = t;
+  float g = 0.f;
+#pragma unroll
+  for (int p = 0; p < kReconParts; ++p) g += a.dlat_part[((size_t)b * kReconParts + p) * kLatent + j];   // fixed order
   float* zp = a.latents + (size_t)b * kLatent + j;
   const float z = *zp;
   // ---- loss value + regulariser gradients (reconstruct.py:102-129)
   auto sum256 = [&](float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    named_bar_sync(2, 256);
+    __syncthreads();
     if ((t & 31) == 0) sh[t >> 5] = v;
-    named_bar_sync(2, 256);
+    __syncthreads();
     float r = 0.f;
     for (int i = 0; i < 8; ++i) r += sh[i];
     return r;
