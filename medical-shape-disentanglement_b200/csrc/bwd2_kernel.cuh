@@ -252,6 +252,7 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
       // ===================== dY-stash warp =====================
       // dY_7..dY_1 images for the wgrad kernel: byte-for-byte the smem A tile -> linear copy with
       // coalesced 512 B warp stores (see the forward kernel's stash warp for why not TMA).
+      const uint64_t pol = stash_policy();
       uint32_t par_lo = 0, par_hi = 0;
       for (long long it = 0; it < n_iter; ++it) {
         long long tile = it * gridDim.x + blockIdx.x;
@@ -280,7 +281,7 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
                 }
 #pragma unroll
                 for (int q8 = 0; q8 < 8; ++q8)
-                  dst[(size_t)(half * 4 * kSubBytes) / 16 + (size_t)(i + q8) * 32 + lane] = v[q8];
+                  st_stash(dst + (size_t)(half * 4 * kSubBytes) / 16 + (size_t)(i + q8) * 32 + lane, v[q8], pol);
               }
             }
           }

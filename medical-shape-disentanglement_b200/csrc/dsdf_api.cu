@@ -805,6 +805,10 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   fa.xyz_stride = 4;
   fa.out = pred;
   fa.xstash = w.xstash;
+#ifdef DSDF_DBG_BUILD
+  // diagnostics build only: time the chain kernels without their stash stores (results are then meaningless)
+  if (const char* e = getenv("DSDF_DBG_NOSTASH")) if (atoi(e) & 1) fa.xstash = nullptr;
+#endif
   fa.gout = w.g;
   fa.tile_partials = w.tile_partials;
   fa.fused_loss = 1;
@@ -869,6 +873,9 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
     b2.g = w.g;
     b2.relu_mask = w.relu_mask;
     b2.dystash = w.dystash;
+#ifdef DSDF_DBG_BUILD
+    if (const char* e = getenv("DSDF_DBG_NOSTASH")) if (atoi(e) & 2) b2.dystash = nullptr;
+#endif
     b2.xyz = sdf_data;
     b2.xyz_stride = 4;
     b2.tile_colsum = w.tile_colsum;

@@ -342,6 +342,7 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
     // starves the 4 KB weight-ring loads; not per-row stores from the epilogue registers either:
     // 16 B per 128 B line.)
     if (TRAIN) {
+      const uint64_t pol = stash_policy();
       uint32_t par_lo = 0, par_hi = 0;
       for (long long it = 0; it < n_iter; ++it) {
         long long tile = it * gridDim.x + blockIdx.x;
@@ -372,7 +373,7 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
                 }
 #pragma unroll
                 for (int k = 0; k < 8; ++k)
-                  dst[(size_t)(half * 4 * kSubBytes) / 16 + (size_t)(i + k) * 32 + lane] = v[k];
+                  st_stash(dst + (size_t)(half * 4 * kSubBytes) / 16 + (size_t)(i + k) * 32 + lane, v[k], pol);
               }
             }
           }
