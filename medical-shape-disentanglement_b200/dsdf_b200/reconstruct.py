@@ -96,11 +96,18 @@ def reconstruct_batch(decoder: Decoder, num_iterations: int, shapes: Sequence[Tu
                       num_samples: int = 30000, lr: float = 5e-4, l2reg: bool = False,
                       code_reg_lambda=None, code_reg_type: str = "l2_sq", code_bound=None,
                       dist_mean=None, dist_std=None, dist_weight=0.0, dist_type: str = "zscore_l2",
-                      return_state: bool = False):
+                      return_state: bool = False, first_step: int = 1, n_steps: Optional[int] = None,
+                      state: Optional[Tuple[torch.Tensor, torch.Tensor]] = None):
     """Optimise `latents[n_shapes, 256]` (initial values, not modified) against `shapes[i] = (pos, neg)`
     with per-iteration windows `windows[num_iterations, n_shapes, 2]` (int64).  Returns
     (loss_hist [num_iterations, n_shapes] on the device, optimised latents [n_shapes, 256]) and,
-    with return_state, the Adam moments (exp_avg, exp_avg_sq) as well."""
+    with return_state, the Adam moments (exp_avg, exp_avg_sq) as well.
+
+    The schedule can be run in pieces (to look at the losses, stop early, checkpoint): `first_step` (1-based) and
+    `n_steps` select iterations [first_step, first_step + n_steps) of the `num_iterations` schedule -- the learning
+    rate drop at num_iterations/2 and Adam's bias correction follow the absolute iteration -- and `state` carries
+    the Adam moments returned by the previous piece; `latents` are then the previous piece's result.  Pieces
+    chained this way equal the single call bit for bit."""
     dev = next(decoder.parameters()).device
     if dev.type != "cuda":
         raise _lib.DsdfError("reconstruct needs the decoder on a CUDA device (no CPU path)")
@@ -120,8 +127,20 @@ def reconstruct_batch(decoder: Decoder, num_iterations: int, shapes: Sequence[Tu
     shape_base = torch.tensor(base, dtype=torch.int64).to(dev)
     win = torch.as_tensor(windows, dtype=torch.int64).reshape(num_iterations, n_shapes, 2).contiguous().to(dev)
     lat = latents.detach().to(dev, torch.float32).clone().contiguous()
-    m = torch.zeros_like(lat)
-    v = torch.zeros_like(lat)
+    if n_steps is None:
+        n_steps = num_iterations - (first_step - 1)
+    if first_step < 1 or n_steps < 0 or first_step - 1 + n_steps > num_iterations:
+        raise ValueError(f"iterations [{first_step}, {first_step + n_steps}) are outside the schedule 1..{num_iterations}")
+    if state is None:
+        if first_step != 1:
+            raise ValueError("continuing a schedule (first_step > 1) needs the Adam moments of the previous piece")
+        m = torch.zeros_like(lat)
+        v = torch.zeros_like(lat)
+    else:
+        m = state[0].detach().to(dev, torch.float32).clone().contiguous()
+        v = state[1].detach().to(dev, torch.float32).clone().contiguous()
+        if m.shape != lat.shape or v.shape != lat.shape:
+            raise ValueError("state must be (exp_avg, exp_avg_sq), each shaped like latents")
     hist = torch.zeros(num_iterations, n_shapes, dtype=torch.float32, device=dev)
     reg_kind, reg_lambda = _reg_args(l2reg, code_reg_lambda, code_reg_type)
     dist_w = float(dist_weight) if dist_weight is not None else 0.0
@@ -145,7 +164,7 @@ def reconstruct_batch(decoder: Decoder, num_iterations: int, shapes: Sequence[Tu
     ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
     with torch.cuda.device(dev):
         _lib.check(L.dsdf_reconstruct(h, flat.data_ptr(), C.byref(cfg), n_shapes, samples.data_ptr(),
-                                      shape_base.data_ptr(), win.data_ptr(), 1, num_iterations,
+                                      shape_base.data_ptr(), win.data_ptr(), int(first_step), int(n_steps),
                                       lat.data_ptr(), m.data_ptr(), v.data_ptr(), ws.data_ptr(), ws.numel(),
                                       hist.data_ptr(), _stream_ptr(dev)), h, L)
     # keep every buffer the enqueued kernels use alive until they have run

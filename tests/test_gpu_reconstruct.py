@@ -179,3 +179,28 @@ def test_small_shape_sampler_branch_follows_the_executed_reference():
     losses, latent = dsdf_b200.reconstruct(dec, 20, 256, [pos, neg], 0.01, 0.1, num_samples=800, lr=5e-3, l2reg=True,
                                            return_loss_hist=True)
     assert len(losses) == 20 and np.isfinite(losses).all() and losses[-1] < losses[0]
+
+
+def test_schedule_run_in_pieces_equals_the_single_call_bit_for_bit():
+    """dsdf_reconstruct's first_step / n_steps: the lr drop at num_iterations/2 and Adam's bias correction follow the
+    absolute iteration, so 25 iterations run as 10 + 15 (moments carried over) are the 25-iteration call."""
+    dec, spec, params = make()
+    shapes = [shape(s, n=2048) for s in (4, 5)]
+    iters, num = 25, 500
+    rng = random.Random(8)
+    wins = [orec.draw_windows(1024, 1024, num, iters, rng) for _ in shapes]
+    wt = torch.tensor(wins).permute(1, 0, 2).contiguous()
+    lat0 = torch.randn(2, 256, generator=torch.Generator().manual_seed(3)) * 0.05
+    kw = dict(num_samples=num, lr=5e-3, l2reg=True)
+    hist, lat, m, v = dsdf_b200.reconstruct_batch(dec, iters, shapes, lat0, wt, 0.1, return_state=True, **kw)
+    h1, l1, m1, v1 = dsdf_b200.reconstruct_batch(dec, iters, shapes, lat0, wt, 0.1, return_state=True,
+                                                 first_step=1, n_steps=10, **kw)
+    assert torch.equal(h1[:10], hist[:10]) and float(h1[10:].abs().sum()) == 0.0
+    h2, l2, m2, v2 = dsdf_b200.reconstruct_batch(dec, iters, shapes, l1, wt, 0.1, return_state=True,
+                                                 first_step=11, n_steps=15, state=(m1, v1), **kw)
+    assert torch.equal(h2[10:], hist[10:])
+    assert torch.equal(l2, lat) and torch.equal(m2, m) and torch.equal(v2, v)
+    with pytest.raises(ValueError):
+        dsdf_b200.reconstruct_batch(dec, iters, shapes, l1, wt, 0.1, first_step=11, n_steps=15, **kw)   # no moments
+    with pytest.raises(ValueError):
+        dsdf_b200.reconstruct_batch(dec, iters, shapes, l1, wt, 0.1, first_step=20, n_steps=10, state=(m1, v1), **kw)
