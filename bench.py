@@ -420,8 +420,8 @@ def main():
 
     if rank == 0:
         # counted from the ncu launch list (profiles/): renorm | scene_fold, fwd, bwd, wgrad + 8 reducers |
-        # decoder sqnorm, coef, adam | latent adam | rowscale, weff, fold_fwd2, fold_dgrad2
-        launches_per_step = 1 + 12 + 3 + 1 + 4
+        # decoder sqnorm, coef, adam | latent adam | rowscale_weff, fold_fwd2, fold_dgrad2
+        launches_per_step = 1 + 12 + 3 + 1 + 3
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,

@@ -261,8 +261,7 @@ extern "C" int dsdf_set_weights(dsdf_handle h, const float* params, const dsdf_p
     h->pl.g[l] = lay->g_off[l];
     h->pl.b[l] = lay->b_off[l];
   }
-  k_rowscale<<<(kScaleElems * 32 + 255) / 256, 256, 0, st>>>(params, h->pl, h->scale, h->inv_norm);
-  k_weff<<<(unsigned)((kWeffElems + 255) / 256), 256, 0, st>>>(params, h->pl, h->scale, h->weff);
+  k_rowscale_weff<<<(kScaleElems * 32 + 255) / 256, 256, 0, st>>>(params, h->pl, h->scale, h->inv_norm, h->weff);
   const long long c1 = (long long)kFwdTilesTotal * (kSubBytes / 16);
   // the first-generation images are only read by the A/B kernels (DSDF_FWD_V1 / DSDF_BWD_VER=1)
   if (h->fwd_v1) k_fold_fwd<<<(unsigned)((c1 + 255) / 256), 256, 0, st>>>(h->weff, params, h->pl, h->fwd_img);

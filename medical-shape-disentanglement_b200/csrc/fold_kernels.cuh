@@ -1,8 +1,8 @@
 // Weight preparation, once per optimiser step (north_star (3): "the weight-norm scale g/||v||
 // is folded into the weights once per step"):
-//   k_rowscale   : scale[l][o] = g/||v||_row for weight-normalised layers, 1 otherwise
-//                  (nn.utils.weight_norm, reference networks/deep_sdf_decoder.py:49-53)
-//   k_weff       : fp32 effective weights in reference layout (used by the small fp32 kernels)
+//   k_rowscale_weff : scale[l][o] = g/||v||_row for weight-normalised layers, 1 otherwise
+//                  (nn.utils.weight_norm, reference networks/deep_sdf_decoder.py:49-53) and the fp32
+//                  effective weights in reference layout (read by the image builders and the small fp32 kernels)
 //   k_fold_fwd   : bf16 forward image  (B tiles [128 n x 64 k] + E tiles, layout.cuh)
 //   k_fold_dgrad : bf16 dgrad image    (B tiles [128 i x 64 o] of W^T)
 #pragma once
@@ -32,42 +32,35 @@ __host__ __device__ constexpr int scale_off(int l) {
 }
 constexpr int kScaleElems = scale_off(kNumLin);  // 3838 rows
 
-// one warp per output row
-__global__ void k_rowscale(const float* __restrict__ params, ParamLayout pl,
-                           float* __restrict__ scale, float* __restrict__ inv_norm) {
+// Weight-norm fold, one warp per output row: scale = g / ||v|| (1 for a plain Linear), inv_norm for the
+// weight-norm backward, and the effective fp32 row weff = v * scale in the reference [out, in] layout.
+__global__ void k_rowscale_weff(const float* __restrict__ params, ParamLayout pl,
+                                float* __restrict__ scale, float* __restrict__ inv_norm,
+                                float* __restrict__ weff) {
   const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
+  if (gw == 0 && lane == 0) weff[kWeffElems] = params[pl.b[8]];   // lin8 bias rides behind the weights
   if (gw >= kScaleElems) return;
   int l = 0;
   while (l + 1 < kNumLin && gw >= scale_off(l + 1)) ++l;
   const int o = gw - scale_off(l);
-  if (pl.g[l] < 0) {
-    if (lane == 0) { scale[gw] = 1.f; inv_norm[gw] = 1.f; }
-    return;
-  }
   const int in = ref_in(l);
   const float* v = params + pl.w[l] + (long long)o * in;
-  float ss = 0.f;
-  for (int i = lane; i < in; i += 32) ss = fmaf(v[i], v[i], ss);
+  float sc = 1.f;
+  if (pl.g[l] >= 0) {
+    float ss = 0.f;
+    for (int i = lane; i < in; i += 32) ss = fmaf(v[i], v[i], ss);
 #pragma unroll
-  for (int s = 16; s > 0; s >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, s);
-  if (lane == 0) {
+    for (int s = 16; s > 0; s >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, s);
     const float nrm = sqrtf(ss);
-    inv_norm[gw] = 1.f / nrm;
-    scale[gw] = params[pl.g[l] + o] / nrm;
+    sc = params[pl.g[l] + o] / nrm;
+    if (lane == 0) { inv_norm[gw] = 1.f / nrm; scale[gw] = sc; }
+  } else if (lane == 0) {
+    scale[gw] = 1.f;
+    inv_norm[gw] = 1.f;
   }
-}
-
-__global__ void k_weff(const float* __restrict__ params, ParamLayout pl,
-                       const float* __restrict__ scale, float* __restrict__ weff) {
-  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i == 0) weff[kWeffElems] = params[pl.b[8]];   // lin8 bias rides behind the weights
-  if (i >= kWeffElems) return;
-  int l = 0;
-  while (l + 1 < kNumLin && i >= weff_off(l + 1)) ++l;
-  const long long e = i - weff_off(l);
-  const int o = (int)(e / ref_in(l));
-  weff[i] = params[pl.w[l] + e] * scale[scale_off(l) + o];
+  float* w = weff + weff_off(l) + (long long)o * in;
+  for (int i = lane; i < in; i += 32) w[i] = v[i] * sc;
 }
 
 __device__ __forceinline__ float weff_at(const float* weff, int l, int o, int i) {

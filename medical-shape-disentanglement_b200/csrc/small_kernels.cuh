@@ -59,6 +59,7 @@ __global__ void k_seg_colsum(const float* __restrict__ tile_colsum, int tiles_pe
   const int b = blockIdx.x, which = blockIdx.y, c = threadIdx.x;
   const float* src = tile_colsum + ((size_t)b * tiles_per_seg * 2 + which) * kHidden + c;
   float s = 0.f;
+#pragma unroll 16
   for (int t = 0; t < tiles_per_seg; ++t) s += src[(size_t)t * 2 * kHidden];
   seg_sum[((size_t)b * 2 + which) * kHidden + c] = s;
 }
@@ -82,7 +83,7 @@ __global__ void __launch_bounds__(1024) k_lat_grad_seg(const float* __restrict__
   const float* w4 = weff + weff_off(4) + kX3 + j;       // [512][512]
   float a0 = 0.f, a4 = 0.f;
   const int c0 = part * (kHidden / 4);
-#pragma unroll 8
+#pragma unroll 16
   for (int c = c0; c < c0 + kHidden / 4; ++c) {
     a0 = fmaf(s0[c], __ldg(w0 + (size_t)c * kIn0), a0);
     a4 = fmaf(s4[c], __ldg(w4 + (size_t)c * kHidden), a4);
@@ -201,21 +202,21 @@ __global__ void k_reduce_cta(const float* __restrict__ cta_partials, int n_cta,
   if (job < 6) {
     const int ls[6] = {1, 2, 3, 5, 6, 7};
     float s = 0.f;
-#pragma unroll 4
+#pragma unroll 16
     for (int k = 0; k < n_cta; ++k) s += cta_partials[(size_t)k * kCtaPartialFloats + kPartDb + job * kHidden + c];
     if (c < ref_out(ls[job])) grads[pl.b[ls[job]] + c] = s;
   } else if (job < 12) {
     const int i = (job - 6) / 3, e = (job - 6) % 3, l = i == 0 ? 0 : 4;
     if (xyz_col(l, e) < 0) return;
     float s = 0.f;
-#pragma unroll 4
+#pragma unroll 16
     for (int k = 0; k < n_cta; ++k)
       s += cta_partials[(size_t)k * kCtaPartialFloats + kPartXyz + (i * kHidden + c) * 3 + e];
     dweff[weff_off(l) + (size_t)c * ref_in(l) + xyz_col(l, e)] = s;
   } else if (job < 14) {
     const int i = job - 12;
     float s = 0.f;
-#pragma unroll 4
+#pragma unroll 16
     for (int b = 0; b < n_seg; ++b) s += seg_sum[((size_t)b * 2 + i) * kHidden + c];
     grads[pl.b[i == 0 ? 0 : 4] + c] = s;
   } else if (job == 14) {
@@ -232,7 +233,7 @@ __global__ void k_reduce_cta(const float* __restrict__ cta_partials, int n_cta,
     }
   } else if (n_cta_dw8 > 0) {   // dW8 partials of the forward kernel's epilogue (or the v1 backward kernel);
     float s = 0.f;              // 0: the wgrad kernel produced dW8 (autograd entries: g unknown in the forward)
-#pragma unroll 4
+#pragma unroll 16
     for (int k = 0; k < n_cta_dw8; ++k) s += cta_partials[(size_t)k * kCtaPartialFloats + kPartW8 + c];
     dweff[weff_off(8) + c] = s;
   }
