@@ -1,4 +1,5 @@
-"""Loss-trajectory diagnostic: fused path vs oracle vs a 1e-6-perturbed oracle (inherent chaos)."""
+"""Loss-trajectory diagnostic (test infrastructure, not collected by pytest): fused path vs oracle vs a 1e-6-perturbed
+oracle (inherent chaos).  python tests/diag_gpu_traj.py  -> profiles/r01_trajectory_chaos*.log"""
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "medical-shape-disentanglement_b200")); sys.path.insert(0, os.path.join(ROOT, "tests"))
