@@ -293,7 +293,7 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
   } else if (warp < 12) {
     // ===================== epilogue warps =====================
     setmaxnreg_inc<176>();
-    const int t = threadIdx.x - 128;      // 0..255
+    [[maybe_unused]] const int t = threadIdx.x - 128;      // 0..255
     const int q = warp & 3;               // TMEM lane quarter this warp may access
     const int j = (warp - 4) >> 2;        // which 128 columns of a half
     const uint32_t r = q * 32 + lane;     // row inside the tile

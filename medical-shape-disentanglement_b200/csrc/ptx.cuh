@@ -70,8 +70,7 @@ __device__ __noinline__ void hang_report(uint32_t bar_addr, uint32_t parity) {
 #define DSDF_HANG_CHECK(n, addr, par)
 #endif
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  unsigned n_spin = 0;
-  (void)n_spin;
+  [[maybe_unused]] unsigned n_spin = 0;   // counted only in DSDF_HANG_TRAP builds
   while (!mbar_try_wait(bar, parity)) {
     DSDF_HANG_CHECK(n_spin, smem_u32(bar), parity);
   }
@@ -269,8 +268,7 @@ __device__ __forceinline__ void mbar_arrive_cluster_relaxed(uint32_t bar_cluster
 // wait with acquire at cluster scope (pairs with mbar_arrive_cluster from the peer CTA)
 __device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
-  unsigned n_spin = 0;
-  (void)n_spin;
+  [[maybe_unused]] unsigned n_spin = 0;   // counted only in DSDF_HANG_TRAP builds
   do {
     asm volatile(
         "{\n\t.reg .pred P;\n\t"
