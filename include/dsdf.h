@@ -116,7 +116,9 @@ size_t dsdf_train_workspace_bytes(dsdf_handle h, int64_t max_rows, int64_t max_s
  *   reg_lambda_ramp = CodeRegularizationLambda * min(1, epoch/100) (0 disables; :609-613)
  * Outputs: grads (flat, dsdf_param_layout addressing, OVERWRITTEN), lat_grad [num_scenes,256]
  * (dense, OVERWRITTEN: zero for scenes not in the batch, as nn.Embedding(sparse=False)),
- * pred [n] (tanh output, un-clamped), loss_out[0] = L1 term, loss_out[1] = regulariser term. */
+ * pred [n] (tanh output, un-clamped), loss_out[0] = L1 term, loss_out[1] = regulariser term,
+ * loss_out[3] = 0, or 1 + position of the first seg_id outside [0, num_scenes) (nn.Embedding raises on such
+ * an index; here the step runs with that id replaced by 0 and reports it -- loss_out has 4 floats). */
 int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const float* table,
                        int64_t num_scenes, const int64_t* seg_ids, int64_t n_seg,
                        int64_t rows_per_seg, const float* sdf_data, int64_t n_total,
@@ -124,10 +126,11 @@ int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const float* table,
                        size_t workspace_bytes, float* grads, float* lat_grad, float* pred,
                        float* loss_out, void* stream);
 
-/* nn.Embedding(max_norm) lookup side effect (train_deep_sdf.py:429,598): rows seg_ids[b] with
- * norm > max_norm are scaled in place by max_norm/(norm+1e-7). */
-int dsdf_renorm_rows(dsdf_handle h, float* table, const int64_t* seg_ids, int64_t n_seg,
-                     float max_norm, void* stream);
+/* nn.Embedding(max_norm) lookup side effect (train_deep_sdf.py:429,598): rows seg_ids[b] of
+ * table[num_scenes,256] with norm > max_norm are scaled in place by max_norm/(norm+1e-7); ids outside
+ * [0, num_scenes) are skipped (dsdf_train_fwd_bwd reports them). */
+int dsdf_renorm_rows(dsdf_handle h, float* table, int64_t num_scenes, const int64_t* seg_ids,
+                     int64_t n_seg, float max_norm, void* stream);
 
 /* torch.nn.utils.clip_grad_norm_(params, max_norm) + torch.optim.Adam step
  * (train_deep_sdf.py:780-784, 445-454) over one flat buffer.  max_norm <= 0: no clipping.

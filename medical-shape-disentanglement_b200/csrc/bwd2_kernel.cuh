@@ -20,7 +20,7 @@
 // (9 dgrad GEMMs, ReLU masks, tanh', bias grads).  In scene mode the latent/xyz columns of
 // dX0 and dX4 are never materialised: sum_rows dX[:, latent] = colsum(dY) * W[:, latent].
 #pragma once
-#include "bwd_kernel.cuh"
+#include "common.cuh"
 #include "fwd3_kernel.cuh"
 #include "layout.cuh"
 #include "ptx.cuh"

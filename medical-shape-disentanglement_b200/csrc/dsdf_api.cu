@@ -1,7 +1,7 @@
 // C-ABI entry points (include/dsdf.h) of the B200-native DeepSDF hot path.
 // Host side only orchestrates launches on the caller's stream; all arithmetic is in the
-// sm_100a kernels (fwd_kernel.cuh, bwd_kernel.cuh, wgrad_kernel.cuh, small_kernels.cuh,
-// fold_kernels.cuh).  There is deliberately no CPU path: if no CUDA device / kernel image is
+// sm_100a kernels (fwd3_kernel.cuh, bwd2_kernel.cuh, wgrad2_kernel.cuh, small_kernels.cuh,
+// fold_kernels.cuh, recon_kernels.cuh, dense_kernels.cuh).  There is deliberately no CPU path: if no CUDA device / kernel image is
 // available every entry fails with DSDF_ECUDA.
 #include <cuda_runtime.h>
 
@@ -13,21 +13,25 @@
 #include <vector>
 
 #include "../../include/dsdf.h"
-#include "bwd_kernel.cuh"
 #include "bwd2_kernel.cuh"
+#include "common.cuh"
 #include "dense_kernels.cuh"
 #include "fold_kernels.cuh"
-#include "fwd_kernel.cuh"
-#include "fwd2_kernel.cuh"
 #include "fwd3_kernel.cuh"
 #include "layout.cuh"
 #include "recon_kernels.cuh"
-#include "selftest.cuh"
 #include "small_kernels.cuh"
-#include "wgrad_kernel.cuh"
 #include "wgrad2_kernel.cuh"
+#ifdef DSDF_DIAG_BUILD   // diagnostics variant only (build.py DSDF_BUILD_VARIANT): descriptor self-tests, MMA-rate probe
+#include "selftest.cuh"
+#endif
 
 using namespace dsdf;
+
+// partial-sum slots of the wgrad schedule (one per (CTA pair, work segment))
+static inline int wg2_max_slots(int num_sms) { return 3 * (num_sms / 2) + 32; }
+// segments per launch of the fold-mode inference entries (per-segment E steps: 32 KB each, handle-owned)
+constexpr long long kInferSegs = 256;
 
 struct dsdf_handle_s {
   dsdf_config cfg;
@@ -35,37 +39,29 @@ struct dsdf_handle_s {
   int num_sms = 0;
   std::string err;
   // handle-owned device buffers (bf16 shadows + small fp32 derived state)
-  uint8_t* fwd_img = nullptr;
-  uint8_t* dg_img = nullptr;
-  uint8_t* w2_img = nullptr;     // v2 forward K-step stream
-  uint8_t* dg2_img = nullptr;    // v2 dgrad K-step stream
-  int bwd_ver = 2;               // DSDF_BWD_VER=1: previous-generation backward kernel (A/B timing)
-  uint8_t* scene_e = nullptr;    // fold-mode per-segment E steps for the inference entries
-  long long scene_e_cap = 0;     // segments
-  int fwd_cl = 2;                // cluster size of the v2 forward chain (DSDF_FWD_CL = 1|2|4)
-  int fwd_ver = 3;               // DSDF_FWD_VER=2: previous-generation forward kernel (A/B timing)
-  int fwd_cg = 2;                // DSDF_FWD_CG=1: never pair CTAs (cta_group::1 only)
-  bool fwd_v1 = false;           // DSDF_FWD_V1=1: previous-generation forward kernel (A/B timing)
-  unsigned long long* dbg = nullptr;   // DSDF_DBG=1: per-CTA cycle counters (dsdf_debug_read)
+  uint8_t* w2_img = nullptr;     // forward K-step stream
+  uint8_t* dg2_img = nullptr;    // dgrad K-step stream
+  uint8_t* scene_e = nullptr;    // fold-mode per-segment E steps for the inference entries (kInferSegs, fixed)
+  // A/B knobs: fixed in the product build; the diagnostics variant (-DDSDF_DIAG_BUILD) reads DSDF_FWD_CG,
+  // DSDF_WG_QUAD, DSDF_DW8_WGRAD from the environment at dsdf_create
+  int fwd_cg = 2;                // 1: never pair CTAs (cta_group::1 only)
+  int dw8_wgrad = 0;             // 1: dW8 as a wgrad item instead of the forward epilogue
+  int wg_quad = 1;               // 0: item-major wgrad schedule (every out-chunk pair re-reads X from HBM)
+  unsigned long long* dbg = nullptr;   // diagnostics variant + DSDF_DBG=1: per-CTA cycle counters (dsdf_debug_read)
   float* weff = nullptr;
   float* scale = nullptr;
   float* inv_norm = nullptr;
-  WgItem* wg_items = nullptr;
-  int wg_items_cap = 0;
-  long long wg_items_tiles = -1;
-  int wg_n_items = 0;
-  WgLayout wg_layout{};
-  // v2 wgrad schedule (rebuilt when the tile count changes)
+  // wgrad schedule (rebuilt on the host when the tile count changes; fixed-capacity device buffers + pinned
+  // staging, uploaded asynchronously on the caller's stream: no allocation, no synchronisation per call)
   WgSeg* wg2_segs = nullptr;
   int* wg2_seg_begin = nullptr;
+  uint8_t* wg2_stage = nullptr;        // pinned host staging for both arrays
+  cudaEvent_t wg2_uploaded = nullptr;  // last upload has been consumed by the copy engine
   long long wg2_tiles = -1;
   int wg2_with_l8 = -1;          // schedule currently holds a lin8 item (autograd entries) or not (fused step)
   int wg2_pairs = 0;
   int wg2_slots = 0;
   Wg2Layout wg2_layout{};
-  int wg_ver = 2;                // DSDF_WG_VER=1: previous-generation wgrad kernel
-  int dw8_wgrad = 0;             // DSDF_DW8_WGRAD=1: dW8 as a wgrad item (previous split), for A/B timing
-  int wg_quad = 1;               // DSDF_WG_QUAD=0: item-major schedule (every out-chunk pair re-reads X from HBM)
   ParamLayout pl{};
   const float* params_ptr = nullptr;   // caller's flat fp32 parameters at the last dsdf_set_weights
   bool weights_set = false;
@@ -107,20 +103,6 @@ static thread_local std::string g_err;
 
 static int set_kernel_attrs(dsdf_handle h) {
   if (h->attrs_set) return DSDF_OK;
-  CU(h, cudaFuncSetAttribute(k_forward<MODE_DENSE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmemBytes));
-  CU(h, cudaFuncSetAttribute(k_forward<MODE_TABLE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmemBytes));
-  CU(h, cudaFuncSetAttribute(k_forward<MODE_GRID, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmemBytes));
-  CU(h, cudaFuncSetAttribute(k_forward<MODE_TABLE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmemBytes));
-#define F2ATTR(MODE, FOLD, TRAIN)                                                                                   \
-  CU(h, cudaFuncSetAttribute(k_forward2<MODE, FOLD, TRAIN, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kF2SmemBytes)); \
-  CU(h, cudaFuncSetAttribute(k_forward2<MODE, FOLD, TRAIN, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kF2SmemBytes)); \
-  CU(h, cudaFuncSetAttribute(k_forward2<MODE, FOLD, TRAIN, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kF2SmemBytes));
-  F2ATTR(MODE_DENSE, false, false)
-  F2ATTR(MODE_TABLE, false, false)
-  F2ATTR(MODE_TABLE, true, false)
-  F2ATTR(MODE_GRID, true, false)
-  F2ATTR(MODE_TABLE, true, true)
-#undef F2ATTR
 #define F3ATTR(MODE, FOLD, TRAIN)                                                                                   \
   CU(h, cudaFuncSetAttribute(k_forward3<MODE, FOLD, TRAIN, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, F3<1>::kSmemBytes)); \
   CU(h, cudaFuncSetAttribute(k_forward3<MODE, FOLD, TRAIN, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, F3<2>::kSmemBytes));
@@ -135,12 +117,9 @@ static int set_kernel_attrs(dsdf_handle h) {
   CU(h, cudaFuncSetAttribute(k_forward3<MODE_TABLE, true, true, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, F3<2>::kSmemBytes));
   CU(h, cudaFuncSetAttribute(k_backward2<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, B2<1>::kSmemBytes));
   CU(h, cudaFuncSetAttribute(k_backward2<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, B2<2>::kSmemBytes));
-  CU(h, cudaFuncSetAttribute(k_backward, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmemBytes));
   CU(h, cudaFuncSetAttribute(k_backward2<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, B2<1>::kSmemBytes));
   CU(h, cudaFuncSetAttribute(k_backward2<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, B2<2>::kSmemBytes));
-  CU(h, cudaFuncSetAttribute(k_wgrad, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgSmemBytes));
   CU(h, cudaFuncSetAttribute(k_wgrad2, cudaFuncAttributeMaxDynamicSharedMemorySize, kW2SmemBytes));
-  CU(h, cudaFuncSetAttribute(k_selftest_gemm, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
   h->attrs_set = true;
   return DSDF_OK;
 }
@@ -176,30 +155,23 @@ extern "C" int dsdf_create(const dsdf_config* cfg, dsdf_handle* out) {
               cfg->device, prop.major, prop.minor);
   }
   h->num_sms = prop.multiProcessorCount;
-  if (const char* e = getenv("DSDF_FWD_CL")) {
-    const int cl = atoi(e);
-    if (cl == 1 || cl == 2 || cl == 4) h->fwd_cl = cl;
-  }
-  if (const char* e = getenv("DSDF_FWD_V1")) h->fwd_v1 = atoi(e) != 0;
-  if (const char* e = getenv("DSDF_FWD_VER")) h->fwd_ver = atoi(e) == 2 ? 2 : 3;
+#ifdef DSDF_DIAG_BUILD
   if (const char* e = getenv("DSDF_FWD_CG")) h->fwd_cg = atoi(e) == 1 ? 1 : 2;
-  if (const char* e = getenv("DSDF_BWD_VER")) h->bwd_ver = atoi(e) == 1 ? 1 : 2;
-  if (const char* e = getenv("DSDF_WG_VER")) h->wg_ver = atoi(e) == 1 ? 1 : 2;
   if (const char* e = getenv("DSDF_WG_QUAD")) h->wg_quad = atoi(e) != 0;
   if (const char* e = getenv("DSDF_DW8_WGRAD")) h->dw8_wgrad = atoi(e) != 0;
-  if (h->bwd_ver == 1) h->wg_ver = 1;   // the v1 backward computes dW8 itself
-#ifdef DSDF_ARCH_SIREN
-  // the sine epilogues exist in the current-generation kernels only
-  h->fwd_v1 = false; h->fwd_ver = 3; h->bwd_ver = 2; h->wg_ver = 2;
-#endif
   if (const char* e = getenv("DSDF_DBG")) {
     if (atoi(e) != 0 && cudaMalloc(&h->dbg, (size_t)h->num_sms * kDbgSlots * 8) == cudaSuccess)
       cudaMemset(h->dbg, 0, (size_t)h->num_sms * kDbgSlots * 8);
   }
-  bool ok = cudaMalloc(&h->fwd_img, (size_t)kFwdTilesTotal * kSubBytes) == cudaSuccess &&
-            cudaMalloc(&h->w2_img, (size_t)kW2Steps * kStepBytes) == cudaSuccess &&
-            cudaMalloc(&h->dg_img, (size_t)kDgTilesTotal * kSubBytes) == cudaSuccess &&
+#endif
+  const size_t sched_bytes = (size_t)wg2_max_slots(h->num_sms) * sizeof(WgSeg) + (size_t)(h->num_sms + 2) * sizeof(int);
+  bool ok = cudaMalloc(&h->w2_img, (size_t)kW2Steps * kStepBytes) == cudaSuccess &&
             cudaMalloc(&h->dg2_img, (size_t)kDg2Steps * kStepBytes) == cudaSuccess &&
+            cudaMalloc(&h->scene_e, (size_t)kInferSegs * kSceneESteps * kStepBytes) == cudaSuccess &&
+            cudaMalloc(&h->wg2_segs, (size_t)wg2_max_slots(h->num_sms) * sizeof(WgSeg)) == cudaSuccess &&
+            cudaMalloc(&h->wg2_seg_begin, (size_t)(h->num_sms + 2) * sizeof(int)) == cudaSuccess &&
+            cudaHostAlloc((void**)&h->wg2_stage, sched_bytes, cudaHostAllocDefault) == cudaSuccess &&
+            cudaEventCreateWithFlags(&h->wg2_uploaded, cudaEventDisableTiming) == cudaSuccess &&
             cudaMalloc(&h->weff, (size_t)(kWeffElems + 16) * 4) == cudaSuccess &&
             cudaMalloc(&h->scale, (size_t)kScaleElems * 4) == cudaSuccess &&
             cudaMalloc(&h->inv_norm, (size_t)kScaleElems * 4) == cudaSuccess;
@@ -220,17 +192,16 @@ extern "C" int dsdf_create(const dsdf_config* cfg, dsdf_handle* out) {
 
 extern "C" int dsdf_destroy(dsdf_handle h) {
   if (!h) return DSDF_OK;
-  cudaFree(h->fwd_img);
-  cudaFree(h->dg_img);
   cudaFree(h->w2_img);
   cudaFree(h->dg2_img);
   cudaFree(h->scene_e);
   cudaFree(h->weff);
   cudaFree(h->scale);
   cudaFree(h->inv_norm);
-  cudaFree(h->wg_items);
   cudaFree(h->wg2_segs);
   cudaFree(h->wg2_seg_begin);
+  if (h->wg2_stage) cudaFreeHost(h->wg2_stage);
+  if (h->wg2_uploaded) cudaEventDestroy(h->wg2_uploaded);
   cudaFree(h->dbg);
   for (cudaEvent_t e : h->prof_events) cudaEventDestroy(e);
   delete h;
@@ -262,13 +233,8 @@ extern "C" int dsdf_set_weights(dsdf_handle h, const float* params, const dsdf_p
     h->pl.b[l] = lay->b_off[l];
   }
   k_rowscale_weff<<<(kScaleElems * 32 + 255) / 256, 256, 0, st>>>(params, h->pl, h->scale, h->inv_norm, h->weff);
-  const long long c1 = (long long)kFwdTilesTotal * (kSubBytes / 16);
-  // the first-generation images are only read by the A/B kernels (DSDF_FWD_V1 / DSDF_BWD_VER=1)
-  if (h->fwd_v1) k_fold_fwd<<<(unsigned)((c1 + 255) / 256), 256, 0, st>>>(h->weff, params, h->pl, h->fwd_img);
   const long long c3 = (long long)kW2Steps * (kStepBytes / 16);
   k_fold_fwd2<<<(unsigned)((c3 + 255) / 256), 256, 0, st>>>(h->weff, params, h->pl, h->w2_img);
-  const long long c2 = (long long)kDgTilesTotal * (kSubBytes / 16);
-  if (h->bwd_ver == 1) k_fold_dgrad<<<(unsigned)((c2 + 255) / 256), 256, 0, st>>>(h->weff, h->dg_img);
   const long long c4 = (long long)kDg2Steps * (kStepBytes / 16);
   k_fold_dgrad2<<<(unsigned)((c4 + 255) / 256), 256, 0, st>>>(h->weff, h->dg2_img);
   CU(h, cudaGetLastError());
@@ -277,42 +243,6 @@ extern "C" int dsdf_set_weights(dsdf_handle h, const float* params, const dsdf_p
   return DSDF_OK;
 }
 
-static unsigned grid_for(dsdf_handle h, long long n_rows) {
-  const long long tiles = (n_rows + kTileM - 1) / kTileM;
-  return (unsigned)(tiles < h->num_sms ? tiles : h->num_sms);
-}
-
-// ---- v2 forward launcher: persistent grid of clusters ------------------------------------------
-template <int MODE, bool FOLD, bool TRAIN, int CL>
-static cudaError_t launch_fwd2_cl(dsdf_handle h, const FwdArgs& a, cudaStream_t st) {
-  const long long tiles = (a.n_rows + kTileM - 1) / kTileM;
-  long long g = tiles < h->num_sms ? tiles : h->num_sms;
-  g = (g / CL) * CL;
-  if (g < CL) g = CL;
-  cudaLaunchConfig_t cfg;
-  memset(&cfg, 0, sizeof(cfg));
-  cfg.gridDim = dim3((unsigned)g);
-  cfg.blockDim = dim3(kF2Threads);
-  cfg.dynamicSmemBytes = kF2SmemBytes;
-  cfg.stream = st;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = CL;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
-  return cudaLaunchKernelEx(&cfg, k_forward2<MODE, FOLD, TRAIN, CL>, a);
-}
-template <int MODE, bool FOLD, bool TRAIN>
-static cudaError_t launch_fwd2(dsdf_handle h, const FwdArgs& a, cudaStream_t st) {
-  const long long tiles = (a.n_rows + kTileM - 1) / kTileM;
-  int cl = h->fwd_cl;
-  while (cl > 1 && tiles < cl) cl >>= 1;
-  if (cl == 4) return launch_fwd2_cl<MODE, FOLD, TRAIN, 4>(h, a, st);
-  if (cl == 2) return launch_fwd2_cl<MODE, FOLD, TRAIN, 2>(h, a, st);
-  return launch_fwd2_cl<MODE, FOLD, TRAIN, 1>(h, a, st);
-}
 // ---- v3 forward launcher: persistent grid, CTA pairs (cta_group::2) when `pair_ok` -------------
 template <int MODE, bool FOLD, bool TRAIN, int CG, bool DROP = false>
 static cudaError_t launch_fwd3_cg(dsdf_handle h, const FwdArgs& a, cudaStream_t st) {
@@ -339,20 +269,18 @@ static cudaError_t launch_fwd3_cg(dsdf_handle h, const FwdArgs& a, cudaStream_t 
 // shorter than 256 rows-aligned, see callers)
 template <int MODE, bool FOLD, bool TRAIN, bool DROP = false>
 static cudaError_t launch_fwd(dsdf_handle h, const FwdArgs& a, cudaStream_t st, bool pair_ok) {
-  if (h->fwd_ver == 2 && !DROP) return launch_fwd2<MODE, FOLD, TRAIN>(h, a, st);
   const long long tiles = (a.n_rows + kTileM - 1) / kTileM;
   if (pair_ok && h->fwd_cg == 2 && tiles >= 2) return launch_fwd3_cg<MODE, FOLD, TRAIN, 2, DROP>(h, a, st);
   return launch_fwd3_cg<MODE, FOLD, TRAIN, 1, DROP>(h, a, st);
 }
-// per-segment E steps for the fold-mode inference entries (handle-owned, grown on demand)
-static int ensure_scene_e(dsdf_handle h, long long n_seg) {
-  if (n_seg <= h->scene_e_cap) return DSDF_OK;
-  cudaFree(h->scene_e);
-  h->scene_e = nullptr;
-  h->scene_e_cap = 0;
-  CU(h, cudaMalloc(&h->scene_e, (size_t)n_seg * kSceneESteps * kStepBytes));
-  h->scene_e_cap = n_seg;
-  return DSDF_OK;
+// common fields of every forward launch
+static void fwd_args_init(dsdf_handle h, FwdArgs& a, long long n) {
+  memset(&a, 0, sizeof(a));
+  a.w8 = h->weff + weff_off(8);
+  a.b8 = h->weff + kWeffElems;   // lin8 bias rides behind the effective weights (k_rowscale_weff)
+  a.n_rows = n;
+  a.w2img = h->w2_img;
+  a.dbg = h->dbg;
 }
 
 extern "C" int dsdf_forward_dense(dsdf_handle h, const float* input, int64_t n, float* out,
@@ -361,20 +289,10 @@ extern "C" int dsdf_forward_dense(dsdf_handle h, const float* input, int64_t n, 
   if (!h->weights_set) DSDF_FAIL(h, DSDF_EINVAL, "dsdf_set_weights has not been called");
   if (n <= 0) return DSDF_OK;
   FwdArgs a;
-  memset(&a, 0, sizeof(a));
-  a.wimg = h->fwd_img;
-  a.w8 = h->weff + weff_off(8);
-  a.b8 = h->weff + kWeffElems;  // see k_copy_b8 below
-  a.n_rows = n;
+  fwd_args_init(h, a, n);
   a.input = input;
   a.out = out;
-  a.w2img = h->w2_img;
-  a.dbg = h->dbg;
-  if (h->fwd_v1) {
-    k_forward<MODE_DENSE, false><<<grid_for(h, n), kFwdThreads, kFwdSmemBytes, (cudaStream_t)stream>>>(a);
-  } else {
-    CU(h, (launch_fwd<MODE_DENSE, false, false>(h, a, (cudaStream_t)stream, true)));
-  }
+  CU(h, (launch_fwd<MODE_DENSE, false, false>(h, a, (cudaStream_t)stream, true)));
   CU(h, cudaGetLastError());
   return DSDF_OK;
 }
@@ -388,33 +306,37 @@ extern "C" int dsdf_forward_segments(dsdf_handle h, const float* table, const in
   if (seg_ids && (n_seg <= 0 || rows_per_seg <= 0 || n_seg * rows_per_seg < n))
     DSDF_FAIL(h, DSDF_EINVAL, "segments do not cover n rows");
   if (n <= 0) return DSDF_OK;
+  cudaStream_t st = (cudaStream_t)stream;
   FwdArgs a;
-  memset(&a, 0, sizeof(a));
-  a.wimg = h->fwd_img;
-  a.w8 = h->weff + weff_off(8);
-  a.b8 = h->weff + kWeffElems;
-  a.n_rows = n;
+  fwd_args_init(h, a, n);
   a.table = table;
   a.seg_ids = (const long long*)seg_ids;
   a.rows_per_seg = seg_ids ? rows_per_seg : n;
   a.xyzs = xyz;
   a.xyz_stride = xyz_stride;
   a.out = out;
-  a.w2img = h->w2_img;
-  a.dbg = h->dbg;
-  if (h->fwd_v1) {
-    k_forward<MODE_TABLE, false><<<grid_for(h, n), kFwdThreads, kFwdSmemBytes, (cudaStream_t)stream>>>(a);
-  } else if (!seg_ids || rows_per_seg % kTileM == 0) {
-    // every 128-row tile lies inside one segment: fold W[:, latent] z into a per-segment bias
+  if (!seg_ids || rows_per_seg % kTileM == 0) {
+    // every 128-row tile lies inside one segment: fold W[:, latent] z into a per-segment bias.  The
+    // per-segment E steps live in the handle's fixed kInferSegs-segment buffer: longer id lists go in chunks.
     const long long ns = seg_ids ? n_seg : 1;
-    int rc = ensure_scene_e(h, ns);
-    if (rc != DSDF_OK) return rc;
+    const bool pair_ok = !seg_ids || rows_per_seg % (2 * kTileM) == 0;
     a.scene_e = h->scene_e;
-    k_scene_fold<<<dim3((unsigned)ns, 2, kFoldSplit), 512, 0, (cudaStream_t)stream>>>(
-        h->weff, h->params_ptr, h->pl, table, (const long long*)seg_ids, h->scene_e);
-    CU(h, (launch_fwd<MODE_TABLE, true, false>(h, a, (cudaStream_t)stream, !seg_ids || rows_per_seg % (2 * kTileM) == 0)));
+    for (long long s0 = 0; s0 < ns; s0 += kInferSegs) {
+      const long long cs = ns - s0 < kInferSegs ? ns - s0 : kInferSegs;
+      const long long r0 = s0 * a.rows_per_seg;
+      if (r0 >= n) break;
+      long long cn = cs * a.rows_per_seg;
+      if (cn > n - r0) cn = n - r0;
+      a.seg_ids = seg_ids ? (const long long*)seg_ids + s0 : nullptr;
+      a.xyzs = xyz + r0 * xyz_stride;
+      a.out = out + r0;
+      a.n_rows = cn;
+      k_scene_fold<<<dim3((unsigned)cs, 2, kFoldSplit), 512, 0, st>>>(h->weff, h->params_ptr, h->pl, table,
+                                                                  a.seg_ids, h->scene_e);
+      CU(h, (launch_fwd<MODE_TABLE, true, false>(h, a, st, pair_ok)));
+    }
   } else {
-    CU(h, (launch_fwd<MODE_TABLE, false, false>(h, a, (cudaStream_t)stream, true)));
+    CU(h, (launch_fwd<MODE_TABLE, false, false>(h, a, st, true)));
   }
   CU(h, cudaGetLastError());
   return DSDF_OK;
@@ -428,28 +350,16 @@ extern "C" int dsdf_decode_grid(dsdf_handle h, const float* latent, int32_t grid
   if (grid_n < 2 || lo < 0 || hi > n3 || lo > hi) DSDF_FAIL(h, DSDF_EINVAL, "bad grid range");
   if (hi == lo) return DSDF_OK;
   FwdArgs a;
-  memset(&a, 0, sizeof(a));
-  a.wimg = h->fwd_img;
-  a.w8 = h->weff + weff_off(8);
-  a.b8 = h->weff + kWeffElems;
-  a.n_rows = hi - lo;
+  fwd_args_init(h, a, hi - lo);
   a.table = latent;
   a.grid_n = grid_n;
   a.grid_lo = lo;
   a.voxel_size = (float)(2.0 / (grid_n - 1));
   a.out = out;
-  a.w2img = h->w2_img;
-  a.dbg = h->dbg;
-  if (h->fwd_v1) {
-    k_forward<MODE_GRID, false><<<grid_for(h, a.n_rows), kFwdThreads, kFwdSmemBytes, (cudaStream_t)stream>>>(a);
-  } else {
-    int rc = ensure_scene_e(h, 1);
-    if (rc != DSDF_OK) return rc;
-    a.scene_e = h->scene_e;
-    k_scene_fold<<<dim3(1, 2, kFoldSplit), 512, 0, (cudaStream_t)stream>>>(h->weff, h->params_ptr, h->pl, latent,
-                                                               nullptr, h->scene_e);
-    CU(h, (launch_fwd<MODE_GRID, true, false>(h, a, (cudaStream_t)stream, true)));
-  }
+  a.scene_e = h->scene_e;
+  k_scene_fold<<<dim3(1, 2, kFoldSplit), 512, 0, (cudaStream_t)stream>>>(h->weff, h->params_ptr, h->pl, latent,
+                                                             nullptr, h->scene_e);
+  CU(h, (launch_fwd<MODE_GRID, true, false>(h, a, (cudaStream_t)stream, true)));
   CU(h, cudaGetLastError());
   return DSDF_OK;
 }
@@ -476,8 +386,6 @@ extern "C" int dsdf_grid_coords(dsdf_handle h, int32_t grid_n, int64_t lo, int64
 }
 
 // ------------------------------------------------------------------------------------ training
-// partial-sum slots of the v2 wgrad schedule (one per (CTA pair, work segment))
-static inline int wg2_max_slots(int num_sms) { return 3 * (num_sms / 2) + 32; }
 
 namespace {
 struct Ws {
@@ -500,7 +408,6 @@ struct Ws {
 };
 inline size_t al(size_t x) { return (x + 1023) & ~(size_t)1023; }
 
-constexpr int kWgMaxItems = 26 * 8;
 
 Ws carve(uint8_t* base, long long max_rows, long long max_seg, int num_sms) {
   const size_t tiles = (size_t)((max_rows + kTileM - 1) / kTileM);
@@ -514,9 +421,7 @@ Ws carve(uint8_t* base, long long max_rows, long long max_seg, int num_sms) {
   w.tile_colsum = (float*)take(tiles * 2 * kHidden * 4);
   w.cta_partials = (float*)take((size_t)num_sms * kCtaPartialFloats * 4);
   {
-    const size_t v1 = (size_t)kWgMaxItems * kTileM * kHidden * 4;
-    const size_t v2 = (size_t)wg2_max_slots(num_sms) * 256 * kHidden * 4;
-    w.wg_partials = (float*)take(v1 > v2 ? v1 : v2);
+    w.wg_partials = (float*)take((size_t)wg2_max_slots(num_sms) * 256 * kHidden * 4);
   }
   w.seg_sum = (float*)take((size_t)max_seg * 2 * kHidden * 4);
   w.dlat_seg = (float*)take((size_t)max_seg * kLatent * 4);
@@ -534,49 +439,6 @@ Ws carve(uint8_t* base, long long max_rows, long long max_seg, int num_sms) {
 extern "C" size_t dsdf_train_workspace_bytes(dsdf_handle h, int64_t max_rows, int64_t max_segments) {
   if (!h) return 0;
   return carve(nullptr, max_rows, max_segments, h->num_sms).total + 1024;
-}
-
-// wgrad work items for `tiles` row tiles: layers 1..7, out chunks, K splits
-static int build_wg_items(dsdf_handle h, long long tiles, cudaStream_t st) {
-  if (h->wg_items_tiles == tiles) return DSDF_OK;
-  int base_items = 0;
-  for (int l = 1; l <= 7; ++l) base_items += (l == 3) ? 2 : 4;   // 26
-  int n_split = h->num_sms / base_items;
-  if (n_split < 1) n_split = 1;
-  if (n_split > 8) n_split = 8;
-  if (n_split > tiles) n_split = (int)(tiles > 0 ? tiles : 1);
-  std::vector<WgItem> items;
-  int idx = 0;
-  for (int l = 1; l <= 7; ++l) {
-    h->wg_layout.item_base[l] = idx;
-    const int n_oc = (l == 3) ? 2 : 4;
-    for (int oc = 0; oc < n_oc; ++oc)
-      for (int s = 0; s < n_split; ++s) {
-        WgItem it;
-        it.layer = l;
-        it.oc = oc;
-        it.n_sub = (l == 4) ? 4 : 8;
-        it.split = s;
-        it.tile_lo = tiles * s / n_split;
-        it.tile_hi = tiles * (s + 1) / n_split;
-        items.push_back(it);
-        ++idx;
-      }
-  }
-  h->wg_layout.item_base[0] = 0;
-  h->wg_layout.n_split = n_split;
-  if ((int)items.size() > h->wg_items_cap) {
-    cudaFree(h->wg_items);
-    h->wg_items = nullptr;
-    CU(h, cudaMalloc(&h->wg_items, items.size() * sizeof(WgItem)));
-    h->wg_items_cap = (int)items.size();
-  }
-  CU(h, cudaMemcpyAsync(h->wg_items, items.data(), items.size() * sizeof(WgItem),
-                        cudaMemcpyHostToDevice, st));
-  CU(h, cudaStreamSynchronize(st));  // items vector goes out of scope; once per shape change
-  h->wg_n_items = (int)items.size();
-  h->wg_items_tiles = tiles;
-  return DSDF_OK;
 }
 
 // v2 wgrad schedule: items (layer 1..8, 256-row out chunk) x tiles, cut into equal-cost contiguous
@@ -681,15 +543,17 @@ static int build_wg2_schedule(dsdf_handle h, long long tiles, cudaStream_t st, b
     if (sg.slot < h->wg2_layout.slot_lo[item]) h->wg2_layout.slot_lo[item] = sg.slot;
     if (sg.slot + 1 > h->wg2_layout.slot_hi[item]) h->wg2_layout.slot_hi[item] = sg.slot + 1;
   }
-  cudaFree(h->wg2_segs);
-  cudaFree(h->wg2_seg_begin);
-  h->wg2_segs = nullptr;
-  h->wg2_seg_begin = nullptr;
-  CU(h, cudaMalloc(&h->wg2_segs, segs.size() * sizeof(WgSeg)));
-  CU(h, cudaMalloc(&h->wg2_seg_begin, seg_begin.size() * sizeof(int)));
-  CU(h, cudaMemcpyAsync(h->wg2_segs, segs.data(), segs.size() * sizeof(WgSeg), cudaMemcpyHostToDevice, st));
-  CU(h, cudaMemcpyAsync(h->wg2_seg_begin, seg_begin.data(), seg_begin.size() * sizeof(int), cudaMemcpyHostToDevice, st));
-  CU(h, cudaStreamSynchronize(st));   // host vectors go out of scope; once per shape change
+  if ((int)seg_begin.size() > h->num_sms + 2) DSDF_FAIL(h, DSDF_EINVAL, "internal: wgrad schedule has too many CTA pairs");
+  // upload through the pinned staging buffer, asynchronously on the caller's stream; the staging bytes may be
+  // rewritten only after the previous upload has been consumed (an event wait that happens on a shape change only)
+  CU(h, cudaEventSynchronize(h->wg2_uploaded));
+  WgSeg* stage_segs = reinterpret_cast<WgSeg*>(h->wg2_stage);
+  int* stage_begin = reinterpret_cast<int*>(h->wg2_stage + (size_t)wg2_max_slots(h->num_sms) * sizeof(WgSeg));
+  memcpy(stage_segs, segs.data(), segs.size() * sizeof(WgSeg));
+  memcpy(stage_begin, seg_begin.data(), seg_begin.size() * sizeof(int));
+  CU(h, cudaMemcpyAsync(h->wg2_segs, stage_segs, segs.size() * sizeof(WgSeg), cudaMemcpyHostToDevice, st));
+  CU(h, cudaMemcpyAsync(h->wg2_seg_begin, stage_begin, seg_begin.size() * sizeof(int), cudaMemcpyHostToDevice, st));
+  CU(h, cudaEventRecord(h->wg2_uploaded, st));
   h->wg2_pairs = n_pairs;
   h->wg2_slots = (int)segs.size();
   h->wg2_tiles = tiles;
@@ -699,7 +563,7 @@ static int build_wg2_schedule(dsdf_handle h, long long tiles, cudaStream_t st, b
 
 // wgrad GEMMs (lin1..lin8) over the stashed images + ordered split-K reduction into dweff
 static int launch_wgrad2(dsdf_handle h, const uint8_t* xstash, const uint8_t* dystash, const uint8_t* g_img,
-                         float* partials, float* dweff, cudaStream_t st) {
+                         float* partials, float* dweff, cudaStream_t st, bool prof = false) {
   Wg2Args w2;
   w2.segs = h->wg2_segs;
   w2.seg_begin = h->wg2_seg_begin;
@@ -721,6 +585,7 @@ static int launch_wgrad2(dsdf_handle h, const uint8_t* xstash, const uint8_t* dy
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   CU(h, cudaLaunchKernelEx(&cfg, k_wgrad2, w2));
+  if (prof) prof_mark(h, st);
   k_reduce_wgrad2<<<dim3(kHidden, h->wg2_with_l8 ? 8 : 7), kHidden, 0, st>>>(partials, h->wg2_layout, dweff);
   return DSDF_OK;
 }
@@ -769,9 +634,7 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
     DSDF_FAIL(h, DSDF_EUNSUPPORTED,
               "fused step needs scene-contiguous segments with SamplesPerScene %% 128 == 0 (got %lld)",
               (long long)rows_per_seg);
-  if (n_total <= 0) DSDF_FAIL(h, DSDF_EINVAL, "n_total must be positive");
-  if (h->drop.layers != 0 && (h->fwd_v1 || h->bwd_ver == 1))
-    DSDF_FAIL(h, DSDF_EUNSUPPORTED, "dropout needs the v3 forward / v2 backward kernels");
+  if (n_total <= 0 || num_scenes <= 0) DSDF_FAIL(h, DSDF_EINVAL, "n_total and num_scenes must be positive");
   cudaStream_t st = (cudaStream_t)stream;
   const long long n = n_seg * rows_per_seg;
   const long long tiles = n / kTileM;
@@ -781,22 +644,17 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   if ((size_t)(base - (uint8_t*)workspace) + w.total > workspace_bytes)
     DSDF_FAIL(h, DSDF_ENOMEM, "workspace too small: need %zu bytes, have %zu", w.total + 1024,
               workspace_bytes);
-  // current-generation kernels: the forward epilogue accumulates dW8 = g^T X8 itself (no X8 stash, no lin8
-  // wgrad item); DSDF_DW8_WGRAD=1 keeps the previous split for A/B timing
-  const bool dw8_fwd = h->wg_ver == 2 && !h->fwd_v1 && h->fwd_ver == 3 && !h->dw8_wgrad;
-  int rc = h->wg_ver == 1 ? build_wg_items(h, tiles, st) : build_wg2_schedule(h, tiles, st, !dw8_fwd);
+  // the forward epilogue accumulates dW8 = g^T X8 itself (no X8 stash, no lin8 wgrad item); the diagnostics
+  // variant can keep the previous split (dW8 as a wgrad item) for A/B timing
+  const bool dw8_fwd = !h->dw8_wgrad;
+  int rc = build_wg2_schedule(h, tiles, st, !dw8_fwd);
   if (rc != DSDF_OK) return rc;
 
   const float inv_n = 1.0f / (float)n_total;
-  const unsigned grid = grid_for(h, n);
 
   // ---- forward (gather + 9 layers + tanh + clamped L1 + dL/ds), stashing activations
   FwdArgs fa;
-  memset(&fa, 0, sizeof(fa));
-  fa.wimg = h->fwd_img;
-  fa.w8 = h->weff + weff_off(8);
-  fa.b8 = h->weff + kWeffElems;
-  fa.n_rows = n;
+  fwd_args_init(h, fa, n);
   fa.table = table;
   fa.seg_ids = (const long long*)seg_ids;
   fa.rows_per_seg = rows_per_seg;
@@ -815,11 +673,9 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   fa.inv_n_total = inv_n;
   const bool prof = h->profile && (int)h->prof_events.size() + kProfEventsPerCall <= kProfMaxCalls * kProfEventsPerCall;
   if (prof) prof_mark(h, st);
-  fa.w2img = h->w2_img;
-  fa.dbg = h->dbg;
   fa.scene_e = w.scene_e;
   fa.relu_mask = w.relu_mask;
-  fa.g_img = (h->wg_ver == 2 && !dw8_fwd) ? w.g_img : nullptr;
+  fa.g_img = dw8_fwd ? nullptr : w.g_img;
   if (dw8_fwd) {
     fa.dw8_partials = w.cta_partials + kPartW8;
     fa.dw8_stride = kCtaPartialFloats;
@@ -834,92 +690,45 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
     if (g < cg) g = cg;
     fwd_ctas = (int)g;
   }
-  if (h->fwd_v1) {
-    k_forward<MODE_TABLE, true><<<grid, kFwdThreads, kFwdSmemBytes, st>>>(fa);
-  } else {
-    k_scene_fold<<<dim3((unsigned)n_seg, 2, kFoldSplit), 512, 0, st>>>(h->weff, params, h->pl, table,
-                                                          (const long long*)seg_ids, w.scene_e);
-    fa.drop = h->drop;
-    if (h->drop.layers != 0)
-      CU(h, (launch_fwd<MODE_TABLE, true, true, true>(h, fa, st, pair_ok)));
-    else
-      CU(h, (launch_fwd<MODE_TABLE, true, true>(h, fa, st, pair_ok)));
-  }
+  // seg_ids outside [0, num_scenes) would index the latent table out of bounds (nn.Embedding raises): the step
+  // runs on a sanitised copy and reports the first bad position in loss_out[3]
+  k_sanitize_ids<<<1, 256, 0, st>>>((const long long*)seg_ids, (int)n_seg, num_scenes, w.ids, loss_out + 3);
+  seg_ids = (const int64_t*)w.ids;
+  fa.seg_ids = w.ids;
+  k_scene_fold<<<dim3((unsigned)n_seg, 2, kFoldSplit), 512, 0, st>>>(h->weff, params, h->pl, table,
+                                                        (const long long*)seg_ids, w.scene_e);
+  fa.drop = h->drop;
+  if (h->drop.layers != 0)
+    CU(h, (launch_fwd<MODE_TABLE, true, true, true>(h, fa, st, pair_ok)));
+  else
+    CU(h, (launch_fwd<MODE_TABLE, true, true>(h, fa, st, pair_ok)));
   if (prof) prof_mark(h, st);
 
   // ---- backward dgrad chain + reducers
-  BwdArgs ba;
-  memset(&ba, 0, sizeof(ba));
-  ba.n_rows = n;
-  ba.dgimg = h->dg_img;
-  ba.w8 = h->weff + weff_off(8);
-  ba.g = w.g;
-  ba.xstash = w.xstash;
-  ba.dystash = w.dystash;
-  ba.xyz = sdf_data;
-  ba.xyz_stride = 4;
-  ba.tile_colsum = w.tile_colsum;
-  ba.cta_partials = w.cta_partials;
-  unsigned bwd_grid = grid;
-  if (h->bwd_ver == 1) {
-    k_backward<<<grid, kBwdThreads, kBwdSmemBytes, st>>>(ba);
-  } else {
-    Bwd2Args b2;
-    memset(&b2, 0, sizeof(b2));
-    b2.n_rows = n;
-    b2.dg2img = h->dg2_img;
-    b2.w8 = h->weff + weff_off(8);
-    b2.g = w.g;
-    b2.relu_mask = w.relu_mask;
-    b2.dystash = w.dystash;
+  Bwd2Args b2;
+  memset(&b2, 0, sizeof(b2));
+  b2.n_rows = n;
+  b2.dg2img = h->dg2_img;
+  b2.w8 = h->weff + weff_off(8);
+  b2.g = w.g;
+  b2.relu_mask = w.relu_mask;
+  b2.dystash = w.dystash;
 #ifdef DSDF_DBG_BUILD
-    if (const char* e = getenv("DSDF_DBG_NOSTASH")) if (atoi(e) & 2) b2.dystash = nullptr;
+  if (const char* e = getenv("DSDF_DBG_NOSTASH")) if (atoi(e) & 2) b2.dystash = nullptr;
 #endif
-    b2.xyz = sdf_data;
-    b2.xyz_stride = 4;
-    b2.tile_colsum = w.tile_colsum;
-    b2.cta_partials = w.cta_partials;
-    b2.drop = h->drop;
-    int rc2 = launch_backward2(h, b2, tiles, st, &bwd_grid);
-    if (rc2 != DSDF_OK) return rc2;
-  }
+  b2.xyz = sdf_data;
+  b2.xyz_stride = 4;
+  b2.tile_colsum = w.tile_colsum;
+  b2.cta_partials = w.cta_partials;
+  b2.drop = h->drop;
+  unsigned bwd_grid = 0;
+  rc = launch_backward2(h, b2, tiles, st, &bwd_grid);
+  if (rc != DSDF_OK) return rc;
   if (prof) prof_mark(h, st);
 
   // ---- wgrad GEMMs (lin1..lin7) + split-K reduction
-  WgArgs wa;
-  wa.items = h->wg_items;
-  wa.xstash = w.xstash;
-  wa.dystash = w.dystash;
-  wa.partials = w.wg_partials;
-  if (h->wg_ver == 1) {
-    k_wgrad<<<h->wg_n_items, kWgThreads, kWgSmemBytes, st>>>(wa);
-    if (prof) prof_mark(h, st);
-    k_reduce_wgrad<<<dim3(kHidden, 7), kHidden, 0, st>>>(w.wg_partials, h->wg_layout, w.dweff);
-  } else {
-    Wg2Args w2;
-    w2.segs = h->wg2_segs;
-    w2.seg_begin = h->wg2_seg_begin;
-    w2.xstash = w.xstash;
-    w2.dystash = w.dystash;
-    w2.g_img = w.g_img;
-    w2.partials = w.wg_partials;
-    cudaLaunchConfig_t cfg;
-    memset(&cfg, 0, sizeof(cfg));
-    cfg.gridDim = dim3((unsigned)(2 * h->wg2_pairs));
-    cfg.blockDim = dim3(kW2Threads);
-    cfg.dynamicSmemBytes = kW2SmemBytes;
-    cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = 2;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    CU(h, cudaLaunchKernelEx(&cfg, k_wgrad2, w2));
-    if (prof) prof_mark(h, st);
-    k_reduce_wgrad2<<<dim3(kHidden, h->wg2_with_l8 ? 8 : 7), kHidden, 0, st>>>(w.wg_partials, h->wg2_layout, w.dweff);
-  }
+  rc = launch_wgrad2(h, w.xstash, w.dystash, w.g_img, w.wg_partials, w.dweff, st, prof);
+  if (rc != DSDF_OK) return rc;
 
   // ---- segmented (scene-contiguous) reductions: latent grads, latent columns of dW0/dW4, biases
   const float reg_coef = reg_lambda_ramp * (float)rows_per_seg * inv_n;
@@ -932,8 +741,7 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   k_dw_latent<<<dim3(kHidden, 2), kLatent, 0, st>>>(w.seg_sum, table, (const long long*)seg_ids,
                                                     (int)n_seg, w.dweff);
   k_reduce_cta<<<16, kHidden, 0, st>>>(w.cta_partials, (int)bwd_grid, w.seg_sum, (int)n_seg,
-                                      w.tile_partials, tiles, h->pl, grads, w.dweff,
-                                      h->wg_ver == 1 ? (int)bwd_grid : (dw8_fwd ? fwd_ctas : 0));
+                                      w.tile_partials, tiles, h->pl, grads, w.dweff, dw8_fwd ? fwd_ctas : 0);
   k_param_grads<<<(kScaleElems * 32 + 255) / 256, 256, 0, st>>>(w.dweff, params, h->pl, h->scale,
                                                                 h->inv_norm, grads);
   k_loss<<<1, 1024, 0, st>>>(w.tile_partials, tiles, inv_n, w.seg_norm, (int)n_seg, reg_coef, loss_out);
@@ -960,15 +768,9 @@ extern "C" int dsdf_dense_forward_train(dsdf_handle h, const float* input, int64
   if ((size_t)(base - (uint8_t*)workspace) + w.total > workspace_bytes)
     DSDF_FAIL(h, DSDF_ENOMEM, "workspace too small: need %zu bytes, have %zu", w.total + 1024, workspace_bytes);
   FwdArgs a;
-  memset(&a, 0, sizeof(a));
-  a.wimg = h->fwd_img;
-  a.w8 = h->weff + weff_off(8);
-  a.b8 = h->weff + kWeffElems;
-  a.n_rows = n;
+  fwd_args_init(h, a, n);
   a.input = input;
   a.out = out;
-  a.w2img = h->w2_img;
-  a.dbg = h->dbg;
   a.xstash = w.xstash;
   a.relu_mask = w.relu_mask;
   const long long tiles = (n + kTileM - 1) / kTileM;
@@ -985,7 +787,6 @@ extern "C" int dsdf_dense_backward(dsdf_handle h, const float* params, const flo
                                    size_t workspace_bytes, float* grads, float* dinput, void* stream) {
   if (!h || !params || !input || !out || !dout || !workspace || !grads) DSDF_FAIL(h, DSDF_EINVAL, "null argument");
   if (!h->weights_set) DSDF_FAIL(h, DSDF_EINVAL, "dsdf_set_weights has not been called");
-  if (h->bwd_ver == 1 || h->wg_ver == 1) DSDF_FAIL(h, DSDF_EUNSUPPORTED, "dense backward needs the v2 kernels");
   if (n <= 0) return DSDF_OK;
   cudaStream_t st = (cudaStream_t)stream;
   uint8_t* base = (uint8_t*)(((uintptr_t)workspace + 1023) & ~(uintptr_t)1023);
@@ -1074,11 +875,7 @@ extern "C" int dsdf_segments_forward_train(dsdf_handle h, const float* params, c
   if ((size_t)(base - (uint8_t*)workspace) + w.total > workspace_bytes)
     DSDF_FAIL(h, DSDF_ENOMEM, "workspace too small: need %zu bytes, have %zu", w.total + 1024, workspace_bytes);
   FwdArgs fa;
-  memset(&fa, 0, sizeof(fa));
-  fa.wimg = h->fwd_img;
-  fa.w8 = h->weff + weff_off(8);
-  fa.b8 = h->weff + kWeffElems;
-  fa.n_rows = n;
+  fwd_args_init(h, fa, n);
   fa.table = latents;
   fa.seg_ids = w.ids;
   fa.rows_per_seg = rows_per_seg;
@@ -1087,8 +884,6 @@ extern "C" int dsdf_segments_forward_train(dsdf_handle h, const float* params, c
   fa.out = out;
   fa.xstash = w.xstash;
   fa.relu_mask = w.relu_mask;
-  fa.w2img = h->w2_img;
-  fa.dbg = h->dbg;
   fa.scene_e = w.scene_e;
   k_iota<<<(unsigned)((n_seg + 255) / 256), 256, 0, st>>>(w.ids, n_seg);
   k_scene_fold<<<dim3((unsigned)n_seg, 2, kFoldSplit), 512, 0, st>>>(h->weff, params, h->pl, latents, w.ids, w.scene_e);
@@ -1105,7 +900,6 @@ extern "C" int dsdf_segments_backward(dsdf_handle h, const float* params, const 
                                       float* dlatents, void* stream) {
   if (!h || !params || !latents || !xyz || !out || !dout || !workspace || !grads || !dlatents)
     DSDF_FAIL(h, DSDF_EINVAL, "null argument");
-  if (h->bwd_ver == 1 || h->wg_ver == 1) DSDF_FAIL(h, DSDF_EUNSUPPORTED, "needs the v2 kernels");
   if (n_seg <= 0 || rows_per_seg <= 0 || rows_per_seg % kTileM != 0)
     DSDF_FAIL(h, DSDF_EUNSUPPORTED, "segments need rows_per_seg %% 128 == 0");
   cudaStream_t st = (cudaStream_t)stream;
@@ -1264,11 +1058,7 @@ extern "C" int dsdf_reconstruct(dsdf_handle h, const float* params, const dsdf_r
               workspace_bytes);
 
   FwdArgs fa;
-  memset(&fa, 0, sizeof(fa));
-  fa.wimg = h->fwd_img;
-  fa.w8 = h->weff + weff_off(8);
-  fa.b8 = h->weff + kWeffElems;
-  fa.n_rows = n;
+  fwd_args_init(h, fa, n);
   fa.table = latents;
   fa.seg_ids = w.ids;
   fa.rows_per_seg = rows_pad;
@@ -1281,8 +1071,6 @@ extern "C" int dsdf_reconstruct(dsdf_handle h, const float* params, const dsdf_r
   fa.fused_loss = 1;
   fa.clamp_dist = cfg->clamp_dist;
   fa.inv_n_total = 1.0f / (float)num;          // L1Loss() = mean over num_samples (reconstruct.py:102)
-  fa.w2img = h->w2_img;
-  fa.dbg = h->dbg;
   fa.scene_e = w.scene_e;
   fa.relu_mask = w.relu_mask;                   // xstash / g_img stay null: frozen decoder, no wgrad
 
@@ -1381,11 +1169,12 @@ extern "C" int dsdf_debug_read(dsdf_handle h, uint64_t* out, int32_t max_words) 
   return n;
 }
 
-extern "C" int dsdf_renorm_rows(dsdf_handle h, float* table, const int64_t* seg_ids, int64_t n_seg,
-                                float max_norm, void* stream) {
+extern "C" int dsdf_renorm_rows(dsdf_handle h, float* table, int64_t num_scenes, const int64_t* seg_ids,
+                                int64_t n_seg, float max_norm, void* stream) {
   if (!h || !table || !seg_ids) DSDF_FAIL(h, DSDF_EINVAL, "null argument");
   if (n_seg <= 0) return DSDF_OK;
-  k_renorm_rows<<<(unsigned)n_seg, kLatent, 0, (cudaStream_t)stream>>>(table, (const long long*)seg_ids, (int)n_seg, max_norm);
+  k_renorm_rows<<<(unsigned)n_seg, kLatent, 0, (cudaStream_t)stream>>>(table, (const long long*)seg_ids, (int)n_seg,
+                                                                   num_scenes, max_norm);
   CU(h, cudaGetLastError());
   return DSDF_OK;
 }
@@ -1414,6 +1203,7 @@ extern "C" int dsdf_clip_adam(dsdf_handle h, float* params, float* grads, float*
   return DSDF_OK;
 }
 
+#ifdef DSDF_DIAG_BUILD
 extern "C" int dsdf_selftest_gemm(int32_t kind, const void* a_img, const void* b_img, float* d_out,
                                   void* stream) {
   if (!a_img || !b_img || !d_out || kind < 0 || kind > 1) {
@@ -1457,6 +1247,18 @@ extern "C" int dsdf_selftest_mma_rate(int32_t kind, int32_t iters, int32_t n_cta
   if (e != cudaSuccess) { g_err = cudaGetErrorString(e); return DSDF_ECUDA; }
   return DSDF_OK;
 }
+
+#else
+// product build: the self-test / micro-benchmark kernels are not compiled in (diagnostics variant only)
+extern "C" int dsdf_selftest_gemm(int32_t, const void*, const void*, float*, void*) {
+  g_err = "diagnostics entry: build the variant with -DDSDF_DIAG_BUILD (build.py DSDF_BUILD_VARIANT=diag)";
+  return DSDF_EUNSUPPORTED;
+}
+extern "C" int dsdf_selftest_mma_rate(int32_t, int32_t, int32_t, uint64_t*) {
+  g_err = "diagnostics entry: build the variant with -DDSDF_DIAG_BUILD (build.py DSDF_BUILD_VARIANT=diag)";
+  return DSDF_EUNSUPPORTED;
+}
+#endif
 
 // diagnostics builds (-DDSDF_HANG_TRAP): mapped host buffer the device writes deadlock reports to
 extern "C" int dsdf_debug_hang_buffer(uint32_t** host_ptr) {

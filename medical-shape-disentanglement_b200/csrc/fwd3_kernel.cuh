@@ -27,8 +27,7 @@
 // 8x relu, tanh), deep_sdf/utils.py:86-97 (expand + cat) and, in TRAIN mode,
 // train_deep_sdf.py:598-606 (gather, cat, clamp, L1/N).
 #pragma once
-#include "fwd2_kernel.cuh"
-#include "fwd_kernel.cuh"
+#include "common.cuh"
 #include "layout.cuh"
 #include "ptx.cuh"
 

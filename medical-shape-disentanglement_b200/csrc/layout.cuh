@@ -62,20 +62,6 @@ __host__ __device__ __forceinline__ uint32_t sub_chunk_off(uint32_t r, uint32_t 
   return (r >> 3) * 1024u + (r & 7u) * 128u + (((ch ^ r) & 7u) << 4);
 }
 
-// ---- forward weight image -------------------------------------------------------------
-// per layer l (0..7): KB(l) k-blocks x NC(l) n-chunks of B tiles [128 n x 64 k] (one SUB each,
-// r = n local, c = k local), ordered kb-major then nc; followed by one E tile (SUB) holding,
-// for n-chunk j, its 16 E columns at c = 16*j .. 16*j+15.
-__host__ __device__ constexpr int fwd_kb(int l) { return l == 0 ? 4 : 8; }
-__host__ __device__ constexpr int fwd_nc(int l) { return l == 3 ? 2 : 4; }
-__host__ __device__ constexpr int fwd_tiles(int l) { return fwd_kb(l) * fwd_nc(l) + 1; }
-__host__ __device__ constexpr int fwd_tile_base(int l) {
-  int b = 0;
-  for (int i = 0; i < l; ++i) b += fwd_tiles(i);
-  return b;
-}
-constexpr int kFwdTilesTotal = fwd_tile_base(8);  // 17+33+33+17+33+33+33+33 = 232
-
 // ---- v2 forward weight stream ("K-step image") ----------------------------------------------
 // The v2 forward chain consumes B as a stream of K-steps: one step = [256 n x 16 k] bf16 = 8 KB in
 // the canonical no-swizzle K-major UMMA layout (8 n-rows x 16 B core matrices, 128 B each):
@@ -104,20 +90,6 @@ __host__ __device__ constexpr int w2_step(int l, int h, int s) {
 constexpr int kW2Steps = w2_layer_base(8);  // 34 + 66*2 + 33 + 66*4 = 463 steps = 3.79 MB
 // per-segment E image (fold mode): [seg][which: lin0, lin4][h] steps
 constexpr int kSceneESteps = 4;
-
-// ---- dgrad weight image (W^T) -----------------------------------------------------------
-// layer l (1..7): D[r, i] = sum_o dY[r,o] W[o,i];  B tiles [128 i x 64 o], ordered kb(o)-major
-// then nc(i).  "scene mode" only needs i in the x3 part for lin4 (NC = 2).
-// lin0 / full lin4 (general dense-input backward) are appended after the scene-mode tiles.
-__host__ __device__ constexpr int dg_kb(int l) { return l == 3 ? 4 : 8; }   // out / 64
-__host__ __device__ constexpr int dg_nc(int l) { return l == 4 ? 2 : 4; }   // in(pad) / 128
-__host__ __device__ constexpr int dg_tiles(int l) { return l == 0 ? 0 : dg_kb(l) * dg_nc(l); }
-__host__ __device__ constexpr int dg_tile_base(int l) {
-  int b = 0;
-  for (int i = 1; i < l; ++i) b += dg_tiles(i);
-  return b;
-}
-constexpr int kDgTilesTotal = dg_tile_base(8);  // 32+32+16+16+32+32+32 = 192
 
 // ---- v2 dgrad weight stream ("K-step image" of W^T) -------------------------------------------
 // The v2 backward chain computes dX_l[128 x in] = dY_l[128 x out] W_l as, per output half h

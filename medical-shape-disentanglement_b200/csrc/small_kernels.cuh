@@ -9,11 +9,10 @@
 //   :780-782  clip_grad_norm_: coef = min(1, c/(||g||_2 + 1e-6)) over decoder params only
 //   :784      Adam(betas=(.9,.999), eps=1e-8) over decoder params and ALL latent rows
 #pragma once
-#include "bwd_kernel.cuh"
+#include "common.cuh"
 #include "fold_kernels.cuh"
 #include "layout.cuh"
 #include "ptx.cuh"
-#include "wgrad_kernel.cuh"
 #include "wgrad2_kernel.cuh"
 
 namespace dsdf {
@@ -42,14 +41,34 @@ __device__ __forceinline__ bool first_occurrence(const long long* __restrict__ s
 }
 
 __global__ void k_renorm_rows(float* __restrict__ table, const long long* __restrict__ seg_ids,
-                              int n_seg, float max_norm) {
+                              int n_seg, long long num_scenes, float max_norm) {
   __shared__ float sh[8];
   const int b = blockIdx.x;
   if (b >= n_seg || !first_occurrence(seg_ids, b)) return;      // block-uniform
+  if (seg_ids[b] < 0 || seg_ids[b] >= num_scenes) return;       // reported by k_sanitize_ids in the step itself
   float* row = table + seg_ids[b] * kLatent;
   const float x = row[threadIdx.x];
   const float nrm = sqrtf(block_sum_256(x * x, sh));
   if (nrm > max_norm) row[threadIdx.x] = x * (max_norm / (nrm + 1e-7f));
+}
+
+// ---- scene-id guard: nn.Embedding raises on an index outside [0, num_embeddings) (a device-side assert on CUDA).
+// Here: ids are copied into the workspace with bad ones replaced by 0 (so no kernel of the step can index the
+// latent table out of bounds) and status[0] = 1 + position of the first bad id (0 = all good); the host wrapper
+// turns a non-zero status into an exception when it reads the step's scalars.  One block.
+__global__ void k_sanitize_ids(const long long* __restrict__ ids, int n_seg, long long num_scenes,
+                               long long* __restrict__ out, float* __restrict__ status) {
+  __shared__ int first_bad;
+  if (threadIdx.x == 0) first_bad = 0x7fffffff;
+  __syncthreads();
+  for (int b = threadIdx.x; b < n_seg; b += blockDim.x) {
+    const long long id = ids[b];
+    const bool ok = id >= 0 && id < num_scenes;
+    out[b] = ok ? id : 0;
+    if (!ok) atomicMin(&first_bad, b);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) status[0] = first_bad == 0x7fffffff ? 0.f : (float)(first_bad + 1);
 }
 
 // ---- per-segment column sums of dY0 / dY4: seg_sum[b][which][c] -----------------------------
@@ -134,26 +153,6 @@ __global__ void k_dw_latent(const float* __restrict__ seg_sum, const float* __re
 }
 
 // ---- split-K wgrad partial reduction into the reference-layout fp32 gradient ----------------
-struct WgLayout {
-  int item_base[8];   // first item of layer l (1..7)
-  int n_split;
-};
-// grid (512 rows o, 7 layers), 512 threads (i pad)
-__global__ void k_reduce_wgrad(const float* __restrict__ partials, WgLayout wl,
-                               float* __restrict__ dweff) {
-  const int l = blockIdx.y + 1, o = blockIdx.x, ip = threadIdx.x;
-  if (o >= ref_out(l)) return;
-  const int npad = (l == 4) ? 256 : 512;
-  if (ip >= npad) return;
-  const int ic = pad_to_ref_col(l, ip);
-  if (ic < 0) return;
-  const int oc = o >> 7, orow = o & 127;
-  const float* p = partials + ((size_t)(wl.item_base[l] + oc * wl.n_split) * kTileM + orow) * kHidden + ip;
-  float s = 0.f;
-  for (int k = 0; k < wl.n_split; ++k) s += p[(size_t)k * kTileM * kHidden];
-  dweff[weff_off(l) + (size_t)o * ref_in(l) + ic] = s;
-}
-
 // v2 schedule: item (layer l, out-chunk pair) -> contiguous partial slots [slot_lo, slot_hi)
 struct Wg2Layout {
   int item_base[9];   // first item of layer l (1..8)

@@ -9,6 +9,7 @@ Python only owns the tensors; all arithmetic is in libdsdf_b200.so.
 from __future__ import annotations
 
 import torch
+from torch.autograd.function import once_differentiable
 
 from . import _lib
 from .decoder import _stream_ptr
@@ -34,6 +35,7 @@ class _DecoderFn(torch.autograd.Function):
         return out.view(n, 1)
 
     @staticmethod
+    @once_differentiable   # opaque C kernels: double backward / create_graph=True must raise, not return zeros
     def backward(ctx, dout):
         dec, x, out = ctx.dec, ctx.x, ctx.out
         L = dec.L
@@ -89,6 +91,7 @@ class _SegmentsFn(torch.autograd.Function):
         return out.view(n_seg * p, 1)
 
     @staticmethod
+    @once_differentiable
     def backward(ctx, dout):
         dec, lat, q, out = ctx.dec, ctx.lat, ctx.q, ctx.out
         L = dec.L

@@ -125,7 +125,17 @@ def reconstruct_batch(decoder: Decoder, num_iterations: int, shapes: Sequence[Tu
         blocks += [pos.reshape(-1, 4), neg.reshape(-1, 4)]
     samples = torch.cat(blocks, 0).to(dev, torch.float32).contiguous()
     shape_base = torch.tensor(base, dtype=torch.int64).to(dev)
-    win = torch.as_tensor(windows, dtype=torch.int64).reshape(num_iterations, n_shapes, 2).contiguous().to(dev)
+    win = torch.as_tensor(windows, dtype=torch.int64).reshape(num_iterations, n_shapes, 2).contiguous()
+    # every window must lie inside its shape's pos / neg block (the gather kernel reads start .. start + half)
+    half = num_samples // 2
+    if win.numel():
+        sizes = torch.tensor([[pos.shape[0], neg.shape[0]] for pos, neg in shapes], dtype=torch.int64)
+        wc = win.cpu()
+        if int(wc.min()) < 0 or bool((wc + half > sizes[None]).any()):
+            bad = ((wc < 0) | (wc + half > sizes[None])).nonzero()[0].tolist()
+            raise IndexError(f"window {bad} (iteration, shape, pos/neg) = {int(wc[tuple(bad)])} + {half} rows leaves the "
+                             f"shape's block of {int(sizes[bad[1], bad[2]])} rows")
+    win = win.to(dev)
     lat = latents.detach().to(dev, torch.float32).clone().contiguous()
     if n_steps is None:
         n_steps = num_iterations - (first_step - 1)
@@ -151,9 +161,16 @@ def reconstruct_batch(decoder: Decoder, num_iterations: int, shapes: Sequence[Tu
         if t not in _DIST_KINDS:
             raise ValueError(f"Unknown dist_type: {dist_type}")
         dist_kind = _DIST_KINDS[t]
-        dm = torch.as_tensor(dist_mean, dtype=torch.float32).reshape(-1).to(dev).contiguous()
+        # the kernel indexes [j] for j < 256: broadcast scalars / [1,256] the way torch would (reconstruct.py:58-70)
+        dm = torch.as_tensor(dist_mean, dtype=torch.float32).reshape(-1).to(dev)
+        dm = dm.expand(LATENT).contiguous() if dm.numel() == 1 else dm.contiguous()
+        if dm.numel() != LATENT:
+            raise ValueError(f"dist_mean must have 1 or {LATENT} elements, got {dm.numel()}")
         if dist_std is not None:
-            ds = torch.clamp(torch.as_tensor(dist_std, dtype=torch.float32).reshape(-1).to(dev), min=1e-8).contiguous()
+            ds = torch.clamp(torch.as_tensor(dist_std, dtype=torch.float32).reshape(-1).to(dev), min=1e-8)
+            ds = ds.expand(LATENT).contiguous() if ds.numel() == 1 else ds.contiguous()
+            if ds.numel() != LATENT:
+                raise ValueError(f"dist_std must have 1 or {LATENT} elements, got {ds.numel()}")
     cfg = ReconstructCfg(num_iterations, num_samples, float(clamp_dist), float(lr), reg_kind, reg_lambda,
                          float(code_bound) if code_bound is not None else 0.0, dist_kind, dist_w,
                          dm.data_ptr() if dm is not None else None, ds.data_ptr() if ds is not None else None)

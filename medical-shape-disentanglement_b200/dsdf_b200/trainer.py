@@ -28,9 +28,16 @@ from . import _lib
 from .decoder import LATENT, Decoder, _stream_ptr
 
 
+# loss switches of train_deep_sdf.py:286-327 that the fused step does not compute.  `UseEikonal` is built
+# (fused second-order path, StepConfig.use_eikonal).  The two latent-only priors act on the [B, 256] batch
+# latents, not on the decoder path: they can be supplied as `aux_latent_loss` to FusedTrainer.step.
+_UNSUPPORTED_LOSS_KEYS = ("UseIsometryLoss", "UseGradMetricIsotropyLoss")
+_LATENT_ONLY_LOSS_KEYS = ("UseCovarianceLoss", "UseGMMPriorLoss")
+
+
 @dataclass
 class StepConfig:
-    """Subset of specs.json read by the step (train_deep_sdf.py:276-285, 243, 346)."""
+    """Subset of specs.json read by the step (train_deep_sdf.py:243-346)."""
     clamp_dist: float = 0.1                 # ClampingDistance
     code_reg: bool = True                   # CodeRegularization
     code_reg_lambda: float = 1e-4           # CodeRegularizationLambda
@@ -39,18 +46,38 @@ class StepConfig:
     code_init_std: float = 1.0              # CodeInitStdDev
     lr_decoder: float = 5e-4                # LearningRateSchedule[0] (Step)
     lr_latent: float = 1e-3                 # LearningRateSchedule[1] (Step)
-    lr_interval: int = 500
-    lr_factor: float = 0.5
+    lr_interval: int = 500                  # LearningRateSchedule[0].Interval
+    lr_factor: float = 0.5                  # LearningRateSchedule[0].Factor
+    lr_interval_latent: Optional[int] = None    # LearningRateSchedule[1].Interval (None: same as [0])
+    lr_factor_latent: Optional[float] = None    # LearningRateSchedule[1].Factor
     betas: tuple = (0.9, 0.999)
     eps: float = 1e-8
     dropout_seed: int = 0                   # key of the Philox dropout stream (NetworkSpecs.dropout)
+    use_eikonal: bool = False               # UseEikonal (train_deep_sdf.py:286,724-729)
+    eikonal_lambda: float = 0.002           # hard-coded in the reference (:727)
 
     @staticmethod
-    def from_specs(specs: dict) -> "StepConfig":
+    def from_specs(specs: dict, latent_only_losses_handled: bool = False) -> "StepConfig":
+        """Read the step's keys the way train_deep_sdf.py does (get_spec_with_default, :191-195).  A switch
+        that changes the objective and is not computed by the fused step raises, naming the key (SURVEY.md
+        H13): training a different loss silently is worse than not training.  `latent_only_losses_handled`:
+        the caller passes the covariance / GMM prior term as `aux_latent_loss` to FusedTrainer.step."""
+        for k in _UNSUPPORTED_LOSS_KEYS:
+            if specs.get(k, False):
+                raise NotImplementedError(
+                    f"specs[{k!r}] = true: this loss back-propagates through decoder Jacobians "
+                    "(deep_sdf/loss.py) and is not part of the fused step; use the reference NetworkArch for it")
+        for k in _LATENT_ONLY_LOSS_KEYS:
+            if specs.get(k, False) and not latent_only_losses_handled:
+                raise NotImplementedError(
+                    f"specs[{k!r}] = true: a prior on the batch latents (train_deep_sdf.py:737-764), outside the "
+                    "decoder path; compute it in torch on trainer.lat_vecs rows and pass it to "
+                    "FusedTrainer.step(aux_latent_loss=...), then call from_specs(..., latent_only_losses_handled=True)")
         sch = specs["LearningRateSchedule"]
-        for s in sch[:2]:
+        for i, s in enumerate(sch[:2]):
             if s["Type"] != "Step":
-                raise NotImplementedError(f"LearningRateSchedule type {s['Type']}: pass lr explicitly to step()")
+                raise NotImplementedError(f"LearningRateSchedule[{i}].Type = {s['Type']!r}: only 'Step' is built in; "
+                                          "pass lr_decoder / lr_latent explicitly to step()")
         return StepConfig(
             clamp_dist=specs["ClampingDistance"],
             code_reg=specs.get("CodeRegularization", True),
@@ -60,6 +87,8 @@ class StepConfig:
             code_init_std=specs.get("CodeInitStdDev", 1.0),
             lr_decoder=sch[0]["Initial"], lr_latent=sch[1]["Initial"],
             lr_interval=sch[0]["Interval"], lr_factor=sch[0]["Factor"],
+            lr_interval_latent=sch[1]["Interval"], lr_factor_latent=sch[1]["Factor"],
+            use_eikonal=bool(specs.get("UseEikonal", False)),
         )
 
 
@@ -99,9 +128,15 @@ class FusedTrainer:
 
     # ---------------------------------------------------------------- helpers
     def lr(self, which: int, epoch: int) -> float:
+        # one StepLearningRateSchedule per parameter group (train_deep_sdf.py:247-265, lr_scheduling.py:16-24)
         c = self.cfg
-        init = c.lr_decoder if which == 0 else c.lr_latent
-        return init * (c.lr_factor ** (epoch // c.lr_interval))   # lr_scheduling.py:16-24
+        if which == 0:
+            init, interval, factor = c.lr_decoder, c.lr_interval, c.lr_factor
+        else:
+            init = c.lr_latent
+            interval = c.lr_interval if c.lr_interval_latent is None else c.lr_interval_latent
+            factor = c.lr_factor if c.lr_factor_latent is None else c.lr_factor_latent
+        return init * (factor ** (epoch // interval))
 
     def _workspace(self, h, rows: int, segs: int):
         key = (rows, segs)

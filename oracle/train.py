@@ -7,6 +7,7 @@ Follows /root/reference/train_deep_sdf.py:
   * step prologue             :555-577  reshape, gt clamp, scene-id expansion, batch_split chunks
   * chunk body                :594-616  gather (renorm side effect) -> cat -> decoder -> clamp ->
                                         L1(sum)/N_total + lambda*min(1,epoch/100)*sum||z||/N_total
+  * Eikonal term              :286,563,724-729  0.002*mean((1-||d clamp(pred)/d xyz||)^2), create_graph=True
   * backward                  :731
   * clip + step               :780-784  clip_grad_norm_(decoder.parameters(), c) then Adam step
 
@@ -42,6 +43,7 @@ class TrainConfig:
     lr_interval: int = 500
     lr_factor: float = 0.5
     batch_split: int = 1
+    use_eikonal: bool = False        # specs["UseEikonal"] (train_deep_sdf.py:286)
 
 
 def step_lr(initial: float, interval: int, factor: float, epoch: int) -> float:
@@ -116,6 +118,8 @@ class OracleTrainer:
         n_total = m if n_total is None else n_total      # F9: global row count
         p = m // scene_ids.numel()
         xyz = sdf_data[:, 0:3]
+        if c.use_eikonal:
+            xyz = xyz.detach().clone().requires_grad_(True)      # :562-563 (xyz.requires_grad = True)
         gt = torch.clamp(sdf_data[:, 3:4], -c.clamp_dist, c.clamp_dist)
         idx = scene_ids.unsqueeze(-1).repeat(1, p).view(-1)
         xyz_c = torch.chunk(xyz, c.batch_split)
@@ -123,6 +127,7 @@ class OracleTrainer:
         gt_c = torch.chunk(gt, c.batch_split)
         sdf_loss = 0.0
         reg_loss = 0.0
+        self.last_eikonal_loss = 0.0
         preds = []
         for i in range(c.batch_split):
             bv = self.lat_vecs(idx_c[i])
@@ -146,6 +151,14 @@ class OracleTrainer:
                 reg = (c.code_reg_lambda * min(1, epoch / 100) * l2) / n_total
                 chunk_loss = chunk_loss + reg
                 reg_loss += float(reg.item())
+            if c.use_eikonal:
+                # train_deep_sdf.py:724-729, verbatim arithmetic (pred is the CLAMPED prediction)
+                grad_outputs = torch.ones_like(pred, requires_grad=True)
+                gradients = torch.autograd.grad(pred, [xyz_c[i]], grad_outputs=grad_outputs, create_graph=True,
+                                                allow_unused=True, retain_graph=True)[0]
+                eikonal_loss = 0.002 * ((1. - torch.linalg.vector_norm(gradients, dim=1)) ** 2).mean()
+                chunk_loss = chunk_loss + eikonal_loss
+                self.last_eikonal_loss += float(eikonal_loss.item())
             chunk_loss.backward()
             preds.append(pred.detach())
         return sdf_loss, reg_loss, torch.cat(preds, 0)
@@ -161,8 +174,8 @@ class OracleTrainer:
                                                          self.cfg.grad_clip, norm_type=2))
         if apply:
             self.opt.step()
-        return {"loss": sdf_loss + reg_loss, "sdf_loss": sdf_loss, "reg_loss": reg_loss,
-                "grad_norm": gnorm, "pred": pred}
+        return {"loss": sdf_loss + reg_loss + self.last_eikonal_loss, "sdf_loss": sdf_loss, "reg_loss": reg_loss,
+                "eikonal_loss": self.last_eikonal_loss, "grad_norm": gnorm, "pred": pred}
 
     # convenience for tests
     def decoder_grads(self) -> Dict[str, torch.Tensor]:
