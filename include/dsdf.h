@@ -114,17 +114,24 @@ size_t dsdf_train_workspace_bytes(dsdf_handle h, int64_t max_rows, int64_t max_s
  *   n_total  global row count the loss is normalised by (train_deep_sdf.py:558,606; under
  *            scene sharding = sum over ranks)
  *   reg_lambda_ramp = CodeRegularizationLambda * min(1, epoch/100) (0 disables; :609-613)
+ *   eikonal_lambda = 0.002 when specs["UseEikonal"] (train_deep_sdf.py:286,724-729), 0 disables: adds
+ *            lambda * mean_rows (1 - ||d clamp(pred) / d xyz||)^2 (mean over n_total) and its gradient, computed
+ *            without double backward: dgrad chain -> per-row (eps, xyz') -> the forward chain recomputed on the
+ *            perturbed input with the first pass's ReLU masks -> one wgrad (ReLU decoder family only)
  * Outputs: grads (flat, dsdf_param_layout addressing, OVERWRITTEN), lat_grad [num_scenes,256]
  * (dense, OVERWRITTEN: zero for scenes not in the batch, as nn.Embedding(sparse=False)),
  * pred [n] (tanh output, un-clamped), loss_out[0] = L1 term, loss_out[1] = regulariser term,
- * loss_out[3] = 0, or 1 + position of the first seg_id outside [0, num_scenes) (nn.Embedding raises on such
- * an index; here the step runs with that id replaced by 0 and reports it -- loss_out has 4 floats). */
+ * loss_out[2] = Eikonal term, loss_out[3] = 0, or 1 + position of the first seg_id outside [0, num_scenes) (nn.Embedding raises on such
+ * an index; here the step runs with that id replaced by 0 and reports it -- loss_out has 4 floats).
+ * grads_ready_event (nullable cudaEvent_t): recorded on `stream` as soon as `grads` is final, before the
+ * latent-gradient kernels: a scene-sharded caller starts its all-reduce of `grads` on a side stream there
+ * (replaces nn.DataParallel's reduce_add of replica gradients, train_deep_sdf.py:352). */
 int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const float* table,
                        int64_t num_scenes, const int64_t* seg_ids, int64_t n_seg,
                        int64_t rows_per_seg, const float* sdf_data, int64_t n_total,
-                       float clamp_dist, float reg_lambda_ramp, void* workspace,
+                       float clamp_dist, float reg_lambda_ramp, float eikonal_lambda, void* workspace,
                        size_t workspace_bytes, float* grads, float* lat_grad, float* pred,
-                       float* loss_out, void* stream);
+                       float* loss_out, void* grads_ready_event, void* stream);
 
 /* nn.Embedding(max_norm) lookup side effect (train_deep_sdf.py:429,598): rows seg_ids[b] of
  * table[num_scenes,256] with norm > max_norm are scaled in place by max_norm/(norm+1e-7); ids outside

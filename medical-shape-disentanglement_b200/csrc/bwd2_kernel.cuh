@@ -40,6 +40,13 @@ struct Bwd2Args {
   float* cta_partials;        // [grid][kCtaPartialFloats]
   DropoutArgs drop;           // DROP: layers + scale (the keep bits already sit in relu_mask)
   int stash_dy0;              // dense-input backward: also stash dY0 (slot 0) for the dInput / dW0 kernels
+  // EIK: the Eikonal term's per-row quantities (train_deep_sdf.py:724-729; algebra in tests/eikonal_algebra.py)
+  const float* pred;          // [n] tanh output of the forward pass
+  const float4* wx;           // [2][512] fp32 (x, y, z, 0) xyz columns of lin0 / lin4 (k_build_wx)
+  float clamp_dist;
+  float eik_c2;               // 2 * lambda / N_total
+  float4* eik_row;            // out [n]: perturbed input of the recompute pass (x', y', z', eps)
+  float* eik_tile;            // out [tiles][2]: sum_rows (1 - ||G||)^2, sum_rows eps * g
 };
 
 template <int CG>
@@ -53,7 +60,11 @@ struct B2 {
   static constexpr uint32_t kAuxW8 = 528;       // 512 floats
   static constexpr uint32_t kAuxG = kAuxW8 + 2048;      // 128 floats
   static constexpr uint32_t kAuxXyz = kAuxG + 512;      // 128 x 3 floats
-  static constexpr uint32_t kSmemBytes = kSmemAux + kAuxXyz + 1536;
+  static constexpr uint32_t kAuxWx = kAuxXyz + 1536;    // EIK: 2 x 512 float4
+  static constexpr uint32_t kAuxJ = kAuxWx + 16384;     // EIK: 128 float4 (partial d s / d xyz of the other column half)
+  static constexpr uint32_t kAuxRho = kAuxJ + 2048;     // EIK: 128 floats (1 + eps)
+  static constexpr uint32_t kAuxRed = kAuxRho + 512;    // EIK: 16 floats
+  static constexpr uint32_t kSmemBytes = kSmemAux + kAuxRed + 64;
 };
 constexpr int kB2Threads = 512;
 
@@ -69,16 +80,6 @@ __device__ __forceinline__ void setmaxnreg_dec() {
   asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N));
 }
 
-// 32 fp32 dX columns -> zero where the ReLU mask bit (31 - i) is clear -> 16 packed bf16x2
-__device__ __forceinline__ void mask_pack32(const uint32_t (&v)[32], uint32_t m, uint32_t* p) {
-#pragma unroll
-  for (int i = 0; i < 16; ++i) {
-    const float lo = (m & (0x80000000u >> (2 * i))) ? __uint_as_float(v[2 * i]) : 0.f;
-    const float hi = (m & (0x40000000u >> (2 * i))) ? __uint_as_float(v[2 * i + 1]) : 0.f;
-    p[i] = pack_bf16x2(lo, hi);
-  }
-}
-
 #ifdef DSDF_ARCH_SIREN
 // 32 fp32 dX columns * stashed activation derivative 30 cos(30 x) (16 packed bf16x2) -> 16 packed bf16x2
 __device__ __forceinline__ void deriv_mul_pack32(const uint32_t (&v)[32], const uint32_t* d, uint32_t* p) {
@@ -89,8 +90,26 @@ __device__ __forceinline__ void deriv_mul_pack32(const uint32_t (&v)[32], const 
 }
 #endif
 
-template <int CG, bool DROP = false>
+// partial d s / d xyz of one row over 32 columns: j += sum_i (mask_i ? v_i : 0) * w[i].xyz  (w in shared memory,
+// the same address for the whole warp: broadcast loads)
+__device__ __forceinline__ void j_acc32(const uint32_t (&v)[32], uint32_t m, const float4* w, float& jx, float& jy,
+                                        float& jz) {
+#pragma unroll
+  for (int i = 0; i < 32; ++i) {
+    const float d = (m & (0x80000000u >> i)) ? __uint_as_float(v[i]) : 0.f;
+    const float4 ww = w[i];
+    jx = fmaf(d, ww.x, jx);
+    jy = fmaf(d, ww.y, jy);
+    jz = fmaf(d, ww.z, jz);
+  }
+}
+
+// EIK: additionally accumulates, per row, j = g (d s / d xyz) from dY4 and dY0, turns it into the Eikonal term's
+// scalars at the end of the tile (||G||, eps, xyz'), writes them for the recompute pass and lets the reducers
+// weight the layer-0 sums with them (the sums of layers 1..7 are corrected by k_eik_corr).
+template <int CG, bool DROP = false, bool EIK = false>
 __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
+  static_assert(!(EIK && DROP), "the Eikonal pass is not built together with dropout");
   using C = B2<CG>;
   constexpr int kRing = C::kRing;
   constexpr uint32_t kSlice = C::kSlice;
@@ -114,6 +133,10 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
   float* w8s = reinterpret_cast<float*>(smem + C::kSmemAux + C::kAuxW8);
   float* gs = reinterpret_cast<float*>(smem + C::kSmemAux + C::kAuxG);
   float* xyzs = reinterpret_cast<float*>(smem + C::kSmemAux + C::kAuxXyz);
+  [[maybe_unused]] float4* wxs = reinterpret_cast<float4*>(smem + C::kSmemAux + C::kAuxWx);
+  [[maybe_unused]] float4* jpart = reinterpret_cast<float4*>(smem + C::kSmemAux + C::kAuxJ);
+  [[maybe_unused]] float* rhos = reinterpret_cast<float*>(smem + C::kSmemAux + C::kAuxRho);
+  [[maybe_unused]] float* ered = reinterpret_cast<float*>(smem + C::kSmemAux + C::kAuxRed);
 
   if ((s_base & 1023u) != 0) __trap();
   const uint32_t crank = CG > 1 ? cluster_ctarank() : 0u;
@@ -139,6 +162,8 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
     if (CG > 1) tmem_alloc2<512>(tmem_slot); else tmem_alloc<512>(tmem_slot);
   }
   for (int i = threadIdx.x; i < kHidden; i += blockDim.x) w8s[i] = a.w8[i];
+  if (EIK)
+    for (int i = threadIdx.x; i < 2 * kHidden; i += blockDim.x) wxs[i] = a.wx[i];
   tc_fence_before();
   __syncthreads();
   if (CG > 1) cluster_sync_all();
@@ -339,6 +364,8 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
       }
       first = false;
       float gr = valid ? __ldg(a.g + row) : 0.f;
+      [[maybe_unused]] const float th = (EIK && valid) ? __ldg(a.pred + row) : 0.f;
+      [[maybe_unused]] float jx = 0.f, jy = 0.f, jz = 0.f;         // EIK: this thread's share of g (d s / d xyz)
       if (DROP && ((a.drop.layers >> 7) & 1u)) gr *= a.drop.scale;   // dropout after lin7's ReLU
       if (j == 0) {
         gs[r] = gr;
@@ -402,6 +429,8 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
 #else
           if (DROP && ((a.drop.layers >> lm) & 1u)) mask_scale_pack32(v, mk[c], a.drop.scale, held + 16 * c);
           else mask_pack32(v, mk[c], held + 16 * c);
+          if (EIK && (lm == kSkipLayer || lm == 0))
+            j_acc32(v, mk[c], wxs + (lm == 0 ? 0 : kHidden) + j * 128 + c * 32, jx, jy, jz);
 #endif
         }
         if (has_h1) {
@@ -431,12 +460,59 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
 #else
             if (DROP && ((a.drop.layers >> lm) & 1u)) mask_scale_pack32(v, mk[4 + c], a.drop.scale, p);
             else mask_pack32(v, mk[4 + c], p);
+            if (EIK && (lm == kSkipLayer || lm == 0))
+              j_acc32(v, mk[4 + c], wxs + (lm == 0 ? 0 : kHidden) + 256 + j * 128 + c * 32, jx, jy, jz);
 #endif
             store_chunk32(a_base, r, (uint32_t)(256 + j * 128 + c * 32), p);
           }
           tc_fence_before();
           if (l - 1 >= 1 && b2_in_hi(l - 1)) publish(a_hi, a_hi_c); else __syncwarp();
           if (l - 1 >= 1 || a.stash_dy0) stash_ready(s_hi);
+        }
+        if (!(EIK && l == 1)) tell_reducers();
+      }
+      if (EIK) {
+        // ---- end of the tile: dY0 sits in A.  Per row (tests/eikonal_algebra.py):
+        //   G = sigma J, J = j / g;  coef = c2 (1 - 1/||G||);  eps = -2 t coef ||G||^2 / g;  xyz' = (1+eps) xyz + (sigma/g) coef G
+        // The reducers then weight the layer-0 sums: bias / latent column sums with 1 + eps, xyz columns with xyz'.
+        if (j == 1) jpart[r] = make_float4(jx, jy, jz, 0.f);
+        named_bar_sync(1, 256);
+        if (j == 0) {
+          const float4 o = jpart[r];
+          jx += o.x; jy += o.y; jz += o.z;
+          const float d = a.clamp_dist;
+          const float sigma = (th >= -d && th <= d) ? 1.f - th * th : 0.f;
+          float x = xyzs[r * 3], y = xyzs[r * 3 + 1], z = xyzs[r * 3 + 2];
+          float eps = 0.f, gn = 0.f;
+          if (gr != 0.f) {
+            const float ratio = sigma / gr;               // = N sign(pred - gt)
+            const float gx = jx * ratio, gy = jy * ratio, gz = jz * ratio;
+            gn = sqrtf(fmaf(gx, gx, fmaf(gy, gy, gz * gz)));
+            if (gn > 0.f) {
+              const float coef = a.eik_c2 * (1.f - 1.f / gn);
+              eps = -2.f * th * coef * gn * gn / gr;
+              const float k = ratio * coef;
+              x = fmaf(eps, x, x) + k * gx;
+              y = fmaf(eps, y, y) + k * gy;
+              z = fmaf(eps, z, z) + k * gz;
+            }
+          }
+          float e_loss = valid ? (1.f - gn) * (1.f - gn) : 0.f;
+          float e_g = eps * gr;
+          if (valid) a.eik_row[row] = make_float4(x, y, z, eps);
+          rhos[r] = 1.f + eps;
+          xyzs[r * 3] = x; xyzs[r * 3 + 1] = y; xyzs[r * 3 + 2] = z;
+#pragma unroll
+          for (int o2 = 16; o2 > 0; o2 >>= 1) {
+            e_loss += __shfl_xor_sync(0xffffffffu, e_loss, o2);
+            e_g += __shfl_xor_sync(0xffffffffu, e_g, o2);
+          }
+          if (lane == 0) { ered[q * 2] = e_loss; ered[q * 2 + 1] = e_g; }
+        }
+        named_bar_sync(1, 256);
+        if (t == 0 && tile_valid) {
+          a.eik_tile[tile * 2] = (ered[0] + ered[2]) + (ered[4] + ered[6]);
+          a.eik_tile[tile * 2 + 1] = (ered[1] + ered[3]) + (ered[5] + ered[7]);
         }
         tell_reducers();
       }
@@ -485,7 +561,12 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
               uint32_t w0, w1;
               asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(w0), "=r"(w1) : "r"(s_base + C::kSmemA + off));
               const float d0 = bf16_lo(w0), d1 = bf16_hi(w0), d2 = bf16_lo(w1), d3 = bf16_hi(w1);
-              s[0] += d0; s[1] += d1; s[2] += d2; s[3] += d3;
+              if (EIK && l == 0) {            // bias / latent column sums see the row's total upstream (1 + eps) g
+                const float rho = rhos[r];
+                s[0] = fmaf(rho, d0, s[0]); s[1] = fmaf(rho, d1, s[1]); s[2] = fmaf(rho, d2, s[2]); s[3] = fmaf(rho, d3, s[3]);
+              } else {
+                s[0] += d0; s[1] += d1; s[2] += d2; s[3] += d3;
+              }
               const float x = xyzs[r * 3], y = xyzs[r * 3 + 1], z = xyzs[r * 3 + 2];
               dwx[xi][0][0] = fmaf(d0, x, dwx[xi][0][0]); dwx[xi][0][1] = fmaf(d0, y, dwx[xi][0][1]); dwx[xi][0][2] = fmaf(d0, z, dwx[xi][0][2]);
               dwx[xi][1][0] = fmaf(d1, x, dwx[xi][1][0]); dwx[xi][1][1] = fmaf(d1, y, dwx[xi][1][1]); dwx[xi][1][2] = fmaf(d1, z, dwx[xi][1][2]);

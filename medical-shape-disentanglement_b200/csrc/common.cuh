@@ -64,6 +64,10 @@ struct FwdArgs {
   // non-null => X8 is not stashed and the wgrad kernel has no lin8 item.
   float* dw8_partials;
   long long dw8_stride;
+  // v3 TAN (Eikonal recompute pass, k_forward3<..., TAN>): per-row perturbed input (x', y', z', eps) written by
+  // k_backward2<EIK>, and dL/ds of the L1 term (the forward's gout) for dW8 = sum_r g_r Xt8[r,:]
+  const float4* eik_row;
+  const float* g_tan;
   // diagnostics (nullable): per-CTA cycle counters, see dsdf_debug_read
   unsigned long long* dbg;
 };
@@ -173,6 +177,25 @@ __device__ __forceinline__ void write_e_row_ns(uint32_t e_base, uint32_t r, floa
   st_shared_v4(base, u(xh) | (u(yh) << 16), u(zh) | (u(xl) << 16), u(yl) | (u(zl) << 16),
                u(xh) | (u(yh) << 16));
   st_shared_v4(base + 128u, u(zh) | (one << 16), one, 0u, 0u);
+}
+
+// A-side E row of the Eikonal recompute pass: the perturbed coordinates xyz' split in THREE bf16 terms (the
+// perturbation is ~1e-3 of xyz: two terms would resolve it to ~1 %) and the bias multiplier 1 + eps as 1 + bf16(eps):
+// [xh yh zh xl yl zl xh yh | zh 1 1 eps xr yr zr 0]  against  [wh wh wh wh wh wh wl wl | wl bh bl bh wh wh wh 0]
+__device__ __forceinline__ void write_e_row_tan(uint32_t e_base, uint32_t r, float x, float y, float z, float eps) {
+  auto u = [](__nv_bfloat16 b) -> uint32_t { return (uint32_t)__bfloat16_as_ushort(b); };
+  auto split3 = [](float v, __nv_bfloat16& h, __nv_bfloat16& l, __nv_bfloat16& rr) {
+    h = __float2bfloat16_rn(v);
+    const float d1 = v - __bfloat162float(h);
+    l = __float2bfloat16_rn(d1);
+    rr = __float2bfloat16_rn(d1 - __bfloat162float(l));
+  };
+  __nv_bfloat16 xh, xl, xr, yh, yl, yr, zh, zl, zr;
+  split3(x, xh, xl, xr); split3(y, yh, yl, yr); split3(z, zh, zl, zr);
+  const uint32_t one = 0x3F80u;
+  const uint32_t base = e_base + (r >> 3) * 256u + (r & 7u) * 16u;
+  st_shared_v4(base, u(xh) | (u(yh) << 16), u(zh) | (u(xl) << 16), u(yl) | (u(zl) << 16), u(xh) | (u(yh) << 16));
+  st_shared_v4(base + 128u, u(zh) | (one << 16), one | (u(__float2bfloat16_rn(eps)) << 16), u(xr) | (u(yr) << 16), u(zr));
 }
 
 // 32 fp32 accumulator columns -> ReLU -> 16 packed bf16x2

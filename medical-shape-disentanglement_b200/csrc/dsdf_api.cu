@@ -51,6 +51,7 @@ struct dsdf_handle_s {
   float* weff = nullptr;
   float* scale = nullptr;
   float* inv_norm = nullptr;
+  float4* wx = nullptr;          // [2][512] fp32 xyz columns of lin0 / lin4 (Eikonal backward)
   // wgrad schedule (rebuilt on the host when the tile count changes; fixed-capacity device buffers + pinned
   // staging, uploaded asynchronously on the caller's stream: no allocation, no synchronisation per call)
   WgSeg* wg2_segs = nullptr;
@@ -115,6 +116,12 @@ static int set_kernel_attrs(dsdf_handle h) {
 #undef F3ATTR
   CU(h, cudaFuncSetAttribute(k_forward3<MODE_TABLE, true, true, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, F3<1>::kSmemBytes));
   CU(h, cudaFuncSetAttribute(k_forward3<MODE_TABLE, true, true, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, F3<2>::kSmemBytes));
+#ifndef DSDF_ARCH_SIREN
+  CU(h, cudaFuncSetAttribute(k_forward3<MODE_TABLE, true, true, 1, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, F3<1>::kSmemBytes));
+  CU(h, cudaFuncSetAttribute(k_forward3<MODE_TABLE, true, true, 2, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, F3<2>::kSmemBytes));
+  CU(h, cudaFuncSetAttribute(k_backward2<1, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, B2<1>::kSmemBytes));
+  CU(h, cudaFuncSetAttribute(k_backward2<2, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, B2<2>::kSmemBytes));
+#endif
   CU(h, cudaFuncSetAttribute(k_backward2<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, B2<1>::kSmemBytes));
   CU(h, cudaFuncSetAttribute(k_backward2<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, B2<2>::kSmemBytes));
   CU(h, cudaFuncSetAttribute(k_backward2<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, B2<1>::kSmemBytes));
@@ -174,7 +181,8 @@ extern "C" int dsdf_create(const dsdf_config* cfg, dsdf_handle* out) {
             cudaEventCreateWithFlags(&h->wg2_uploaded, cudaEventDisableTiming) == cudaSuccess &&
             cudaMalloc(&h->weff, (size_t)(kWeffElems + 16) * 4) == cudaSuccess &&
             cudaMalloc(&h->scale, (size_t)kScaleElems * 4) == cudaSuccess &&
-            cudaMalloc(&h->inv_norm, (size_t)kScaleElems * 4) == cudaSuccess;
+            cudaMalloc(&h->inv_norm, (size_t)kScaleElems * 4) == cudaSuccess &&
+            cudaMalloc(&h->wx, (size_t)2 * kHidden * sizeof(float4)) == cudaSuccess;
   if (!ok) {
     dsdf_destroy(h);
     DSDF_FAIL((dsdf_handle) nullptr, DSDF_ENOMEM, "cudaMalloc of weight shadows failed");
@@ -198,6 +206,7 @@ extern "C" int dsdf_destroy(dsdf_handle h) {
   cudaFree(h->weff);
   cudaFree(h->scale);
   cudaFree(h->inv_norm);
+  cudaFree(h->wx);
   cudaFree(h->wg2_segs);
   cudaFree(h->wg2_seg_begin);
   if (h->wg2_stage) cudaFreeHost(h->wg2_stage);
@@ -237,6 +246,9 @@ extern "C" int dsdf_set_weights(dsdf_handle h, const float* params, const dsdf_p
   k_fold_fwd2<<<(unsigned)((c3 + 255) / 256), 256, 0, st>>>(h->weff, params, h->pl, h->w2_img);
   const long long c4 = (long long)kDg2Steps * (kStepBytes / 16);
   k_fold_dgrad2<<<(unsigned)((c4 + 255) / 256), 256, 0, st>>>(h->weff, h->dg2_img);
+#ifndef DSDF_ARCH_SIREN
+  k_build_wx<<<4, 256, 0, st>>>(h->weff, h->wx);
+#endif
   CU(h, cudaGetLastError());
   h->params_ptr = params;
   h->weights_set = true;
@@ -244,7 +256,7 @@ extern "C" int dsdf_set_weights(dsdf_handle h, const float* params, const dsdf_p
 }
 
 // ---- v3 forward launcher: persistent grid, CTA pairs (cta_group::2) when `pair_ok` -------------
-template <int MODE, bool FOLD, bool TRAIN, int CG, bool DROP = false>
+template <int MODE, bool FOLD, bool TRAIN, int CG, bool DROP = false, bool TAN = false>
 static cudaError_t launch_fwd3_cg(dsdf_handle h, const FwdArgs& a, cudaStream_t st) {
   const long long tiles = (a.n_rows + kTileM - 1) / kTileM;
   long long g = tiles < h->num_sms ? tiles : h->num_sms;
@@ -263,15 +275,15 @@ static cudaError_t launch_fwd3_cg(dsdf_handle h, const FwdArgs& a, cudaStream_t 
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  return cudaLaunchKernelEx(&cfg, k_forward3<MODE, FOLD, TRAIN, CG, DROP>, a);
+  return cudaLaunchKernelEx(&cfg, k_forward3<MODE, FOLD, TRAIN, CG, DROP, TAN>, a);
 }
 // pair_ok: both tiles of a pair may share the B operand (always true unless FOLD segments are
 // shorter than 256 rows-aligned, see callers)
-template <int MODE, bool FOLD, bool TRAIN, bool DROP = false>
+template <int MODE, bool FOLD, bool TRAIN, bool DROP = false, bool TAN = false>
 static cudaError_t launch_fwd(dsdf_handle h, const FwdArgs& a, cudaStream_t st, bool pair_ok) {
   const long long tiles = (a.n_rows + kTileM - 1) / kTileM;
-  if (pair_ok && h->fwd_cg == 2 && tiles >= 2) return launch_fwd3_cg<MODE, FOLD, TRAIN, 2, DROP>(h, a, st);
-  return launch_fwd3_cg<MODE, FOLD, TRAIN, 1, DROP>(h, a, st);
+  if (pair_ok && h->fwd_cg == 2 && tiles >= 2) return launch_fwd3_cg<MODE, FOLD, TRAIN, 2, DROP, TAN>(h, a, st);
+  return launch_fwd3_cg<MODE, FOLD, TRAIN, 1, DROP, TAN>(h, a, st);
 }
 // common fields of every forward launch
 static void fwd_args_init(dsdf_handle h, FwdArgs& a, long long n) {
@@ -387,6 +399,8 @@ extern "C" int dsdf_grid_coords(dsdf_handle h, int32_t grid_n, int64_t lo, int64
 
 // ------------------------------------------------------------------------------------ training
 
+static inline int eik_corr_blocks(int num_sms) { return 4 * num_sms; }
+
 namespace {
 struct Ws {
   uint8_t* xstash;
@@ -404,6 +418,9 @@ struct Ws {
   uint8_t* scene_e;
   uint32_t* relu_mask;
   uint8_t* g_img;
+  float4* eik_row;       // Eikonal: per-row (x', y', z', eps)
+  float* eik_tile;       // Eikonal: per-tile {sum (1-||G||)^2, sum eps g}
+  float* eik_corr;       // Eikonal: k_eik_corr block partials
   size_t total;
 };
 inline size_t al(size_t x) { return (x + 1023) & ~(size_t)1023; }
@@ -431,6 +448,9 @@ Ws carve(uint8_t* base, long long max_rows, long long max_seg, int num_sms) {
   w.scene_e = take((size_t)max_seg * kSceneESteps * kStepBytes);
   w.relu_mask = (uint32_t*)take(tiles * kActAuxTileBytes);
   w.g_img = take(tiles * kSubBytes);
+  w.eik_row = (float4*)take(tiles * kTileM * sizeof(float4));
+  w.eik_tile = (float*)take(tiles * 2 * 4);
+  w.eik_corr = (float*)take((size_t)eik_corr_blocks(num_sms) * kCorrFloats * 4);
   w.total = o;
   return w;
 }
@@ -609,7 +629,14 @@ static int launch_backward2(dsdf_handle h, const Bwd2Args& b2, long long tiles, 
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  if (b2.drop.layers != 0) {
+  if (b2.eik_row) {
+#ifndef DSDF_ARCH_SIREN
+    if (cg == 2) CU(h, (cudaLaunchKernelEx(&cfg, k_backward2<2, false, true>, b2)));
+    else CU(h, (cudaLaunchKernelEx(&cfg, k_backward2<1, false, true>, b2)));
+#else
+    DSDF_FAIL(h, DSDF_EUNSUPPORTED, "the Eikonal term is built for the ReLU decoder family only");
+#endif
+  } else if (b2.drop.layers != 0) {
     if (cg == 2) CU(h, (cudaLaunchKernelEx(&cfg, k_backward2<2, true>, b2)));
     else CU(h, (cudaLaunchKernelEx(&cfg, k_backward2<1, true>, b2)));
   } else {
@@ -623,12 +650,18 @@ static int launch_backward2(dsdf_handle h, const Bwd2Args& b2, long long tiles, 
 extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const float* table,
                                   int64_t num_scenes, const int64_t* seg_ids, int64_t n_seg,
                                   int64_t rows_per_seg, const float* sdf_data, int64_t n_total,
-                                  float clamp_dist, float reg_lambda_ramp, void* workspace,
-                                  size_t workspace_bytes, float* grads, float* lat_grad,
-                                  float* pred, float* loss_out, void* stream) {
+                                  float clamp_dist, float reg_lambda_ramp, float eikonal_lambda,
+                                  void* workspace, size_t workspace_bytes, float* grads, float* lat_grad,
+                                  float* pred, float* loss_out, void* grads_ready_event, void* stream) {
   if (!h || !params || !table || !seg_ids || !sdf_data || !workspace || !grads || !lat_grad ||
       !pred || !loss_out)
     DSDF_FAIL(h, DSDF_EINVAL, "null argument");
+  const bool eik = eikonal_lambda != 0.f;
+#ifdef DSDF_ARCH_SIREN
+  if (eik) DSDF_FAIL(h, DSDF_EUNSUPPORTED, "UseEikonal is built for the ReLU decoder family only (sine layers have a second derivative)");
+#endif
+  if (eik && h->drop.layers != 0)
+    DSDF_FAIL(h, DSDF_EUNSUPPORTED, "UseEikonal together with NetworkSpecs.dropout is not built");
   if (!h->weights_set) DSDF_FAIL(h, DSDF_EINVAL, "dsdf_set_weights has not been called");
   if (n_seg <= 0 || rows_per_seg <= 0 || rows_per_seg % kTileM != 0)
     DSDF_FAIL(h, DSDF_EUNSUPPORTED,
@@ -646,7 +679,7 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
               workspace_bytes);
   // the forward epilogue accumulates dW8 = g^T X8 itself (no X8 stash, no lin8 wgrad item); the diagnostics
   // variant can keep the previous split (dW8 as a wgrad item) for A/B timing
-  const bool dw8_fwd = !h->dw8_wgrad;
+  const bool dw8_fwd = !h->dw8_wgrad || eik;
   int rc = build_wg2_schedule(h, tiles, st, !dw8_fwd);
   if (rc != DSDF_OK) return rc;
 
@@ -676,10 +709,13 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   fa.scene_e = w.scene_e;
   fa.relu_mask = w.relu_mask;
   fa.g_img = dw8_fwd ? nullptr : w.g_img;
-  if (dw8_fwd) {
+  if (dw8_fwd && !eik) {
     fa.dw8_partials = w.cta_partials + kPartW8;
     fa.dw8_stride = kCtaPartialFloats;
   }
+  // Eikonal (train_deep_sdf.py:724-729; tests/eikonal_algebra.py): this pass only decides the ReLU masks and the
+  // L1 upstream; the activations the wgrad contracts are written by the recompute pass after the dgrad chain
+  if (eik) fa.xstash = nullptr;
   const bool pair_ok = rows_per_seg % (2 * kTileM) == 0;
   // CTAs of the forward launch (launch_fwd3_cg): one dW8 partial each
   int fwd_ctas = 0;
@@ -721,30 +757,65 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   b2.tile_colsum = w.tile_colsum;
   b2.cta_partials = w.cta_partials;
   b2.drop = h->drop;
+  if (eik) {
+    b2.pred = pred;
+    b2.wx = h->wx;
+    b2.clamp_dist = clamp_dist;
+    b2.eik_c2 = 2.0f * eikonal_lambda * inv_n;
+    b2.eik_row = w.eik_row;
+    b2.eik_tile = w.eik_tile;
+  }
   unsigned bwd_grid = 0;
   rc = launch_backward2(h, b2, tiles, st, &bwd_grid);
   if (rc != DSDF_OK) return rc;
   if (prof) prof_mark(h, st);
 
+  int n_corr = 0;
+  if (eik) {
+#ifndef DSDF_ARCH_SIREN
+    // ---- recompute pass: the chain again over (xyz', 1 + eps) with the stored masks -> Xt stash, dW8
+    FwdArgs ta = fa;
+    ta.xstash = w.xstash;
+    ta.eik_row = w.eik_row;
+    ta.g_tan = w.g;
+    ta.out = nullptr;
+    ta.gout = nullptr;
+    ta.tile_partials = nullptr;
+    ta.fused_loss = 0;
+    ta.dw8_partials = w.cta_partials + kPartW8;
+    ta.dw8_stride = kCtaPartialFloats;
+    CU(h, (launch_fwd<MODE_TABLE, true, true, false, true>(h, ta, st, pair_ok)));
+    // ---- eps-weighted corrections of the row sums that are not GEMMs (bias grads, colsum(dY4), dW4[:, xyz])
+    n_corr = eik_corr_blocks(h->num_sms);
+    if (n_corr > tiles) n_corr = (int)tiles;
+    k_eik_corr<<<n_corr, 256, 0, st>>>(w.dystash, w.eik_row, sdf_data, tiles, w.tile_colsum, w.eik_corr);
+#endif
+  }
+
   // ---- wgrad GEMMs (lin1..lin7) + split-K reduction
   rc = launch_wgrad2(h, w.xstash, w.dystash, w.g_img, w.wg_partials, w.dweff, st, prof);
   if (rc != DSDF_OK) return rc;
 
-  // ---- segmented (scene-contiguous) reductions: latent grads, latent columns of dW0/dW4, biases
+  // ---- segmented (scene-contiguous) reductions.  Decoder gradient first (it is what a multi-GPU caller
+  // all-reduces: `grads_ready_event` is recorded as soon as `grads` is final, so the collective can run on a side
+  // stream under the latent-gradient kernels below and the latent Adam that follows), then the latent side.
   const float reg_coef = reg_lambda_ramp * (float)rows_per_seg * inv_n;
   k_seg_colsum<<<dim3((unsigned)n_seg, 2), kHidden, 0, st>>>(w.tile_colsum, tiles_per_seg, w.seg_sum);
+  k_dw_latent<<<dim3(kHidden, 2), kLatent, 0, st>>>(w.seg_sum, table, (const long long*)seg_ids,
+                                                    (int)n_seg, w.dweff);
+  k_reduce_cta<<<16, kHidden, 0, st>>>(w.cta_partials, (int)bwd_grid, w.seg_sum, (int)n_seg,
+                                      w.tile_partials, tiles, h->pl, grads, w.dweff, dw8_fwd ? fwd_ctas : 0,
+                                      eik ? w.eik_corr : nullptr, n_corr, eik ? w.eik_tile : nullptr);
+  k_param_grads<<<(kScaleElems * 32 + 255) / 256, 256, 0, st>>>(w.dweff, params, h->pl, h->scale,
+                                                                h->inv_norm, grads);
+  if (grads_ready_event) CU(h, cudaEventRecord((cudaEvent_t)grads_ready_event, st));
   k_lat_grad_seg<<<(unsigned)n_seg, 1024, 0, st>>>(w.seg_sum, h->weff, table,
                                                       (const long long*)seg_ids, reg_coef,
                                                       w.dlat_seg, w.seg_norm);
   CU(h, cudaMemsetAsync(lat_grad, 0, (size_t)num_scenes * kLatent * 4, st));
   k_lat_grad_scatter<<<(unsigned)n_seg, kLatent, 0, st>>>(w.dlat_seg, (const long long*)seg_ids, (int)n_seg, lat_grad);
-  k_dw_latent<<<dim3(kHidden, 2), kLatent, 0, st>>>(w.seg_sum, table, (const long long*)seg_ids,
-                                                    (int)n_seg, w.dweff);
-  k_reduce_cta<<<16, kHidden, 0, st>>>(w.cta_partials, (int)bwd_grid, w.seg_sum, (int)n_seg,
-                                      w.tile_partials, tiles, h->pl, grads, w.dweff, dw8_fwd ? fwd_ctas : 0);
-  k_param_grads<<<(kScaleElems * 32 + 255) / 256, 256, 0, st>>>(w.dweff, params, h->pl, h->scale,
-                                                                h->inv_norm, grads);
-  k_loss<<<1, 1024, 0, st>>>(w.tile_partials, tiles, inv_n, w.seg_norm, (int)n_seg, reg_coef, loss_out);
+  k_loss<<<1, 1024, 0, st>>>(w.tile_partials, tiles, inv_n, w.seg_norm, (int)n_seg, reg_coef, loss_out,
+                             eik ? w.eik_tile : nullptr, eikonal_lambda);
   if (prof) prof_mark(h, st);
   CU(h, cudaGetLastError());
   return DSDF_OK;

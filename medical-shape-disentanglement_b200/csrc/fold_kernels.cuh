@@ -72,7 +72,9 @@ __device__ __forceinline__ float weff_at(const float* weff, int l, int o, int i)
 namespace dsdf {
 
 // E-step row of output feature o of layer l with bias value `bias`:
-// [wxh wyh wzh | wxh wyh wzh | wxl wyl wzl | bh | bl | 0 x5]  (two 16 B chunks)
+// [wxh wyh wzh | wxh wyh wzh | wxl wyl wzl | bh | bl | bh | wxh wyh wzh | 0]  (two 16 B chunks)
+// Columns 11..14 only meet non-zero A columns in the Eikonal recompute pass (k_forward3<TAN>: A = [.. | eps |
+// third-order xyz residual]); every other caller writes zeros there, so they change nothing.
 __device__ __forceinline__ void e_step_row(const float* weff, int l, int o, bool o_valid,
                                            float bias, uint4& c0, uint4& c1) {
   float v[16];
@@ -85,11 +87,11 @@ __device__ __forceinline__ void e_step_row(const float* weff, int l, int o, bool
       if (xc >= 0) {
         const float w = weff_at(weff, l, o, xc);
         const float wh = __bfloat162float(__float2bfloat16_rn(w));
-        v[e] = wh; v[3 + e] = wh; v[6 + e] = w - wh;
+        v[e] = wh; v[3 + e] = wh; v[6 + e] = w - wh; v[12 + e] = wh;
       }
     }
     const float bh = __bfloat162float(__float2bfloat16_rn(bias));
-    v[9] = bh; v[10] = bias - bh;
+    v[9] = bh; v[10] = bias - bh; v[11] = bh;
   }
   c0 = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
   c1 = make_uint4(pack_bf16x2(v[8], v[9]), pack_bf16x2(v[10], v[11]), pack_bf16x2(v[12], v[13]), pack_bf16x2(v[14], v[15]));
@@ -153,6 +155,19 @@ __global__ void k_fold_dgrad2(const float* __restrict__ weff, uint8_t* __restric
   w.x = pack_bf16x2(vals[0], vals[1]); w.y = pack_bf16x2(vals[2], vals[3]);
   w.z = pack_bf16x2(vals[4], vals[5]); w.w = pack_bf16x2(vals[6], vals[7]);
   *reinterpret_cast<uint4*>(img + (size_t)step * kStepBytes + (size_t)within * 16) = w;
+}
+
+// fp32 xyz columns of lin0 / lin4 as float4 rows (x, y, z, 0): wx[c] = W0[c, 256..258], wx[512 + c] = W4[c, 509..511]
+// (the Eikonal backward's per-row d s / d xyz = sum_c dY0[c] W0x[c] + dY4[c] W4x[c]).  1024 threads.
+__global__ void k_build_wx(const float* __restrict__ weff, float4* __restrict__ wx) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 2 * kHidden) return;
+  const int l = i < kHidden ? 0 : kSkipLayer, c = i & (kHidden - 1);
+  float v[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+  for (int e = 0; e < 3; ++e)
+    if (xyz_col(l, e) >= 0) v[e] = weff_at(weff, l, c, xyz_col(l, e));
+  wx[i] = make_float4(v[0], v[1], v[2], 0.f);
 }
 
 // Fold mode: per-segment E steps of lin0 / lin4 with bias' = b + W[:, latent] z_seg (fp32).

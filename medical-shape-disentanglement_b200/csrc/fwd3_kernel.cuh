@@ -86,7 +86,26 @@ __device__ __forceinline__ void mask_scale_pack32(const uint32_t (&v)[32], uint3
   }
 }
 
+// 32 fp32 columns -> zero where the mask bit (31 - i) is clear -> 16 packed bf16x2
+__device__ __forceinline__ void mask_pack32(const uint32_t (&v)[32], uint32_t m, uint32_t* p) {
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const float lo = (m & (0x80000000u >> (2 * i))) ? __uint_as_float(v[2 * i]) : 0.f;
+    const float hi = (m & (0x40000000u >> (2 * i))) ? __uint_as_float(v[2 * i + 1]) : 0.f;
+    p[i] = pack_bf16x2(lo, hi);
+  }
+}
+
 #ifdef DSDF_ARCH_SIREN
+// sin / cos of y = 30 x with |y| possibly tens of radians (trained SIRENs): the hardware
+// approximation's absolute error grows with |y|, so reduce first -- Cody-Waite with 2 pi = C1 + C2, C1 exact in
+// 9 bits (k C1 is exact for |k| < 2^15, i.e. |y| < 2e5) -- and evaluate on r in [-pi, pi] where it is ~2^-21.
+__device__ __forceinline__ void sincos_reduced(float y, float& s, float& c) {
+  const float k = rintf(y * 0.15915494309189535f);
+  float r = fmaf(-k, 6.28125f, y);
+  r = fmaf(-k, 1.9353071795864769e-3f, r);
+  __sincosf(r, &s, &c);
+}
 // networks/modules.py:4-14 Sine: 32 fp32 pre-activations -> sin(30 x) (16 packed bf16x2 in p) and the
 // derivative 30 cos(30 x) (16 packed bf16x2 in d); returns sum_i sin(30 x_i) w[i] when w != nullptr.
 __device__ __forceinline__ float sine_pack32(const uint32_t (&v)[32], uint32_t* p, uint32_t* d, const float* w) {
@@ -94,8 +113,8 @@ __device__ __forceinline__ float sine_pack32(const uint32_t (&v)[32], uint32_t* 
 #pragma unroll
   for (int i = 0; i < 16; ++i) {
     float s0, c0, s1, c1;
-    __sincosf(30.f * __uint_as_float(v[2 * i]), &s0, &c0);
-    __sincosf(30.f * __uint_as_float(v[2 * i + 1]), &s1, &c1);
+    sincos_reduced(30.f * __uint_as_float(v[2 * i]), s0, c0);
+    sincos_reduced(30.f * __uint_as_float(v[2 * i + 1]), s1, c1);
     p[i] = pack_bf16x2(s0, s1);
     d[i] = pack_bf16x2(30.f * c0, 30.f * c1);
     if (w) acc = fmaf(s1, w[2 * i + 1], fmaf(s0, w[2 * i], acc));
@@ -118,9 +137,14 @@ __device__ __forceinline__ void deriv_load(const uint8_t* aux_tile, int l, int c
 }
 #endif
 
-template <int MODE, bool FOLD, bool TRAIN, int CG, bool DROP = false>
+// TAN: the Eikonal recompute pass (train_deep_sdf.py:724-729 without double backward, tests/eikonal_algebra.py):
+// the same chain over the perturbed per-row input (x', y', z', eps) of FwdArgs::eik_row, with the ReLU decisions
+// READ from the first pass's bit-masks instead of taken from the sign (the map is then linear in the input), no
+// output / loss; stashes Xt_l = (1 + eps) h_l + tangent and accumulates dW8 = sum_r g_r Xt8[r, :].
+template <int MODE, bool FOLD, bool TRAIN, int CG, bool DROP = false, bool TAN = false>
 __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
   static_assert(!DROP || TRAIN, "dropout exists in training mode only");
+  static_assert(!TAN || (TRAIN && FOLD && !DROP && MODE == MODE_TABLE), "the recompute pass is a fold-mode training pass");
   using C = F3<CG>;
   constexpr int kRing = C::kRing;
   constexpr uint32_t kSlice = C::kSlice;
@@ -421,11 +445,27 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
         if (TRAIN && tile_valid) deriv_store(aux_tile, l, (int)(col >> 5), r, d);
         return 0u;
       };
+      auto load_masks = [](int) {};        // (the recompute pass exists for the ReLU family only)
 #else
       uint32_t* mask_tile = TRAIN ? a.relu_mask + (size_t)tile * (8 * 16 * kTileM) + r : nullptr;
+      [[maybe_unused]] uint32_t mk[8];     // TAN: this thread's 8 mask words of the current layer (h0: 0..3, h1: 4..7)
+      auto load_masks = [&](int l) {
+        if (TAN) {
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            mk[c] = __ldg(mask_tile + (size_t)(l * 16 + j * 4 + c) * kTileM);
+            mk[4 + c] = (l != 3) ? __ldg(mask_tile + (size_t)(l * 16 + 8 + j * 4 + c) * kTileM) : 0u;
+          }
+        }
+      };
       // ReLU (+ dropout) of 32 accumulator columns -> packed bf16; stores and returns the mask word
       auto act_pack32 = [&](const uint32_t (&v)[32], int l, uint32_t col, uint32_t* p) -> uint32_t {
         uint32_t m;
+        if (TAN) {                          // the first pass's decision (preloaded per layer), not this pass's sign
+          m = mk[((col >> 8) << 2) | ((col >> 5) & 3u)];
+          mask_pack32(v, m, p);
+          return m;
+        }
         if (DROP && ((a.drop.layers >> l) & 1u)) {
           m = pos_mask32(v) & dropout_keep32(a.drop, a.drop.row_base + row0 + r, l, (int)(col >> 5));
           mask_scale_pack32(v, m, a.drop.scale, p);
@@ -443,15 +483,21 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
       if (t < kTileM) {
         long long row = row0 + t;
         row = row < a.n_rows ? row : a.n_rows - 1;
-        float x, y, z;
-        load_xyz<MODE>(a, row, x, y, z, gt);
-        write_e_row_ns(s_base + C::kSmemEA, t, x, y, z);
+        if (TAN) {
+          const float4 e = __ldg(a.eik_row + row);
+          write_e_row_tan(s_base + C::kSmemEA, t, e.x, e.y, e.z, e.w);
+        } else {
+          float x, y, z;
+          load_xyz<MODE>(a, row, x, y, z, gt);
+          write_e_row_ns(s_base + C::kSmemEA, t, x, y, z);
+        }
       }
       publish(a_lo_c);
 
 #pragma unroll 1
       for (int l = 0; l < 7; ++l) {
         const bool has_h1 = (l != 3);
+        load_masks(l);
         // ---- half 0: TMEM -> ReLU -> bf16, held in registers while the MMAs still read A
         uint32_t held[64];
         {
@@ -529,7 +575,42 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
 
       // ---- lin7 epilogue fused with lin8 (512 -> 1), tanh, loss
       float acc = 0.f;
-      {
+      if (TAN) {
+        // recompute pass: Xt8 = mask7 . (lin7 output) goes through the A tile only for dW8 = g^T Xt8 below
+        uint32_t held[64];
+        load_masks(7);
+        mbar_wait(&d_done[0], par_d0);
+        par_d0 ^= 1;
+        tc_fence_after();
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint32_t v[32];
+          const uint32_t col = (uint32_t)(j * 128 + c * 32);
+          tmem_ld_32x32(tmem + tlane + col, v);
+          tmem_ld_wait();
+          act_pack32(v, 7, col, held + 16 * c);
+        }
+        mbar_wait(&d_done[1], par_d1);
+        par_d1 ^= 1;
+        tc_fence_after();
+        mbar_wait(s_done, par_s);
+        par_s ^= 1;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) store_chunk32(a_base, r, (uint32_t)(j * 128 + c * 32), held + 16 * c);
+        __syncwarp();
+        stash_ready(s_lo);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint32_t v[32], p[16];
+          const uint32_t col = (uint32_t)(256 + j * 128 + c * 32);
+          tmem_ld_32x32(tmem + tlane + col, v);
+          tmem_ld_wait();
+          act_pack32(v, 7, col, p);
+          store_chunk32(a_base, r, col, p);
+        }
+        __syncwarp();
+        stash_ready(s_hi);
+      } else {
         uint32_t held[TRAIN ? 64 : 1];
         mbar_wait(&d_done[0], par_d0);
         par_d0 ^= 1;
@@ -614,6 +695,13 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
         }
       }
       tc_fence_before();
+      if (TAN) {
+        if (j == 0) {
+          const long long row = row0 + r;
+          gsm[r] = (tile_valid && row < a.n_rows) ? __ldg(a.g_tan + row) : 0.f;
+        }
+        named_bar_sync(1, kActThreads);     // gsm and the A tile (Xt8) are complete
+      } else {
       if (j == 1) part[r] = acc;
       named_bar_sync(1, kActThreads);
       if (j == 0) {
@@ -659,11 +747,14 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
           if (lane == 0) { red[q * 2] = lossr; red[q * 2 + 1] = g; }
         }
       }
-      if (TRAIN && a.fused_loss) {
-        named_bar_sync(1, kActThreads);
-        if (t == 0 && tile_valid) {
-          a.tile_partials[tile * 2] = (red[0] + red[2]) + (red[4] + red[6]);
-          a.tile_partials[tile * 2 + 1] = (red[1] + red[3]) + (red[5] + red[7]);
+      }   // !TAN
+      if (TAN || (TRAIN && a.fused_loss)) {
+        if (!TAN) {
+          named_bar_sync(1, kActThreads);
+          if (t == 0 && tile_valid) {
+            a.tile_partials[tile * 2] = (red[0] + red[2]) + (red[4] + red[6]);
+            a.tile_partials[tile * 2 + 1] = (red[1] + red[3]) + (red[5] + red[7]);
+          }
         }
         if (a.dw8_partials) {
           // dW8[c] += sum_r g[r] X8[r, c] straight from the A tile (train_deep_sdf.py:731 for lin8.weight):
@@ -686,7 +777,7 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
         named_bar_sync(1, kActThreads);   // part[] is rewritten by the next tile
       }
     }
-    if (TRAIN && a.fused_loss && a.dw8_partials) {
+    if ((TAN || (TRAIN && a.fused_loss)) && a.dw8_partials) {
       float* o = a.dw8_partials + (size_t)blockIdx.x * a.dw8_stride;
       o[2 * t] = dw8a;
       o[2 * t + 1] = dw8b;

@@ -187,6 +187,114 @@ __global__ void k_reduce_wgrad2(const float* __restrict__ partials, Wg2Layout wl
   dweff[weff_off(l) + (size_t)o * ref_in(l) + ic] = s;
 }
 
+// ---- Eikonal term: row-weighted column sums of the stashed dY_l, l = 1..7 ---------------------------------
+// The dgrad chain runs with the L1 upstream g; the Eikonal term adds eps_r g_r on row r (known only at the end of
+// the chain, tests/eikonal_algebra.py), so every sum over rows that is not a wgrad GEMM needs a correction:
+//   db_l      += sum_r eps_r dY_l[r, :]                       l in {1,2,3,5,6,7}  -> corr[block][slot][512]
+//   colsum(dY4) per tile += sum_r eps_r dY4[r, :]             (-> db4, latent grads, latent columns of dW4)
+//   dW4[:, xyz] += sum_r dY4[r, :] (xyz'_r - xyz_r)                                -> corr[block][6*512 + c*3 + e]
+// (layer 0 is weighted inside k_backward2<EIK>; the weight matrices get theirs through the recompute pass.)
+// HBM-bound: reads the dY stash once (6.5 x 128 KB per tile).  grid = any, 256 threads; block b takes tiles
+// b, b + grid, ...; thread = (16-byte chunk ch = t & 7, rows (t >> 3) + 32 i): a warp reads 4 full 128-byte rows.
+constexpr int kCorrFloats = 6 * kHidden + kHidden * 3;
+__global__ void __launch_bounds__(256, 4) k_eik_corr(const uint8_t* __restrict__ dystash,
+                                                     const float4* __restrict__ eik_row,
+                                                     const float* __restrict__ sdf_data, long long n_tiles,
+                                                     float* __restrict__ tile_colsum, float* __restrict__ corr) {
+  __shared__ float w_eps[kTileM], w_dx[kTileM], w_dy[kTileM], w_dz[kTileM];
+  __shared__ float red[8][4][64];
+  __shared__ float db_acc[6][kHidden];
+  __shared__ float dwx_acc[kHidden * 3];
+  const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+  const uint32_t ch = t & 7, rg = t >> 3;
+  for (int i = t; i < 6 * kHidden; i += 256) (&db_acc[0][0])[i] = 0.f;
+  for (int i = t; i < 3 * kHidden; i += 256) dwx_acc[i] = 0.f;
+  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    __syncthreads();
+    if (t < kTileM) {
+      const long long row = tile * kTileM + t;
+      const float4 e = __ldg(eik_row + row);
+      const float4 x = __ldg(reinterpret_cast<const float4*>(sdf_data) + row);
+      w_eps[t] = e.w; w_dx[t] = e.x - x.x; w_dy[t] = e.y - x.y; w_dz[t] = e.z - x.z;
+    }
+    __syncthreads();
+    const uint8_t* dy_tile = dystash + (size_t)tile * kStashTileBytes;
+#pragma unroll 1
+    for (int l = 1; l <= 7; ++l) {
+      const int nsub = l == 3 ? 4 : 8;
+      const bool skip = l == kSkipLayer;
+#pragma unroll 1
+      for (int sub = 0; sub < nsub; ++sub) {
+        const uint8_t* base = dy_tile + (size_t)l * kTileBytes + (size_t)sub * kSubBytes;
+        uint4 v[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          v[i] = __ldg(reinterpret_cast<const uint4*>(base + sub_chunk_off(rg + 32 * i, ch)));
+        float acc[4][8];
+#pragma unroll
+        for (int w = 0; w < 4; ++w)
+#pragma unroll
+          for (int k = 0; k < 8; ++k) acc[w][k] = 0.f;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const uint32_t r = rg + 32 * i;
+          const uint32_t wd[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+          const float we = w_eps[r];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const float lo = bf16_lo(wd[k]), hi = bf16_hi(wd[k]);
+            acc[0][2 * k] = fmaf(we, lo, acc[0][2 * k]);
+            acc[0][2 * k + 1] = fmaf(we, hi, acc[0][2 * k + 1]);
+          }
+          if (skip && kXyzAtSkip) {
+            const float wx = w_dx[r], wy = w_dy[r], wz = w_dz[r];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const float lo = bf16_lo(wd[k]), hi = bf16_hi(wd[k]);
+              acc[1][2 * k] = fmaf(wx, lo, acc[1][2 * k]); acc[1][2 * k + 1] = fmaf(wx, hi, acc[1][2 * k + 1]);
+              acc[2][2 * k] = fmaf(wy, lo, acc[2][2 * k]); acc[2][2 * k + 1] = fmaf(wy, hi, acc[2][2 * k + 1]);
+              acc[3][2 * k] = fmaf(wz, lo, acc[3][2 * k]); acc[3][2 * k + 1] = fmaf(wz, hi, acc[3][2 * k + 1]);
+            }
+          }
+        }
+        const int nw = (skip && kXyzAtSkip) ? 4 : 1;
+        // the 4 row groups of a warp (lane bits 3, 4), fixed order
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+          if (w < nw) {                   // block-uniform
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+              float a0 = acc[w][k];
+              a0 += __shfl_xor_sync(0xffffffffu, a0, 8);
+              a0 += __shfl_xor_sync(0xffffffffu, a0, 16);
+              if (lane < 8) red[warp][w][ch * 8 + k] = a0;
+            }
+          }
+        }
+        __syncthreads();
+        if (t < 64 * nw) {
+          const int w = t >> 6, c = t & 63;
+          float sum = 0.f;
+#pragma unroll
+          for (int k = 0; k < 8; ++k) sum += red[k][w][c];
+          const int col = sub * 64 + c;
+          if (w == 0) {
+            if (skip) tile_colsum[((size_t)tile * 2 + 1) * kHidden + col] += sum;   // single writer per (tile, col)
+            else db_acc[db_slot(l)][col] += sum;
+          } else {
+            dwx_acc[col * 3 + (w - 1)] += sum;
+          }
+        }
+        __syncthreads();
+      }
+    }
+  }
+  __syncthreads();
+  float* out = corr + (size_t)blockIdx.x * kCorrFloats;
+  for (int i = t; i < 6 * kHidden; i += 256) out[i] = (&db_acc[0][0])[i];
+  for (int i = t; i < 3 * kHidden; i += 256) out[6 * kHidden + i] = dwx_acc[i];
+}
+
 // ---- reducer-warp partials (per CTA) -> bias grads, dW8, xyz columns of dW0/dW4 -----------------
 // grid 16 jobs x 512 threads (column c); every job sums its partials in a fixed order (deterministic):
 //   0..5   db of lin {1,2,3,5,6,7}        6..11  xyz column e of dW{0,4}   (job - 6 = 3 i + e)
@@ -195,7 +303,9 @@ __global__ void k_reduce_cta(const float* __restrict__ cta_partials, int n_cta,
                              const float* __restrict__ seg_sum, int n_seg,
                              const float* __restrict__ tile_partials, long long n_tiles,
                              ParamLayout pl, float* __restrict__ grads,
-                             float* __restrict__ dweff, int n_cta_dw8) {
+                             float* __restrict__ dweff, int n_cta_dw8,
+                             const float* __restrict__ corr = nullptr, int n_corr = 0,
+                             const float* __restrict__ eik_tile = nullptr) {
   __shared__ float sh[16];
   const int c = threadIdx.x, job = blockIdx.x;
   if (job < 6) {
@@ -203,6 +313,8 @@ __global__ void k_reduce_cta(const float* __restrict__ cta_partials, int n_cta,
     float s = 0.f;
 #pragma unroll 16
     for (int k = 0; k < n_cta; ++k) s += cta_partials[(size_t)k * kCtaPartialFloats + kPartDb + job * kHidden + c];
+#pragma unroll 16
+    for (int k = 0; k < n_corr; ++k) s += corr[(size_t)k * kCorrFloats + job * kHidden + c];   // Eikonal: sum eps dY
     if (c < ref_out(ls[job])) grads[pl.b[ls[job]] + c] = s;
   } else if (job < 12) {
     const int i = (job - 6) / 3, e = (job - 6) % 3, l = i == 0 ? 0 : 4;
@@ -211,6 +323,10 @@ __global__ void k_reduce_cta(const float* __restrict__ cta_partials, int n_cta,
 #pragma unroll 16
     for (int k = 0; k < n_cta; ++k)
       s += cta_partials[(size_t)k * kCtaPartialFloats + kPartXyz + (i * kHidden + c) * 3 + e];
+    if (i == 1) {
+#pragma unroll 16
+      for (int k = 0; k < n_corr; ++k) s += corr[(size_t)k * kCorrFloats + 6 * kHidden + c * 3 + e];
+    }
     dweff[weff_off(l) + (size_t)c * ref_in(l) + xyz_col(l, e)] = s;
   } else if (job < 14) {
     const int i = job - 12;
@@ -220,7 +336,8 @@ __global__ void k_reduce_cta(const float* __restrict__ cta_partials, int n_cta,
     grads[pl.b[i == 0 ? 0 : 4] + c] = s;
   } else if (job == 14) {
     float s = 0.f;
-    for (long long t = c; t < n_tiles; t += blockDim.x) s += tile_partials[t * 2 + 1];
+    for (long long t = c; t < n_tiles; t += blockDim.x)
+      s += tile_partials[t * 2 + 1] + (eik_tile ? eik_tile[t * 2 + 1] : 0.f);   // db8 = sum (1 + eps) g
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
     if ((c & 31) == 0) sh[c >> 5] = s;
@@ -272,18 +389,26 @@ __global__ void k_param_grads(const float* __restrict__ dweff, const float* __re
 // one block, 1024 threads.  loss_out[0] = sdf loss, loss_out[1] = reg loss
 __global__ void k_loss(const float* __restrict__ tile_partials, long long n_tiles, float inv_n,
                        const float* __restrict__ seg_norm, int n_seg, float reg_coef,
-                       float* __restrict__ loss_out) {
-  __shared__ float sh[32];
-  float s = 0.f;
-  for (long long t = threadIdx.x; t < n_tiles; t += blockDim.x) s += tile_partials[t * 2];
+                       float* __restrict__ loss_out, const float* __restrict__ eik_tile = nullptr,
+                       float eik_lambda = 0.f) {
+  __shared__ float sh[32], she[32];
+  float s = 0.f, se = 0.f;
+  for (long long t = threadIdx.x; t < n_tiles; t += blockDim.x) {
+    s += tile_partials[t * 2];
+    if (eik_tile) se += eik_tile[t * 2];
+  }
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = s;
+  for (int o = 16; o > 0; o >>= 1) {
+    s += __shfl_xor_sync(0xffffffffu, s, o);
+    se += __shfl_xor_sync(0xffffffffu, se, o);
+  }
+  if ((threadIdx.x & 31) == 0) { sh[threadIdx.x >> 5] = s; she[threadIdx.x >> 5] = se; }
   __syncthreads();
   if (threadIdx.x == 0) {
-    float t = 0.f;
-    for (int i = 0; i < (int)(blockDim.x >> 5); ++i) t += sh[i];
+    float t = 0.f, te = 0.f;
+    for (int i = 0; i < (int)(blockDim.x >> 5); ++i) { t += sh[i]; te += she[i]; }
     loss_out[0] = t * inv_n;
+    loss_out[2] = eik_lambda * te * inv_n;     // train_deep_sdf.py:727 (this rank's rows / N_total)
     float r = 0.f;
     for (int b = 0; b < n_seg; ++b) r += seg_norm[b];
     loss_out[1] = reg_coef * r;   // reg_coef = lambda*ramp*P/N

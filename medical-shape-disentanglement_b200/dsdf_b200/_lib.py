@@ -81,8 +81,8 @@ def lib(arch: str = "deep_sdf_decoder"):
     L.dsdf_grid_coords.restype = C.c_int
     L.dsdf_train_workspace_bytes.argtypes = [vp, i64, i64]
     L.dsdf_train_workspace_bytes.restype = sz
-    L.dsdf_train_fwd_bwd.argtypes = [vp, vp, vp, i64, vp, i64, i64, vp, i64, f32, f32, vp, sz,
-                                     vp, vp, vp, vp, vp]
+    L.dsdf_train_fwd_bwd.argtypes = [vp, vp, vp, i64, vp, i64, i64, vp, i64, f32, f32, f32, vp, sz,
+                                     vp, vp, vp, vp, vp, vp]
     L.dsdf_train_fwd_bwd.restype = C.c_int
     L.dsdf_renorm_rows.argtypes = [vp, vp, i64, vp, i64, f32, vp]
     L.dsdf_renorm_rows.restype = C.c_int

@@ -125,6 +125,20 @@ class FusedTrainer:
         self._ws_key = None
         self._pred = None
         self.dropout_row_base = 0               # global index of this rank's first row (sharded runs)
+        self._last_ids = None
+        # scene-sharded runs: the decoder-gradient all-reduce goes to a side stream as soon as the gradient is final
+        # (event recorded inside dsdf_train_fwd_bwd), under the latent-gradient kernels and the latent Adam
+        self._comm_stream = None
+        self._grads_ready = None
+        if process_group is not None and torch.distributed.get_world_size(process_group) > 1:
+            self._comm_stream = torch.cuda.Stream(device=dev)
+            self._grads_ready = torch.cuda.Event()
+            self._grads_ready.record(torch.cuda.current_stream(dev))     # instantiates the cudaEvent_t handle
+        if cfg.use_eikonal and decoder._arch != "deep_sdf_decoder":
+            raise NotImplementedError("specs['UseEikonal'] = true is built for NetworkArch deep_sdf_decoder only "
+                                      "(sine layers have a non-zero second derivative)")
+        if cfg.use_eikonal and decoder.dropout and decoder.dropout_prob > 0:
+            raise NotImplementedError("specs['UseEikonal'] together with a non-empty NetworkSpecs.dropout is not built")
 
     # ---------------------------------------------------------------- helpers
     def lr(self, which: int, epoch: int) -> float:
@@ -159,12 +173,24 @@ class FusedTrainer:
         flat = dec.flat_params()
         if self.grads.data_ptr() == 0 or self.grads.numel() != flat.numel():
             raise RuntimeError("decoder parameters were re-laid out after the trainer was built")
-        assert sdf_data.is_cuda and indices.is_cuda, "inputs must already be on the GPU"
+        if not sdf_data.is_cuda:
+            raise _lib.DsdfError("sdf_data must already be on the GPU (there is no CPU path)")
         sdf = sdf_data.reshape(-1, 4).contiguous().float()
         ids = indices.reshape(-1).contiguous().to(torch.int64)
         n_seg = ids.numel()
         rows = sdf.shape[0]
+        if n_seg == 0 or rows % n_seg != 0:
+            raise ValueError(f"{rows} sample rows do not split evenly over {n_seg} scenes "
+                             "(train_deep_sdf.py:571-577 repeats every scene id SamplesPerScene times)")
         p = rows // n_seg
+        # nn.Embedding raises on an index outside the table (train_deep_sdf.py:598).  Host-resident ids (what the
+        # reference's DataLoader yields) are checked here for free; device-resident ids are checked by the step
+        # itself (loss_buf[3], see check_status) so that no host sync is forced on the hot path.
+        if not ids.is_cuda:
+            if n_seg and (int(ids.min()) < 0 or int(ids.max()) >= self.num_scenes):
+                raise IndexError(f"scene index out of range [0, {self.num_scenes}): "
+                                 f"min {int(ids.min())}, max {int(ids.max())}")
+            ids = ids.to(self.device, non_blocking=True)
         if n_total is None:
             n_total = rows
             if self.pg is not None:
@@ -182,47 +208,82 @@ class FusedTrainer:
             _lib.check(L.dsdf_set_dropout(h, drop_layers, float(dec.dropout_prob), int(c.dropout_seed),
                                           self.step_count, int(self.dropout_row_base)), h, L)
             if c.code_bound is not None:
-                _lib.check(L.dsdf_renorm_rows(h, table.data_ptr(), ids.data_ptr(), n_seg,
+                _lib.check(L.dsdf_renorm_rows(h, table.data_ptr(), self.num_scenes, ids.data_ptr(), n_seg,
                                               float(c.code_bound), st), h, L)
             ramp = c.code_reg_lambda * min(1, epoch / 100) if c.code_reg else 0.0
             _lib.check(L.dsdf_train_fwd_bwd(
                 h, flat.data_ptr(), table.data_ptr(), self.num_scenes, ids.data_ptr(), n_seg, p,
-                sdf.data_ptr(), int(n_total), float(c.clamp_dist), float(ramp), ws.data_ptr(),
+                sdf.data_ptr(), int(n_total), float(c.clamp_dist), float(ramp),
+                float(c.eikonal_lambda) if c.use_eikonal else 0.0, ws.data_ptr(),
                 ws.numel(), self.grads.data_ptr(), self.lat_grad.data_ptr(),
-                self._pred.data_ptr(), self.loss_buf.data_ptr(), st), h, L)
+                self._pred.data_ptr(), self.loss_buf.data_ptr(),
+                self._grads_ready.cuda_event if self._grads_ready is not None else None, st), h, L)
+        self._last_ids = ids
         return self._pred
+
+    def check_status(self) -> None:
+        """Raise if the last step saw a scene index outside [0, num_scenes) (one D2H read; nn.Embedding's
+        IndexError / device-side assert).  The step itself ran with that id replaced by 0."""
+        bad = int(self.loss_buf[3].item())
+        if bad:
+            raise IndexError(f"scene index out of range [0, {self.num_scenes}) at batch position {bad - 1}")
 
     def step(self, sdf_data: torch.Tensor, indices: torch.Tensor, epoch: int,
              n_total: Optional[int] = None, lr_decoder: Optional[float] = None,
-             lr_latent: Optional[float] = None) -> Dict[str, torch.Tensor]:
+             lr_latent: Optional[float] = None, aux_latent_loss=None) -> Dict[str, torch.Tensor]:
+        """One optimisation step.  `aux_latent_loss(latents[U, 256]) -> scalar`: an extra torch loss on the rows of
+        the UNIQUE batch scenes (the reference's covariance / GMM prior terms, train_deep_sdf.py:737-764); its
+        gradient is added to the latent gradient before Adam (its own parameters, if any, are the caller's)."""
         L = self.decoder.L
         c = self.cfg
         self.forward_backward(sdf_data, indices, epoch, n_total)
-        if self.pg is not None and torch.distributed.get_world_size(self.pg) > 1:
-            # only the ~1.84 M-element decoder gradient crosses NVLink; SUM (F9)
-            torch.distributed.all_reduce(self.grads, op=torch.distributed.ReduceOp.SUM, group=self.pg)
+        if aux_latent_loss is not None:
+            uniq = torch.unique(self._last_ids)
+            z = self.lat_vecs.weight.data.index_select(0, uniq).requires_grad_(True)
+            with torch.enable_grad():
+                aux = aux_latent_loss(z)
+            (gz,) = torch.autograd.grad(aux, [z], allow_unused=True)
+            if gz is not None:
+                self.lat_grad.index_add_(0, uniq, gz.to(self.lat_grad.dtype))
         self.step_count += 1
         h = self.decoder.handle()
         flat = self.decoder.flat_params()
         st = _stream_ptr(self.device)
+        cur = torch.cuda.current_stream(self.device)
         lr0 = self.lr(0, epoch) if lr_decoder is None else lr_decoder
         lr1 = self.lr(1, epoch) if lr_latent is None else lr_latent
         b1, b2 = c.betas
+        work = None
+        if self._comm_stream is not None:
+            # only the ~1.84 M-element decoder gradient crosses NVLink; SUM, not mean (F9: the loss is normalised
+            # by the GLOBAL row count).  Issued on the side stream behind the grads-ready event, so it runs under
+            # the rest of the backward (latent-gradient reduction) and the latent Adam below.
+            with torch.cuda.stream(self._comm_stream):
+                self._comm_stream.wait_event(self._grads_ready)
+                work = torch.distributed.all_reduce(self.grads, op=torch.distributed.ReduceOp.SUM, group=self.pg,
+                                                    async_op=True)
         with torch.cuda.device(self.device):
-            _lib.check(L.dsdf_clip_adam(
-                h, flat.data_ptr(), self.grads.data_ptr(), self.exp_avg.data_ptr(),
-                self.exp_avg_sq.data_ptr(), flat.numel(),
-                float(c.grad_clip) if c.grad_clip is not None else 0.0, float(lr0), b1, b2, c.eps,
-                self.step_count, self.scratch.data_ptr(), st), h, L)
             table = self.lat_vecs.weight.data
             _lib.check(L.dsdf_clip_adam(
                 h, table.data_ptr(), self.lat_grad.data_ptr(), self.lat_exp_avg.data_ptr(),
                 self.lat_exp_avg_sq.data_ptr(), table.numel(), 0.0, float(lr1), b1, b2, c.eps,
                 self.step_count, self.scratch_lat.data_ptr(), st), h, L)
+            if work is not None:
+                with torch.cuda.stream(self._comm_stream):
+                    work.wait()                               # comm stream waits for the collective ...
+                cur.wait_stream(self._comm_stream)            # ... and the step's stream for the comm stream
+            _lib.check(L.dsdf_clip_adam(
+                h, flat.data_ptr(), self.grads.data_ptr(), self.exp_avg.data_ptr(),
+                self.exp_avg_sq.data_ptr(), flat.numel(),
+                float(c.grad_clip) if c.grad_clip is not None else 0.0, float(lr0), b1, b2, c.eps,
+                self.step_count, self.scratch.data_ptr(), st), h, L)
         self.decoder.sync_weights(force=True)
-        # device scalars, no host sync: [0] L1 term, [1] regulariser term (this rank's share)
-        return {"sdf_loss": self.loss_buf[0], "reg_loss": self.loss_buf[1],
-                "grad_norm": self.scratch[0]}
+        # device scalars, no host sync: [0] L1 term, [1] regulariser term, [2] Eikonal term (this rank's share),
+        # [3] scene-id status (check_status).  The gradient norm is only computed when the step clips
+        # (train_deep_sdf.py:780-782), otherwise None.
+        return {"sdf_loss": self.loss_buf[0], "reg_loss": self.loss_buf[1], "eikonal_loss": self.loss_buf[2],
+                "status": self.loss_buf[3],
+                "grad_norm": self.scratch[0] if c.grad_clip is not None else None}
 
     # ---------------------------------------------------------------- checkpoint interchange
     def optimizer_state_dict(self, epoch: int = 0) -> dict:

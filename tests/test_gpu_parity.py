@@ -49,7 +49,11 @@ def test_native_library_is_loaded():
 
 
 def test_umma_descriptor_selftests():
+    """Runs against the diagnostics variant only (DSDF_LIB=...libdsdf_b200.diag.so); the product library does not
+    carry the self-test kernels."""
     L = _lib.lib()
+    if L.dsdf_selftest_gemm(0, None, None, None, None) == -4:
+        pytest.skip("self-test kernels are compiled into the diagnostics variant only")
     torch.manual_seed(1)
     A = torch.randn(128, 64).bfloat16().float(); B = torch.randn(128, 64).bfloat16().float()
     d = torch.zeros(128, 128, device="cuda")
@@ -450,37 +454,31 @@ def test_dataparallel_wrapper_is_a_pass_through():
         assert torch.equal(dp2(x), a)
 
 
-@pytest.mark.parametrize("env", [
-    {"DSDF_DW8_WGRAD": "1"},            # dW8 as a wgrad item instead of the forward epilogue
-    {"DSDF_WG_QUAD": "0"},              # wgrad: one CTA pair per range instead of the side-by-side quad walk
-    {"DSDF_FWD_CG": "1"},               # forward without CTA pairs
-    {"DSDF_FWD_VER": "2"},              # previous-generation forward
-    {"DSDF_WG_VER": "1"},               # previous-generation wgrad
-    {"DSDF_BWD_VER": "1"},              # previous-generation backward (+ wgrad)
-    {"DSDF_FWD_V1": "1"},               # first-generation forward
-])
-def test_ab_kernel_generations_agree_with_the_shipping_path(env, monkeypatch):
-    """The library keeps earlier kernel generations selectable by environment variable (read at dsdf_create) for A/B
-    timing; each must compute the same step as the default path (different summation orders, so not bit-equal)."""
+def test_product_library_carries_no_diagnostics_or_kernel_generation_switches(monkeypatch):
+    """The superseded kernel generations and the DSDF_* A/B switches of round 1 are gone from the product library:
+    the self-test / micro-benchmark entries answer DSDF_EUNSUPPORTED (they exist in the diagnostics variant,
+    build.py DSDF_BUILD_VARIANT=diag DSDF_BUILD_DEFS=-DDSDF_DIAG_BUILD) and an environment switch changes nothing."""
+    import ctypes as C
+    L = _lib.lib()
+    if "DSDF_LIB" not in __import__("os").environ:
+        assert L.dsdf_selftest_gemm(0, None, None, None, None) == -4
+        assert L.dsdf_selftest_mma_rate(0, 1, 1, (C.c_uint64 * 1)()) == -4
     S, B, P = 6, 4, 512
     data = synth.scene_samples(S, P, seed=3).cuda()
     ids = torch.tensor([0, 2, 3, 5])
 
     def run():
         dec, tr = _fresh_trainer(S)
-        pred = tr.forward_backward(data[ids], ids.cuda(), 40).clone()
+        tr.forward_backward(data[ids], ids.cuda(), 40)
         torch.cuda.synchronize()
-        return pred, tr.grads.clone(), tr.lat_grad.clone(), tr.loss_buf[:2].clone()
+        return tr.grads.clone(), tr.lat_grad.clone(), tr.loss_buf[:2].clone()
 
-    p0, g0, l0, s0 = run()
-    for k, v in env.items():
-        monkeypatch.setenv(k, v)
-    p1, g1, l1, s1 = run()
-    assert (p0 - p1).abs().max().item() <= 2e-4          # a tenth of the SDF tolerance (v1 has no hi/lo xyz split)
-    torch.testing.assert_close(s1, s0, rtol=1e-4, atol=1e-9)
-    assert cos(g1, g0) >= 0.9999
-    assert cos(l1, l0) >= 0.9999
-    assert torch.equal(l1 != 0, l0 != 0)
+    g0, l0, s0 = run()
+    for k in ("DSDF_FWD_CG", "DSDF_WG_QUAD", "DSDF_DW8_WGRAD", "DSDF_FWD_VER", "DSDF_BWD_VER", "DSDF_WG_VER", "DSDF_FWD_V1"):
+        monkeypatch.setenv(k, "1" if k != "DSDF_WG_QUAD" else "0")
+    g1, l1, s1 = run()
+    if "DSDF_LIB" not in __import__("os").environ:
+        assert torch.equal(g0, g1) and torch.equal(l0, l1) and torch.equal(s0, s1)
 
 
 def test_duplicate_scene_ids_in_one_batch():

@@ -9,12 +9,13 @@ import pytest
 import torch
 
 import dsdf_b200
-from common import spec_for
+from common import REF_DIR, spec_for
 from dsdf_b200 import _lib, dist
 from dsdf_b200.trainer import StepConfig
 from oracle import deepsdf
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+have_ref = os.path.isdir(os.path.join(REF_DIR, "networks"))
 KW = dict(dims=[512] * 8, dropout=[], dropout_prob=0.2, latent_in=[4], xyz_in_all=False,
           use_tanh=False, latent_dropout=False, weight_norm=True)
 
@@ -97,9 +98,87 @@ def test_step_config_from_reference_specs():
     import json
     specs = json.loads("""{"ClampingDistance":0.1,"CodeRegularization":true,"CodeRegularizationLambda":1e-4,
       "CodeBound":1.0,"GradientClipNorm":1.0,"LearningRateSchedule":[
-      {"Type":"Step","Initial":0.0005,"Interval":500,"Factor":0.5},{"Type":"Step","Initial":0.001,"Interval":500,"Factor":0.5}]}""")
+      {"Type":"Step","Initial":0.0005,"Interval":500,"Factor":0.5},{"Type":"Step","Initial":0.001,"Interval":250,"Factor":0.25}]}""")
     c = StepConfig.from_specs(specs)
     assert (c.clamp_dist, c.code_bound, c.grad_clip, c.lr_decoder, c.lr_latent) == (0.1, 1.0, 1.0, 5e-4, 1e-3)
+    assert not c.use_eikonal
+    # one StepLearningRateSchedule PER parameter group (train_deep_sdf.py:247-265), not group 0's for both
+    assert (c.lr_interval, c.lr_factor, c.lr_interval_latent, c.lr_factor_latent) == (500, 0.5, 250, 0.25)
+    tr = dsdf_b200.FusedTrainer.__new__(dsdf_b200.FusedTrainer)
+    tr.cfg = c
+    assert tr.lr(0, 600) == pytest.approx(5e-4 * 0.5) and tr.lr(1, 600) == pytest.approx(1e-3 * 0.25 ** 2)
+    specs["LearningRateSchedule"][1]["Type"] = "Warmup"
+    with pytest.raises(NotImplementedError, match=r"LearningRateSchedule\[1\]"):
+        StepConfig.from_specs(specs)
+
+
+def _shipped_specs():
+    import json
+    with open(os.path.join(ROOT, "tests", "golden", "stage1_specs.json")) as f:
+        return json.load(f)
+
+
+@pytest.mark.parametrize("name", ["ADNI/minimal_eikonal", "ADNI/minimal_eikonal_gmm", "OAI-ZIB/minimal_eikonal",
+                                  "OAI-ZIB/minimal_eikonal_gmm"])
+def test_every_shipped_stage1_spec_is_read_faithfully_or_refused(name):
+    """All four shipped Stage-1 experiments (committed copy of their key sets, tests/golden/make_golden_specs.py).
+    The objective the fused step computes must be the one the spec asks for: UseEikonal is honoured; a spec that
+    also switches on a latent prior is refused, naming the key, unless the caller supplies that term."""
+    specs = _shipped_specs()[name]
+    assert specs["UseEikonal"] is True and specs["NetworkSpecs"]["norm_layers"] == []
+    dec = dsdf_b200.Decoder(specs["CodeLength"], **specs["NetworkSpecs"])      # NetworkSpecs are in the supported matrix
+    assert sum(p.numel() for p in dec.parameters()) == 1_839_358
+    if specs.get("UseGMMPriorLoss", False):
+        with pytest.raises(NotImplementedError, match="UseGMMPriorLoss"):
+            StepConfig.from_specs(specs)
+        c = StepConfig.from_specs(specs, latent_only_losses_handled=True)
+    else:
+        c = StepConfig.from_specs(specs)
+    assert c.use_eikonal and c.eikonal_lambda == 0.002
+    assert (c.clamp_dist, c.code_bound, c.grad_clip, c.code_reg_lambda) == (0.1, 1.0, 1.0, 1e-4)
+    assert (c.lr_decoder, c.lr_latent) == (5e-4, 1e-3)
+    for key in ("UseIsometryLoss", "UseGradMetricIsotropyLoss", "UseCovarianceLoss"):
+        bad = dict(specs, **{key: True})
+        with pytest.raises(NotImplementedError, match=key):
+            StepConfig.from_specs(bad)
+
+
+@pytest.mark.parametrize("arch,ref_arch", [("deep_sdf_decoder_b200", "deep_sdf_decoder"), ("siren_decoder_b200", "siren_decoder")])
+def test_drop_in_is_selected_the_way_every_reference_caller_selects_an_architecture(arch, ref_arch):
+    """train_deep_sdf.py:225 / reconstruct.py:225 / deep_sdf/workspace.py:56:
+    arch = __import__("networks." + specs["NetworkArch"], fromlist=["Decoder"]); arch.Decoder(latent, **NetworkSpecs)."""
+    integ = os.path.join(ROOT, "integration")
+    saved = {k: sys.modules.pop(k) for k in list(sys.modules) if k == "networks" or k.startswith("networks.")}
+    sys.path.insert(0, integ)
+    try:
+        mod = __import__("networks." + arch, fromlist=["Decoder"])
+        if ref_arch == "deep_sdf_decoder":
+            dec = mod.Decoder(256, **_shipped_specs()["ADNI/minimal_eikonal"]["NetworkSpecs"])
+            assert isinstance(dec, dsdf_b200.Decoder)
+            assert list(dec.state_dict())[:2] == ["lin0.weight", "lin0.bias"]
+        else:
+            from oracle import siren
+            dec = mod.Decoder(256, **siren.network_specs())
+            assert list(dec.state_dict())[0].startswith("decoder.lin0.")
+        if have_ref:                                   # with the reference checkout on the path both packages merge
+            sys.path.insert(sys.path.index(integ) + 1, REF_DIR)
+            for k in [k for k in sys.modules if k == "networks" or k.startswith("networks.")]:
+                sys.modules.pop(k)
+            ours = __import__("networks." + arch, fromlist=["Decoder"])
+            ref = __import__("networks." + ref_arch, fromlist=["Decoder"])
+            assert ours.Decoder is not ref.Decoder
+            kw = _shipped_specs()["ADNI/minimal_eikonal"]["NetworkSpecs"] if ref_arch == "deep_sdf_decoder" else siren.network_specs()
+            torch.manual_seed(0); a = ours.Decoder(256, **kw)
+            torch.manual_seed(0); b = ref.Decoder(256, **kw)
+            sa, sb = a.state_dict(), b.state_dict()
+            assert list(sa) == list(sb) and all(torch.equal(sa[k], sb[k]) for k in sa)
+    finally:
+        for p_ in (integ, REF_DIR):
+            while p_ in sys.path:
+                sys.path.remove(p_)
+        for k in [k for k in sys.modules if k == "networks" or k.startswith("networks.")]:
+            sys.modules.pop(k)
+        sys.modules.update(saved)
 
 
 def test_scene_partition_is_a_partition():
