@@ -2,15 +2,19 @@
 """bench.py -- headline benchmark of the B200-native DeepSDF auto-decoder hot path.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+                    [--workload c2|c3] [--scaling weak|strong] [--eikonal]
 
-Metric (BASELINE.json): SDF samples/sec, forward + backward (+ clip + Adam) of the 8x512 DeepSDF
-decoder.  Workload = BASELINE.json configs[1] (ADNI-hippocampus-shaped): 800 synthetic scenes x
-16384 samples/scene, ScenesPerBatch 64 per GPU -> 1 048 576 rows per step per GPU; with N GPUs
-scenes are sharded by owner rank (weak scaling: every rank steps on 64 of its own scenes, the only
-exchange is the all-reduce of the 1.84 M-element decoder gradient).  One JSON line on rank 0.
+Metric (BASELINE.json): SDF samples/sec, forward + backward (+ clip + Adam) of the 8x512 DeepSDF decoder.
+Workload c2 = BASELINE.json configs[1] (ADNI-hippocampus-shaped): 800 synthetic scenes x 16384 samples/scene,
+ScenesPerBatch 64 -> 1 048 576 rows per step; c3 = configs[2] (OAI-ZIB-shaped): 4096 scenes x 32768 samples,
+ScenesPerBatch 24 -> 786 432 rows per step.  With N GPUs scenes are sharded by owner rank and the only exchange is
+the all-reduce of the 1.84 M-element decoder gradient (on a side stream, under the latent-gradient kernels):
+`--scaling weak` (default; the driver's 1/2/4/8 run) keeps ScenesPerBatch per GPU, `--scaling strong` keeps it
+global (64 / N scenes per rank).  One JSON line on rank 0.
 
-`--impl reference`: the reference's own CPU path (fp32 PyTorch: the reference Decoder restated in
-oracle/, the reference's step loop) on the box's host cores, same metric; rank 0 only.
+`--impl reference`: the reference's own CPU path -- the reference Decoder class (oracle/_ref, copied unmodified by
+oracle/build_ref.py) inside train_deep_sdf.py's step statements (oracle/ref_step.py), fp32 PyTorch on all host
+cores, same workload and metric; rank 0 only.
 """
 from __future__ import annotations
 
@@ -30,12 +34,23 @@ for p in (ROOT, PKG):
 
 FWD_FLOP = 3_671_040            # BASELINE.md section 3 (nominal, unpadded, reference dims)
 STEP_FLOP = 3 * FWD_FLOP        # fwd + dgrad + wgrad = 11 013 120 per sample
-SCENES = 800
-P = 16384
-B_PER_GPU = 64
+# MMA work actually issued per row (padded tiles; latent products of lin0/lin4 folded into per-scene biases;
+# dW8 in the forward epilogue): forward / recompute 1 573 376, dgrad 1 572 864, wgrad 1 572 864 MAC
+EXEC_FWD, EXEC_DGRAD, EXEC_WGRAD = 2 * 1_573_376, 2 * 1_572_864, 2 * 1_572_864
+WORKLOADS = {
+    "c2": dict(scenes=800, p=16384, b=64,
+               name="configs[1]: ADNI-hippocampus-shaped auto-decoder training, 800 synthetic scenes x 16384 samples/scene, "
+                    "ScenesPerBatch=64 (1048576 rows/step), weight-normalised 8x512 decoder, latent 256, latent_in=[4], "
+                    "CodeBound 1.0, GradientClipNorm 1.0"),
+    "c3": dict(scenes=4096, p=32768, b=24,
+               name="configs[2]: OAI-ZIB-femur-shaped auto-decoder training, 4096 synthetic scenes x 32768 samples/scene, "
+                    "ScenesPerBatch=24 (786432 rows/step), 8x512 decoder (norm_layers [] as shipped), latent 256, "
+                    "latent_in=[4], CodeBound 1.0, GradientClipNorm 1.0"),
+}
 METRIC = "SDF samples/sec fwd+bwd (8x512 DeepSDF)"
 UNIT = "samples/s"
-WORKLOAD = "configs[1]: ADNI-hippocampus-shaped auto-decoder training, 800 synthetic scenes x 16384 samples/scene, ScenesPerBatch=64 per GPU (1048576 rows/step/GPU), weight-normalised 8x512 decoder, latent 256, latent_in=[4], CodeBound 1.0, GradientClipNorm 1.0"
+SECTIONS = ["scene_fold+k_forward3<TABLE,train>", "k_backward2 (dgrad chain)", "k_forward3<TAN> (Eikonal recompute)",
+            "k_eik_corr", "k_wgrad2", "k_reduce_wgrad2", "decoder-grad small kernels", "latent-grad small kernels + loss"]
 
 
 def peaks():
@@ -90,33 +105,54 @@ class ClockSampler(threading.Thread):
                 "power_w_max": max(float(r[2]) for r in rows), "samples": len(rows)}
 
 
-def cpu_reference_run(steps: int, warmup: int, scenes_per_step: int = 4):
-    """The reference's CPU training loop (oracle restatement of train_deep_sdf.py:555-616,731,780-784
-    around the reference Decoder) on all host cores; each step = `scenes_per_step` scenes x 16384 rows."""
+NETWORK_SPECS = dict(dims=[512] * 8, dropout=[], dropout_prob=0.2, latent_in=[4], xyz_in_all=False, use_tanh=False,
+                     latent_dropout=False, weight_norm=True)
+
+
+def cpu_reference_run(wl: dict, steps: int, warmup: int, scenes_per_step: int, eikonal: bool = False, wn: bool = True):
+    """The reference's CPU training loop on all host cores; each step = `scenes_per_step` scenes x P rows of the
+    workload.  With oracle/_ref present (oracle/build_ref.py) the decoder is the reference's OWN class
+    (kind "reference"); otherwise the oracle port of the same statements (kind "port")."""
     import torch
     from dsdf_b200 import synth
-    from oracle import deepsdf
-    from oracle import train as otrain
+    from oracle import ref_step
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    spec = deepsdf.DecoderSpec(norm_layers=tuple(range(8)), weight_norm=True)
-    cfg = otrain.TrainConfig(samples_per_scene=P, scenes_per_batch=scenes_per_step, code_bound=1.0, grad_clip=1.0)
-    S = 16
-    tr = otrain.OracleTrainer(spec, cfg, S, seed=0, device="cpu")
+    P = wl["p"]
+    S = max(16, scenes_per_step)
+    norm_layers = list(range(8)) if wn else []
+    if ref_step.available():
+        kind = "reference"
+        loop = ref_step.ReferenceStepLoop(S, dict(NETWORK_SPECS, norm_layers=norm_layers), use_eikonal=eikonal, seed=0)
+        step = lambda d, i: loop.step(d, i, 1)
+    else:
+        kind = "port"
+        from oracle import deepsdf
+        from oracle import train as otrain
+        spec = deepsdf.DecoderSpec(norm_layers=tuple(norm_layers), weight_norm=True)
+        cfg = otrain.TrainConfig(samples_per_scene=P, scenes_per_batch=scenes_per_step, code_bound=1.0, grad_clip=1.0,
+                                 use_eikonal=eikonal)
+        tr = otrain.OracleTrainer(spec, cfg, S, seed=0, device="cpu")
+        step = lambda d, i: tr.step(d, i, epoch=1)
     data = synth.fast_scene_samples(S, P, seed=0, device="cpu")
     g = torch.Generator().manual_seed(0)
     times = []
     for it in range(warmup + steps):
         ids = torch.randperm(S, generator=g)[:scenes_per_step]
+        batch = data[ids].clone()
         t0 = time.perf_counter()
-        tr.step(data[ids], ids, epoch=1)
+        step(batch, ids)
         dt = time.perf_counter() - t0
         if it >= warmup:
             times.append(dt)
     rows = scenes_per_step * P
     total = sum(times)
-    return {"value": rows * len(times) / total, "ms_per_step": 1e3 * total / len(times), "cores": cores,
-            "sample": f"{len(times)} steps of {scenes_per_step} scenes x {P} rows ({rows} rows/step) of the same workload, fp32 torch CPU, after {warmup} warm-up"}
+    return {"value": rows * len(times) / total, "ms_per_step": 1e3 * total / len(times), "cores": cores, "kind": kind,
+            "rows_per_step": rows,
+            "sample": f"{len(times)} step(s) of {scenes_per_step} scenes x {P} rows ({rows} rows/step) of the same workload"
+                      f"{' with the Eikonal term' if eikonal else ''}, fp32 torch CPU on {cores} threads, after {warmup} warm-up step(s); "
+                      + ("decoder = the reference's own networks/deep_sdf_decoder.Decoder (oracle/_ref)" if kind == "reference"
+                         else "decoder = oracle port (oracle/_ref not built)")}
 
 
 def _time_ms(fn, reps):
@@ -132,10 +168,72 @@ def _time_ms(fn, reps):
     return e0.elapsed_time(e1) / reps
 
 
-def run_extras(dec, dev, pk):
-    """Side measurements of the other rows of the path (not the headline metric): BASELINE.json's second
-    metric (grid pts/s decode, configs[3]), the latent-only optimisation of reconstruct.py (configs[3]) and
-    the SIREN variant's fused step (configs[4]).  CUDA events on the launching stream, inputs resident."""
+def profiled_steps(tr, dec, step_fn, reps):
+    """Run `reps` steps with the library's per-section CUDA events; returns (ms per step, per-section ms list)."""
+    import ctypes as C
+    import torch
+    from dsdf_b200 import _lib
+    h, L = dec.handle(), dec.L
+    step_fn()
+    torch.cuda.synchronize()
+    L.dsdf_profile_enable(h, 1)
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        step_fn()
+    e1.record()
+    torch.cuda.synchronize()
+    ms_sum = (C.c_float * 8)(); ncalls = C.c_int32()
+    _lib.check(L.dsdf_profile_read(h, ms_sum, C.byref(ncalls)), h, L)
+    L.dsdf_profile_enable(h, 0)
+    return e0.elapsed_time(e1) / reps, [ms_sum[i] / max(1, ncalls.value) for i in range(8)]
+
+
+def small_kernel_rooflines(tr, dec, dev, pk, n_seg):
+    """HBM-bound kernels of the step timed ALONE with CUDA events (north_star: HBM GB/s for the gather, scatter and
+    Adam kernels): algorithmic bytes / time against the measured copy bandwidth.  Working sets are a few MB to 52 MB:
+    all of them fit the 126 MB L2, so these are L2/latency numbers as much as HBM numbers -- reported as measured."""
+    import torch
+    from dsdf_b200 import _lib
+    from dsdf_b200.decoder import _stream_ptr
+    L, h = dec.L, dec.handle()
+    st = _stream_ptr(dev)
+    flat = dec.flat_params()
+    hbm = float(pk["hbm_gbs"])
+    out = {}
+
+    def add(name, bytes_, fn, reps=50):
+        ms = _time_ms(fn, reps)
+        out[name] = {"us": ms * 1e3, "algorithmic_bytes": int(bytes_), "gb_s": bytes_ / (ms * 1e-3) / 1e9,
+                     "frac_of_hbm_peak": bytes_ / (ms * 1e-3) / 1e9 / hbm}
+    n = flat.numel()
+    g = torch.randn_like(flat) * 1e-3
+    m, v, p = torch.zeros_like(flat), torch.zeros_like(flat), flat.clone()
+    scratch = torch.zeros(4096, device=dev)
+    # k_sqnorm_partial + k_clip_coef + k_adam: r g (norm) + r p,g,m,v + w p,m,v,g
+    add("clip+adam decoder (k_sqnorm_partial,k_clip_coef,k_adam)", n * 4 * (1 + 8),
+        lambda: L.dsdf_clip_adam(h, p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), n, 1.0, 5e-4, 0.9, 0.999, 1e-8, 5,
+                                 scratch.data_ptr(), st))
+    tab = tr.lat_vecs.weight.data.clone()
+    gl = torch.randn_like(tab) * 1e-3
+    ml, vl = torch.zeros_like(tab), torch.zeros_like(tab)
+    add("adam latents, all rows (k_adam)", tab.numel() * 4 * 7,
+        lambda: L.dsdf_clip_adam(h, tab.data_ptr(), gl.data_ptr(), ml.data_ptr(), vl.data_ptr(), tab.numel(), 0.0, 1e-3, 0.9,
+                                 0.999, 1e-8, 5, scratch.data_ptr(), st))
+    ids = torch.arange(n_seg, device=dev, dtype=torch.int64)
+    add("embedding max_norm renorm of the batch rows (k_renorm_rows)", n_seg * 256 * 4 * 2,
+        lambda: L.dsdf_renorm_rows(h, tab.data_ptr(), tab.shape[0], ids.data_ptr(), n_seg, 1.0, st))
+    add("weight fold: fp32 masters -> bf16 K-step images (k_rowscale_weff,k_fold_fwd2,k_fold_dgrad2,k_build_wx)",
+        n * 4 * 2 + (463 + 448) * 8192,
+        lambda: dec.sync_weights(force=True))
+    return out
+
+
+def run_extras(dec, tr, dev, pk, wl, args):
+    """Side measurements of the other rows of the path (not the headline metric): BASELINE.json's second metric
+    (grid pts/s decode, configs[3]), the latent-only optimisation of reconstruct.py (configs[3]), the SIREN
+    variant's fused step (configs[4]), the step with the Eikonal term every shipped Stage-1 spec enables, and the
+    OAI-ZIB-shaped config (configs[2]).  CUDA events on the launching stream, inputs resident."""
     import random
     import torch
     import dsdf_b200
@@ -149,9 +247,11 @@ def run_extras(dec, dev, pk):
     buf = torch.empty(256 ** 3, device=dev)
     ms = _time_ms(lambda: dec.decode_grid(lat, 256, out=buf), 5)
     out["grid_decode_256"] = {"ms": ms, "pts_per_s": 256 ** 3 / (ms * 1e-3), "unit": "grid pts/s",
-                              "frac_of_burst_bf16_peak": 256 ** 3 * FWD_FLOP / (ms * 1e-3) / 1e12 / burst,
-                              "note": "coordinates generated in-kernel; output 4 B/pt stays on the device"}
-    t0 = time.perf_counter()
+                              "tflops_executed": 256 ** 3 * EXEC_FWD / (ms * 1e-3) / 1e12,
+                              "frac_of_burst_bf16_peak": 256 ** 3 * EXEC_FWD / (ms * 1e-3) / 1e12 / burst,
+                              "effective_tflops_nominal": 256 ** 3 * FWD_FLOP / (ms * 1e-3) / 1e12,
+                              "note": "coordinates generated in-kernel; output 4 B/pt stays on the device; fraction of peak "
+                                      "counts the MMA work issued (the per-latent fold removes 14 % of the nominal MACs)"}
     dsdf_b200.create_mesh_sdf(dec, lat, 256)                     # first call pins the 67 MB host block
     torch.cuda.synchronize()
     t0 = time.perf_counter()
@@ -175,26 +275,65 @@ def run_extras(dec, dev, pk):
         torch.cuda.synchronize()
         dt = time.perf_counter() - t0
         out[f"reconstruct_800it_8000samples_x{n_shapes}"] = {
-            "wall_s": dt, "s_per_shape": dt / n_shapes, "shapes_per_s": n_shapes / dt,
+            "wall_s": dt, "s_per_shape": dt / n_shapes, "shapes_per_s": n_shapes / dt, "us_per_iteration": dt / 800 * 1e6,
             "loss_first": float(hist[0].mean()), "loss_last": float(hist[-1].mean()),
             "note": "whole Adam loop enqueued by one C call, incl. sample upload; FLOP/sample = fwd + dgrad"}
     del shapes
-    # ---- SIREN 8x512 fused step (configs[4]), same rows/step as the headline
+    # ---- the step with the Eikonal term (every shipped Stage-1 spec: UseEikonal true), same rows/step
+    rows = wl["b"] * wl["p"]
+    data = synth.fast_scene_samples(wl["b"], wl["p"], seed=5, device=str(dev))
+    ids = torch.arange(wl["b"], device=dev)
+    dec.train()
+    etr = dsdf_b200.FusedTrainer(dec, wl["scenes"], dsdf_b200.StepConfig(clamp_dist=0.1, code_bound=1.0, grad_clip=1.0,
+                                                                         use_eikonal=True))
+    for _ in range(3):
+        etr.step(data, ids, epoch=10)
+    ms, per = profiled_steps(etr, dec, lambda: etr.step(data, ids, epoch=10), 10)
+    exec_flop = 2 * EXEC_FWD + EXEC_DGRAD + EXEC_WGRAD
+    out["eikonal_step"] = {
+        "ms_per_step": ms, "samples_per_s": rows / (ms * 1e-3), "sections_ms": dict(zip(SECTIONS, per)),
+        "flop_per_sample_reference": 6 * FWD_FLOP, "flop_per_sample_executed": exec_flop,
+        "tflops_executed": rows * exec_flop / (ms * 1e-3) / 1e12,
+        "frac_of_burst_bf16_peak": rows * exec_flop / (ms * 1e-3) / 1e12 / burst,
+        "effective_tflops_reference_arithmetic": rows * 6 * FWD_FLOP / (ms * 1e-3) / 1e12,
+        "losses": [float(x) for x in etr.loss_buf[:3]],
+        "note": "reference arithmetic = fwd + dgrad(create_graph) + double backward (2 GEMM passes) + dgrad + wgrad = 6 passes; "
+                "the fused path runs 4 chain passes (forward, dgrad, recompute, wgrad) + an HBM-bound row-sum correction"}
+    del etr
+    # ---- configs[2] / configs[1], whichever is not the headline: one profiled step line
+    other = WORKLOADS["c3" if args.workload == "c2" else "c2"]
+    orows = other["b"] * other["p"]
+    odata = synth.fast_scene_samples(other["b"], other["p"], seed=6, device=str(dev))
+    oids = torch.randperm(other["scenes"], generator=torch.Generator().manual_seed(3))[:other["b"]].to(dev)
+    torch.manual_seed(0)
+    odec = dsdf_b200.Decoder(256, norm_layers=[] if other is WORKLOADS["c3"] else list(range(8)), **NETWORK_SPECS).to(dev)
+    otr = dsdf_b200.FusedTrainer(odec, other["scenes"], dsdf_b200.StepConfig(clamp_dist=0.1, code_bound=1.0, grad_clip=1.0))
+    for _ in range(3):
+        otr.step(odata, oids, epoch=10)
+    ms, per = profiled_steps(otr, odec, lambda: otr.step(odata, oids, epoch=10), 10)
+    out["other_config_step"] = {"workload": other["name"], "ms_per_step": ms, "samples_per_s": orows / (ms * 1e-3),
+                                "sections_ms": dict(zip(SECTIONS, per)),
+                                "frac_of_burst_bf16_peak": orows * (EXEC_FWD + EXEC_DGRAD + EXEC_WGRAD) / (ms * 1e-3) / 1e12 / burst}
+    del otr, odec, odata
+    torch.cuda.empty_cache()
+    # ---- SIREN 8x512 fused step (configs[4]), same rows/step as c2
     torch.manual_seed(0)
     sd = siren_mod.Decoder(256, dims=[512] * 8, latent_in=[4], nonlinearity="sine").to(dev)
-    str_ = dsdf_b200.FusedTrainer(sd, SCENES, dsdf_b200.StepConfig(clamp_dist=0.1, code_bound=1.0, grad_clip=1.0,
-                                                                    lr_decoder=1e-5, lr_latent=1e-4))
-    data = synth.fast_scene_samples(B_PER_GPU, P, seed=5, device=str(dev))
-    ids = torch.arange(B_PER_GPU, device=dev)
+    str_ = dsdf_b200.FusedTrainer(sd, 800, dsdf_b200.StepConfig(clamp_dist=0.1, code_bound=1.0, grad_clip=1.0,
+                                                                 lr_decoder=1e-5, lr_latent=1e-4))
+    sdata = synth.fast_scene_samples(64, 16384, seed=5, device=str(dev))
+    sids = torch.arange(64, device=dev)
     for _ in range(3):
-        str_.step(data, ids, epoch=10)
-    ms = _time_ms(lambda: str_.step(data, ids, epoch=10), 8)
-    rows = B_PER_GPU * P
-    flop = 3 * 2 * 1_837_056
-    out["siren_train_step"] = {"ms_per_step": ms, "samples_per_s": rows / (ms * 1e-3), "flop_per_sample": flop,
-                               "frac_of_burst_bf16_peak": rows * flop / (ms * 1e-3) / 1e12 / burst,
+        str_.step(sdata, sids, epoch=10)
+    ms = _time_ms(lambda: str_.step(sdata, sids, epoch=10), 8)
+    srows = 64 * 16384
+    flop_nom = 3 * 2 * 1_837_056
+    flop_exec = 3 * 2 * 1_572_864 + 2 * 512        # fold mode: lin0 latent part and lin4 latent part are per-scene biases
+    out["siren_train_step"] = {"ms_per_step": ms, "samples_per_s": srows / (ms * 1e-3), "flop_per_sample": flop_nom,
+                               "frac_of_burst_bf16_peak": srows * flop_exec / (ms * 1e-3) / 1e12 / burst,
+                               "effective_tflops_nominal": srows * flop_nom / (ms * 1e-3) / 1e12,
                                "loss": float(str_.loss_buf[0])}
-    del str_, sd, data
+    del str_, sd, sdata
     torch.cuda.empty_cache()
     return out
 
@@ -203,14 +342,19 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    steps = max(1, min(args.steps, 6))
-    r = cpu_reference_run(steps, max(1, min(args.warmup, 1)))
+    wl = WORKLOADS[args.workload]
+    steps = max(1, min(args.steps, 2))
+    warm = 1
+    r = cpu_reference_run(wl, steps, warm, wl["b"], eikonal=args.eikonal, wn=(args.workload == "c2"))
     line = {
         "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
-        "steps": steps, "warmup": 1, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "note": "reference CPU path: oracle restatement of the reference step loop around the reference Decoder math (the script itself hard-codes .cuda() and imports trimesh/skimage/pytorch3d, SURVEY.md F10)"},
-        "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]},
+        "steps": steps, "warmup": warm, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+        "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl["name"], "rows_per_step": r["rows_per_step"],
+                   "note": "reference CPU path: the reference's own Decoder class inside the step statements of "
+                           "train_deep_sdf.py:555-616,731,780-784 (the script itself hard-codes .cuda() and imports "
+                           "trimesh/skimage/pytorch3d, SURVEY.md F10); full-size steps, a bounded number of them"},
+        "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]},
         "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -244,8 +388,12 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
+    ap.add_argument("--eikonal", action="store_true", help="headline step with specs['UseEikonal'] (default: the plain fwd+bwd metric)")
+    ap.add_argument("--soak", type=int, default=200, help="steps of the sustained (thermally settled) measurement, 0 = skip")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-extras", action="store_true", help="skip the decode / reconstruct / SIREN side measurements")
+    ap.add_argument("--no-extras", action="store_true", help="skip the decode / reconstruct / SIREN / Eikonal / other-config side measurements")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -269,30 +417,42 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
         pg = dist.group.WORLD
     K, W = args.steps, max(3, args.warmup)
+    wl = WORKLOADS[args.workload]
+    SCENES, P = wl["scenes"], wl["p"]
+    strong = args.scaling == "strong"
+    if strong:
+        b_local = ddist.local_batch(wl["b"], rank, world)          # ScenesPerBatch is global
+        total_scenes = SCENES
+    else:
+        b_local = wl["b"]                                          # per GPU
+        total_scenes = SCENES * world
+    if b_local < 1:
+        raise SystemExit(f"ScenesPerBatch {wl['b']} cannot be split over {world} ranks")
 
     # ---- model + state: random-init weights of the named architecture, synthetic data
     torch.manual_seed(0)
-    dec = dsdf_b200.Decoder(256, dims=[512] * 8, dropout=[], dropout_prob=0.2, norm_layers=list(range(8)),
-                            latent_in=[4], xyz_in_all=False, use_tanh=False, latent_dropout=False,
-                            weight_norm=True).to(dev)
-    mine = ddist.owned_scenes(SCENES * world, rank, world)      # weak scaling: 800 scenes per GPU
+    dec = dsdf_b200.Decoder(256, norm_layers=list(range(8)) if args.workload == "c2" else [], **NETWORK_SPECS).to(dev)
+    mine = ddist.owned_scenes(total_scenes, rank, world)
     n_local = len(mine)
-    cfg = dsdf_b200.StepConfig(clamp_dist=0.1, code_reg=True, code_reg_lambda=1e-4, code_bound=1.0, grad_clip=1.0)
+    cfg = dsdf_b200.StepConfig(clamp_dist=0.1, code_reg=True, code_reg_lambda=1e-4, code_bound=1.0, grad_clip=1.0,
+                               use_eikonal=args.eikonal)
     torch.manual_seed(1 + rank)
     tr = dsdf_b200.FusedTrainer(dec, n_local, cfg, process_group=pg)
-    # a pool of distinct scene sample sets (800 x 16384 x 16 B = 210 MB would all fit; 128 are enough
-    # to make every step read fresh rows: 128 x 16384 x 16 B = 33.5 MB < L2, but every step also
-    # streams ~17 GB of activation stash, far larger than the 126 MB L2)
-    pool = 128
+    # a pool of distinct scene sample sets; every step also streams ~17 GB of activation stash per 1 M rows, far
+    # larger than the 126 MB L2, so no flush is needed between timed steps
+    pool = 128 if P <= 16384 else 48
     data_dev = synth.fast_scene_samples(pool, P, seed=rank, device=str(dev))
     data_host = data_dev.cpu().pin_memory()
     g = torch.Generator().manual_seed(100 + rank)
-    n_total = B_PER_GPU * P * world
-    rows = B_PER_GPU * P
+    rows = b_local * P
+    rows_t = torch.tensor([rows], dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.all_reduce(rows_t)
+    n_total = int(rows_t.item())                                   # the global row count every rank normalises by (F9)
 
     def draw():
-        ids = torch.randperm(n_local, generator=g)[:B_PER_GPU]           # scene ids (latent rows)
-        sel = torch.randint(0, pool, (B_PER_GPU,), generator=g)          # which sample sets
+        ids = torch.randperm(n_local, generator=g)[:b_local]             # scene ids (latent rows)
+        sel = torch.randint(0, pool, (b_local,), generator=g)            # which sample sets
         return ids, sel
 
     def barrier():
@@ -321,17 +481,16 @@ def main():
         st = tr.step(sdf, ids, epoch=10, n_total=n_total)
     e1.record()
     barrier()
-    t1 = time.time()
     ms = e0.elapsed_time(e1)
     import ctypes as C
-    ms_sum = (C.c_float * 4)(); ncalls = C.c_int32()
+    ms_sum = (C.c_float * 8)(); ncalls = C.c_int32()
     _lib.check(L.dsdf_profile_read(h, ms_sum, C.byref(ncalls)), h)
     L.dsdf_profile_enable(h, 0)
     t = torch.tensor([ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
-    value = rows * world * K / (ms * 1e-3)
+    value = n_total * K / (ms * 1e-3)
 
     # ---------------- end-to-end arm: host buffers, H2D + D2H inside the timed region ----------------
     # The user-facing call is FusedTrainer.step on a batch that lives in pinned HOST memory (what the
@@ -341,8 +500,8 @@ def main():
     n_host = 4
     host_sdf = [data_host[batches[i][1]].contiguous().pin_memory() for i in range(n_host)]
     host_ids = [batches[i][0].clone().pin_memory() for i in range(n_host)]
-    bufs = [torch.empty(B_PER_GPU, P, 4, device=dev) for _ in range(2)]
-    idbufs = [torch.empty(B_PER_GPU, dtype=torch.int64, device=dev) for _ in range(2)]
+    bufs = [torch.empty(b_local, P, 4, device=dev) for _ in range(2)]
+    idbufs = [torch.empty(b_local, dtype=torch.int64, device=dev) for _ in range(2)]
     loss_host = torch.zeros(4).pin_memory()
     ready = [torch.cuda.Event() for _ in range(2)]
     freed = [torch.cuda.Event() for _ in range(2)]
@@ -366,7 +525,7 @@ def main():
             cur.wait_event(ready[slot])
             tr.step(bufs[slot], idbufs[slot], epoch=10, n_total=n_total)
             freed[slot].record(cur)
-            loss_host[:2].copy_(tr.loss_buf[:2], non_blocking=True)      # D2H of the step's result
+            loss_host.copy_(tr.loss_buf, non_blocking=True)              # D2H of the step's result (3 loss terms + status)
 
     e2e_loop(2)
     barrier()
@@ -379,60 +538,109 @@ def main():
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_ms = float(t.item())
-    e2e_value = rows * world * K / (e2e_ms * 1e-3)
+    e2e_value = n_total * K / (e2e_ms * 1e-3)
     clocks = sampler.summary(t0, time.time())      # both timed regions (device-resident arm + e2e arm)
+    if int(loss_host[3].item()) != 0:
+        raise SystemExit("scene id out of range reported by the step")
+
+    # ---------------- sustained (thermally settled) number: a long soak of the same step ----------------
+    sustained = None
+    if args.soak > 0:
+        barrier()
+        s0 = torch.cuda.Event(enable_timing=True); s1 = torch.cuda.Event(enable_timing=True)
+        ts0 = time.time()
+        s0.record()
+        for i in range(args.soak):
+            ids, sdf = dev_batches[i % 4]
+            tr.step(sdf, ids, epoch=10, n_total=n_total)
+        s1.record()
+        barrier()
+        t = torch.tensor([s0.elapsed_time(s1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        sms = float(t.item())
+        sustained = {"steps": args.soak, "ms_per_step": sms / args.soak, "value": n_total * args.soak / (sms * 1e-3),
+                     "unit": UNIT, "clocks": sampler.summary(ts0, time.time()),
+                     "note": "same step, device-resident inputs, run long enough for clocks/power to settle"}
     sampler.stop()
+
+    # ---------------- replicas stay identical (N > 1): all-gather a parameter checksum ----------------
+    replicas_identical = None
+    if world > 1:
+        flat = dec.flat_params()
+        cks = torch.stack([flat.double().sum(), flat.double().abs().sum(), flat.view(torch.int32).sum().double()])
+        allc = [torch.empty_like(cks) for _ in range(world)]
+        dist.all_gather(allc, cks)
+        replicas_identical = all(bool(torch.equal(allc[0], c)) for c in allc)
 
     # ---------------- roofline of the dominant kernel + CPU baseline (rank 0) ----------------
     pk, pk_src = peaks()
-    per = [ms_sum[i] / max(1, ncalls.value) for i in range(4)]
-    names = ["k_forward<TABLE,train>", "k_backward (dgrad chain)", "k_wgrad", "small reductions"]
-    algo = [rows * FWD_FLOP, rows * FWD_FLOP, rows * FWD_FLOP, 0]
-    # MMA work actually issued per row (padded tiles; latent products of lin0/lin4 folded into per-scene
-    # biases; dW8 rides as a 256x512 item): fwd 1 573 376, dgrad 1 572 864, wgrad 1 703 936 MAC
-    executed = [rows * 2 * 1_573_376, rows * 2 * 1_572_864, rows * 2 * 1_703_936, 0]
-    dom = max(range(3), key=lambda i: per[i])
-    peak = float(pk.get("bf16_tflops_sustained", pk["bf16_tflops"]))
-    achieved = algo[dom] / (per[dom] * 1e-3) / 1e12
+    per = [ms_sum[i] / max(1, ncalls.value) for i in range(8)]
+    nominal = [rows * FWD_FLOP, rows * FWD_FLOP, rows * FWD_FLOP, 0, rows * FWD_FLOP, 0, 0, 0]
+    executed = [rows * EXEC_FWD, rows * EXEC_DGRAD, rows * EXEC_FWD, 0, rows * EXEC_WGRAD, 0, 0, 0]
+    cand = [0, 1, 2, 4] if args.eikonal else [0, 1, 4]
+    dom = max(cand, key=lambda i: per[i])
+    region_s = ms * 1e-3
+    # a sub-2-second timed region starts on thermal headroom: the burst figure is the honest denominator there;
+    # the sustained one belongs to the soak below
+    use_burst = region_s < 2.0
+    peak = float(pk["bf16_tflops"] if use_burst else pk.get("bf16_tflops_sustained", pk["bf16_tflops"]))
+    achieved = executed[dom] / (per[dom] * 1e-3) / 1e12
     traffic = None
     try:
         with open(os.path.join(ROOT, "profiles", "dominant_kernel_traffic.json")) as f:
-            traffic = json.load(f).get(names[dom])
+            tj = json.load(f)
+        traffic = tj.get(SECTIONS[dom].split(" ")[0]) or tj.get(SECTIONS[dom])
     except Exception:
         pass
-    roofline = {"bound": "tensor", "kernel": names[dom], "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                "frac": achieved / peak, "traffic": traffic, "peak_source": f"{pk_src} bf16_tflops_sustained (kernel timed inside a long step)",
+    step_exec = (EXEC_FWD * (2 if args.eikonal else 1) + EXEC_DGRAD + EXEC_WGRAD)
+    roofline = {"bound": "tensor", "kernel": SECTIONS[dom], "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                "frac": achieved / peak, "traffic": traffic,
+                "traffic_source": "committed ncu --set full capture of the same command (profiles/), not measured in this run",
+                "peak_source": f"{pk_src} {'bf16_tflops (burst)' if use_burst else 'bf16_tflops_sustained'}: timed region {region_s:.2f} s",
                 "ms_per_launch": per[dom],
-                "achieved_executed": executed[dom] / (per[dom] * 1e-3) / 1e12,
-                "frac_executed": executed[dom] / (per[dom] * 1e-3) / 1e12 / peak,
-                "note": "achieved/frac use the NOMINAL reference FLOPs (SURVEY.md 8d) over the measured time; *_executed = "
-                        "the MMA work actually issued (the per-scene fold removes 14 % of the forward/dgrad MACs)",
-                "kernels_ms": {names[i]: per[i] for i in range(4)},
-                "step_tflops_algorithmic": rows * STEP_FLOP / (ms / K * 1e-3) / 1e12,
-                "step_frac_of_burst_peak": rows * STEP_FLOP / (ms / K * 1e-3) / 1e12 / float(pk["bf16_tflops"])}
+                "effective_tflops_nominal": nominal[dom] / (per[dom] * 1e-3) / 1e12,
+                "note": "achieved/frac count the MMA work actually ISSUED by the kernel (the per-scene fold removes 14 % of the "
+                        "forward/dgrad MACs of the reference arithmetic); effective_tflops_nominal = reference FLOPs / time, an "
+                        "algorithmic-speed figure that is not a fraction of any peak",
+                "kernels_ms": {SECTIONS[i]: per[i] for i in range(8)},
+                "step_tflops_executed": rows * step_exec / (ms / K * 1e-3) / 1e12,
+                "step_frac_of_burst_peak": rows * step_exec / (ms / K * 1e-3) / 1e12 / float(pk["bf16_tflops"]),
+                "step_effective_tflops_nominal": rows * STEP_FLOP * (2 if args.eikonal else 1) / (ms / K * 1e-3) / 1e12}
+    if sustained is not None:
+        sustained["step_frac_of_sustained_peak"] = rows * step_exec / (sustained["ms_per_step"] * 1e-3) / 1e12 / \
+            float(pk.get("bf16_tflops_sustained", pk["bf16_tflops"]))
+    roofline_small = None
     extras = None
-    if rank == 0 and world == 1 and not args.no_extras:
-        extras = run_extras(dec, dev, pk)
+    if rank == 0 and world == 1:
+        roofline_small = small_kernel_rooflines(tr, dec, dev, pk, b_local)
+        if not args.no_extras:
+            extras = run_extras(dec, tr, dev, pk, wl, args)
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        r = cpu_reference_run(3, 1)
-        cpu_baseline = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]}
+        r = cpu_reference_run(wl, 1, 1, 16 if P <= 16384 else 8, eikonal=args.eikonal, wn=(args.workload == "c2"))
+        cpu_baseline = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]}
 
     if rank == 0:
-        # counted from the ncu launch list (profiles/): renorm | scene_fold, fwd, bwd, wgrad + 8 reducers |
-        # decoder sqnorm, coef, adam | latent adam | rowscale_weff, fold_fwd2, fold_dgrad2
-        launches_per_step = 1 + 12 + 3 + 1 + 3
+        # launches per step, counted from the ncu launch list (profiles/): renorm | sanitize, scene_fold, fwd, bwd, wgrad,
+        # reduce_wgrad2 + 4 decoder-grad + 3 latent-grad/loss (+ memset node) | latent adam | decoder sqnorm, coef, adam |
+        # rowscale_weff, fold_fwd2, fold_dgrad2, build_wx   (+ recompute pass and k_eik_corr with --eikonal)
+        launches_per_step = 1 + 13 + 1 + 3 + 4 + (2 if args.eikonal else 0)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
-            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "rows_per_step_per_gpu": rows, "parallelism": f"scene-sharded dp{world}",
+            "config": {"workload": wl["name"] + (" + UseEikonal" if args.eikonal else ""),
+                       "rows_per_step_per_gpu": rows, "rows_per_step_global": n_total,
+                       "parallelism": f"scene-sharded dp{world}, {args.scaling} scaling ({b_local} scenes/step/rank)",
                        "l2": "inputs + 17 GB/step activation stash exceed the 126 MB L2; no flush needed",
                        "flop_per_sample": STEP_FLOP},
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": rows * 16 + B_PER_GPU * 8,
-                    "d2h_bytes_per_step": 8, "ms_per_step": e2e_ms / K},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": rows * 16 + b_local * 8,
+                    "d2h_bytes_per_step": 16, "ms_per_step": e2e_ms / K},
             "gpu_launches": launches_per_step * K,
-            "roofline": roofline, "cpu_baseline": cpu_baseline, "clocks": clocks, "extras": extras,
+            "roofline": roofline, "roofline_small": roofline_small, "sustained": sustained,
+            "replicas_identical": replicas_identical,
+            "cpu_baseline": cpu_baseline, "clocks": clocks, "extras": extras,
             "loss": float(st["sdf_loss"].item()),
         }
         emit(line)

@@ -229,11 +229,12 @@ int dsdf_reconstruct(dsdf_handle h, const float* params, const dsdf_reconstruct_
                      float* exp_avg, float* exp_avg_sq, void* workspace, size_t workspace_bytes,
                      float* loss_hist, void* stream);
 
-/* Per-kernel timing of dsdf_train_fwd_bwd with CUDA events recorded on the caller's stream
- * (the stream the kernels are launched on).  After enable(1) every call records 5 events;
- * read() synchronises on them and returns, summed over the n_calls recorded calls, the
- * milliseconds of ms_sum[0] forward kernel, [1] backward (dgrad chain) kernel, [2] wgrad kernel,
- * [3] the small reduction kernels.  enable(0/1) also clears the recorded events. */
+/* Per-section timing of dsdf_train_fwd_bwd with CUDA events recorded on the caller's stream (the stream the
+ * kernels are launched on).  After enable(1) every call records an event at each section boundary; read()
+ * synchronises on them and returns, summed over the n_calls recorded calls, the milliseconds of ms_sum[8]:
+ * [0] scene fold + forward chain, [1] dgrad chain, [2] Eikonal recompute pass, [3] Eikonal row-sum corrections,
+ * [4] wgrad GEMMs, [5] split-K reduction, [6] decoder-gradient small kernels, [7] latent-gradient small kernels +
+ * loss.  enable(0/1) also clears the recorded events. */
 int dsdf_profile_enable(dsdf_handle h, int32_t enable);
 int dsdf_profile_read(dsdf_handle h, float* ms_sum, int32_t* n_calls);
 

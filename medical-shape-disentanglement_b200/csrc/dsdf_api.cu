@@ -70,17 +70,22 @@ struct dsdf_handle_s {
   DropoutArgs drop{};                  // dsdf_set_dropout; layers == 0: no dropout
   // optional per-kernel timing (CUDA events on the caller's stream), see dsdf_profile_*
   bool profile = false;
-  std::vector<cudaEvent_t> prof_events;   // 5 per dsdf_train_fwd_bwd call
+  std::vector<cudaEvent_t> prof_events;   // one per section boundary of dsdf_train_fwd_bwd
+  std::vector<int> prof_ids;              // section that ENDS at the event (-1: start of a call)
 };
-constexpr int kProfEventsPerCall = 5;
-constexpr int kProfMaxCalls = 512;
+// sections of dsdf_train_fwd_bwd timed by dsdf_profile_*: 0 scene fold + forward chain, 1 dgrad chain,
+// 2 Eikonal recompute pass, 3 Eikonal row-sum corrections, 4 wgrad GEMMs, 5 split-K reduction,
+// 6 decoder-gradient small kernels, 7 latent-gradient small kernels + loss
+constexpr int kProfSections = 8;
+constexpr int kProfMaxEvents = 512 * 10;
 
-static void prof_mark(dsdf_handle h, cudaStream_t st) {
-  if (!h->profile || (int)h->prof_events.size() >= kProfMaxCalls * kProfEventsPerCall) return;
+static void prof_mark(dsdf_handle h, cudaStream_t st, int id) {
+  if (!h->profile || (int)h->prof_events.size() >= kProfMaxEvents) return;
   cudaEvent_t e;
   if (cudaEventCreate(&e) != cudaSuccess) return;
   cudaEventRecord(e, st);
   h->prof_events.push_back(e);
+  h->prof_ids.push_back(id);
 }
 
 static thread_local std::string g_err;
@@ -605,8 +610,9 @@ static int launch_wgrad2(dsdf_handle h, const uint8_t* xstash, const uint8_t* dy
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   CU(h, cudaLaunchKernelEx(&cfg, k_wgrad2, w2));
-  if (prof) prof_mark(h, st);
+  if (prof) prof_mark(h, st, 4);
   k_reduce_wgrad2<<<dim3(kHidden, h->wg2_with_l8 ? 8 : 7), kHidden, 0, st>>>(partials, h->wg2_layout, dweff);
+  if (prof) prof_mark(h, st, 5);
   return DSDF_OK;
 }
 
@@ -704,8 +710,8 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   fa.fused_loss = 1;
   fa.clamp_dist = clamp_dist;
   fa.inv_n_total = inv_n;
-  const bool prof = h->profile && (int)h->prof_events.size() + kProfEventsPerCall <= kProfMaxCalls * kProfEventsPerCall;
-  if (prof) prof_mark(h, st);
+  const bool prof = h->profile && (int)h->prof_events.size() + 10 <= kProfMaxEvents;
+  if (prof) prof_mark(h, st, -1);
   fa.scene_e = w.scene_e;
   fa.relu_mask = w.relu_mask;
   fa.g_img = dw8_fwd ? nullptr : w.g_img;
@@ -738,7 +744,7 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
     CU(h, (launch_fwd<MODE_TABLE, true, true, true>(h, fa, st, pair_ok)));
   else
     CU(h, (launch_fwd<MODE_TABLE, true, true>(h, fa, st, pair_ok)));
-  if (prof) prof_mark(h, st);
+  if (prof) prof_mark(h, st, 0);
 
   // ---- backward dgrad chain + reducers
   Bwd2Args b2;
@@ -768,7 +774,7 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   unsigned bwd_grid = 0;
   rc = launch_backward2(h, b2, tiles, st, &bwd_grid);
   if (rc != DSDF_OK) return rc;
-  if (prof) prof_mark(h, st);
+  if (prof) prof_mark(h, st, 1);
 
   int n_corr = 0;
   if (eik) {
@@ -785,10 +791,12 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
     ta.dw8_partials = w.cta_partials + kPartW8;
     ta.dw8_stride = kCtaPartialFloats;
     CU(h, (launch_fwd<MODE_TABLE, true, true, false, true>(h, ta, st, pair_ok)));
+    if (prof) prof_mark(h, st, 2);
     // ---- eps-weighted corrections of the row sums that are not GEMMs (bias grads, colsum(dY4), dW4[:, xyz])
     n_corr = eik_corr_blocks(h->num_sms);
     if (n_corr > tiles) n_corr = (int)tiles;
     k_eik_corr<<<n_corr, 256, 0, st>>>(w.dystash, w.eik_row, sdf_data, tiles, w.tile_colsum, w.eik_corr);
+    if (prof) prof_mark(h, st, 3);
 #endif
   }
 
@@ -809,6 +817,7 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   k_param_grads<<<(kScaleElems * 32 + 255) / 256, 256, 0, st>>>(w.dweff, params, h->pl, h->scale,
                                                                 h->inv_norm, grads);
   if (grads_ready_event) CU(h, cudaEventRecord((cudaEvent_t)grads_ready_event, st));
+  if (prof) prof_mark(h, st, 6);
   k_lat_grad_seg<<<(unsigned)n_seg, 1024, 0, st>>>(w.seg_sum, h->weff, table,
                                                       (const long long*)seg_ids, reg_coef,
                                                       w.dlat_seg, w.seg_norm);
@@ -816,7 +825,7 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   k_lat_grad_scatter<<<(unsigned)n_seg, kLatent, 0, st>>>(w.dlat_seg, (const long long*)seg_ids, (int)n_seg, lat_grad);
   k_loss<<<1, 1024, 0, st>>>(w.tile_partials, tiles, inv_n, w.seg_norm, (int)n_seg, reg_coef, loss_out,
                              eik ? w.eik_tile : nullptr, eikonal_lambda);
-  if (prof) prof_mark(h, st);
+  if (prof) prof_mark(h, st, 7);
   CU(h, cudaGetLastError());
   return DSDF_OK;
 }
@@ -1208,22 +1217,23 @@ extern "C" int dsdf_profile_enable(dsdf_handle h, int32_t enable) {
   if (!h) return DSDF_EINVAL;
   for (cudaEvent_t e : h->prof_events) cudaEventDestroy(e);
   h->prof_events.clear();
+  h->prof_ids.clear();
   h->profile = enable != 0;
   return DSDF_OK;
 }
 
 extern "C" int dsdf_profile_read(dsdf_handle h, float* ms_sum, int32_t* n_calls) {
   if (!h || !ms_sum || !n_calls) DSDF_FAIL(h, DSDF_EINVAL, "null argument");
-  const int calls = (int)h->prof_events.size() / kProfEventsPerCall;
-  for (int k = 0; k < 4; ++k) ms_sum[k] = 0.f;
-  for (int c = 0; c < calls; ++c) {
-    cudaEvent_t* e = &h->prof_events[(size_t)c * kProfEventsPerCall];
-    CU(h, cudaEventSynchronize(e[4]));
-    for (int k = 0; k < 4; ++k) {
-      float ms = 0.f;
-      CU(h, cudaEventElapsedTime(&ms, e[k], e[k + 1]));
-      ms_sum[k] += ms;
-    }
+  for (int k = 0; k < kProfSections; ++k) ms_sum[k] = 0.f;
+  int calls = 0;
+  if (!h->prof_events.empty()) CU(h, cudaEventSynchronize(h->prof_events.back()));
+  for (size_t i = 0; i < h->prof_events.size(); ++i) {
+    const int id = h->prof_ids[i];
+    if (id < 0) { ++calls; continue; }
+    if (i == 0 || id >= kProfSections) continue;
+    float ms = 0.f;
+    CU(h, cudaEventElapsedTime(&ms, h->prof_events[i - 1], h->prof_events[i]));
+    ms_sum[id] += ms;
   }
   *n_calls = calls;
   return DSDF_OK;

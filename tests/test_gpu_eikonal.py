@@ -34,8 +34,38 @@ def make(wn, seed=0, scale=1.0):
     return dec.cuda(), spec_for(wn), params
 
 
+_TRAINED = {}
+
+
+def trained(wn, steps=250):
+    """'Trained-like' weights: the ORACLE (double backward, fp32, on the GPU) fits 8 synthetic scenes for a few hundred
+    steps with the Eikonal term on, so that ||d pred / d xyz|| is of order 1 near the surface, both clamp branches
+    are live and the ReLU patterns are those of a real SDF rather than of an initialisation.  Cached per session."""
+    if wn not in _TRAINED:
+        S, B, P = 8, 4, 2048
+        cfg = otrain.TrainConfig(samples_per_scene=P, scenes_per_batch=B, code_bound=1.0, grad_clip=1.0, use_eikonal=True,
+                                 lr_decoder=1e-3, lr_latent=2e-3)
+        orc = otrain.OracleTrainer(spec_for(wn), cfg, S, seed=0, device="cuda")
+        data = synth.scene_samples(S, P, seed=1).cuda()
+        g = torch.Generator().manual_seed(3)
+        for it in range(steps):
+            ids = torch.randperm(S, generator=g)[:B]
+            r = orc.step(data[ids], ids, 50)
+        _TRAINED[wn] = ({k: v.detach().cpu().clone() for k, v in orc.params.items()},
+                        orc.lat_vecs.weight.data.cpu().clone(), r)
+    return _TRAINED[wn]
+
+
 def pair(wn, S, B, P, scale, eik, lat0=None, bound=1.0, clip=1.0):
-    dec, spec, params = make(wn, scale=scale)
+    """scale = 'trained': weights/latents from trained(wn) (S must be 8); else init weights times `scale`."""
+    if scale == "trained":
+        params, lat0, _ = trained(wn)
+        torch.manual_seed(0)
+        dec = dsdf_b200.Decoder(256, norm_layers=list(range(8)) if wn else [], **KW)
+        dec.load_state_dict(params)
+        dec, spec = dec.cuda(), spec_for(wn)
+    else:
+        dec, spec, params = make(wn, scale=scale)
     cfg = otrain.TrainConfig(samples_per_scene=P, scenes_per_batch=B, code_bound=bound, grad_clip=clip, use_eikonal=eik)
     orc = otrain.OracleTrainer(spec, cfg, S, seed=0, device="cuda", params=params, latents=lat0)
     tr = dsdf_b200.FusedTrainer(dec, S, dsdf_b200.StepConfig(code_bound=bound, grad_clip=clip, use_eikonal=eik),
@@ -47,9 +77,9 @@ def flat_ref(dec, orc):
     return torch.cat([orc.params[n].grad.flatten() for n, _ in dec.named_parameters()])
 
 
-# scale 1: fresh init (||G|| ~ 0.05, nothing clamped); 2.4: "trained-like" (||G|| ~ 1, both clamp branches live)
-@pytest.mark.parametrize("wn,S,B,P,scale", [(False, 4, 2, 256, 1.0), (False, 8, 4, 1024, 2.4), (True, 6, 3, 512, 2.0),
-                                           (False, 5, 1, 128, 2.4)])
+# scale 1: fresh init (||G|| ~ 0.01, nothing clamped); 2.0: 70 % of the rows inside the clamp; "trained": see trained()
+@pytest.mark.parametrize("wn,S,B,P,scale", [(False, 4, 2, 256, 1.0), (False, 8, 4, 1024, "trained"), (True, 8, 3, 512, "trained"),
+                                           (False, 5, 1, 128, 2.0), (True, 6, 3, 512, 2.0)])
 def test_eikonal_step_matches_double_backward_oracle(wn, S, B, P, scale):
     data = synth.scene_samples(S, P, seed=1).cuda()
     ids = torch.randperm(S, generator=torch.Generator().manual_seed(7))[:B]
@@ -78,6 +108,8 @@ def test_eikonal_step_matches_double_backward_oracle(wn, S, B, P, scale):
     d_got = res[True][0] - res[False][0]
     d_ref = res[True][1] - res[False][1]
     assert float(d_ref.norm()) > 0
+    print(f"eikonal share: |d_ref|/|g| = {float(d_ref.norm() / res[True][1].norm()):.3e}, cos(d_got, d_ref) = {cos(d_got, d_ref):.4f}, "
+          f"|d_got|/|d_ref| = {float(d_got.norm() / d_ref.norm()):.3f}, flat cos = {cos(res[True][0], res[True][1]):.6f}")
     assert cos(d_got, d_ref) >= 0.9, cos(d_got, d_ref)
     assert float(d_got.norm()) == pytest.approx(float(d_ref.norm()), rel=0.15)
 
@@ -110,7 +142,7 @@ def test_eikonal_optimiser_steps_follow_the_oracle():
     """clip + Adam after the Eikonal backward: 4 steps, re-locked to the oracle's state after each (the same
     protocol as test_train_step_gradients_match_oracle), loss terms within 1 % at every step."""
     S, B, P = 8, 4, 512
-    dec, orc, tr = pair(False, S, B, P, 2.4, True)
+    dec, orc, tr = pair(False, S, B, P, "trained", True)
     data = synth.scene_samples(S, P, seed=1).cuda()
     g = torch.Generator().manual_seed(3)
     for it in range(4):
@@ -137,7 +169,7 @@ def test_eikonal_step_is_deterministic_and_additive():
     """Size-independent properties: bit-identical reruns (no float atomics on the new path either); the Eikonal loss
     and the decoder gradient of a batch = sum over its scene halves at the same global normaliser."""
     S, B, P = 16, 8, 2048
-    dec, spec, params = make(False, scale=2.4)
+    dec, spec, params = make(False, scale=2.0)
     lat0 = torch.randn(S, 256, generator=torch.Generator().manual_seed(4)) / 16.0
     tr = dsdf_b200.FusedTrainer(dec, S, dsdf_b200.StepConfig(code_bound=1.0, use_eikonal=True), latents=lat0)
     data = synth.scene_samples(S, P, seed=2).cuda()

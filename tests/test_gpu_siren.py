@@ -114,12 +114,16 @@ def test_fused_train_step_matches_oracle():
         assert float(st["sdf_loss"]) == pytest.approx(st_ref["sdf_loss"], rel=1e-2)
 
 
-def _scaled_params(params, scale):
-    """A 'trained-like' SIREN: hidden weights scaled so that the pre-activations 30 x reach tens of radians
-    (at sine_init they stay within a few radians and the hardware sin/cos approximation is never stressed)."""
+def _phase_shifted_params(params, k=5):
+    """The same function with LARGE sine arguments: every hidden bias is shifted by 2 pi k / 30, i.e. every argument
+    of sin(30 x) by 2 pi k (~31 rad for k = 5).  sin is periodic, so outputs and gradients are mathematically
+    unchanged and the network stays as well conditioned as at initialisation -- scaling the weights instead would
+    raise the Lipschitz constant by 30 |W| per layer and measure bf16 chaos, not the trig evaluation."""
+    import math
     out = {}
-    for k, v in params.items():
-        out[k] = v * scale if (k.endswith("weight") and not k.startswith("decoder.lin8")) else v.clone()
+    for name, v in params.items():
+        hidden_bias = name.endswith("bias") and not name.startswith("decoder.lin8")
+        out[name] = v + (2 * math.pi * k / 30.0) if hidden_bias else v.clone()
     return out
 
 
@@ -127,7 +131,7 @@ def test_large_pre_activations_keep_parity():
     """SURVEY.md H10 / VERDICT r1 weak #3: |30 x| >> pi.  The epilogue reduces the argument (Cody-Waite) before the
     hardware sin/cos; outputs and gradients must hold the same bars as at init."""
     dec, params = make()
-    big = _scaled_params(params, 3.0)
+    big = _phase_shifted_params(params)
     dec.load_state_dict(big)
     n = 2048
     gen = torch.Generator().manual_seed(6)
@@ -139,7 +143,7 @@ def test_large_pre_activations_keep_parity():
     with torch.no_grad():
         h = torch.nn.functional.linear(x, p_ref["decoder.lin0.weight"], p_ref["decoder.lin0.bias"])
         h1 = torch.nn.functional.linear(torch.sin(30 * h), p_ref["decoder.lin1.weight"], p_ref["decoder.lin1.bias"])
-        assert float((30 * h1).abs().max()) > 25.0
+        assert float((30 * h1).abs().min()) > 25.0 and float((30 * h).abs().min()) > 25.0
     x_ref = x.clone().requires_grad_(True)
     out_ref = siren.forward(p_ref, x_ref)
     w = torch.linspace(-1, 1, n, device="cuda")[:, None]
@@ -147,7 +151,10 @@ def test_large_pre_activations_keep_parity():
     x1 = x.clone().requires_grad_(True)
     out = dec(x1)
     (out * w).sum().backward()
-    assert (out - out_ref).abs().max().item() <= 2e-3 * max(1.0, float(out_ref.abs().max()))
+    assert (out - out_ref).abs().max().item() <= 2e-3
+    # and against the UNSHIFTED network in the oracle: the shift is a mathematical no-op
+    base = siren.forward({k: v.cuda() for k, v in params.items()}, x)
+    assert (out - base).abs().max().item() <= 2e-3
     flat_ref = torch.cat([p_ref[k].grad.flatten() for k, _ in dec.named_parameters()])
     flat = torch.cat([p.grad.flatten() for _, p in dec.named_parameters()])
     assert cos(flat, flat_ref) >= 0.999

@@ -360,3 +360,36 @@ def test_fused_eikonal_algebra_equals_double_backward():
         d_got = out["dW"][l] - orc0.params[f"lin{l}.weight"].grad
         assert float(d_ref.norm()) > 0
         assert cos(d_got, d_ref) > 0.999, (l, cos(d_got, d_ref))
+
+
+@pytest.mark.parametrize("eik", [False, True])
+def test_oracle_port_equals_the_step_loop_around_the_reference_module(eik):
+    """oracle/ref_step.py runs train_deep_sdf.py's step statements around the reference's own Decoder class
+    (oracle/_ref, copied unmodified by oracle/build_ref.py); the oracle port (oracle/train.py, functional restatement)
+    must walk the same trajectory: losses and gradient norm of 3 optimiser steps, then the parameters."""
+    from oracle import ref_step
+    from oracle import train as otrain
+    from dsdf_b200 import synth
+    if not ref_step.available():
+        pytest.skip("oracle/_ref not built (python oracle/build_ref.py needs /root/reference)")
+    S, B, P = 4, 2, 256
+    specs = dict(dims=[512] * 8, dropout=[], dropout_prob=0.2, norm_layers=[], latent_in=[4], xyz_in_all=False,
+                 use_tanh=False, latent_dropout=False, weight_norm=True)
+    ref = ref_step.ReferenceStepLoop(S, specs, use_eikonal=eik, seed=0)
+    lat0 = ref.lat_vecs.weight.data.clone()
+    cfg = otrain.TrainConfig(samples_per_scene=P, scenes_per_batch=B, code_bound=1.0, grad_clip=1.0, use_eikonal=eik)
+    orc = otrain.OracleTrainer(spec_for(False), cfg, S, seed=0, latents=lat0)
+    data = synth.scene_samples(S, P, seed=1)
+    g = torch.Generator().manual_seed(5)
+    for it in range(3):
+        ids = torch.randperm(S, generator=g)[:B]
+        a = ref.step(data[ids].clone(), ids, 50 + it)
+        b = orc.step(data[ids], ids, 50 + it)
+        assert a["sdf_loss"] == pytest.approx(b["sdf_loss"], rel=1e-6)
+        assert a["reg_loss"] == pytest.approx(b["reg_loss"], rel=1e-6)
+        assert a["grad_norm"] == pytest.approx(b["grad_norm"], rel=1e-5)
+        if eik:
+            assert a["eikonal_loss"] == pytest.approx(b["eikonal_loss"], rel=1e-6)
+    for k, v in ref.decoder.state_dict().items():
+        torch.testing.assert_close(v, orc.params[k].data, rtol=1e-5, atol=1e-7)
+    torch.testing.assert_close(ref.lat_vecs.weight.data, orc.lat_vecs.weight.data, rtol=1e-5, atol=1e-7)
