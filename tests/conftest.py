@@ -3,6 +3,8 @@ import sys
 
 import pytest
 
+os.environ.setdefault("CUBLAS_WORKSPACE_CONFIG", ":4096:8")   # lets test helpers ask torch for deterministic cuBLAS
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 PKG = os.path.join(ROOT, "medical-shape-disentanglement_b200")
 for p in (ROOT, PKG):

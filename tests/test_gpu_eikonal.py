@@ -42,6 +42,11 @@ def trained(wn, steps=250):
     steps with the Eikonal term on, so that ||d pred / d xyz|| is of order 1 near the surface, both clamp branches
     are live and the ReLU patterns are those of a real SDF rather than of an initialisation.  Cached per session."""
     if wn not in _TRAINED:
+        # torch's embedding backward accumulates with float atomics on CUDA; 250 chaotic steps amplify that into a
+        # different "trained" state per run, which made the small-batch bars below flaky.  Deterministic kernels
+        # (sort-based embedding backward; CUBLAS_WORKSPACE_CONFIG is set in conftest.py) pin the state per image.
+        prev = torch.are_deterministic_algorithms_enabled()
+        torch.use_deterministic_algorithms(True, warn_only=True)
         S, B, P = 8, 4, 2048
         cfg = otrain.TrainConfig(samples_per_scene=P, scenes_per_batch=B, code_bound=1.0, grad_clip=1.0, use_eikonal=True,
                                  lr_decoder=1e-3, lr_latent=2e-3)
@@ -51,6 +56,7 @@ def trained(wn, steps=250):
         for it in range(steps):
             ids = torch.randperm(S, generator=g)[:B]
             r = orc.step(data[ids], ids, 50)
+        torch.use_deterministic_algorithms(prev)
         _TRAINED[wn] = ({k: v.detach().cpu().clone() for k, v in orc.params.items()},
                         orc.lat_vecs.weight.data.cpu().clone(), r)
     return _TRAINED[wn]
