@@ -27,7 +27,8 @@
 
 namespace dsdf {
 
-struct Bwd2Args {
+struct alignas(64) Bwd2Args {
+  CUtensorMap tmap_dg;        // CTA-pair launches: tensor map over dg2img (common.cuh kMapRowBytes)
   long long n_rows;
   const uint8_t* dg2img;      // dgrad K-step stream
   const float* w8;            // [512]
@@ -108,7 +109,7 @@ __device__ __forceinline__ void j_acc32(const uint32_t (&v)[32], uint32_t m, con
 // scalars at the end of the tile (||G||, eps, xyz'), writes them for the recompute pass and lets the reducers
 // weight the layer-0 sums with them (the sums of layers 1..7 are corrected by k_eik_corr).
 template <int CG, bool DROP = false, bool EIK = false>
-__global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
+__global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const __grid_constant__ Bwd2Args a) {
   static_assert(!(EIK && DROP), "the Eikonal pass is not built together with dropout");
   using C = B2<CG>;
   constexpr int kRing = C::kRing;
@@ -144,7 +145,7 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < kRing; ++i) {
-      mbar_init(&full[i], leader ? CG : 1);
+      mbar_init(&full[i], 1);              // one arrive.expect_tx by the leader's producer for both CTAs' bytes
       mbar_init(&empty[i], 1);
     }
     mbar_init(a_lo, 8 * CG);
@@ -189,15 +190,24 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
             const int halves = b2_has_h1(l) ? 2 : 1;
 #pragma unroll 1
             for (int h = 0; h < halves; ++h) {
-              const uint8_t* w = a.dg2img + (size_t)dg2_step(l, h, 0) * kStepBytes + crank * kSlice;
+              const long long w_off = (long long)dg2_step(l, h, 0) * kStepBytes + crank * kSlice;
+              const uint8_t* w = a.dg2img + w_off;
+              int y = (int)(w_off / kMapRowBytes);
 #pragma unroll 1
               for (int g = 0; g < groups; ++g) {
 #pragma unroll
                 for (int u = 0; u < kRing; ++u) {
                   mbar_wait(&empty[u], ph ^ 1);
-                  mbar_arrive_expect_tx(&full[u], kSlice);
-                  bulk_g2s(smem + C::kSmemRing + u * kSlice, w, kSlice, &full[u]);
-                  w += kStepBytes;
+                  if (CG > 1) {
+                    // each CTA's half of the K-step reports to the LEADER's barrier (UTMALDG.2CTA): no relay hop
+                    if (leader) mbar_arrive_expect_tx(&full[u], CG * kSlice);
+                    tma2_load_2d(s_base + C::kSmemRing + u * kSlice, &a.tmap_dg, 0, y, full_c + u * 8);
+                    y += (int)(kStepBytes / kMapRowBytes);
+                  } else {
+                    mbar_arrive_expect_tx(&full[u], kSlice);
+                    bulk_g2s(smem + C::kSmemRing + u * kSlice, w, kSlice, &full[u]);
+                    w += kStepBytes;
+                  }
                 }
                 ph ^= 1;
               }
@@ -205,28 +215,8 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const Bwd2Args a) {
           }
         }
       }
-    } else if (warp == 1 && !leader) {
-      // ===================== peer CTA: relay "my half of the step has landed" =====================
-      if (elect_one()) {
-        uint32_t ph = 0;
-        for (long long it = 0; it < n_iter; ++it) {
-#pragma unroll 1
-          for (int l = 7; l >= 1; --l) {
-            const int n_groups = (dg2_ksteps(l) / kRing) * (b2_has_h1(l) ? 2 : 1);
-#pragma unroll 1
-            for (int g = 0; g < n_groups; ++g) {
-#pragma unroll
-              for (int u = 0; u < kRing; ++u) {
-                mbar_wait(&full[u], ph);
-                mbar_arrive_cluster_relaxed(full_c + u * 8);
-              }
-              ph ^= 1;
-            }
-          }
-        }
-      }
-    } else if (warp == 1) {
-      // ===================== MMA issuer (leader CTA only) =====================
+    } else if (warp == 1 && leader) {
+      // ===================== MMA issuer (leader CTA only; the peer's warp 1 idles) =====================
       if (elect_one()) {
         constexpr uint32_t idesc = umma_idesc_bf16(128 * CG, 256, false, false);
         const uint64_t a_desc0 = umma_smem_desc(s_base + C::kSmemA, 16, 1024);

@@ -21,7 +21,14 @@ namespace dsdf {
 
 enum : int { MODE_DENSE = 0, MODE_TABLE = 1, MODE_GRID = 2 };
 
-struct FwdArgs {
+// A linear byte stream (weight K-steps, per-scene E steps) seen as a 2-D tensor of 1 KB rows (256 x u32) so that a
+// {256, 4} box is one 4 KB CTA slice of a K-step: y = byte offset / 1024 (host encoder: dsdf_api.cu make_stream_map)
+constexpr uint32_t kMapRowBytes = 1024;
+
+struct alignas(64) FwdArgs {
+  // CTA-pair launches: tensor maps over w2img and scene_e (first members: 64-byte aligned in the parameter space)
+  CUtensorMap tmap_w;
+  CUtensorMap tmap_e;
   long long n_rows;
   // MODE_DENSE: input [n,259] fp32 (latent | xyz)
   const float* input;

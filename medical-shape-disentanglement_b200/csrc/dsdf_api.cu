@@ -42,6 +42,10 @@ struct dsdf_handle_s {
   uint8_t* w2_img = nullptr;     // forward K-step stream
   uint8_t* dg2_img = nullptr;    // dgrad K-step stream
   uint8_t* scene_e = nullptr;    // fold-mode per-segment E steps for the inference entries (kInferSegs, fixed)
+  // tensor maps over the three handle-owned streams (encoded once at dsdf_create) + a 2-entry cache for the
+  // caller-workspace scene_e buffers (training / reconstruct), re-encoded on the host only when base or size change
+  CUtensorMap tmap_w{}, tmap_dg{}, tmap_e{};
+  struct MapCache { const void* base = nullptr; size_t bytes = 0; CUtensorMap map{}; } ws_map[3];
   // A/B knobs: fixed in the product build; the diagnostics variant (-DDSDF_DIAG_BUILD) reads DSDF_FWD_CG,
   // DSDF_WG_QUAD, DSDF_DW8_WGRAD from the environment at dsdf_create
   int fwd_cg = 2;                // 1: never pair CTAs (cta_group::1 only)
@@ -106,6 +110,52 @@ static thread_local std::string g_err;
       DSDF_FAIL(h, DSDF_ECUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), \
                 __FILE__, __LINE__);                                                   \
   } while (0)
+
+// ---- tensor maps for the CTA-pair weight loads (UTMALDG.2D.2CTA, ptx.cuh tma2_load_2d) ----------------------
+// A linear byte stream seen as [rows of 1 KB][256 x u32], box {256, 4} = one 4 KB CTA slice of a K-step, no
+// swizzle / interleave: the box lands in shared memory as the same 4 KB byte for byte.  The encoder is a host-side
+// driver function without a runtime-API twin; it is fetched through the runtime (no libcuda link dependency).
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static PFN_encodeTiled encode_tiled_fn() {
+  static PFN_encodeTiled fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      p = nullptr;
+    return (PFN_encodeTiled)p;
+  }();
+  return fn;
+}
+static int make_stream_map(dsdf_handle h, CUtensorMap* out, const void* base, size_t bytes) {
+  PFN_encodeTiled enc = encode_tiled_fn();
+  if (!enc) DSDF_FAIL(h, DSDF_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
+  if (((uintptr_t)base & 15) != 0 || bytes % 4096 != 0 || bytes == 0)
+    DSDF_FAIL(h, DSDF_EINVAL, "stream map: base %p / size %zu must be 16-byte aligned / a multiple of 4 KB", base, bytes);
+  const cuuint64_t dims[2] = {kMapRowBytes / 4, (cuuint64_t)(bytes / kMapRowBytes)};
+  const cuuint64_t strides[1] = {kMapRowBytes};
+  const cuuint32_t box[2] = {kMapRowBytes / 4, 4};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<void*>(base), dims, strides, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) DSDF_FAIL(h, DSDF_ECUDA, "cuTensorMapEncodeTiled failed (%d) for %p + %zu", (int)r, base, bytes);
+  return DSDF_OK;
+}
+// map over a caller-workspace scene_e buffer (slot 0: training step, 1: segments autograd entry, 2: reconstruct)
+static int ws_scene_map(dsdf_handle h, int slot, const void* base, size_t bytes, CUtensorMap* out) {
+  auto& c = h->ws_map[slot];
+  if (c.base != base || c.bytes != bytes) {
+    int rc = make_stream_map(h, &c.map, base, bytes);
+    if (rc != DSDF_OK) return rc;
+    c.base = base;
+    c.bytes = bytes;
+  }
+  *out = c.map;
+  return DSDF_OK;
+}
 
 static int set_kernel_attrs(dsdf_handle h) {
   if (h->attrs_set) return DSDF_OK;
@@ -193,6 +243,9 @@ extern "C" int dsdf_create(const dsdf_config* cfg, dsdf_handle* out) {
     DSDF_FAIL((dsdf_handle) nullptr, DSDF_ENOMEM, "cudaMalloc of weight shadows failed");
   }
   int rc = set_kernel_attrs(h);
+  if (rc == DSDF_OK) rc = make_stream_map(h, &h->tmap_w, h->w2_img, (size_t)kW2Steps * kStepBytes);
+  if (rc == DSDF_OK) rc = make_stream_map(h, &h->tmap_dg, h->dg2_img, (size_t)kDg2Steps * kStepBytes);
+  if (rc == DSDF_OK) rc = make_stream_map(h, &h->tmap_e, h->scene_e, (size_t)kInferSegs * kSceneESteps * kStepBytes);
   if (rc != DSDF_OK) {
     std::string m = h->err;
     dsdf_destroy(h);
@@ -297,6 +350,8 @@ static void fwd_args_init(dsdf_handle h, FwdArgs& a, long long n) {
   a.b8 = h->weff + kWeffElems;   // lin8 bias rides behind the effective weights (k_rowscale_weff)
   a.n_rows = n;
   a.w2img = h->w2_img;
+  a.tmap_w = h->tmap_w;
+  a.tmap_e = h->tmap_e;          // handle-owned scene_e (inference entries); workspace callers overwrite it
   a.dbg = h->dbg;
 }
 
@@ -421,6 +476,7 @@ struct Ws {
   long long* ids;        // identity segment ids (segments autograd entry)
   float* dweff;
   uint8_t* scene_e;
+  size_t scene_e_bytes;
   uint32_t* relu_mask;
   uint8_t* g_img;
   float4* eik_row;       // Eikonal: per-row (x', y', z', eps)
@@ -450,7 +506,8 @@ Ws carve(uint8_t* base, long long max_rows, long long max_seg, int num_sms) {
   w.seg_norm = (float*)take((size_t)max_seg * 4);
   w.ids = (long long*)take((size_t)max_seg * 8);
   w.dweff = (float*)take((size_t)kWeffElems * 4);
-  w.scene_e = take((size_t)max_seg * kSceneESteps * kStepBytes);
+  w.scene_e_bytes = (size_t)max_seg * kSceneESteps * kStepBytes;
+  w.scene_e = take(w.scene_e_bytes);
   w.relu_mask = (uint32_t*)take(tiles * kActAuxTileBytes);
   w.g_img = take(tiles * kSubBytes);
   w.eik_row = (float4*)take(tiles * kTileM * sizeof(float4));
@@ -713,6 +770,7 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   const bool prof = h->profile && (int)h->prof_events.size() + 10 <= kProfMaxEvents;
   if (prof) prof_mark(h, st, -1);
   fa.scene_e = w.scene_e;
+  if (int mrc = ws_scene_map(h, 0, w.scene_e, w.scene_e_bytes, &fa.tmap_e)) return mrc;
   fa.relu_mask = w.relu_mask;
   fa.g_img = dw8_fwd ? nullptr : w.g_img;
   if (dw8_fwd && !eik) {
@@ -751,6 +809,7 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   memset(&b2, 0, sizeof(b2));
   b2.n_rows = n;
   b2.dg2img = h->dg2_img;
+  b2.tmap_dg = h->tmap_dg;
   b2.w8 = h->weff + weff_off(8);
   b2.g = w.g;
   b2.relu_mask = w.relu_mask;
@@ -881,6 +940,7 @@ extern "C" int dsdf_dense_backward(dsdf_handle h, const float* params, const flo
   memset(&b2, 0, sizeof(b2));
   b2.n_rows = n;
   b2.dg2img = h->dg2_img;
+  b2.tmap_dg = h->tmap_dg;
   b2.w8 = h->weff + weff_off(8);
   b2.g = w.g;
   b2.relu_mask = w.relu_mask;
@@ -965,6 +1025,7 @@ extern "C" int dsdf_segments_forward_train(dsdf_handle h, const float* params, c
   fa.xstash = w.xstash;
   fa.relu_mask = w.relu_mask;
   fa.scene_e = w.scene_e;
+  if (int mrc = ws_scene_map(h, 1, w.scene_e, w.scene_e_bytes, &fa.tmap_e)) return mrc;
   k_iota<<<(unsigned)((n_seg + 255) / 256), 256, 0, st>>>(w.ids, n_seg);
   k_scene_fold<<<dim3((unsigned)n_seg, 2, kFoldSplit), 512, 0, st>>>(h->weff, params, h->pl, latents, w.ids, w.scene_e);
   CU(h, (launch_fwd<MODE_TABLE, true, true>(h, fa, st, rows_per_seg % (2 * kTileM) == 0)));
@@ -997,6 +1058,7 @@ extern "C" int dsdf_segments_backward(dsdf_handle h, const float* params, const 
   memset(&b2, 0, sizeof(b2));
   b2.n_rows = n;
   b2.dg2img = h->dg2_img;
+  b2.tmap_dg = h->tmap_dg;
   b2.w8 = h->weff + weff_off(8);
   b2.g = w.g;
   b2.relu_mask = w.relu_mask;
@@ -1073,6 +1135,7 @@ struct RWs {
   float* cta_partials;
   float* seg_sum;
   uint8_t* scene_e;
+  size_t scene_e_bytes;
   uint32_t* relu_mask;
   float* loss_sink;      // [n_shapes] when the caller wants no loss history
   size_t total;
@@ -1095,7 +1158,8 @@ RWs recon_carve(uint8_t* base, long long n_shapes, long long num_samples, int nu
   w.tile_colsum = (float*)take(tiles * 2 * kHidden * 4);
   w.cta_partials = (float*)take((size_t)num_sms * kCtaPartialFloats * 4);
   w.seg_sum = (float*)take((size_t)n_shapes * kReconParts * kLatent * 4);   // latent-gradient partials
-  w.scene_e = take((size_t)n_shapes * kSceneESteps * kStepBytes);
+  w.scene_e_bytes = (size_t)n_shapes * kSceneESteps * kStepBytes;
+  w.scene_e = take(w.scene_e_bytes);
   w.relu_mask = (uint32_t*)take(tiles * kActAuxTileBytes);
   w.loss_sink = (float*)take((size_t)n_shapes * 4);
   w.total = o;
@@ -1152,12 +1216,14 @@ extern "C" int dsdf_reconstruct(dsdf_handle h, const float* params, const dsdf_r
   fa.clamp_dist = cfg->clamp_dist;
   fa.inv_n_total = 1.0f / (float)num;          // L1Loss() = mean over num_samples (reconstruct.py:102)
   fa.scene_e = w.scene_e;
+  if (int mrc = ws_scene_map(h, 2, w.scene_e, w.scene_e_bytes, &fa.tmap_e)) return mrc;
   fa.relu_mask = w.relu_mask;                   // xstash / g_img stay null: frozen decoder, no wgrad
 
   Bwd2Args b2;
   memset(&b2, 0, sizeof(b2));
   b2.n_rows = n;
   b2.dg2img = h->dg2_img;
+  b2.tmap_dg = h->tmap_dg;
   b2.w8 = h->weff + weff_off(8);
   b2.g = w.g;
   b2.relu_mask = w.relu_mask;

@@ -142,7 +142,7 @@ __device__ __forceinline__ void deriv_load(const uint8_t* aux_tile, int l, int c
 // READ from the first pass's bit-masks instead of taken from the sign (the map is then linear in the input), no
 // output / loss; stashes Xt_l = (1 + eps) h_l + tangent and accumulates dW8 = sum_r g_r Xt8[r, :].
 template <int MODE, bool FOLD, bool TRAIN, int CG, bool DROP = false, bool TAN = false>
-__global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
+__global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const __grid_constant__ FwdArgs a) {
   static_assert(!DROP || TRAIN, "dropout exists in training mode only");
   static_assert(!TAN || (TRAIN && FOLD && !DROP && MODE == MODE_TABLE), "the recompute pass is a fold-mode training pass");
   using C = F3<CG>;
@@ -179,13 +179,14 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
   const bool leader = crank == 0;
 
   if (threadIdx.x == 0) {
-    // full barriers: own copy (arrive.expect_tx) + in the leader one relayed arrive per peer copy
+    // full barriers: ONE arrive.expect_tx (the leader's producer, for the bytes of both CTAs); in a pair every
+    // CTA's tensor-map copy reports its bytes to the leader's barrier (the peer's own copies are unused)
     for (int i = 0; i < kRing; ++i) {
-      mbar_init(&full[i], leader ? CG : 1);
+      mbar_init(&full[i], 1);
       mbar_init(&empty[i], 1);
     }
     for (int i = 0; i < 2; ++i) {
-      mbar_init(&e_full[i], leader ? CG : 1);
+      mbar_init(&e_full[i], 1);
       mbar_init(&e_empty[i], 1);
       mbar_init(&d_done[i], 1);
     }
@@ -225,65 +226,58 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const FwdArgs a) {
       for (long long it = 0; it < n_iter; ++it) {
         long long tile = it * gridDim.x + blockIdx.x;
         tile = tile < n_tiles ? tile : n_tiles - 1;
-        const uint8_t* se = nullptr;
+        long long se_off = 0;                 // byte offset of this tile's scene E steps in scene_e
         if (FOLD) {
           const long long seg = (MODE == MODE_TABLE && a.seg_ids) ? (tile * kTileM) / a.rows_per_seg : 0;
-          se = a.scene_e + (size_t)seg * kSceneESteps * kStepBytes;
+          se_off = seg * (long long)(kSceneESteps * kStepBytes);
         }
 #pragma unroll 1
         for (int l = 0; l < 8; ++l) {
           const int ksteps = f2_used_ksteps<FOLD>(l);
 #pragma unroll 1
           for (int h = 0; h < w2_halves(l); ++h) {
-            const uint8_t* w = a.w2img + (size_t)w2_step(l, h, 0) * kStepBytes + crank * kSlice;
-            const uint8_t* esrc = (FOLD && (l == 0 || l == kSkipLayer))
-                                      ? se + (size_t)((l == 0 ? 0 : 2) + h) * kStepBytes + crank * kSlice
-                                      : w;
+            const long long w_off = (long long)w2_step(l, h, 0) * kStepBytes + crank * kSlice;
+            const bool scene_step = FOLD && (l == 0 || l == kSkipLayer);
+            const long long e_off = scene_step ? se_off + (long long)((l == 0 ? 0 : 2) + h) * kStepBytes + crank * kSlice
+                                               : w_off;
             mbar_wait(&e_empty[es], eph ^ 1);
-            mbar_arrive_expect_tx(&e_full[es], kSlice);
-            bulk_g2s(smem + C::kSmemERing + es * kSlice, esrc, kSlice, &e_full[es]);
+            if (CG > 1) {
+              if (leader) mbar_arrive_expect_tx(&e_full[es], CG * kSlice);
+              tma2_load_2d(s_base + C::kSmemERing + es * kSlice, scene_step ? &a.tmap_e : &a.tmap_w, 0,
+                           (int)(e_off / kMapRowBytes), e_full_c + es * 8);
+            } else {
+              mbar_arrive_expect_tx(&e_full[es], kSlice);
+              bulk_g2s(smem + C::kSmemERing + es * kSlice, (scene_step ? a.scene_e : a.w2img) + e_off, kSlice, &e_full[es]);
+            }
             es ^= 1;
             eph ^= (es == 0);
-            w += kStepBytes;
+            if (CG > 1) {
+              int y = (int)((w_off + kStepBytes) / kMapRowBytes);
 #pragma unroll 4
-            for (int k = 0; k < ksteps; ++k) {
-              mbar_wait(&empty[st], ph ^ 1);
-              mbar_arrive_expect_tx(&full[st], kSlice);
-              bulk_g2s(smem + C::kSmemRing + st * kSlice, w, kSlice, &full[st]);
-              w += kStepBytes;
-              if (++st == (uint32_t)kRing) { st = 0; ph ^= 1; }
+              for (int k = 0; k < ksteps; ++k) {
+                mbar_wait(&empty[st], ph ^ 1);
+                if (leader) mbar_arrive_expect_tx(&full[st], CG * kSlice);
+                tma2_load_2d(s_base + C::kSmemRing + st * kSlice, &a.tmap_w, 0, y, full_c + st * 8);
+                y += (int)(kStepBytes / kMapRowBytes);
+                if (++st == (uint32_t)kRing) { st = 0; ph ^= 1; }
+              }
+            } else {
+              const uint8_t* w = a.w2img + w_off + kStepBytes;
+#pragma unroll 4
+              for (int k = 0; k < ksteps; ++k) {
+                mbar_wait(&empty[st], ph ^ 1);
+                mbar_arrive_expect_tx(&full[st], kSlice);
+                bulk_g2s(smem + C::kSmemRing + st * kSlice, w, kSlice, &full[st]);
+                w += kStepBytes;
+                if (++st == (uint32_t)kRing) { st = 0; ph ^= 1; }
+              }
             }
           }
         }
       }
     }
-  } else if (warp == 1 && !leader) {
-    // ===================== peer CTA: relay "my half of the step has landed" to the leader =====
-    // (a bulk copy can only signal an mbarrier of the CTA it writes to)
-    if (elect_one()) {
-      uint32_t ph = 0, st = 0, es = 0, eph = 0;
-      for (long long it = 0; it < n_iter; ++it) {
-#pragma unroll 1
-        for (int l = 0; l < 8; ++l) {
-          const int ksteps = f2_used_ksteps<FOLD>(l);
-#pragma unroll 1
-          for (int h = 0; h < w2_halves(l); ++h) {
-            mbar_wait(&e_full[es], eph);
-            mbar_arrive_cluster_relaxed(e_full_c + es * 8);
-            es ^= 1;
-            eph ^= (es == 0);
-#pragma unroll 4
-            for (int k = 0; k < ksteps; ++k) {
-              mbar_wait(&full[st], ph);
-              mbar_arrive_cluster_relaxed(full_c + st * 8);
-              if (++st == (uint32_t)kRing) { st = 0; ph ^= 1; }
-            }
-          }
-        }
-      }
-    }
-  } else if (warp == 1) {
-    // ===================== MMA issuer (leader CTA only) =====================
+  } else if (warp == 1 && leader) {
+    // ===================== MMA issuer (leader CTA only; the peer's warp 1 idles) =====================
     if (elect_one()) {
       constexpr uint32_t idesc = umma_idesc_bf16(128 * CG, 256, false, false);
       const uint64_t ea_desc = umma_smem_desc_ns(s_base + C::kSmemEA, 128, 256);

@@ -2,6 +2,7 @@
 // tcgen05 (alloc / mma / commit / ld / fences), UMMA shared-memory + instruction descriptors.
 // Hand-written for this repo; no CUTLASS/CuTe dependency.
 #pragma once
+#include <cuda.h>          // CUtensorMap (type only; the encoder is fetched through cudaGetDriverEntryPoint)
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -288,6 +289,18 @@ __device__ __forceinline__ void bulk_g2s_bar(void* smem_dst, const void* gmem_sr
       "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
           "r"(smem_u32(smem_dst)),
       "l"(gmem_src), "r"(bytes), "r"(bar_cluster_addr)
+      : "memory");
+}
+// Tensor-map TMA load of a CTA pair (SASS: UTMALDG.2D.2CTA): box (x, y) of the 2-D tensor behind `tmap` -> this
+// CTA's shared memory at `smem_dst`; the complete_tx lands on the mbarrier at shared::cluster address
+// `bar_cluster_addr`, which may belong to EITHER CTA of the pair -- so the peer's half of a weight K-step reports
+// straight to the leader's `full` barrier (no relay hop; plain bulk copies can only signal the CTA they write to).
+__device__ __forceinline__ void tma2_load_2d(uint32_t smem_dst, const CUtensorMap* tmap, int x, int y,
+                                             uint32_t bar_cluster_addr) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes "
+      "[%0], [%1, {%2, %3}], [%4];" ::"r"(smem_dst),
+      "l"(reinterpret_cast<uint64_t>(tmap)), "r"(x), "r"(y), "r"(bar_cluster_addr)
       : "memory");
 }
 template <uint32_t kCols>
