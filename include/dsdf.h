@@ -260,6 +260,12 @@ int dsdf_selftest_mma_rate(int32_t kind, int32_t iters, int32_t n_cta, uint64_t*
  * buf[0] = record count, records at buf[4 + 4*i].  DSDF_EUNSUPPORTED in the product build. */
 int dsdf_debug_hang_buffer(uint32_t** host_ptr);
 
+/* Diagnostics builds only (-DDSDF_PROGRESS): every warp leader of the dgrad chain kernel posts its position
+ * ((tile iteration << 16) | (layer << 8) | stage) before each barrier wait into this mapped host buffer
+ * (word blockIdx * 64 + warp * 4, first 16 blocks), readable while a kernel hangs (tools/gpu_progress.py).
+ * DSDF_EUNSUPPORTED in the product build. */
+int dsdf_debug_progress_buffer(uint32_t** host_ptr);
+
 #ifdef __cplusplus
 }
 #endif

@@ -129,7 +129,10 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const __grid_consta
   uint64_t* red_done = bars + 37;        // reducers -> epilogue: A may be overwritten
   uint64_t* s_lo = bars + 38;            // epilogue -> stash warp: dY columns 0..255 written
   uint64_t* s_hi = bars + 39;            // epilogue -> stash warp: dY columns 256..511 written
-  uint64_t* s_done = bars + 40;          // stash warp -> epilogue: dY tile copied to HBM
+  uint64_t* s_done = bars + 40;          // stash warp -> epilogue: dY columns 0..255 copied to HBM
+  uint64_t* s_done_hi = bars + 41;       // stash warp -> epilogue: dY columns 256..511 copied to HBM
+  uint64_t* red_done_hi = bars + 42;     // reducer warps 14,15 (columns 256..511) -> epilogue (red_done: warps 12,13)
+  uint64_t* lo_free = bars + 43;         // MMA -> epilogue: the layer's last read of A columns 0..255 has retired
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + C::kSmemAux + C::kAuxTmem);
   float* w8s = reinterpret_cast<float*>(smem + C::kSmemAux + C::kAuxW8);
   float* gs = reinterpret_cast<float*>(smem + C::kSmemAux + C::kAuxG);
@@ -153,10 +156,13 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const __grid_consta
     mbar_init(&d_done[0], 1);
     mbar_init(&d_done[1], 1);
     mbar_init(dy_ready, 8);
-    mbar_init(red_done, 4);
+    mbar_init(red_done, 2);
+    mbar_init(red_done_hi, 2);
     mbar_init(s_lo, 8);
     mbar_init(s_hi, 8);
     mbar_init(s_done, 1);
+    mbar_init(s_done_hi, 1);
+    mbar_init(lo_free, 1);
     fence_mbar_init();
   }
   if (warp == 2) {
@@ -233,6 +239,7 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const __grid_consta
           for (int l = 7; l >= 1; --l) {
             const int groups = dg2_ksteps(l) / kRing;
             const int halves = b2_has_h1(l) ? 2 : 1;
+            DSDF_PROG(0, ((unsigned)it << 16) | ((unsigned)l << 8) | 1u);
             mbar_wait(a_lo, par_lo);
             par_lo ^= 1;
             tc_fence_after();
@@ -241,6 +248,7 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const __grid_consta
               const uint32_t d_addr = tmem + h * 256;
 #pragma unroll 1
               for (int g = 0; g < groups; ++g) {
+                DSDF_PROG(0, ((unsigned)it << 16) | ((unsigned)l << 8) | (unsigned)(16 + h * 4 + g));
                 if (h == 0 && g * kRing == 16) {   // first K-step that reads dY columns 256..511
                   mbar_wait(a_hi, par_hi);
                   par_hi ^= 1;
@@ -256,6 +264,9 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const __grid_consta
                   commit(&empty[u]);
                 }
                 ph ^= 1;
+                // K-steps 0..15 (A columns 0..255) of the layer's last half are issued: once they retire the epilogue
+                // may put the next layer's columns 0..255 in place, under K-steps 16..31
+                if (h == halves - 1 && (g + 1) * kRing == 16) commit(lo_free);
               }
               commit(&d_done[h]);
             }
@@ -280,7 +291,9 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const __grid_consta
           const uint32_t src = s_base + C::kSmemA;
 #pragma unroll 1
           for (int half = 0; half < 2; ++half) {
-            if (half == 1 && k == 3) break;                   // dY3 has 256 columns
+            if (half == 1 && k == 3) break;                   // dY3 has 256 columns (and no s_done_hi phase: an arrive
+                                                              // not gated by s_hi could lap a slow epilogue warp)
+            DSDF_PROG(0, ((unsigned)it << 16) | ((unsigned)k << 8) | (unsigned)(1 + half));
             if (half == 0) { mbar_wait(s_lo, par_lo); par_lo ^= 1; }
             else { mbar_wait(s_hi, par_hi); par_hi ^= 1; }
             if (tile_valid && a.dystash) {    // frozen-decoder callers pass no stash (no wgrad)
@@ -299,9 +312,9 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const __grid_consta
                   st_stash(dst + (size_t)(half * 4 * kSubBytes) / 16 + (size_t)(i + q8) * 32 + lane, v[q8], pol);
               }
             }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(half == 0 ? s_done : s_done_hi);
           }
-          __syncwarp();
-          if (lane == 0) mbar_arrive(s_done);
         }
       }
     }
@@ -314,7 +327,13 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const __grid_consta
     const uint32_t r = q * 32 + lane;     // row inside the tile
     const uint32_t tlane = (uint32_t)(q * 32) << 16;
     const uint32_t a_base = s_base + C::kSmemA;
-    uint32_t par_d0 = 0, par_d1 = 0, par_rd = 0, par_s = 0;
+    // phase parities of the seven barriers this role waits on, packed into one register (the epilogue is at its
+    // register cap): bit 0 d_done[0], 1 d_done[1], 2 red_done, 3 red_done_hi, 4 s_done, 5 s_done_hi, 6 lo_free
+    uint32_t pars = 0;
+    auto wait_flip = [&](uint64_t* bar, uint32_t bit) {
+      mbar_wait(bar, (pars >> bit) & 1u);
+      pars ^= 1u << bit;
+    };
     auto stash_ready = [&](uint64_t* bar) {   // after this warp's A stores (+ __syncwarp)
       if (lane == 0) mbar_arrive(bar);
     };
@@ -344,12 +363,13 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const __grid_consta
       const uint32_t* mask_tile = a.relu_mask + (size_t)tile * (8 * 16 * kTileM) + r;
 #endif
       // previous tile: reducers done with dY0, stash stores done reading A
+      DSDF_PROG(0, ((unsigned)it << 16) | (9u << 8) | 1u);
       if (!first) {
-        mbar_wait(red_done, par_rd);
-        par_rd ^= 1;
+        wait_flip(red_done, 2u);
+        wait_flip(red_done_hi, 3u);
         if (a.stash_dy0) {                  // ... and the stash warp has copied the previous tile's dY0
-          mbar_wait(s_done, par_s);
-          par_s ^= 1;
+          wait_flip(s_done, 4u);
+          wait_flip(s_done_hi, 5u);
         }
       }
       first = false;
@@ -404,8 +424,8 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const __grid_consta
 #endif
         // ---- half 0: TMEM -> mask -> bf16, held in registers while the MMAs still read A
         uint32_t held[64];
-        mbar_wait(&d_done[0], par_d0);
-        par_d0 ^= 1;
+        DSDF_PROG(0, ((unsigned)it << 16) | ((unsigned)l << 8) | 2u);
+        wait_flip(&d_done[0], 0u);
         tc_fence_after();
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
@@ -423,20 +443,33 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const __grid_consta
             j_acc32(v, mk[c], wxs + (lm == 0 ? 0 : kHidden) + j * 128 + c * 32, jx, jy, jz);
 #endif
         }
-        if (has_h1) {
-          mbar_wait(&d_done[1], par_d1);    // every MMA of layer l has retired: A is free
-          par_d1 ^= 1;
-          tc_fence_after();
-        }
-        mbar_wait(red_done, par_rd);        // ... the reducers have read dY_l
-        par_rd ^= 1;
-        mbar_wait(s_done, par_s);           // ... and the stash warp has copied it
-        par_s ^= 1;
+        // columns 0..255 of A are free once the layer's last half has retired its K-steps 0..15 (lo_free), the
+        // reducer warps 12,13 have summed them and the stash warp has copied them: the next layer's columns 0..255
+        // go in under K-steps 16..31, so the next layer's first MMAs follow this layer's last ones without a bubble
+        DSDF_PROG(0, ((unsigned)it << 16) | ((unsigned)l << 8) | 3u);
+        wait_flip(lo_free, 6u);
+        tc_fence_after();
+        DSDF_PROG(0, ((unsigned)it << 16) | ((unsigned)l << 8) | 4u);
+        wait_flip(red_done, 2u);
+        DSDF_PROG(0, ((unsigned)it << 16) | ((unsigned)l << 8) | 5u);
+        wait_flip(s_done, 4u);
 #pragma unroll
         for (int c = 0; c < 4; ++c) store_chunk32(a_base, r, (uint32_t)(j * 128 + c * 32), held + 16 * c);
         tc_fence_before();
         if (l - 1 >= 1) { publish(a_lo, a_lo_c); stash_ready(s_lo); }
         else if (a.stash_dy0) { __syncwarp(); stash_ready(s_lo); }
+        DSDF_PROG(0, ((unsigned)it << 16) | ((unsigned)l << 8) | 6u);
+        if (has_h1) {
+          wait_flip(&d_done[1], 1u);    // every MMA of layer l has retired: columns 256..511 are free ...
+          tc_fence_after();
+        }
+        DSDF_PROG(0, ((unsigned)it << 16) | ((unsigned)l << 8) | 7u);
+        wait_flip(red_done_hi, 3u);     // ... the reducers have read them
+        DSDF_PROG(0, ((unsigned)it << 16) | ((unsigned)l << 8) | 8u);
+        if (l != 3) {                       // ... and the stash warp has copied them (dY3 has no such half)
+          wait_flip(s_done_hi, 5u);
+        }
+        DSDF_PROG(0, ((unsigned)it << 16) | ((unsigned)l << 8) | 9u);
         if (has_h1) {
 #pragma unroll
           for (int c = 0; c < 4; ++c) {
@@ -537,6 +570,7 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const __grid_consta
       tile = tile_valid ? tile : n_tiles - 1;
 #pragma unroll
       for (int l = 7; l >= 0; --l) {
+        DSDF_PROG(0, ((unsigned)it << 16) | ((unsigned)l << 8) | 1u);
         mbar_wait(dy_ready, par_dy);
         par_dy ^= 1;
         const bool active = (l != 3) || (rt < 64);   // dY3 has 256 columns
@@ -582,7 +616,7 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const __grid_consta
           }
         }
         __syncwarp();
-        if (lane == 0) mbar_arrive(red_done);
+        if (lane == 0) mbar_arrive(rt < 64 ? red_done : red_done_hi);
       }
     }
     float* out = a.cta_partials + (size_t)blockIdx.x * kCtaPartialFloats;

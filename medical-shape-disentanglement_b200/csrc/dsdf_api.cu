@@ -1408,6 +1408,26 @@ extern "C" int dsdf_selftest_mma_rate(int32_t, int32_t, int32_t, uint64_t*) {
 #endif
 
 // diagnostics builds (-DDSDF_HANG_TRAP): mapped host buffer the device writes deadlock reports to
+extern "C" int dsdf_debug_progress_buffer(uint32_t** host_ptr) {
+#ifdef DSDF_PROGRESS
+  static uint32_t* buf = nullptr;
+  if (!buf) {
+    if (cudaHostAlloc((void**)&buf, 16 * 64 * 4, cudaHostAllocMapped) != cudaSuccess) return DSDF_ECUDA;
+    memset(buf, 0, 16 * 64 * 4);
+    unsigned int* dptr = nullptr;
+    if (cudaHostGetDevicePointer((void**)&dptr, buf, 0) != cudaSuccess) return DSDF_ECUDA;
+    volatile unsigned int* v = dptr;
+    if (cudaMemcpyToSymbol(g_prog, &v, sizeof(v)) != cudaSuccess) return DSDF_ECUDA;
+  }
+  if (host_ptr) *host_ptr = buf;
+  return DSDF_OK;
+#else
+  (void)host_ptr;
+  g_err = "library was not built with -DDSDF_PROGRESS";
+  return DSDF_EUNSUPPORTED;
+#endif
+}
+
 extern "C" int dsdf_debug_hang_buffer(uint32_t** host_ptr) {
 #ifdef DSDF_HANG_TRAP
   static uint32_t* buf = nullptr;

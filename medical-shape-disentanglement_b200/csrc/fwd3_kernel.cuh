@@ -164,7 +164,9 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const __grid_constan
   uint64_t* d_done = bars + 70;          // [2] MMA -> epilogue: half h accumulated
   uint64_t* s_lo = bars + 72;            // TRAIN: epilogue -> stash warp: A SUB 0..3 written
   uint64_t* s_hi = bars + 73;            //        epilogue -> stash warp: A SUB 4..7 written
-  uint64_t* s_done = bars + 74;          //        stash warp -> epilogue: A tile copied to HBM
+  uint64_t* s_done = bars + 74;          //        stash warp -> epilogue: A SUB 0..3 copied to HBM
+  uint64_t* s_done_hi = bars + 75;       //        stash warp -> epilogue: A SUB 4..7 copied to HBM
+  uint64_t* lo_free = bars + 80;         // MMA -> epilogue: the layer's last read of A SUB 0..3 has retired (both CTAs)
   uint64_t* a_sub = bars + 76;           // [3] epilogue -> MMA at a layer boundary: A SUB 1 / 2 / 3 written
                                          // (a_lo then only means SUB 0: the MMAs of the next layer start
                                          //  after 16 KB of A stores instead of 64 KB)
@@ -196,6 +198,8 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const __grid_constan
     mbar_init(s_lo, 8);
     mbar_init(s_hi, 8);
     mbar_init(s_done, 1);
+    mbar_init(s_done_hi, 1);
+    mbar_init(lo_free, 1);
     fence_mbar_init();
   }
   if (warp == 2) {
@@ -341,7 +345,11 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const __grid_constan
                 commit(&empty[st]);
                 if (++st == (uint32_t)kRing) { st = 0; ph ^= 1; }
               }
+              // the layer's last half has read A SUB 0..3 for the last time: the epilogue may overwrite them with
+              // the next layer's input while K-steps 16..31 (SUB 4..7) are still running
+              if (h == w2_halves(l) - 1 && sub == 3 && ksteps > 16) commit(lo_free);
             }
+            if (h == w2_halves(l) - 1 && ksteps <= 16) commit(lo_free);
             commit(&d_done[h]);
           }
           if (l >= 1) par_sub ^= 1;
@@ -372,7 +380,8 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const __grid_constan
           const uint32_t src = s_base + C::kSmemA;
 #pragma unroll 1
           for (int half = 0; half < 2; ++half) {
-            if (half == 1 && l == 3 && FOLD) break;          // lin3 has 256 outputs (x3 part)
+            if (half == 1 && l == 3 && FOLD) break;          // lin3 has 256 outputs (x3 part): nothing to copy, and no
+                                                             // s_done_hi phase (an ungated arrive could lap a slow warp)
             if (half == 0) { mbar_wait(s_lo, par_lo); par_lo ^= 1; }
             else { mbar_wait(s_hi, par_hi); par_hi ^= 1; }
             // frozen-decoder callers pass no stash (no wgrad); X8 (slot 7) is consumed on-chip when the
@@ -393,9 +402,9 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const __grid_constan
                   st_stash(dst + (size_t)(half * 4 * kSubBytes) / 16 + (size_t)(i + k) * 32 + lane, v[k], pol);
               }
             }
+            __syncwarp();                                     // every lane's ld.shared of this half has returned
+            if (lane == 0) mbar_arrive(half == 0 ? s_done : s_done_hi);
           }
-          __syncwarp();
-          if (lane == 0) mbar_arrive(s_done);
         }
       }
     }
@@ -407,7 +416,7 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const __grid_constan
     const uint32_t r = q * 32 + lane;     // row inside the tile
     const uint32_t tlane = (uint32_t)(q * 32) << 16;
     const uint32_t a_base = s_base + C::kSmemA;
-    uint32_t par_d0 = 0, par_d1 = 0, par_s = 1;   // par_s: first wait passes (nothing copied yet)
+    uint32_t par_d0 = 0, par_d1 = 0, par_lf = 0, par_s = 1, par_sh = 1;   // par_s / par_sh: first wait passes (nothing copied yet)
     auto stash_ready = [&](uint64_t* bar) {       // after publish(): this warp's A stores are done
       if (TRAIN && lane == 0) mbar_arrive(bar);
     };
@@ -425,6 +434,42 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const __grid_constan
         else { __threadfence_block(); mbar_arrive_cluster_relaxed(bar_c); }
       }
     };
+    // this thread's input row of a tile: (x, y, z, gt) -- or the recompute pass's (x', y', z', eps) -- fetched one
+    // tile ahead so the global-load latency is not part of the tile boundary
+    auto fetch_row = [&](long long it_) -> float4 {
+      float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (t < kTileM && it_ < n_iter) {
+        long long tl = it_ * gridDim.x + blockIdx.x;
+        tl = tl < n_tiles ? tl : n_tiles - 1;
+        long long row = tl * kTileM + t;
+        row = row < a.n_rows ? row : a.n_rows - 1;
+        if (TAN) e = __ldg(a.eik_row + row);
+        else load_xyz<MODE>(a, row, e.x, e.y, e.z, e.w);
+      }
+      return e;
+    };
+    // dW8[c] += sum_r g[r] X8[r, c] straight from the A tile (train_deep_sdf.py:731 for lin8.weight): thread t owns
+    // columns 2t, 2t+1; a warp reads one 128-byte swizzled row per step (conflict-free).  Runs AFTER the next tile's
+    // prologue has been published, i.e. under the next tile's layer-0 MMAs.
+    int dw8_pending = 0;                    // 1: accumulate the finished tile, 2: only the barrier (padding tile)
+    auto dw8_flush = [&]() {
+      if (!dw8_pending) return;
+      if (dw8_pending == 1) {
+        const uint32_t c0 = (uint32_t)(2 * t) & 63u;
+        const uint32_t sub = a_base + (uint32_t)(t >> 5) * kSubBytes;
+#pragma unroll 8
+        for (uint32_t rr = 0; rr < (uint32_t)kTileM; ++rr) {
+          uint32_t wv;
+          asm volatile("ld.shared.b32 %0, [%1];" : "=r"(wv) : "r"(sub + sub_off(rr, c0)));
+          const float gr = gsm[rr];
+          dw8a = fmaf(gr, __uint_as_float(wv << 16), dw8a);
+          dw8b = fmaf(gr, __uint_as_float(wv & 0xFFFF0000u), dw8b);
+        }
+      }
+      named_bar_sync(1, kActThreads);       // the tile in flight rewrites gsm and the A tile
+      dw8_pending = 0;
+    };
+    float4 row_cur = fetch_row(0);
     for (long long it = 0; it < n_iter; ++it) {
       long long tile = it * gridDim.x + blockIdx.x;
       const bool tile_valid = tile < n_tiles;
@@ -472,21 +517,19 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const __grid_constan
       };
 #endif
       // ---- tile prologue: E_A rows (+ layer-0 latent gather when not folded)
-      if (!FOLD) gather_latent<MODE>(a, row0, a_base, t);
-      float gt = 0.f;
+      if (!FOLD) {
+        // dense input: the latent goes into A SUB 0..3 -- after the stash warp has copied the previous tile's X8 out of
+        // them (layer 0's epilogue below then has nothing to wait for: nothing is stashed in between)
+        if (TRAIN) { mbar_wait(s_done, par_s); par_s ^= 1; }
+        gather_latent<MODE>(a, row0, a_base, t);
+      }
+      const float gt = row_cur.w;
       if (t < kTileM) {
-        long long row = row0 + t;
-        row = row < a.n_rows ? row : a.n_rows - 1;
-        if (TAN) {
-          const float4 e = __ldg(a.eik_row + row);
-          write_e_row_tan(s_base + C::kSmemEA, t, e.x, e.y, e.z, e.w);
-        } else {
-          float x, y, z;
-          load_xyz<MODE>(a, row, x, y, z, gt);
-          write_e_row_ns(s_base + C::kSmemEA, t, x, y, z);
-        }
+        if (TAN) write_e_row_tan(s_base + C::kSmemEA, t, row_cur.x, row_cur.y, row_cur.z, row_cur.w);
+        else write_e_row_ns(s_base + C::kSmemEA, t, row_cur.x, row_cur.y, row_cur.z);
       }
       publish(a_lo_c);
+      dw8_flush();                          // the previous tile's dW8 share, under this tile's layer-0 MMAs
 
 #pragma unroll 1
       for (int l = 0; l < 7; ++l) {
@@ -508,23 +551,23 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const __grid_constan
           tmem_ld_wait();
           act_pack32(v, l, (uint32_t)(j * 128 + c * 32), held + 16 * c);
         }
-        if (has_h1) {
+        {
+          // the layer's last read of A SUB 0..3 has retired (mid-way through the last half's K-steps): the next
+          // layer's SUB 0..3 go in NOW, under the K-steps that still read SUB 4..7, so the next layer's first 16
+          // K-steps are issued back to back with this layer's last ones (no layer-boundary bubble)
           const long long c0 = DSDF_DBG_ON(a) ? clock64() : 0;
-          mbar_wait(&d_done[1], par_d1);    // every MMA of layer l has retired: A is free
+          mbar_wait(lo_free, par_lf);
           if (DSDF_DBG_ON(a)) dbg_d1 += clock64() - c0;
-          par_d1 ^= 1;
+          par_lf ^= 1;
           tc_fence_after();
         }
-        const long long c_free = DSDF_DBG_ON(a) ? clock64() : 0;   // tensor pipe idle from here (layer l retired)
-        if (DSDF_DBG_ON(a)) dbg_free += c_free;
-        if (TRAIN) {                        // ... and the stash warp has copied the old A tile
+        if (TRAIN && (FOLD || l > 0)) {     // ... and the stash warp has copied the old SUB 0..3
           const long long c0 = DSDF_DBG_ON(a) ? clock64() : 0;
           mbar_wait(s_done, par_s);
           par_s ^= 1;
           if (DSDF_DBG_ON(a)) dbg_rd += clock64() - c0;
         }
-        // SUB by SUB, so the next layer's first K-steps start after the first 16 KB are in place;
-        // warps 4..7 own SUB 0,1 (columns 0..127), warps 8..11 own SUB 2,3
+        // SUB by SUB; warps 4..7 own SUB 0,1 (columns 0..127), warps 8..11 own SUB 2,3
         tc_fence_before();
         if (j == 0) {
           store_chunk32(a_base, r, 0u, held);
@@ -543,10 +586,15 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const __grid_constan
           publish(a_sub_c + 16);
         }
         stash_ready(s_lo);
-        const long long c_pub = DSDF_DBG_ON(a) ? clock64() : 0;
-        if (DSDF_DBG_ON(a)) dbg_st += c_pub - c_free;
-        // ---- half 1: straight from TMEM into SUB 4..7
+        // ---- half 1: straight from TMEM into SUB 4..7 once every MMA of layer l has retired
         if (has_h1) {
+          const long long c0 = DSDF_DBG_ON(a) ? clock64() : 0;
+          mbar_wait(&d_done[1], par_d1);
+          par_d1 ^= 1;
+          tc_fence_after();
+          const long long c_free = DSDF_DBG_ON(a) ? clock64() : 0;   // layer l retired
+          if (DSDF_DBG_ON(a)) { dbg_st += c_free - c0; dbg_free += c_free; }
+          if (TRAIN && !(FOLD && l == 4)) { mbar_wait(s_done_hi, par_sh); par_sh ^= 1; }   // (slot 3 has no hi half)
 #pragma unroll
           for (int c = 0; c < 4; ++c) {
             uint32_t v[32], p[16];
@@ -558,16 +606,21 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const __grid_constan
           tc_fence_before();
           if (f2_in_hi<FOLD>(l + 1)) publish(a_hi_c); else __syncwarp();
           stash_ready(s_hi);
-          if (DSDF_DBG_ON(a)) dbg_h1 += clock64() - c_pub;
-        } else if (!FOLD) {
-          // skip connection: latent -> SUB 4..7 (reference cat order [x3 | latent | xyz])
-          gather_latent<MODE>(a, row0, a_base + 4 * kSubBytes, t);
-          publish(a_hi_c);
-          stash_ready(s_hi);
+          if (DSDF_DBG_ON(a)) dbg_h1 += clock64() - c_free;
+        } else {
+          if (DSDF_DBG_ON(a)) dbg_free += clock64();                 // (no h1: layer l retired at d_done[0])
+          if (TRAIN) { mbar_wait(s_done_hi, par_sh); par_sh ^= 1; }
+          if (!FOLD) {
+            // skip connection: latent -> SUB 4..7 (reference cat order [x3 | latent | xyz])
+            gather_latent<MODE>(a, row0, a_base + 4 * kSubBytes, t);
+            publish(a_hi_c);
+            stash_ready(s_hi);
+          }
         }
       }
 
       // ---- lin7 epilogue fused with lin8 (512 -> 1), tanh, loss
+      const float4 row_next = fetch_row(it + 1);
       float acc = 0.f;
       if (TAN) {
         // recompute pass: Xt8 = mask7 . (lin7 output) goes through the A tile only for dW8 = g^T Xt8 below
@@ -584,8 +637,8 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const __grid_constan
           tmem_ld_wait();
           act_pack32(v, 7, col, held + 16 * c);
         }
-        mbar_wait(&d_done[1], par_d1);
-        par_d1 ^= 1;
+        mbar_wait(lo_free, par_lf);
+        par_lf ^= 1;
         tc_fence_after();
         mbar_wait(s_done, par_s);
         par_s ^= 1;
@@ -593,6 +646,11 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const __grid_constan
         for (int c = 0; c < 4; ++c) store_chunk32(a_base, r, (uint32_t)(j * 128 + c * 32), held + 16 * c);
         __syncwarp();
         stash_ready(s_lo);
+        mbar_wait(&d_done[1], par_d1);
+        par_d1 ^= 1;
+        tc_fence_after();
+        mbar_wait(s_done_hi, par_sh);
+        par_sh ^= 1;
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           uint32_t v[32], p[16];
@@ -638,8 +696,8 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const __grid_constan
           }
 #endif
         }
-        mbar_wait(&d_done[1], par_d1);
-        par_d1 ^= 1;
+        mbar_wait(lo_free, par_lf);
+        par_lf ^= 1;
         tc_fence_after();
         if (TRAIN) {   // X8 goes through the A tile only to be stashed (wgrad of lin8, ReLU of lin7)
           mbar_wait(s_done, par_s);
@@ -649,6 +707,10 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const __grid_constan
           __syncwarp();
           stash_ready(s_lo);
         }
+        mbar_wait(&d_done[1], par_d1);
+        par_d1 ^= 1;
+        tc_fence_after();
+        if (TRAIN) { mbar_wait(s_done_hi, par_sh); par_sh ^= 1; }
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           uint32_t v[32];
@@ -750,27 +812,13 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const __grid_constan
             a.tile_partials[tile * 2 + 1] = (red[1] + red[3]) + (red[5] + red[7]);
           }
         }
-        if (a.dw8_partials) {
-          // dW8[c] += sum_r g[r] X8[r, c] straight from the A tile (train_deep_sdf.py:731 for lin8.weight):
-          // thread t owns columns 2t, 2t+1; a warp reads one 128-byte swizzled row per step (conflict-free)
-          const uint32_t c0 = (uint32_t)(2 * t) & 63u;
-          const uint32_t sub = a_base + (uint32_t)(t >> 5) * kSubBytes;
-          if (tile_valid) {
-#pragma unroll 8
-            for (uint32_t rr = 0; rr < (uint32_t)kTileM; ++rr) {
-              uint32_t wv;
-              asm volatile("ld.shared.b32 %0, [%1];" : "=r"(wv) : "r"(sub + sub_off(rr, c0)));
-              const float gr = gsm[rr];
-              dw8a = fmaf(gr, __uint_as_float(wv << 16), dw8a);
-              dw8b = fmaf(gr, __uint_as_float(wv & 0xFFFF0000u), dw8b);
-            }
-          }
-          named_bar_sync(1, kActThreads);   // the next tile rewrites gsm and the A tile
-        }
+        if (a.dw8_partials) dw8_pending = tile_valid ? 1 : 2;
       } else {
         named_bar_sync(1, kActThreads);   // part[] is rewritten by the next tile
       }
+      row_cur = row_next;
     }
+    dw8_flush();
     if ((TAN || (TRAIN && a.fused_loss)) && a.dw8_partials) {
       float* o = a.dw8_partials + (size_t)blockIdx.x * a.dw8_stride;
       o[2 * t] = dw8a;

@@ -70,6 +70,18 @@ __device__ __noinline__ void hang_report(uint32_t bar_addr, uint32_t parity) {
 #else
 #define DSDF_HANG_CHECK(n, addr, par)
 #endif
+#ifdef DSDF_PROGRESS
+// diagnostics build: every warp leader posts "where am I" words into mapped host memory (dsdf_debug_progress_buffer),
+// readable by the host while a kernel hangs.  slot = blockIdx.x * 64 + warp * 4 + k
+__device__ volatile unsigned int* g_prog = nullptr;
+#define DSDF_PROG(k, val)                                                                                   \
+  do {                                                                                                      \
+    volatile unsigned int* _p = g_prog;                                                                     \
+    if (_p && (threadIdx.x & 31) == 0 && blockIdx.x < 16) _p[blockIdx.x * 64 + (threadIdx.x >> 5) * 4 + (k)] = (val); \
+  } while (0)
+#else
+#define DSDF_PROG(k, val)
+#endif
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   [[maybe_unused]] unsigned n_spin = 0;   // counted only in DSDF_HANG_TRAP builds
   while (!mbar_try_wait(bar, parity)) {
