@@ -44,6 +44,11 @@ struct dsdf_handle_s {
   uint8_t* scene_e = nullptr;    // fold-mode per-segment E steps for the inference entries (kInferSegs, fixed)
   // tensor maps over the three handle-owned streams (encoded once at dsdf_create) + a 2-entry cache for the
   // caller-workspace scene_e buffers (training / reconstruct), re-encoded on the host only when base or size change
+  // side stream of the fused step: the reductions that only need the dgrad chain's outputs (latent gradients, loss
+  // scalars, bias / xyz / latent-column gradients) run beside the wgrad GEMMs; forked and joined with events on the
+  // caller's stream, so the call is still ordered on that stream alone
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   CUtensorMap tmap_w{}, tmap_dg{}, tmap_e{};
   struct MapCache { const void* base = nullptr; size_t bytes = 0; CUtensorMap map{}; } ws_map[3];
   // A/B knobs: fixed in the product build; the diagnostics variant (-DDSDF_DIAG_BUILD) reads DSDF_FWD_CG,
@@ -234,6 +239,9 @@ extern "C" int dsdf_create(const dsdf_config* cfg, dsdf_handle* out) {
             cudaMalloc(&h->wg2_seg_begin, (size_t)(h->num_sms + 2) * sizeof(int)) == cudaSuccess &&
             cudaHostAlloc((void**)&h->wg2_stage, sched_bytes, cudaHostAllocDefault) == cudaSuccess &&
             cudaEventCreateWithFlags(&h->wg2_uploaded, cudaEventDisableTiming) == cudaSuccess &&
+            cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking) == cudaSuccess &&
+            cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming) == cudaSuccess &&
+            cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming) == cudaSuccess &&
             cudaMalloc(&h->weff, (size_t)(kWeffElems + 16) * 4) == cudaSuccess &&
             cudaMalloc(&h->scale, (size_t)kScaleElems * 4) == cudaSuccess &&
             cudaMalloc(&h->inv_norm, (size_t)kScaleElems * 4) == cudaSuccess &&
@@ -258,6 +266,9 @@ extern "C" int dsdf_create(const dsdf_config* cfg, dsdf_handle* out) {
 
 extern "C" int dsdf_destroy(dsdf_handle h) {
   if (!h) return DSDF_OK;
+  if (h->side) cudaStreamDestroy(h->side);
+  if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+  if (h->ev_join) cudaEventDestroy(h->ev_join);
   cudaFree(h->w2_img);
   cudaFree(h->dg2_img);
   cudaFree(h->scene_e);
@@ -300,13 +311,12 @@ extern "C" int dsdf_set_weights(dsdf_handle h, const float* params, const dsdf_p
     h->pl.b[l] = lay->b_off[l];
   }
   k_rowscale_weff<<<(kScaleElems * 32 + 255) / 256, 256, 0, st>>>(params, h->pl, h->scale, h->inv_norm, h->weff);
-  const long long c3 = (long long)kW2Steps * (kStepBytes / 16);
-  k_fold_fwd2<<<(unsigned)((c3 + 255) / 256), 256, 0, st>>>(h->weff, params, h->pl, h->w2_img);
-  const long long c4 = (long long)kDg2Steps * (kStepBytes / 16);
-  k_fold_dgrad2<<<(unsigned)((c4 + 255) / 256), 256, 0, st>>>(h->weff, h->dg2_img);
 #ifndef DSDF_ARCH_SIREN
-  k_build_wx<<<4, 256, 0, st>>>(h->weff, h->wx);
+  const unsigned fold_blocks = kFoldFwdBlocks + kFoldDgBlocks + kFoldWxBlocks;
+#else
+  const unsigned fold_blocks = kFoldFwdBlocks + kFoldDgBlocks;
 #endif
+  k_fold_images<<<fold_blocks, 256, 0, st>>>(h->weff, params, h->pl, h->w2_img, h->dg2_img, h->wx);
   CU(h, cudaGetLastError());
   h->params_ptr = params;
   h->weights_set = true;
@@ -859,32 +869,38 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
 #endif
   }
 
-  // ---- wgrad GEMMs (lin1..lin7) + split-K reduction
-  rc = launch_wgrad2(h, w.xstash, w.dystash, w.g_img, w.wg_partials, w.dweff, st, prof);
-  if (rc != DSDF_OK) return rc;
-
-  // ---- segmented (scene-contiguous) reductions.  Decoder gradient first (it is what a multi-GPU caller
-  // all-reduces: `grads_ready_event` is recorded as soon as `grads` is final, so the collective can run on a side
-  // stream under the latent-gradient kernels below and the latent Adam that follows), then the latent side.
+  // ---- segmented (scene-contiguous) reductions that need only what the dgrad chain (and the Eikonal passes) left
+  // behind: on the side stream, beside the wgrad GEMMs (they co-reside with the persistent wgrad CTAs: no shared
+  // memory, few registers).  Every kernel writes its own elements with plain stores, fixed summation orders.
   const float reg_coef = reg_lambda_ramp * (float)rows_per_seg * inv_n;
-  k_seg_colsum<<<dim3((unsigned)n_seg, 2), kHidden, 0, st>>>(w.tile_colsum, tiles_per_seg, w.seg_sum);
-  k_dw_latent<<<dim3(kHidden, 2), kLatent, 0, st>>>(w.seg_sum, table, (const long long*)seg_ids,
+  cudaStream_t sd = h->side;
+  CU(h, cudaEventRecord(h->ev_fork, st));
+  CU(h, cudaStreamWaitEvent(sd, h->ev_fork, 0));
+  k_seg_colsum<<<dim3((unsigned)n_seg, 2), kHidden, 0, sd>>>(w.tile_colsum, tiles_per_seg, w.seg_sum);
+  k_dw_latent<<<dim3(kHidden, 2), kLatent, 0, sd>>>(w.seg_sum, table, (const long long*)seg_ids,
                                                     (int)n_seg, w.dweff);
-  k_reduce_cta<<<16, kHidden, 0, st>>>(w.cta_partials, (int)bwd_grid, w.seg_sum, (int)n_seg,
+  k_reduce_cta<<<16, kHidden, 0, sd>>>(w.cta_partials, (int)bwd_grid, w.seg_sum, (int)n_seg,
                                       w.tile_partials, tiles, h->pl, grads, w.dweff, dw8_fwd ? fwd_ctas : 0,
                                       eik ? w.eik_corr : nullptr, n_corr, eik ? w.eik_tile : nullptr);
+  k_lat_grad_seg<<<(unsigned)n_seg, 1024, 0, sd>>>(w.seg_sum, h->weff, table,
+                                                      (const long long*)seg_ids, reg_coef,
+                                                      w.dlat_seg, w.seg_norm);
+  CU(h, cudaMemsetAsync(lat_grad, 0, (size_t)num_scenes * kLatent * 4, sd));
+  k_lat_grad_scatter<<<(unsigned)n_seg, kLatent, 0, sd>>>(w.dlat_seg, (const long long*)seg_ids, (int)n_seg, lat_grad);
+  k_loss<<<1, 1024, 0, sd>>>(w.tile_partials, tiles, inv_n, w.seg_norm, (int)n_seg, reg_coef, loss_out,
+                             eik ? w.eik_tile : nullptr, eikonal_lambda);
+  CU(h, cudaEventRecord(h->ev_join, sd));
+
+  // ---- wgrad GEMMs (lin1..lin7) + split-K reduction on the caller's stream
+  rc = launch_wgrad2(h, w.xstash, w.dystash, w.g_img, w.wg_partials, w.dweff, st, prof);
+  if (rc != DSDF_OK) return rc;
+  CU(h, cudaStreamWaitEvent(st, h->ev_join, 0));
+  // weight-norm backward over the complete effective-weight gradient; `grads` is final after it (a multi-GPU caller
+  // all-reduces it behind `grads_ready_event`)
   k_param_grads<<<(kScaleElems * 32 + 255) / 256, 256, 0, st>>>(w.dweff, params, h->pl, h->scale,
                                                                 h->inv_norm, grads);
   if (grads_ready_event) CU(h, cudaEventRecord((cudaEvent_t)grads_ready_event, st));
-  if (prof) prof_mark(h, st, 6);
-  k_lat_grad_seg<<<(unsigned)n_seg, 1024, 0, st>>>(w.seg_sum, h->weff, table,
-                                                      (const long long*)seg_ids, reg_coef,
-                                                      w.dlat_seg, w.seg_norm);
-  CU(h, cudaMemsetAsync(lat_grad, 0, (size_t)num_scenes * kLatent * 4, st));
-  k_lat_grad_scatter<<<(unsigned)n_seg, kLatent, 0, st>>>(w.dlat_seg, (const long long*)seg_ids, (int)n_seg, lat_grad);
-  k_loss<<<1, 1024, 0, st>>>(w.tile_partials, tiles, inv_n, w.seg_norm, (int)n_seg, reg_coef, loss_out,
-                             eik ? w.eik_tile : nullptr, eikonal_lambda);
-  if (prof) prof_mark(h, st, 7);
+  if (prof) { prof_mark(h, st, 6); prof_mark(h, st, 7); }
   CU(h, cudaGetLastError());
   return DSDF_OK;
 }
@@ -1335,17 +1351,15 @@ extern "C" int dsdf_clip_adam(dsdf_handle h, float* params, float* grads, float*
   cudaStream_t st = (cudaStream_t)stream;
   const int nb = 1024;
   float* part = scratch + 16;
-  if (max_norm > 0.f) {   // the reference computes the norm only when it clips (train_deep_sdf.py:780-782)
+  if (max_norm > 0.f)     // the reference computes the norm only when it clips (train_deep_sdf.py:780-782)
     k_sqnorm_partial<<<nb, 256, 0, st>>>(grads, n, part);
-    k_clip_coef<<<1, 256, 0, st>>>(part, nb, max_norm, scratch);
-  }
   const double bc1 = 1.0 - pow((double)beta1, (double)step);
   const double bc2 = 1.0 - pow((double)beta2, (double)step);
   const float step_size = (float)((double)lr / bc1);
   const float bc2_sqrt = (float)sqrt(bc2);
   const unsigned blocks = (unsigned)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
-  k_adam<<<blocks, 256, 0, st>>>(params, grads, exp_avg, exp_avg_sq, n, max_norm > 0.f ? scratch : nullptr, step_size,
-                                 bc2_sqrt, beta1, beta2, eps, max_norm > 0.f ? 1 : 0);
+  k_adam<<<blocks, 256, 0, st>>>(params, grads, exp_avg, exp_avg_sq, n, max_norm > 0.f ? part : nullptr, nb, max_norm,
+                                 scratch, step_size, bc2_sqrt, beta1, beta2, eps);
   CU(h, cudaGetLastError());
   return DSDF_OK;
 }

@@ -3,8 +3,8 @@
 //   k_rowscale_weff : scale[l][o] = g/||v||_row for weight-normalised layers, 1 otherwise
 //                  (nn.utils.weight_norm, reference networks/deep_sdf_decoder.py:49-53) and the fp32
 //                  effective weights in reference layout (read by the image builders and the small fp32 kernels)
-//   k_fold_fwd2  : bf16 forward K-step stream (layout.cuh w2_*), E steps included
-//   k_fold_dgrad2: bf16 dgrad K-step stream of W^T (layout.cuh dg2_*)
+//   k_fold_images: bf16 forward K-step stream (layout.cuh w2_*, E steps included), bf16 dgrad K-step stream of W^T
+//                  (layout.cuh dg2_*) and the fp32 xyz-column table, one launch
 #pragma once
 #include "layout.cuh"
 #include "ptx.cuh"
@@ -98,9 +98,9 @@ __device__ __forceinline__ void e_step_row(const float* weff, int l, int o, bool
 }
 
 // v2 forward K-step stream (layout.cuh): one thread per 16-byte chunk
-__global__ void k_fold_fwd2(const float* __restrict__ weff, const float* __restrict__ params,
-                            ParamLayout pl, uint8_t* __restrict__ img) {
-  const long long cidx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void fold_fwd2_chunk(long long cidx, const float* __restrict__ weff,
+                                                const float* __restrict__ params, const ParamLayout& pl,
+                                                uint8_t* __restrict__ img) {
   const long long total = (long long)kW2Steps * (kStepBytes / 16);
   if (cidx >= total) return;
   const int step = (int)(cidx / (kStepBytes / 16));
@@ -132,8 +132,8 @@ __global__ void k_fold_fwd2(const float* __restrict__ weff, const float* __restr
 }
 
 // v2 dgrad K-step stream (layout.cuh): one thread per 16-byte chunk
-__global__ void k_fold_dgrad2(const float* __restrict__ weff, uint8_t* __restrict__ img) {
-  const long long cidx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void fold_dgrad2_chunk(long long cidx, const float* __restrict__ weff,
+                                                  uint8_t* __restrict__ img) {
   const long long total = (long long)kDg2Steps * (kStepBytes / 16);
   if (cidx >= total) return;
   const int step = (int)(cidx / (kStepBytes / 16));
@@ -159,8 +159,7 @@ __global__ void k_fold_dgrad2(const float* __restrict__ weff, uint8_t* __restric
 
 // fp32 xyz columns of lin0 / lin4 as float4 rows (x, y, z, 0): wx[c] = W0[c, 256..258], wx[512 + c] = W4[c, 509..511]
 // (the Eikonal backward's per-row d s / d xyz = sum_c dY0[c] W0x[c] + dY4[c] W4x[c]).  1024 threads.
-__global__ void k_build_wx(const float* __restrict__ weff, float4* __restrict__ wx) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void build_wx_elem(int i, const float* __restrict__ weff, float4* __restrict__ wx) {
   if (i >= 2 * kHidden) return;
   const int l = i < kHidden ? 0 : kSkipLayer, c = i & (kHidden - 1);
   float v[3] = {0.f, 0.f, 0.f};
@@ -168,6 +167,24 @@ __global__ void k_build_wx(const float* __restrict__ weff, float4* __restrict__ 
   for (int e = 0; e < 3; ++e)
     if (xyz_col(l, e) >= 0) v[e] = weff_at(weff, l, c, xyz_col(l, e));
   wx[i] = make_float4(v[0], v[1], v[2], 0.f);
+}
+
+// The three images are independent given weff: ONE launch (256 threads), blocks [0, kFoldFwdBlocks) build the forward
+// stream, the next kFoldDgBlocks the dgrad stream, the last 4 the xyz-column table (ReLU family only).
+constexpr unsigned kFoldFwdBlocks = (unsigned)(((long long)kW2Steps * (kStepBytes / 16) + 255) / 256);
+constexpr unsigned kFoldDgBlocks = (unsigned)(((long long)kDg2Steps * (kStepBytes / 16) + 255) / 256);
+constexpr unsigned kFoldWxBlocks = 4;
+__global__ void __launch_bounds__(256) k_fold_images(const float* __restrict__ weff, const float* __restrict__ params,
+                                                     ParamLayout pl, uint8_t* __restrict__ w2_img,
+                                                     uint8_t* __restrict__ dg2_img, float4* __restrict__ wx) {
+  const unsigned b = blockIdx.x;
+  if (b < kFoldFwdBlocks) {
+    fold_fwd2_chunk((long long)b * 256 + threadIdx.x, weff, params, pl, w2_img);
+  } else if (b < kFoldFwdBlocks + kFoldDgBlocks) {
+    fold_dgrad2_chunk((long long)(b - kFoldFwdBlocks) * 256 + threadIdx.x, weff, dg2_img);
+  } else {
+    build_wx_elem((int)((b - kFoldFwdBlocks - kFoldDgBlocks) * 256 + threadIdx.x), weff, wx);
+  }
 }
 
 // Fold mode: per-segment E steps of lin0 / lin4 with bias' = b + W[:, latent] z_seg (fp32).

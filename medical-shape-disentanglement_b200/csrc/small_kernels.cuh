@@ -425,27 +425,23 @@ __global__ void k_sqnorm_partial(const float* __restrict__ g, long long n, float
   const float t = block_sum_256(s, sh);
   if (threadIdx.x == 0) part[blockIdx.x] = t;
 }
-// scal[0] = ||g||_2, scal[1] = clip coefficient
-__global__ void k_clip_coef(const float* __restrict__ part, int n_part, float max_norm,
-                            float* __restrict__ scal) {
-  __shared__ float sh[8];
-  float s = 0.f;
-  for (int i = threadIdx.x; i < n_part; i += blockDim.x) s += part[i];
-  const float t = block_sum_256(s, sh);
-  if (threadIdx.x == 0) {
-    const float nrm = sqrtf(t);
-    scal[0] = nrm;
-    float coef = 1.f;
-    if (max_norm > 0.f) coef = fminf(1.f, max_norm / (nrm + 1e-6f));
-    scal[1] = coef;
-  }
-}
-// torch.optim.Adam (amsgrad=False, wd=0): algorithmic traffic 28 B/param (r: p,g,m,v  w: p,m,v)
+// torch.optim.Adam (amsgrad=False, wd=0): algorithmic traffic 28 B/param (r: p,g,m,v  w: p,m,v).
+// part != nullptr: clip_grad_norm_ first -- every block sums the n_part squared-norm partials in the same fixed order
+// (bit-identical in all blocks), coef = min(1, max_norm / (||g|| + 1e-6)), the gradient is scaled in place as torch does;
+// block 0 publishes scal[0] = ||g||_2, scal[1] = coef.
 __global__ void k_adam(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
-                       float* __restrict__ v, long long n, const float* __restrict__ coef_ptr,
-                       float step_size, float bc2_sqrt, float b1, float b2, float eps,
-                       int write_back_grad) {
-  const float coef = coef_ptr ? coef_ptr[1] : 1.f;
+                       float* __restrict__ v, long long n, const float* __restrict__ part, int n_part,
+                       float max_norm, float* __restrict__ scal, float step_size, float bc2_sqrt, float b1,
+                       float b2, float eps) {
+  float coef = 1.f;
+  if (part) {
+    __shared__ float sh[8];
+    float s = 0.f;
+    for (int i = threadIdx.x; i < n_part; i += blockDim.x) s += part[i];
+    const float nrm = sqrtf(block_sum_256(s, sh));          // the same value in every thread of every block
+    coef = fminf(1.f, max_norm / (nrm + 1e-6f));
+    if (blockIdx.x == 0 && threadIdx.x == 0) { scal[0] = nrm; scal[1] = coef; }
+  }
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
        i += (long long)gridDim.x * blockDim.x) {
     const float gi = g[i] * coef;
@@ -454,7 +450,7 @@ __global__ void k_adam(float* __restrict__ p, float* __restrict__ g, float* __re
     m[i] = mi;
     v[i] = vi;
     p[i] -= step_size * (mi / (sqrtf(vi) / bc2_sqrt + eps));
-    if (write_back_grad) g[i] = gi;   // clip_grad_norm_ scales .grad in place
+    if (part) g[i] = gi;   // clip_grad_norm_ scales .grad in place
   }
 }
 
