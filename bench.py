@@ -564,6 +564,43 @@ def main():
                      "note": "same step, device-resident inputs, run long enough for clocks/power to settle"}
     sampler.stop()
 
+    # ---------------- strong scaling (N > 1): the SAME global batch split over the ranks ----------------
+    # The driver's 1/2/4/8 run is the weak line above (ScenesPerBatch per GPU); this block times, in the same process,
+    # the partition SURVEY.md 8(e) names: global ScenesPerBatch split over the ranks (C2: 8 scenes = 131 072 rows per rank
+    # at W = 8), so that one SCALE file carries both curves.  Also times the decoder-gradient all-reduce itself.
+    strong_line = None
+    if world > 1 and not strong:
+        b_s = ddist.local_batch(wl["b"], rank, world)
+        if b_s >= 1:
+            n_total_s = wl["b"] * P
+            ids_s = [torch.randperm(n_local, generator=g)[:b_s].to(dev) for _ in range(4)]
+            sdf_s = [data_dev[torch.randint(0, pool, (b_s,), generator=g).to(dev)].contiguous() for _ in range(4)]
+            for i in range(W):
+                tr.step(sdf_s[i % 4], ids_s[i % 4], epoch=10, n_total=n_total_s)
+            KS = max(K, 50)
+            tr.time_comm = True
+            tr.comm_events.clear()
+            barrier()
+            q0 = torch.cuda.Event(enable_timing=True); q1 = torch.cuda.Event(enable_timing=True)
+            q0.record()
+            for i in range(KS):
+                tr.step(sdf_s[i % 4], ids_s[i % 4], epoch=10, n_total=n_total_s)
+            q1.record()
+            barrier()
+            tr.time_comm = False
+            t = torch.tensor([q0.elapsed_time(q1)], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            s_ms = float(t.item()) / KS
+            ar = sorted(a.elapsed_time(b) for a, b in tr.comm_events)
+            strong_line = {"scaling": "strong", "value": n_total_s / (s_ms * 1e-3), "unit": UNIT, "ms_per_step": s_ms,
+                           "steps": KS, "scenes_per_step_per_rank": b_s, "rows_per_step_per_gpu": b_s * P,
+                           "rows_per_step_global": n_total_s,
+                           "allreduce_ms_median_rank0": ar[len(ar) // 2] if ar else None,
+                           "allreduce_bytes": int(tr.grads.numel()) * 4,
+                           "note": "same binary, same process: global ScenesPerBatch split over the ranks; the all-reduce runs on "
+                                   "a side stream behind the grads-ready event, under the latent Adam; its duration is measured "
+                                   "with CUDA events on that stream (includes waiting for the slowest rank)"}
+
     # ---------------- replicas stay identical (N > 1): all-gather a parameter checksum ----------------
     replicas_identical = None
     if world > 1:
@@ -639,7 +676,7 @@ def main():
                     "d2h_bytes_per_step": 16, "ms_per_step": e2e_ms / K},
             "gpu_launches": launches_per_step * K,
             "roofline": roofline, "roofline_small": roofline_small, "sustained": sustained,
-            "replicas_identical": replicas_identical,
+            "replicas_identical": replicas_identical, "strong_scaling": strong_line,
             "cpu_baseline": cpu_baseline, "clocks": clocks, "extras": extras,
             "loss": float(st["sdf_loss"].item()),
         }

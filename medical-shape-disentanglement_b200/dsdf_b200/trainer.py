@@ -130,6 +130,8 @@ class FusedTrainer:
         # (event recorded inside dsdf_train_fwd_bwd), under the latent-gradient kernels and the latent Adam
         self._comm_stream = None
         self._grads_ready = None
+        self.time_comm = False                  # bench.py: record CUDA events around the collective
+        self.comm_events = []
         if process_group is not None and torch.distributed.get_world_size(process_group) > 1:
             self._comm_stream = torch.cuda.Stream(device=dev)
             self._grads_ready = torch.cuda.Event()
@@ -260,6 +262,9 @@ class FusedTrainer:
             # the rest of the backward (latent-gradient reduction) and the latent Adam below.
             with torch.cuda.stream(self._comm_stream):
                 self._comm_stream.wait_event(self._grads_ready)
+                if self.time_comm:                             # measurement only (bench.py): collective start / end
+                    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+                    e0.record(self._comm_stream)
                 work = torch.distributed.all_reduce(self.grads, op=torch.distributed.ReduceOp.SUM, group=self.pg,
                                                     async_op=True)
         with torch.cuda.device(self.device):
@@ -271,6 +276,9 @@ class FusedTrainer:
             if work is not None:
                 with torch.cuda.stream(self._comm_stream):
                     work.wait()                               # comm stream waits for the collective ...
+                    if self.time_comm:
+                        e1.record(self._comm_stream)
+                        self.comm_events.append((e0, e1))
                 cur.wait_stream(self._comm_stream)            # ... and the step's stream for the comm stream
             _lib.check(L.dsdf_clip_adam(
                 h, flat.data_ptr(), self.grads.data_ptr(), self.exp_avg.data_ptr(),
