@@ -234,11 +234,12 @@ def run_extras(dec, tr, dev, pk, wl, args):
     (grid pts/s decode, configs[3]), the latent-only optimisation of reconstruct.py (configs[3]), the SIREN
     variant's fused step (configs[4]), the step with the Eikonal term every shipped Stage-1 spec enables, and the
     OAI-ZIB-shaped config (configs[2]).  CUDA events on the launching stream, inputs resident."""
+    import ctypes as C
     import random
     import torch
     import dsdf_b200
     import dsdf_b200.siren as siren_mod
-    from dsdf_b200 import synth
+    from dsdf_b200 import _lib, synth
     out = {}
     burst = float(pk["bf16_tflops"])
     # ---- create_mesh grid decode, N = 256 (deep_sdf/mesh.py:32-71), one latent
@@ -258,6 +259,39 @@ def run_extras(dec, tr, dev, pk, wl, args):
     sdf_host = dsdf_b200.create_mesh_sdf(dec, lat, 256)          # incl. the 67 MB D2H, drained slab by slab
     out["grid_decode_256"]["create_mesh_sdf_wall_ms_incl_d2h"] = (time.perf_counter() - t0) * 1e3
     del sdf_host
+    # ---- create_mesh end to end on the device (mesh.py:21-93 + 96-165): decode + iso-surface extraction; only the mesh
+    # leaves the GPU.  A sphere-like SDF of the same grid stands in for the level set (random-init weights have none).
+    ax = torch.linspace(-1, 1, 256, device=dev)
+    vol = (ax[:, None, None] ** 2 + ax[None, :, None] ** 2 + ax[None, None, :] ** 2).sqrt() - 0.6
+    dsdf_b200.marching_cubes(vol, 0.0, (2.0 / 255,) * 3)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    dec.decode_grid(lat, 256, out=buf)
+    v_, f_ = dsdf_b200.marching_cubes(vol, 0.0, (2.0 / 255,) * 3)
+    v_h, f_h = v_.cpu(), f_.cpu()
+    wall = (time.perf_counter() - t0) * 1e3
+    n_pts = 256 ** 3
+    L_ = _lib.lib()
+    efl = torch.empty(n_pts, dtype=torch.uint8, device=dev); cnt = torch.empty(n_pts, dtype=torch.int64, device=dev)
+    stp = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    ms_cls = _time_ms(lambda: L_.dsdf_mc_classify(vol.data_ptr(), 256, 256, 256, 0.0, efl.data_ptr(), cnt.data_ptr(), stp), 10)
+    scan = torch.cumsum(cnt, 0)
+    ms_emit = _time_ms(lambda: L_.dsdf_mc_emit(vol.data_ptr(), 256, 256, 256, 0.0, 1.0, 1.0, 1.0, efl.data_ptr(), scan.data_ptr(),
+                                                v_.data_ptr(), f_.data_ptr(), stp), 10)
+    ms_scan = _time_ms(lambda: torch.cumsum(cnt, 0), 10)
+    hbm = float(pk["hbm_gbs"])
+    out["create_mesh_256_on_device"] = {
+        "wall_ms_decode_plus_extraction_plus_mesh_d2h": wall, "vertices": int(v_h.shape[0]), "faces": int(f_h.shape[0]),
+        "mesh_bytes_to_host": int(v_h.numel() * 4 + f_h.numel() * 4), "grid_bytes_the_reference_moves": n_pts * 4,
+        "k_mc_classify": {"us": ms_cls * 1e3, "algorithmic_bytes": n_pts * (4 + 1 + 8),
+                          "gb_s": n_pts * 13 / (ms_cls * 1e-3) / 1e9, "frac_of_hbm_peak": n_pts * 13 / (ms_cls * 1e-3) / 1e9 / hbm},
+        "prefix_sum_torch_cumsum_int64": {"us": ms_scan * 1e3},
+        "k_mc_emit": {"us": ms_emit * 1e3, "algorithmic_bytes": n_pts * (4 + 1 + 8) + int(v_h.numel() * 4 + f_h.numel() * 4),
+                      "gb_s": (n_pts * 13 + v_h.numel() * 4 + f_h.numel() * 4) / (ms_emit * 1e-3) / 1e9,
+                      "frac_of_hbm_peak": (n_pts * 13 + v_h.numel() * 4 + f_h.numel() * 4) / (ms_emit * 1e-3) / 1e9 / hbm},
+        "note": "bytes: grid 4 B/pt read + edge flags 1 B/pt + packed counts / scan 8 B/pt per pass (+ the mesh written by emit); "
+                "neighbour reads hit L1/L2"}
+    del vol, efl, cnt, scan
     # ---- reconstruct.py: 800 Adam iterations x 8000 samples, frozen decoder (CLI defaults :262-263,345-356)
     shapes = []
     for s_ in range(64):

@@ -250,6 +250,23 @@ int dsdf_debug_read(dsdf_handle h, uint64_t* out, int32_t max_words);
 int dsdf_selftest_gemm(int32_t kind, const void* a_img, const void* b_img, float* d_out,
                        void* stream);
 
+/* ---- iso-surface extraction on the device (replaces the skimage.measure.marching_cubes call of the reference's
+ * deep_sdf/mesh.py:119-121 `convert_sdf_samples_to_ply`; level / spacing as there).  No handle: plain kernels.
+ * sdf = [nx, ny, nz] fp32, x slowest (the reference's sdf_values.reshape(N, N, N)).  Two passes:
+ *   dsdf_mc_classify -> eflags[n] (bits 0..2: the point's +x/+y/+z edge crosses `level`) and
+ *                       counts[n] = crossing edges | triangles of the point's cube << 32;
+ *   the caller takes ONE inclusive prefix sum `scan` over counts (totals = scan[n-1]: V = low 32 bits, T = high),
+ *   dsdf_mc_emit     -> verts[V,3] (grid index x spacing, linear interpolation along the edge; add the voxel-grid
+ *                       origin as mesh.py:127-130 does) and faces[T,3] (int32 indices into verts).
+ * inside = value < level; triangle normals point towards increasing values.  Vertex order: by owning grid point
+ * (linear index), then edge axis.  The triangulation table is derived in tools/gen_mc_tables.py (face-consistent,
+ * crack-free; not Lewiner's table -- see mc_kernels.cuh). */
+int dsdf_mc_classify(const float* sdf, int32_t nx, int32_t ny, int32_t nz, float level, uint8_t* eflags,
+                     int64_t* counts, void* stream);
+int dsdf_mc_emit(const float* sdf, int32_t nx, int32_t ny, int32_t nz, float level, float spacing_x,
+                 float spacing_y, float spacing_z, const uint8_t* eflags, const int64_t* scan, float* verts,
+                 int32_t* faces, void* stream);
+
 /* Diagnostics: tensor-pipe issue-rate micro-benchmark (iters tcgen05.mma M=128 N=256 K=16 on n_cta
  * CTAs); cycles_host[n_cta] = cycles per CTA.  kind bit0: SWIZZLE_128B B operand, bit1: commit per
  * MMA, bit2: N=128.  Synchronises the device. */

@@ -19,6 +19,7 @@
 #include "fold_kernels.cuh"
 #include "fwd3_kernel.cuh"
 #include "layout.cuh"
+#include "mc_kernels.cuh"
 #include "recon_kernels.cuh"
 #include "small_kernels.cuh"
 #include "wgrad2_kernel.cuh"
@@ -1361,6 +1362,40 @@ extern "C" int dsdf_clip_adam(dsdf_handle h, float* params, float* grads, float*
   k_adam<<<blocks, 256, 0, st>>>(params, grads, exp_avg, exp_avg_sq, n, max_norm > 0.f ? part : nullptr, nb, max_norm,
                                  scratch, step_size, bc2_sqrt, beta1, beta2, eps);
   CU(h, cudaGetLastError());
+  return DSDF_OK;
+}
+
+// ------------------------------------------------------------------------------- iso-surface extraction
+static int mc_check(const float* sdf, int32_t nx, int32_t ny, int32_t nz) {
+  if (!sdf) { g_err = "null argument"; return DSDF_EINVAL; }
+  if (nx < 2 || ny < 2 || nz < 2) { g_err = "marching cubes needs at least 2 grid points per axis"; return DSDF_EINVAL; }
+  if ((long long)nx * ny * nz > (1ll << 31)) { g_err = "grid too large (more than 2^31 points)"; return DSDF_EINVAL; }
+  return DSDF_OK;
+}
+extern "C" int dsdf_mc_classify(const float* sdf, int32_t nx, int32_t ny, int32_t nz, float level, uint8_t* eflags,
+                                int64_t* counts, void* stream) {
+  int rc = mc_check(sdf, nx, ny, nz);
+  if (rc != DSDF_OK) return rc;
+  if (!eflags || !counts) { g_err = "null argument"; return DSDF_EINVAL; }
+  const long long n = (long long)nx * ny * nz;
+  McGrid g{nx, ny, nz, level};
+  k_mc_classify<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(sdf, g, eflags, (long long*)counts);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { g_err = cudaGetErrorString(e); return DSDF_ECUDA; }
+  return DSDF_OK;
+}
+extern "C" int dsdf_mc_emit(const float* sdf, int32_t nx, int32_t ny, int32_t nz, float level, float spacing_x,
+                            float spacing_y, float spacing_z, const uint8_t* eflags, const int64_t* scan, float* verts,
+                            int32_t* faces, void* stream) {
+  int rc = mc_check(sdf, nx, ny, nz);
+  if (rc != DSDF_OK) return rc;
+  if (!eflags || !scan) { g_err = "null argument"; return DSDF_EINVAL; }
+  const long long n = (long long)nx * ny * nz;
+  McGrid g{nx, ny, nz, level};
+  k_mc_emit<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(sdf, g, spacing_x, spacing_y, spacing_z, eflags,
+                                                                          (const long long*)scan, verts, faces);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { g_err = cudaGetErrorString(e); return DSDF_ECUDA; }
   return DSDF_OK;
 }
 

@@ -22,7 +22,7 @@ EXPORTS = [
     "dsdf_dense_workspace_bytes", "dsdf_dense_forward_train", "dsdf_dense_backward",
     "dsdf_segments_forward_train", "dsdf_segments_backward", "dsdf_set_dropout", "dsdf_dropout_keep", "dsdf_reconstruct_workspace_bytes", "dsdf_reconstruct",
     "dsdf_selftest_gemm", "dsdf_profile_enable", "dsdf_profile_read", "dsdf_debug_read", "dsdf_selftest_mma_rate", "dsdf_debug_hang_buffer",
-    "dsdf_debug_progress_buffer",
+    "dsdf_debug_progress_buffer", "dsdf_mc_classify", "dsdf_mc_emit",
 ]
 
 
@@ -121,6 +121,10 @@ def lib(arch: str = "deep_sdf_decoder"):
     L.dsdf_debug_hang_buffer.restype = C.c_int
     L.dsdf_debug_progress_buffer.argtypes = [C.POINTER(C.POINTER(C.c_uint32))]
     L.dsdf_debug_progress_buffer.restype = C.c_int
+    L.dsdf_mc_classify.argtypes = [vp, i32, i32, i32, f32, vp, vp, vp]
+    L.dsdf_mc_classify.restype = C.c_int
+    L.dsdf_mc_emit.argtypes = [vp, i32, i32, i32, f32, f32, f32, f32, vp, vp, vp, vp, vp]
+    L.dsdf_mc_emit.restype = C.c_int
     _libs[arch] = L
     return L
 

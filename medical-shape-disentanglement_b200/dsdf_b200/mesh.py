@@ -4,16 +4,26 @@ expressions, including the true-division shear of mesh.py:46-47), the latent is 
 tile instead of expand+cat per chunk, and the N^3 floats drain to pinned host memory slab by slab
 under the kernel instead of one H2D + one D2H per 2^18-point chunk.
 
-Marching cubes / PLY writing (mesh.py:96-165) stay on the host in the reference's own code
-(skimage / plyfile are not available in this image): `create_mesh_sdf` returns exactly the
-`sdf_values.reshape(N, N, N)` tensor that `convert_sdf_samples_to_ply` consumes (mesh.py:70-71).
+Marching cubes + PLY writing (mesh.py:96-165): `marching_cubes` extracts the level set ON THE DEVICE
+(csrc/mc_kernels.cuh through dsdf_mc_classify / dsdf_mc_emit), so `create_mesh` moves vertices and faces to the host
+instead of the 4 N^3-byte grid; `convert_sdf_samples_to_ply` keeps the reference's signature, vertex transform
+(origin + verts, / scale, - offset) and writes the same binary little-endian PLY layout plyfile produces
+(vertex: float x, y, z; face: list uchar int vertex_indices).  `create_mesh_sdf` still returns the
+`sdf_values.reshape(N, N, N)` tensor for callers that want the grid itself (mesh.py:70-71).
 """
 from __future__ import annotations
 
-from typing import Optional
+import ctypes as C
+import logging
+import os
+import tempfile
+import time
+from typing import Optional, Tuple
 
+import numpy as np
 import torch
 
+from . import _lib
 from .decoder import Decoder
 
 
@@ -73,3 +83,123 @@ def decode_grid_sharded(decoder: Decoder, latent_vec: torch.Tensor, N: int, rank
     hi = (N * (rank + 1) // world_size) * N * N
     dev = next(decoder.parameters()).device
     return lo, hi, decoder.decode_grid(latent_vec.to(dev), N, lo, hi)
+
+
+# ---------------------------------------------------------------------------------------------- iso-surface
+@torch.no_grad()
+def marching_cubes(volume: torch.Tensor, level: float = 0.0,
+                   spacing: Tuple[float, float, float] = (1.0, 1.0, 1.0)) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Level-set extraction of a [nx, ny, nz] fp32 CUDA grid on the device: (verts [V,3] fp32, faces [T,3] int32),
+    both CUDA tensors.  verts are in grid-index units times `spacing`, as skimage.measure.marching_cubes returns
+    them (mesh.py:119-121); an empty surface raises ValueError like skimage does ("Surface level must be within
+    volume data range", caught by the reference at mesh.py:122-124)."""
+    if not volume.is_cuda:
+        raise _lib.DsdfError("marching_cubes needs the grid on a CUDA device (there is no CPU path)")
+    vol = volume.contiguous().float()
+    if vol.dim() != 3:
+        raise ValueError("volume must be 3-D")
+    nx, ny, nz = (int(v) for v in vol.shape)
+    L = _lib.lib()
+    n = nx * ny * nz
+    dev = vol.device
+    with torch.cuda.device(dev):
+        st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        eflags = torch.empty(n, dtype=torch.uint8, device=dev)
+        counts = torch.empty(n, dtype=torch.int64, device=dev)
+        _lib.check(L.dsdf_mc_classify(vol.data_ptr(), nx, ny, nz, float(level), eflags.data_ptr(), counts.data_ptr(),
+                                      st), None, L)
+        scan = torch.cumsum(counts, 0)                 # one prefix sum: vertex offsets (low 32 bits) | face offsets
+        total = int(scan[-1].item())                   # the only host sync: output sizes
+        n_v, n_t = total & 0xFFFFFFFF, total >> 32
+        if n_v == 0 or n_t == 0:
+            raise ValueError("Surface level must be within volume data range.")
+        verts = torch.empty(n_v, 3, dtype=torch.float32, device=dev)
+        faces = torch.empty(n_t, 3, dtype=torch.int32, device=dev)
+        _lib.check(L.dsdf_mc_emit(vol.data_ptr(), nx, ny, nz, float(level), float(spacing[0]), float(spacing[1]),
+                                  float(spacing[2]), eflags.data_ptr(), scan.data_ptr(), verts.data_ptr(),
+                                  faces.data_ptr(), st), None, L)
+    return verts, faces
+
+
+def write_ply(filename: str, verts: np.ndarray, faces: np.ndarray) -> None:
+    """Binary little-endian PLY with the two elements the reference writes through plyfile (mesh.py:143-156):
+    vertex (float x, y, z) and face (list uchar int vertex_indices)."""
+    verts = np.ascontiguousarray(verts, dtype="<f4")
+    faces = np.ascontiguousarray(faces, dtype="<i4")
+    header = ("ply\nformat binary_little_endian 1.0\n"
+              f"element vertex {verts.shape[0]}\nproperty float x\nproperty float y\nproperty float z\n"
+              f"element face {faces.shape[0]}\nproperty list uchar int vertex_indices\nend_header\n")
+    rec = np.empty(faces.shape[0], dtype=[("n", "u1"), ("v", "<i4", (3,))])
+    rec["n"] = 3
+    rec["v"] = faces
+    with open(filename, "wb") as f:
+        f.write(header.encode("ascii"))
+        f.write(verts.tobytes())
+        f.write(rec.tobytes())
+
+
+def read_ply(filename: str) -> Tuple[np.ndarray, np.ndarray]:
+    """Reader for the layout `write_ply` (and plyfile, for these two elements) produces."""
+    with open(filename, "rb") as f:
+        n_v = n_f = None
+        while True:
+            line = f.readline().decode("ascii").strip()
+            if line.startswith("element vertex"):
+                n_v = int(line.split()[-1])
+            elif line.startswith("element face"):
+                n_f = int(line.split()[-1])
+            elif line == "end_header":
+                break
+        verts = np.frombuffer(f.read(12 * n_v), dtype="<f4").reshape(n_v, 3)
+        rec = np.frombuffer(f.read(13 * n_f), dtype=[("n", "u1"), ("v", "<i4", (3,))])
+    return verts.copy(), rec["v"].copy()
+
+
+def convert_sdf_samples_to_ply(pytorch_3d_sdf_tensor: torch.Tensor, voxel_grid_origin, voxel_size: float,
+                               ply_filename_out: str, offset=None, scale=None, device=None) -> bool:
+    """Reference signature (mesh.py:96-103).  The grid may live on the host (as the reference passes it) or already
+    on the GPU; extraction runs on the device, the vertex transform of mesh.py:127-136 on the [V,3] result."""
+    start_time = time.time()
+    vol = pytorch_3d_sdf_tensor
+    if not vol.is_cuda:
+        vol = vol.to(device if device is not None else "cuda")
+    try:
+        verts, faces = marching_cubes(vol, level=0.0, spacing=(voxel_size,) * 3)
+    except ValueError as e:
+        logging.error(f"[create_mesh] Caught marching cubes error: {e}.")
+        return False
+    origin = torch.tensor([float(voxel_grid_origin[0]), float(voxel_grid_origin[1]), float(voxel_grid_origin[2])],
+                          dtype=torch.float32, device=verts.device)
+    mesh_points = verts + origin                       # voxel -> camera coordinates (mesh.py:127-130)
+    if scale is not None:
+        mesh_points = mesh_points / scale
+    if offset is not None:
+        mesh_points = mesh_points - torch.as_tensor(offset, dtype=torch.float32, device=verts.device)
+    write_ply(ply_filename_out, mesh_points.cpu().numpy(), faces.cpu().numpy())
+    logging.debug("[create_mesh] converting to ply format and writing to file took {} s".format(time.time() - start_time))
+    return True
+
+
+@torch.no_grad()
+def create_mesh(decoder: Decoder, latent_vec: torch.Tensor, filename: Optional[str] = None, N: int = 512,
+                max_batch: int = 32 ** 3, offset=None, scale=None, return_trimesh: bool = False):
+    """Reference signature (mesh.py:21).  Grid decode and iso-surface extraction both on the device; writes
+    `filename + ".ply"` like the reference.  return_trimesh=True returns (verts, faces) numpy arrays -- trimesh is not
+    a dependency of this package; wrap them with trimesh.Trimesh(verts, faces) where it is installed."""
+    start = time.time()
+    voxel_origin = [-1, -1, -1]
+    voxel_size = 2.0 / (N - 1)
+    sdf = create_mesh_sdf(decoder, latent_vec, N, max_batch, to_cpu=False)
+    logging.debug("[create_mesh] sampling takes: %f" % (time.time() - start))
+    tmp = None
+    ply = filename
+    if not ply:
+        tmp = tempfile.TemporaryDirectory()
+        ply = os.path.join(tmp.name, "create_mesh_ply")
+    ok = convert_sdf_samples_to_ply(sdf, voxel_origin, voxel_size, ply + ".ply", offset, scale)
+    out = None
+    if return_trimesh and ok:
+        out = read_ply(ply + ".ply")
+    if tmp is not None:
+        tmp.cleanup()
+    return out
