@@ -267,6 +267,34 @@ int dsdf_mc_emit(const float* sdf, int32_t nx, int32_t ny, int32_t nz, float lev
                  float spacing_y, float spacing_z, const uint8_t* eflags, const int64_t* scan, float* verts,
                  int32_t* faces, void* stream);
 
+/* ---- SDF-sample generation on the device: CUDA restatement of the reference's src/PreprocessMesh.cpp (its OpenGL path
+ * needs a graphics stack; this needs none).  No handle: plain kernels on raw device pointers.
+ *  dsdf_rasterize_views: PreprocessMesh.cpp:443-477 + src/ShaderProgram.cpp -- orthographic 400 x 400 rasterisation of the
+ *     (already centred) mesh from n_views camera poses; views = [n_views][12] rows of [R | t] (camera = R p + t, the
+ *     ModelViewLookAt matrices); zbuf = n_views * 160000 uint64 scratch.  out_vert / out_norm [n_views][400][400][4] in
+ *     the x-major order ValidPointsFromIm walks (src/Utils.cpp:28-43): (x, y, z, triangle id + 1) and the flat normal
+ *     turned towards the camera; valid[...] = 1 where the reference's w != 0.  Compact with `valid` to get
+ *     point_verts / point_normals.
+ *  dsdf_sample_points: SampleFromSurface (:22-87) + the sample cloud of SampleSDFNearSurface (:104-135): n_surf surface
+ *     points (area CDF `cdf[n_faces]` = inclusive sums of src/Utils.cpp:70-91 TriangleArea), two Gaussian perturbations
+ *     each (std dev stdv1, stdv2), then n_rand uniform points in the cube of side cube_dim; Philox stream keyed by seed
+ *     (the reference seeds from std::random_device).  xyz [2 n_surf + n_rand][3]; surf_out [n_surf][3] or NULL.
+ *  dsdf_knn_sdf: SampleSDFNearSurface :137-172 -- for each xyz row the 11 nearest of the n_pts visible points (exact),
+ *     |n . ray| if closer than stdv else |ray| from the nearest, sign by unanimous vote; sdf_out = NaN where the vote is
+ *     split (the reference drops the sample).  pts / normals are float4 rows; nn_out [n][11] or NULL.
+ *  dsdf_gather_windows: deep_sdf/data.py:112-136 for a batch of HBM-resident scenes: out[s] = cat(pos[ws:ws+half],
+ *     neg[wn:wn+half]) from samples (float4 rows), base[s] = {pos row 0, neg row 0}, win[s] = {ws, wn}. */
+int dsdf_rasterize_views(const float* verts, int64_t n_verts, const int32_t* faces, int64_t n_faces,
+                         const float* views, int32_t n_views, uint64_t* zbuf, float* out_vert, float* out_norm,
+                         uint8_t* valid, void* stream);
+int dsdf_sample_points(const float* verts, const int32_t* faces, const float* cdf, int64_t n_faces, int64_t n_surf,
+                       int64_t n_rand, float stdv1, float stdv2, float cube_dim, uint64_t seed, float* xyz,
+                       float* surf_out, void* stream);
+int dsdf_knn_sdf(const float* xyz, int64_t n, const float* pts, const float* normals, int64_t n_pts, float stdv,
+                 float* sdf_out, int32_t* nn_out, void* stream);
+int dsdf_gather_windows(const float* samples, const int64_t* base, const int64_t* win, int64_t n_scenes, int64_t half,
+                        float* out, void* stream);
+
 /* Diagnostics: tensor-pipe issue-rate micro-benchmark (iters tcgen05.mma M=128 N=256 K=16 on n_cta
  * CTAs); cycles_host[n_cta] = cycles per CTA.  kind bit0: SWIZZLE_128B B operand, bit1: commit per
  * MMA, bit2: N=128.  Synchronises the device. */

@@ -21,6 +21,7 @@
 #include "layout.cuh"
 #include "mc_kernels.cuh"
 #include "recon_kernels.cuh"
+#include "sampler_kernels.cuh"
 #include "small_kernels.cuh"
 #include "wgrad2_kernel.cuh"
 #ifdef DSDF_DIAG_BUILD   // diagnostics variant only (build.py DSDF_BUILD_VARIANT): descriptor self-tests, MMA-rate probe
@@ -1396,6 +1397,58 @@ extern "C" int dsdf_mc_emit(const float* sdf, int32_t nx, int32_t ny, int32_t nz
                                                                           (const long long*)scan, verts, faces);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { g_err = cudaGetErrorString(e); return DSDF_ECUDA; }
+  return DSDF_OK;
+}
+
+// ------------------------------------------------------------------------------- SDF-sample generation
+#define MC_CU(expr)                                                                   \
+  do {                                                                                \
+    cudaError_t _e = (expr);                                                          \
+    if (_e != cudaSuccess) { g_err = cudaGetErrorString(_e); return DSDF_ECUDA; }     \
+  } while (0)
+extern "C" int dsdf_rasterize_views(const float* verts, int64_t n_verts, const int32_t* faces, int64_t n_faces,
+                                    const float* views, int32_t n_views, uint64_t* zbuf, float* out_vert,
+                                    float* out_norm, uint8_t* valid, void* stream) {
+  if (!verts || !faces || !views || !zbuf || !out_vert || !out_norm || !valid) { g_err = "null argument"; return DSDF_EINVAL; }
+  if (n_verts <= 0 || n_faces <= 0 || n_views <= 0 || n_faces > (1ll << 31) - 2) { g_err = "empty mesh / bad sizes"; return DSDF_EINVAL; }
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t px = (size_t)n_views * kRastW * kRastH;
+  MC_CU(cudaMemsetAsync(zbuf, 0xFF, px * 8, st));
+  k_rast_draw<<<dim3((unsigned)((n_faces + 127) / 128), (unsigned)n_views), 128, 0, st>>>(verts, faces, (int)n_faces, views,
+                                                                                       (unsigned long long*)zbuf);
+  k_rast_resolve<<<dim3((kRastW * kRastH + 255) / 256, (unsigned)n_views), 256, 0, st>>>(
+      verts, faces, views, (const unsigned long long*)zbuf, (float4*)out_vert, (float4*)out_norm, valid);
+  MC_CU(cudaGetLastError());
+  return DSDF_OK;
+}
+extern "C" int dsdf_sample_points(const float* verts, const int32_t* faces, const float* cdf, int64_t n_faces,
+                                  int64_t n_surf, int64_t n_rand, float stdv1, float stdv2, float cube_dim, uint64_t seed,
+                                  float* xyz, float* surf_out, void* stream) {
+  if (!verts || !faces || !cdf || !xyz) { g_err = "null argument"; return DSDF_EINVAL; }
+  if (n_faces <= 0 || n_surf < 0 || n_rand < 0 || n_surf + n_rand == 0) { g_err = "bad sizes"; return DSDF_EINVAL; }
+  const long long n = n_surf + n_rand;
+  k_sample_points<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      verts, faces, cdf, (int)n_faces, n_surf, n_rand, stdv1, stdv2, cube_dim, (uint32_t)seed, (uint32_t)(seed >> 32), xyz,
+      surf_out);
+  MC_CU(cudaGetLastError());
+  return DSDF_OK;
+}
+extern "C" int dsdf_knn_sdf(const float* xyz, int64_t n, const float* pts, const float* normals, int64_t n_pts, float stdv,
+                            float* sdf_out, int32_t* nn_out, void* stream) {
+  if (!xyz || !pts || !normals || !sdf_out) { g_err = "null argument"; return DSDF_EINVAL; }
+  if (n <= 0 || n_pts <= 0 || n_pts > (1ll << 31) - 2) { g_err = "bad sizes"; return DSDF_EINVAL; }
+  k_knn_sdf<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(xyz, n, (const float4*)pts, (const float4*)normals,
+                                                                         (int)n_pts, stdv, sdf_out, nn_out);
+  MC_CU(cudaGetLastError());
+  return DSDF_OK;
+}
+extern "C" int dsdf_gather_windows(const float* samples, const int64_t* base, const int64_t* win, int64_t n_scenes,
+                                   int64_t half, float* out, void* stream) {
+  if (!samples || !base || !win || !out) { g_err = "null argument"; return DSDF_EINVAL; }
+  if (n_scenes <= 0 || half <= 0 || n_scenes > 65535) { g_err = "bad sizes"; return DSDF_EINVAL; }
+  k_gather_windows<<<dim3((unsigned)((2 * half + 255) / 256), (unsigned)n_scenes), 256, 0, (cudaStream_t)stream>>>(
+      (const float4*)samples, (const long long*)base, (const long long*)win, half, (float4*)out);
+  MC_CU(cudaGetLastError());
   return DSDF_OK;
 }
 

@@ -44,3 +44,31 @@ def eikonal_golden_check(g, named_grads, latgrad, prefix, rtol_norm, min_cos):
         else:
             assert cos(v.reshape(-1)[::stride], torch.from_numpy(g[prefix + "gs/" + k])) >= min_cos, k
     assert cos(latgrad, torch.from_numpy(g[prefix + "latgrad"])) >= min_cos
+
+
+def icosphere(subdiv: int = 2, radius: float = 0.5, center=(0.0, 0.0, 0.0)):
+    """(verts [nv,3] f32, faces [nf,3] i64) of a subdivided icosahedron, outward winding."""
+    import numpy as np
+    t = (1.0 + 5 ** 0.5) / 2.0
+    v = [(-1, t, 0), (1, t, 0), (-1, -t, 0), (1, -t, 0), (0, -1, t), (0, 1, t), (0, -1, -t), (0, 1, -t),
+         (t, 0, -1), (t, 0, 1), (-t, 0, -1), (-t, 0, 1)]
+    f = [(0, 11, 5), (0, 5, 1), (0, 1, 7), (0, 7, 10), (0, 10, 11), (1, 5, 9), (5, 11, 4), (11, 10, 2), (10, 7, 6),
+         (7, 1, 8), (3, 9, 4), (3, 4, 2), (3, 2, 6), (3, 6, 8), (3, 8, 9), (4, 9, 5), (2, 4, 11), (6, 2, 10), (8, 6, 7),
+         (9, 8, 1)]
+    v = [np.array(p, dtype=np.float64) / np.linalg.norm(p) for p in v]
+    for _ in range(subdiv):
+        cache, nf = {}, []
+
+        def mid(a, b):
+            k = (min(a, b), max(a, b))
+            if k not in cache:
+                m = v[a] + v[b]
+                v.append(m / np.linalg.norm(m))
+                cache[k] = len(v) - 1
+            return cache[k]
+        for a, b, c in f:
+            ab, bc, ca = mid(a, b), mid(b, c), mid(c, a)
+            nf += [(a, ab, ca), (b, bc, ab), (c, ca, bc), (ab, bc, ca)]
+        f = nf
+    verts = (np.array(v) * radius + np.array(center)).astype(np.float32)
+    return verts, np.array(f, dtype=np.int64)
