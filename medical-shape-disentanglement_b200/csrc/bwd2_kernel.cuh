@@ -41,6 +41,7 @@ struct alignas(64) Bwd2Args {
   float* cta_partials;        // [grid][kCtaPartialFloats]
   DropoutArgs drop;           // DROP: layers + scale (the keep bits already sit in relu_mask)
   int stash_dy0;              // dense-input backward: also stash dY0 (slot 0) for the dInput / dW0 kernels
+  int skip_dy7_stash;         // the wgrad kernel rebuilds dY7 itself (wgrad2_kernel.cuh REBUILD): slot 7 is not written
   // EIK: the Eikonal term's per-row quantities (train_deep_sdf.py:724-729; algebra in tests/eikonal_algebra.py)
   const float* pred;          // [n] tanh output of the forward pass
   const float4* wx;           // [2][512] fp32 (x, y, z, 0) xyz columns of lin0 / lin4 (k_build_wx)
@@ -296,7 +297,7 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const __grid_consta
             DSDF_PROG(0, ((unsigned)it << 16) | ((unsigned)k << 8) | (unsigned)(1 + half));
             if (half == 0) { mbar_wait(s_lo, par_lo); par_lo ^= 1; }
             else { mbar_wait(s_hi, par_hi); par_hi ^= 1; }
-            if (tile_valid && a.dystash) {    // frozen-decoder callers pass no stash (no wgrad)
+            if (tile_valid && a.dystash && !(k == 7 && a.skip_dy7_stash)) {    // frozen-decoder callers pass no stash (no wgrad)
 #pragma unroll 1
               for (int i = 0; i < 128; i += 8) {
                 uint4 v[8];

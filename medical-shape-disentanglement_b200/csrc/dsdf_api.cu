@@ -188,7 +188,8 @@ static int set_kernel_attrs(dsdf_handle h) {
   CU(h, cudaFuncSetAttribute(k_backward2<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, B2<2>::kSmemBytes));
   CU(h, cudaFuncSetAttribute(k_backward2<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, B2<1>::kSmemBytes));
   CU(h, cudaFuncSetAttribute(k_backward2<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, B2<2>::kSmemBytes));
-  CU(h, cudaFuncSetAttribute(k_wgrad2, cudaFuncAttributeMaxDynamicSharedMemorySize, kW2SmemBytes));
+  CU(h, cudaFuncSetAttribute(k_wgrad2<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kW2SmemBytes));
+  CU(h, cudaFuncSetAttribute(k_wgrad2<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kW2SmemBytes));
   h->attrs_set = true;
   return DSDF_OK;
 }
@@ -657,14 +658,20 @@ static int build_wg2_schedule(dsdf_handle h, long long tiles, cudaStream_t st, b
 
 // wgrad GEMMs (lin1..lin8) over the stashed images + ordered split-K reduction into dweff
 static int launch_wgrad2(dsdf_handle h, const uint8_t* xstash, const uint8_t* dystash, const uint8_t* g_img,
-                         float* partials, float* dweff, cudaStream_t st, bool prof = false) {
+                         float* partials, float* dweff, cudaStream_t st, bool prof = false,
+                         const float* g = nullptr, const uint32_t* relu_mask = nullptr) {
   Wg2Args w2;
+  memset(&w2, 0, sizeof(w2));
   w2.segs = h->wg2_segs;
   w2.seg_begin = h->wg2_seg_begin;
   w2.xstash = xstash;
   w2.dystash = dystash;
   w2.g_img = g_img;
   w2.partials = partials;
+  const bool rebuild = g != nullptr && relu_mask != nullptr;     // dY7 rebuilt in the kernel instead of read from the stash
+  w2.g = g;
+  w2.w8 = h->weff + weff_off(8);
+  w2.relu_mask = relu_mask;
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3((unsigned)(2 * h->wg2_pairs));
@@ -678,7 +685,8 @@ static int launch_wgrad2(dsdf_handle h, const uint8_t* xstash, const uint8_t* dy
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  CU(h, cudaLaunchKernelEx(&cfg, k_wgrad2, w2));
+  if (rebuild) CU(h, cudaLaunchKernelEx(&cfg, k_wgrad2<true>, w2));
+  else CU(h, cudaLaunchKernelEx(&cfg, k_wgrad2<false>, w2));
   if (prof) prof_mark(h, st, 4);
   k_reduce_wgrad2<<<dim3(kHidden, h->wg2_with_l8 ? 8 : 7), kHidden, 0, st>>>(partials, h->wg2_layout, dweff);
   if (prof) prof_mark(h, st, 5);
@@ -834,6 +842,14 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   b2.tile_colsum = w.tile_colsum;
   b2.cta_partials = w.cta_partials;
   b2.drop = h->drop;
+  // dY7 = g w8^T . mask7 is rebuilt inside the wgrad kernel (ReLU family, no dropout, no Eikonal correction pass that
+  // reads the stash): the dgrad chain then does not stash it
+#ifndef DSDF_ARCH_SIREN
+  const bool rebuild_dy7 = !eik && h->drop.layers == 0;
+#else
+  const bool rebuild_dy7 = false;
+#endif
+  b2.skip_dy7_stash = rebuild_dy7 ? 1 : 0;
   if (eik) {
     b2.pred = pred;
     b2.wx = h->wx;
@@ -894,7 +910,8 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   CU(h, cudaEventRecord(h->ev_join, sd));
 
   // ---- wgrad GEMMs (lin1..lin7) + split-K reduction on the caller's stream
-  rc = launch_wgrad2(h, w.xstash, w.dystash, w.g_img, w.wg_partials, w.dweff, st, prof);
+  rc = launch_wgrad2(h, w.xstash, w.dystash, w.g_img, w.wg_partials, w.dweff, st, prof, rebuild_dy7 ? w.g : nullptr,
+                     rebuild_dy7 ? w.relu_mask : nullptr);
   if (rc != DSDF_OK) return rc;
   CU(h, cudaStreamWaitEvent(st, h->ev_join, 0));
   // weight-norm backward over the complete effective-weight gradient; `grads` is final after it (a multi-GPU caller
@@ -992,7 +1009,7 @@ extern "C" int dsdf_dense_backward(dsdf_handle h, const float* params, const flo
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    CU(h, cudaLaunchKernelEx(&cfg, k_wgrad2, w2));
+    CU(h, cudaLaunchKernelEx(&cfg, k_wgrad2<false>, w2));
     k_reduce_wgrad2<<<dim3(kHidden, 8), kHidden, 0, st>>>(w.wg_partials, h->wg2_layout, w.dweff);
   }
   // latent columns of dW0 / dW4 (wg_partials is free again: stream order)

@@ -21,6 +21,8 @@
 // (train_deep_sdf.py:731) for lin1..lin8; lin0, the latent/xyz columns of lin4 and all bias grads
 // come from the backward kernel's reducer warps and the segmented kernels.
 #pragma once
+#include "common.cuh"
+#include "fwd3_kernel.cuh"   // mask_pack32
 #include "layout.cuh"
 #include "ptx.cuh"
 
@@ -41,6 +43,12 @@ struct Wg2Args {
   const uint8_t* dystash;
   const uint8_t* g_img;      // [tiles][16 KB]: layer-8 "dY"
   float* partials;           // [slots][256][512]
+  // REBUILD: dY7 = g w8^T . mask7 is rebuilt in shared memory by the (otherwise idle) epilogue warps from 512 B of g,
+  // 512 B of w8 and 2 KB of ReLU bits per tile and CTA, instead of being stashed by the dgrad chain and read back
+  // (1 KB/row written + 1 KB/row read less); byte-identical to what k_backward2 would have stashed
+  const float* g;            // [n] dL/ds
+  const float* w8;           // [512]
+  const uint32_t* relu_mask; // forward ReLU bit-masks [tiles][8][16][128]
 };
 
 constexpr int kW2Ring = 8;
@@ -50,6 +58,7 @@ constexpr uint32_t kW2StageBytes = 6 * kW2Slice;           // 2 A slices + 4 B s
 constexpr uint32_t kW2SmemAux = kW2Ring * kW2StageBytes;   // 196608
 constexpr uint32_t kW2SmemBytes = kW2SmemAux + 512;
 
+template <bool REBUILD>
 __global__ void __launch_bounds__(kW2Threads, 1) k_wgrad2(const Wg2Args a) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const uint32_t s_base = smem_u32(smem);
@@ -66,8 +75,10 @@ __global__ void __launch_bounds__(kW2Threads, 1) k_wgrad2(const Wg2Args a) {
   const uint32_t crank = cluster_ctarank();
   const bool leader = crank == 0;
   if (threadIdx.x == 0) {
+    // full: the producer's arrive.expect_tx (+ the relayed arrive of the peer in the leader) and, REBUILD, one more
+    // arrival per stage: the dY7 generator warps for a lin7 stage, the producer itself otherwise
     for (int i = 0; i < kW2Ring; ++i) {
-      mbar_init(&full[i], leader ? 2 : 1);
+      mbar_init(&full[i], (leader ? 2 : 1) + (REBUILD ? 1 : 0));
       mbar_init(&empty[i], 1);
     }
     mbar_init(d_done, 1);
@@ -93,7 +104,8 @@ __global__ void __launch_bounds__(kW2Threads, 1) k_wgrad2(const Wg2Args a) {
       for (int si = seg_lo; si < seg_hi; ++si) {
         const WgSeg sg = a.segs[si];
         const int nb = sg.n_sub / 4;      // B slices per CTA per N half... (2 per half)
-        const uint32_t tx = (2 + 2 * nb) * kW2Slice;
+        const bool gen = REBUILD && sg.layer == 7;          // the A slices come from the generator warps
+        const uint32_t tx = ((gen ? 0 : 2) + 2 * nb) * kW2Slice;
         for (long long tile = sg.tile_lo; tile < sg.tile_hi; ++tile) {
           const uint8_t* dy;
           uint32_t dy_sub2;               // offset of the second M atom
@@ -113,8 +125,11 @@ __global__ void __launch_bounds__(kW2Threads, 1) k_wgrad2(const Wg2Args a) {
             mbar_wait(&empty[st], ph ^ 1);
             mbar_arrive_expect_tx(&full[st], tx);
             uint8_t* dst = smem + st * kW2StageBytes;
-            bulk_g2s(dst, dy + u * kW2Slice, kW2Slice, &full[st]);
-            bulk_g2s(dst + kW2Slice, dy + dy_sub2 + u * kW2Slice, kW2Slice, &full[st]);
+            if (!gen) {
+              if (REBUILD) mbar_arrive(&full[st]);
+              bulk_g2s(dst, dy + u * kW2Slice, kW2Slice, &full[st]);
+              bulk_g2s(dst + kW2Slice, dy + dy_sub2 + u * kW2Slice, kW2Slice, &full[st]);
+            }
             // N half hf covers X SUBs 4hf..4hf+3; this CTA provides SUBs 4hf+2c, 4hf+2c+1
             for (int hf = 0; hf < nb; ++hf) {
               bulk_g2s(dst + (2 + 2 * hf) * kW2Slice, x + (size_t)(4 * hf) * kSubBytes + u * kW2Slice,
@@ -195,8 +210,49 @@ __global__ void __launch_bounds__(kW2Threads, 1) k_wgrad2(const Wg2Args a) {
     const int q = warp & 3;
     const uint32_t r = q * 32 + lane;
     uint32_t par_done = 0;
+    [[maybe_unused]] uint32_t g_ph = 0, g_par = 0;   // REBUILD: the producer's stage sequence, followed in lock step
     for (int si = seg_lo; si < seg_hi; ++si) {
       const WgSeg sg = a.segs[si];
+      if (REBUILD) {
+        const long long nt = sg.tile_hi - sg.tile_lo;
+        if (sg.layer == 7) {
+          // dY7[row, col] = bf16(g[row] * w8[col]) where ReLU bit of X8[row, col] is set: warp q builds the 32 columns
+          // 32 q .. of this CTA's 128 (thread = one row of the 32-row K chunk), exactly k_backward2's expression
+          const uint32_t col = (uint32_t)(256 * sg.ocp + 128 * crank + 32 * q);
+          float w8r[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) w8r[i] = __ldg(a.w8 + col + i);
+          for (long long tile = sg.tile_lo; tile < sg.tile_hi; ++tile) {
+            const uint32_t* mt = a.relu_mask + (size_t)tile * (8 * 16 * kTileM) + (size_t)(7 * 16 + (col >> 5)) * kTileM;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const uint32_t st = g_par * 4 + u;
+              const uint32_t row = 32 * u + lane;
+              const float gr = __ldg(a.g + tile * kTileM + row);
+              const uint32_t m = __ldg(mt + row);
+              uint32_t v[32], p[16];
+#pragma unroll
+              for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(gr * w8r[i]);
+              mask_pack32(v, m, p);
+              mbar_wait(&empty[st], g_ph ^ 1);
+              // slice (q >> 1) of the stage = SUB 2 crank + (q >> 1) of the out chunk, rows 32 u ..; columns 32 (q & 1) ..
+              const uint32_t base = s_base + st * kW2StageBytes + (uint32_t)(q >> 1) * kW2Slice;
+#pragma unroll
+              for (int i = 0; i < 4; ++i)
+                st_shared_v4(base + sub_chunk_off(lane, (uint32_t)((q & 1) * 4 + i)), p[4 * i], p[4 * i + 1], p[4 * i + 2],
+                             p[4 * i + 3]);
+              fence_proxy_async_smem();
+              named_bar_sync(2, 128);
+              if (threadIdx.x == 128) mbar_arrive(&full[st]);
+            }
+            g_par ^= 1;
+            g_ph ^= (g_par == 0);
+          }
+        } else {
+          g_ph ^= (uint32_t)((g_par + nt) >> 1) & 1u;
+          g_par ^= (uint32_t)nt & 1u;
+        }
+      }
       float* out = a.partials + ((size_t)sg.slot * 256 + crank * 128 + r) * kHidden;
       const int ncols = sg.n_sub * 64;
       mbar_wait(d_done, par_done);
