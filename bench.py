@@ -211,7 +211,7 @@ def small_kernel_rooflines(tr, dec, dev, pk, n_seg):
     m, v, p = torch.zeros_like(flat), torch.zeros_like(flat), flat.clone()
     scratch = torch.zeros(4096, device=dev)
     # k_sqnorm_partial + k_clip_coef + k_adam: r g (norm) + r p,g,m,v + w p,m,v,g
-    add("clip+adam decoder (k_sqnorm_partial,k_clip_coef,k_adam)", n * 4 * (1 + 8),
+    add("clip+adam decoder (k_sqnorm_partial,k_adam)", n * 4 * (1 + 8),
         lambda: L.dsdf_clip_adam(h, p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), n, 1.0, 5e-4, 0.9, 0.999, 1e-8, 5,
                                  scratch.data_ptr(), st))
     tab = tr.lat_vecs.weight.data.clone()
@@ -223,7 +223,7 @@ def small_kernel_rooflines(tr, dec, dev, pk, n_seg):
     ids = torch.arange(n_seg, device=dev, dtype=torch.int64)
     add("embedding max_norm renorm of the batch rows (k_renorm_rows)", n_seg * 256 * 4 * 2,
         lambda: L.dsdf_renorm_rows(h, tab.data_ptr(), tab.shape[0], ids.data_ptr(), n_seg, 1.0, st))
-    add("weight fold: fp32 masters -> bf16 K-step images (k_rowscale_weff,k_fold_fwd2,k_fold_dgrad2,k_build_wx)",
+    add("weight fold: fp32 masters -> bf16 K-step images (k_rowscale_weff,k_fold_images)",
         n * 4 * 2 + (463 + 448) * 8192,
         lambda: dec.sync_weights(force=True))
     return out
@@ -694,8 +694,8 @@ def main():
 
     if rank == 0:
         # launches per step, counted from the ncu launch list (profiles/): renorm | sanitize, scene_fold, fwd, bwd, wgrad,
-        # reduce_wgrad2 + 4 decoder-grad + 3 latent-grad/loss (+ memset node) | latent adam | decoder sqnorm, coef, adam |
-        # rowscale_weff, fold_fwd2, fold_dgrad2, build_wx   (+ recompute pass and k_eik_corr with --eikonal)
+        # reduce_wgrad2 + 4 decoder-grad + 3 latent-grad/loss (+ memset node) | latent adam | decoder sqnorm, adam |
+        # rowscale_weff, fold_images   (+ recompute pass and k_eik_corr with --eikonal)
         launches_per_step = 1 + 13 + 1 + 2 + 2 + (2 if args.eikonal else 0)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,

@@ -130,7 +130,12 @@ class _FusedDecoderBase(nn.Module):
             pass
 
     def sync_weights(self, force: bool = False):
-        """Fold fp32 masters -> bf16 tensor-core images if any parameter changed."""
+        """Fold fp32 masters -> bf16 tensor-core images if any parameter changed.
+
+        "Changed" is detected through the parameters' autograd version counters (optimiser steps, `p.copy_()`,
+        `load_state_dict` all bump them).  Writes that go through `p.data` (`p.data.copy_`, `p.data.mul_` -- common in
+        hand-written init / EMA code) do NOT bump that counter: after such a write call `sync_weights(force=True)`
+        (`FusedTrainer.step` always re-folds after its own Adam update)."""
         h = self.handle()
         flat = self.flat_params()
         key = (flat.data_ptr(), tuple(p._version for p in self.parameters()))
