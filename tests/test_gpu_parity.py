@@ -362,6 +362,58 @@ def test_loss_trajectory_free_running_within_reproducibility_horizon():
     assert rel[:horizon].max() <= 0.01
 
 
+def test_free_running_at_the_reference_learning_rates_is_indistinguishable_from_perturbed_reference_runs():
+    """At the SHIPPED learning rates (5e-4 decoder, 1e-3 latents) the reference does not reproduce itself step by step
+    beyond ~50 steps (profiles/r01_trajectory_chaos.log), so the free-running comparison is statistical.  The fused path
+    differs from the fp32 reference by one bf16 rounding of the operands (2^-9 relative) per GEMM; the fair ensemble is
+    therefore reference runs whose INITIAL decoder weights and latents are perturbed once by that much (2^-9 relative,
+    Gaussian) and which then run in exact fp32.  They define the spread of the 50-step window means of the loss; the
+    fused path, free-running on its own optimiser state for the same 400 steps, must sit inside
+    mean +- max(4 sigma, 1 %) in every window, the last one included (it has learnt as much)."""
+    prev_det = torch.are_deterministic_algorithms_enabled()
+    torch.use_deterministic_algorithms(True, warn_only=True)      # reproducible reference ensemble (no float atomics)
+    try:
+        _ensemble_free_running()
+    finally:
+        torch.use_deterministic_algorithms(prev_det)
+
+
+def _ensemble_free_running():
+    S, B, P, steps, win = 16, 8, 2048, 400, 50
+    eps = 2.0 ** -9
+    torch.manual_seed(0)
+    dec, spec, params = make(True)
+    cfg = otrain.TrainConfig(samples_per_scene=P, scenes_per_batch=B, code_bound=1.0, grad_clip=1.0)   # reference LRs
+    base = otrain.OracleTrainer(spec, cfg, S, seed=0, device="cuda", params=params)
+    lat0 = base.lat_vecs.weight.data.clone()
+    runs = [base]
+    for k in range(6):
+        gk = torch.Generator().manual_seed(50 + k)
+        pert_lat = lat0 * (1 + eps * torch.randn(lat0.shape, generator=gk).cuda())
+        pert_par = {n: v * (1 + eps * torch.randn(v.shape, generator=gk)) for n, v in params.items()}
+        runs.append(otrain.OracleTrainer(spec, cfg, S, seed=0, device="cuda", params=pert_par, latents=pert_lat))
+    tr = dsdf_b200.FusedTrainer(dec, S, dsdf_b200.StepConfig(code_bound=1.0, grad_clip=1.0), latents=lat0.clone())
+    data = synth.scene_samples(S, P, seed=2).cuda()
+    g = torch.Generator().manual_seed(11)
+    ref = [[] for _ in runs]
+    ours = []
+    for it in range(steps):
+        ids = torch.randperm(S, generator=g)[:B]
+        epoch = 1 + it // 4
+        for r, o in zip(ref, runs):
+            r.append(o.step(data[ids], ids, epoch)["loss"])
+        st = tr.step(data[ids], ids.cuda(), epoch)
+        ours.append(st["sdf_loss"] + st["reg_loss"])
+    ref = np.array(ref).reshape(len(runs), steps // win, win).mean(2)           # [runs, windows]
+    ours = torch.stack(ours).cpu().numpy().reshape(steps // win, win).mean(1)
+    mu, sd = ref.mean(0), ref.std(0, ddof=1)
+    z = np.abs(ours - mu) / np.maximum(4 * sd, 0.01 * mu)
+    print("window means: reference ensemble", np.round(mu, 6), "+-", np.round(sd, 7), "fused", np.round(ours, 6),
+          "|dev| / allowed per window", np.round(z, 2))
+    assert ref[0, -1] < 0.5 * ref[0, 0]                 # it is a training run
+    assert z.max() <= 1.0
+
+
 def test_error_paths_through_the_c_abi():
     dec, _, _ = make(False)
     tr = dsdf_b200.FusedTrainer(dec, 4, dsdf_b200.StepConfig())
