@@ -210,7 +210,7 @@ def small_kernel_rooflines(tr, dec, dev, pk, n_seg):
     g = torch.randn_like(flat) * 1e-3
     m, v, p = torch.zeros_like(flat), torch.zeros_like(flat), flat.clone()
     scratch = torch.zeros(4096, device=dev)
-    # k_sqnorm_partial + k_clip_coef + k_adam: r g (norm) + r p,g,m,v + w p,m,v,g
+    # k_sqnorm_partial + k_adam (clip coefficient inside): r g (norm) + r p,g,m,v + w p,m,v,g
     add("clip+adam decoder (k_sqnorm_partial,k_adam)", n * 4 * (1 + 8),
         lambda: L.dsdf_clip_adam(h, p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), n, 1.0, 5e-4, 0.9, 0.999, 1e-8, 5,
                                  scratch.data_ptr(), st))

@@ -2,7 +2,7 @@
 // lean issue loops / CTA pairing (tcgen05 cta_group::2) as the v3 forward chain.
 //
 //   warp 0       : weight producer: K-steps of W^T ([256 i x 16 o], layout.cuh dg2_*) -> smem ring
-//   warp 1       : MMA issuer (leader) / full-barrier relay (peer):  dX_l = dY_l W_l as two
+//   warp 1       : MMA issuer (leader; the peer's warp 1 idles):  dX_l = dY_l W_l as two
 //                  256-column halves, M = 128*CG, N = 256, K = 16
 //   warp 2       : TMEM allocator; warp 3 idle
 //   warps 4..11  : epilogue warps: dY7 = g w8 (X8 > 0) from the forward's dL/ds and ReLU bit-mask;
@@ -44,7 +44,7 @@ struct alignas(64) Bwd2Args {
   int skip_dy7_stash;         // the wgrad kernel rebuilds dY7 itself (wgrad2_kernel.cuh REBUILD): slot 7 is not written
   // EIK: the Eikonal term's per-row quantities (train_deep_sdf.py:724-729; algebra in tests/eikonal_algebra.py)
   const float* pred;          // [n] tanh output of the forward pass
-  const float4* wx;           // [2][512] fp32 (x, y, z, 0) xyz columns of lin0 / lin4 (k_build_wx)
+  const float4* wx;           // [2][512] fp32 (x, y, z, 0) xyz columns of lin0 / lin4 (k_fold_images)
   float clamp_dist;
   float eik_c2;               // 2 * lambda / N_total
   float4* eik_row;            // out [n]: perturbed input of the recompute pass (x', y', z', eps)

@@ -2,26 +2,28 @@
 // single-thread issue loops, optional CTA pair (CG = 2: tcgen05 cta_group::2, M = 256 over two SMs).
 //
 //   warp 0      : weight producer (one elected lane): K-steps ([256 n x 16 k] bf16, layout.cuh)
-//                 global -> smem ring with the TMA engine.  CG = 2: each CTA of the pair copies
-//                 ITS HALF of every step (128 n rows) into its own ring and signals the LEADER's
-//                 barrier, so L2 -> SM traffic and ring writes per SM are halved.
-//   warp 1      : MMA issuer (one elected lane of the leader CTA): tcgen05.mma kind::f16,
-//                 M = 128*CG, N = 256, K = 16.  Ring stage indices, barrier addresses and operand
-//                 descriptors are compile-time constants inside fully unrolled groups of kRing
-//                 steps: the loop is a try_wait + UTCHMMA + UTCBAR per step and keeps the tensor
-//                 pipe at its 128-cycle-per-step floor (tools/gpu_mma_rate.py).
-//   warp 2      : TMEM allocator (512 columns); warp 3 idle
-//   warps 4..11 : epilogue warps, as in v2: each layer is two 256-column halves; h0's ReLU'd bf16
-//                 activations are held in registers until the layer's last MMA has retired, then
-//                 become the next layer's A tile; h1 follows straight from TMEM.
+//                 global -> smem ring with the TMA engine.  CG = 2: each CTA of the pair loads ITS HALF
+//                 of every step (128 n rows) into its own ring with a tensor-map load
+//                 (cp.async.bulk.tensor.2d.cta_group::2, SASS UTMALDG.2D.2CTA) whose complete_tx lands on the
+//                 LEADER's `full` barrier; the leader's producer posts one arrive.expect_tx for both halves.
+//   warp 1      : MMA issuer (one elected lane of the leader CTA; the peer's warp 1 idles): tcgen05.mma
+//                 kind::f16, M = 128*CG, N = 256, K = 16; a try_wait + UTCHMMA + UTCBAR per step keeps the
+//                 tensor pipe at its 128-cycle-per-step floor (tools/gpu_mma_rate.py).  After the last
+//                 half's K-steps 0..15 it commits `lo_free`.
+//   warp 2      : TMEM allocator (512 columns); warp 3: activation-stash warp (TRAIN)
+//   warps 4..11 : epilogue warps: each layer is two 256-column halves; h0's ReLU'd bf16 activations are
+//                 held in registers until `lo_free` (the layer's last read of A columns 0..255 has
+//                 retired) and then become the next layer's A columns 0..255 UNDER the K-steps that still
+//                 read columns 256..511, so the next layer's first MMAs follow without a bubble; h1 follows
+//                 straight from TMEM once the layer has retired.
 //
 // E steps (xyz hi/lo + bias through the ones columns; in FOLD mode the per-segment bias
 // b + W[:, latent] z of lin0 / lin4) travel through their own 2-slot ring so that the W ring always
 // advances in multiples of 16 steps.
 //
-// TRAIN mode also writes, per layer, the activation stash (bf16 images, consumed by the wgrad
-// kernel; stored straight from the epilogue registers) and a 1-bit/element ReLU mask (consumed by the backward chain instead of re-reading the
-// 1 KB/row activations).
+// TRAIN mode also writes, per layer, the activation stash (bf16 images = the smem A tile byte for byte, copied
+// out by warp 3 with coalesced stores; consumed by the wgrad kernel) and a 1-bit/element ReLU mask (consumed by
+// the backward chain instead of re-reading the 1 KB/row activations).
 //
 // Replaces, per 128-row tile, reference networks/deep_sdf_decoder.py:74-109 (9x addmm, 2x cat,
 // 8x relu, tanh), deep_sdf/utils.py:86-97 (expand + cat) and, in TRAIN mode,
