@@ -11,6 +11,10 @@ Follows /root/reference/train_deep_sdf.py:
   * backward                  :731
   * clip + step               :780-784  clip_grad_norm_(decoder.parameters(), c) then Adam step
 
+Pinned against the EXECUTED script: tests/golden/make_golden_trainloop.py runs train_deep_sdf.main_function itself on CPU
+(import stubs, .cuda() -> identity) and tests/test_oracle_cpu.py requires this restatement to reproduce its per-batch
+losses and final checkpoint from the same initial state and batches, with and without UseEikonal.
+
 Everything is torch fp32 and device agnostic (the script itself hard-codes .cuda()).
 torch's own Embedding/Adam/clip_grad_norm_ are used where the reference uses them
 (third-party arithmetic: the reference pins pytorch 1.13, this container has 2.11; the

@@ -393,3 +393,55 @@ def test_oracle_port_equals_the_step_loop_around_the_reference_module(eik):
     for k, v in ref.decoder.state_dict().items():
         torch.testing.assert_close(v, orc.params[k].data, rtol=1e-5, atol=1e-7)
     torch.testing.assert_close(ref.lat_vecs.weight.data, orc.lat_vecs.weight.data, rtol=1e-5, atol=1e-7)
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference"), reason="the reference checkout exists in the build container only")
+@pytest.mark.parametrize("eik", [False, True])
+def test_oracle_step_equals_the_executed_reference_training_script(eik):
+    """SURVEY.md 8(c) / VERDICT r1 weak #6: the oracle's train step is no longer pinned to torch primitives only -- the
+    reference's OWN train_deep_sdf.main_function (train_deep_sdf.py:211-1123) is executed here, unmodified, on CPU for three
+    epochs of a tiny experiment (tests/golden/make_golden_trainloop.py: import stubs, .cuda() -> identity, recording
+    DataLoader / Adam / SummaryWriter; none touches the arithmetic).  The oracle, started from the script's initial
+    decoder and latent table and fed the very batches the script's DataLoader yielded, must reproduce the script's
+    per-batch loss, its per-epoch loss terms and its final checkpoint (decoder + latent codes)."""
+    import importlib.util
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "make_golden_trainloop.py")
+    spec_ = importlib.util.spec_from_file_location("make_golden_trainloop", path)
+    mod = importlib.util.module_from_spec(spec_)
+    spec_.loader.exec_module(mod)
+    r = mod.run_reference(eik)
+    sp = r["specs"]
+    sch = sp["LearningRateSchedule"]
+    cfg = otrain.TrainConfig(samples_per_scene=sp["SamplesPerScene"], scenes_per_batch=sp["ScenesPerBatch"],
+                             clamp_dist=sp["ClampingDistance"], code_reg=sp["CodeRegularization"],
+                             code_reg_lambda=sp["CodeRegularizationLambda"], code_bound=sp["CodeBound"],
+                             grad_clip=sp["GradientClipNorm"], lr_decoder=sch[0]["Initial"], lr_latent=sch[1]["Initial"],
+                             lr_interval=sch[0]["Interval"], lr_factor=sch[0]["Factor"], use_eikonal=eik)
+    names = [k[len("module."):] if k.startswith("module.") else k for k in r["final_model"].keys()]
+    # Adam's first parameter group = decoder.parameters() in registration order = state_dict order (no buffers)
+    assert len(names) == len(r["init_decoder"])
+    params = {n: p.clone() for n, p in zip(names, r["init_decoder"])}
+    S = r["init_latents"].shape[0]
+    orc = otrain.OracleTrainer(deepsdf.DecoderSpec(norm_layers=tuple(range(8)), weight_norm=True), cfg, S, seed=0, device="cpu",
+                               params=params, latents=r["init_latents"].clone())
+    per_batch_ref = [v for t, v, _ in r["scalars"] if t == "Loss/train_vanilla"]
+    assert len(per_batch_ref) == len(r["batches"]) == r["epochs"] * r["batches_per_epoch"]
+    ours, eik_terms, reg_terms = [], [], []
+    for i, (sdf_data, indices) in enumerate(r["batches"]):
+        epoch = 1 + i // r["batches_per_epoch"]
+        st = orc.step(sdf_data, indices, epoch)
+        ours.append(st["sdf_loss"] + st["reg_loss"])      # "Loss/train_vanilla" is logged before the Eikonal term is added (:723)
+        eik_terms.append(st["eikonal_loss"])
+        reg_terms.append(st["reg_loss"])
+    assert np.allclose(ours, per_batch_ref, rtol=2e-6, atol=0), (ours, per_batch_ref)
+    per_epoch = lambda xs: [float(np.mean(xs[e * r["batches_per_epoch"]:(e + 1) * r["batches_per_epoch"]])) for e in range(r["epochs"])]
+    ref_reg = [v for t, v, _ in r["scalars"] if t == "Loss/train_reg"]
+    assert np.allclose(per_epoch(reg_terms), ref_reg, rtol=1e-5)
+    if eik:
+        ref_eik = [v for t, v, _ in r["scalars"] if t == "Loss/train_eikonal"]
+        assert np.allclose(per_epoch(eik_terms), ref_eik, rtol=1e-5) and min(ref_eik) > 0
+    # the script's final checkpoint
+    for k, v in r["final_model"].items():
+        n = k[len("module."):] if k.startswith("module.") else k
+        assert torch.allclose(orc.params[n].detach(), v, rtol=0, atol=2e-7), n
+    assert torch.allclose(orc.lat_vecs.weight.data, r["final_latents"], rtol=0, atol=2e-7)
