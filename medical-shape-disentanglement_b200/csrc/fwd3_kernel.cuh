@@ -103,7 +103,9 @@ __device__ __forceinline__ void mask_pack32(const uint32_t (&v)[32], uint32_t m,
 // approximation's absolute error grows with |y|, so reduce first -- Cody-Waite with 2 pi = C1 + C2, C1 exact in
 // 9 bits (k C1 is exact for |k| < 2^15, i.e. |y| < 2e5) -- and evaluate on r in [-pi, pi] where it is ~2^-21.
 __device__ __forceinline__ void sincos_reduced(float y, float& s, float& c) {
-  const float k = rintf(y * 0.15915494309189535f);
+  // round-to-nearest of y / 2 pi by the 1.5 * 2^23 add trick: two FMA-pipe ops instead of F2F/rint on the
+  // quarter-rate conversion pipe the SFU-bound epilogue already saturates (valid for |y / 2 pi| < 2^22)
+  const float k = fmaf(y, 0.15915494309189535f, 12582912.f) - 12582912.f;
   float r = fmaf(-k, 6.28125f, y);
   r = fmaf(-k, 1.9353071795864769e-3f, r);
   __sincosf(r, &s, &c);
