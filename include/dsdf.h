@@ -287,6 +287,18 @@ int dsdf_mc_emit(const float* sdf, int32_t nx, int32_t ny, int32_t nz, float lev
 int dsdf_rasterize_views(const float* verts, int64_t n_verts, const int32_t* faces, int64_t n_faces,
                          const float* views, int32_t n_views, uint64_t* zbuf, float* out_vert, float* out_norm,
                          uint8_t* valid, void* stream);
+/* Allocation-free variant of dsdf_rasterize_views.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same inputs, outputs and results as dsdf_rasterize_views, but the depth buffer is a file-scope
+ * static __device__ array inside the library (DSDF_RAST_STATIC_MAX_VIEWS x 400 x 400 x 8 B = 10.24 MB, held by every
+ * GPU that loads the library until exit) instead of the caller's `zbuf`.  The call makes no cudaMalloc / cudaFree /
+ * allocating library call.  n_views > DSDF_RAST_STATIC_MAX_VIEWS returns DSDF_EINVAL with a message naming the limit
+ * (split the views over several calls).  All calls on one device share the array: it is reset at the start of each
+ * call, and calls whose kernels overlap on the GPU (different streams without an ordering between them) race. */
+#define DSDF_RAST_STATIC_MAX_VIEWS 8
+int dsdf_rasterize_views_static(const float* verts, int64_t n_verts, const int32_t* faces, int64_t n_faces,
+                                const float* views, int32_t n_views, float* out_vert, float* out_norm,
+                                uint8_t* valid, void* stream);
 int dsdf_sample_points(const float* verts, const int32_t* faces, const float* cdf, int64_t n_faces, int64_t n_surf,
                        int64_t n_rand, float stdv1, float stdv2, float cube_dim, uint64_t seed, float* xyz,
                        float* surf_out, void* stream);

@@ -9,6 +9,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -1435,6 +1436,56 @@ extern "C" int dsdf_rasterize_views(const float* verts, int64_t n_verts, const i
                                                                                        (unsigned long long*)zbuf);
   k_rast_resolve<<<dim3((kRastW * kRastH + 255) / 256, (unsigned)n_views), 256, 0, st>>>(
       verts, faces, views, (const unsigned long long*)zbuf, (float4*)out_vert, (float4*)out_norm, valid);
+  MC_CU(cudaGetLastError());
+  return DSDF_OK;
+}
+// Allocation-free variant of dsdf_rasterize_views (no counterpart in the reference; added
+// for callers that may not call cudaMalloc: graph capture, serving loops).  The depth buffer lives
+// in a file-scope device array instead of a caller buffer: kRastStaticMaxViews views x 400 x 400 x 8 B = 10.24 MB,
+// held by every GPU that loads the library until process exit.  In HOST code `g_rast_zbuf` is only the symbol's
+// host-side stand-in, never a device address: the pointer handed to the kernels comes from cudaGetSymbolAddress,
+// taken once per device with that device current.  All calls on a device share the array (it keeps the last
+// call's contents, so it is reset to "empty" = all ones at the start of every call); two calls whose kernels
+// overlap on the GPU (different streams, no ordering between them) race on it.
+constexpr int kRastStaticMaxViews = DSDF_RAST_STATIC_MAX_VIEWS;
+static __device__ __align__(256) unsigned long long g_rast_zbuf[(size_t)kRastStaticMaxViews * kRastW * kRastH];
+constexpr int kMaxDevices = 64;
+static unsigned long long* g_rast_zbuf_dev[kMaxDevices];      // per-device address of g_rast_zbuf (null = not taken yet)
+static std::mutex g_rast_zbuf_mu;
+
+static int rast_static_scratch(unsigned long long** out) {
+  int dev = -1;
+  MC_CU(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) { g_err = "device ordinal beyond the static scratch table"; return DSDF_EINVAL; }
+  std::lock_guard<std::mutex> lock(g_rast_zbuf_mu);
+  if (!g_rast_zbuf_dev[dev]) {
+    unsigned long long* p = nullptr;
+    MC_CU(cudaGetSymbolAddress((void**)&p, g_rast_zbuf));     // the address on the CURRENT device
+    if (!p) { g_err = "cudaGetSymbolAddress returned a null scratch address"; return DSDF_ECUDA; }
+    g_rast_zbuf_dev[dev] = p;
+  }
+  *out = g_rast_zbuf_dev[dev];
+  return DSDF_OK;
+}
+extern "C" int dsdf_rasterize_views_static(const float* verts, int64_t n_verts, const int32_t* faces, int64_t n_faces,
+                                           const float* views, int32_t n_views, float* out_vert, float* out_norm,
+                                           uint8_t* valid, void* stream) {
+  if (!verts || !faces || !views || !out_vert || !out_norm || !valid) { g_err = "null argument"; return DSDF_EINVAL; }
+  if (n_verts <= 0 || n_faces <= 0 || n_views <= 0 || n_faces > (1ll << 31) - 2) { g_err = "empty mesh / bad sizes"; return DSDF_EINVAL; }
+  if (n_views > kRastStaticMaxViews) {
+    g_err = "dsdf_rasterize_views_static: n_views = " + std::to_string(n_views) + " exceeds the static depth buffer (" +
+            std::to_string(kRastStaticMaxViews) + " views per call); split the views or use dsdf_rasterize_views";
+    return DSDF_EINVAL;
+  }
+  unsigned long long* zbuf = nullptr;
+  int rc = rast_static_scratch(&zbuf);
+  if (rc != DSDF_OK) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t px = (size_t)n_views * kRastW * kRastH;
+  MC_CU(cudaMemsetAsync(zbuf, 0xFF, px * 8, st));               // the array keeps the previous call's depths
+  k_rast_draw<<<dim3((unsigned)((n_faces + 127) / 128), (unsigned)n_views), 128, 0, st>>>(verts, faces, (int)n_faces, views, zbuf);
+  k_rast_resolve<<<dim3((kRastW * kRastH + 255) / 256, (unsigned)n_views), 256, 0, st>>>(
+      verts, faces, views, zbuf, (float4*)out_vert, (float4*)out_norm, valid);
   MC_CU(cudaGetLastError());
   return DSDF_OK;
 }

@@ -23,7 +23,7 @@ EXPORTS = [
     "dsdf_segments_forward_train", "dsdf_segments_backward", "dsdf_set_dropout", "dsdf_dropout_keep", "dsdf_reconstruct_workspace_bytes", "dsdf_reconstruct",
     "dsdf_selftest_gemm", "dsdf_profile_enable", "dsdf_profile_read", "dsdf_debug_read", "dsdf_selftest_mma_rate", "dsdf_debug_hang_buffer",
     "dsdf_debug_progress_buffer", "dsdf_mc_classify", "dsdf_mc_emit",
-    "dsdf_rasterize_views", "dsdf_sample_points", "dsdf_knn_sdf", "dsdf_gather_windows",
+    "dsdf_rasterize_views", "dsdf_rasterize_views_static", "dsdf_sample_points", "dsdf_knn_sdf", "dsdf_gather_windows",
 ]
 
 
@@ -128,6 +128,8 @@ def lib(arch: str = "deep_sdf_decoder"):
     L.dsdf_mc_emit.restype = C.c_int
     L.dsdf_rasterize_views.argtypes = [vp, i64, vp, i64, vp, i32, vp, vp, vp, vp, vp]
     L.dsdf_rasterize_views.restype = C.c_int
+    L.dsdf_rasterize_views_static.argtypes = [vp, i64, vp, i64, vp, i32, vp, vp, vp, vp]
+    L.dsdf_rasterize_views_static.restype = C.c_int
     L.dsdf_sample_points.argtypes = [vp, vp, vp, i64, i64, i64, f32, f32, f32, C.c_uint64, vp, vp, vp]
     L.dsdf_sample_points.restype = C.c_int
     L.dsdf_knn_sdf.argtypes = [vp, i64, vp, vp, i64, f32, vp, vp, vp]
