@@ -21,6 +21,7 @@ from __future__ import annotations
 import argparse
 import json
 import os
+import random
 import subprocess
 import sys
 import threading
@@ -635,6 +636,38 @@ def main():
                                    "a side stream behind the grads-ready event, under the latent Adam; its duration is measured "
                                    "with CUDA events on that stream (includes waiting for the slowest rank)"}
 
+    # ---------------- reconstruct.py sharded by shape (N > 1): no collective, shapes/s over all ranks ----------------
+    recon_line = None
+    if world > 1 and not args.no_extras:
+        per_rank, it_r, ns_r = 16, 800, 8000
+        n_sh = per_rank * world
+        rs = random.Random(7)
+        sh_all = []
+        for s_ in range(n_sh):
+            d_ = synth.fast_scene_samples(1, 100000, seed=300 + s_, device=str(dev))[0]
+            sh_all.append((d_[:50000].contiguous(), d_[50000:].contiguous()))
+        wins_r = torch.tensor([[dsdf_b200.draw_windows(50000, 50000, ns_r, 1, rs)[0] for _ in range(n_sh)]
+                               for _ in range(it_r)], dtype=torch.int64)
+        lat_r = torch.randn(n_sh, 256, generator=torch.Generator().manual_seed(9)) * 0.01
+        dec.eval()
+        dsdf_b200.reconstruct_sharded(dec, 8, sh_all, lat_r, wins_r[:8], 0.1, rank, world, num_samples=ns_r, lr=5e-3, l2reg=True)
+        barrier()
+        r0 = torch.cuda.Event(enable_timing=True); r1 = torch.cuda.Event(enable_timing=True)
+        r0.record()
+        lo_r, hi_r, hist_r, _ = dsdf_b200.reconstruct_sharded(dec, it_r, sh_all, lat_r, wins_r, 0.1, rank, world,
+                                                              num_samples=ns_r, lr=5e-3, l2reg=True)
+        r1.record()
+        barrier()
+        t = torch.tensor([r0.elapsed_time(r1)], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        recon_line = {"shapes": n_sh, "shapes_per_rank": hi_r - lo_r, "iterations": it_r, "num_samples": ns_r,
+                      "ms": float(t.item()), "shapes_per_s": n_sh / (float(t.item()) * 1e-3), "scaling": "weak",
+                      "loss_last_rank0": float(hist_r[-1].mean()),
+                      "note": "reconstruct_sharded: contiguous block of the shape list per rank, no collective; CUDA events "
+                              "around the call incl. the rank's sample upload, max over ranks"}
+        del sh_all
+        dec.train()
+
     # ---------------- replicas stay identical (N > 1): all-gather a parameter checksum ----------------
     replicas_identical = None
     if world > 1:
@@ -711,6 +744,7 @@ def main():
             "gpu_launches": launches_per_step * K,
             "roofline": roofline, "roofline_small": roofline_small, "sustained": sustained,
             "replicas_identical": replicas_identical, "strong_scaling": strong_line,
+            "reconstruct_sharded": recon_line,
             "cpu_baseline": cpu_baseline, "clocks": clocks, "extras": extras,
             "loss": float(st["sdf_loss"].item()),
         }

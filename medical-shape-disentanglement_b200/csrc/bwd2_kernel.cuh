@@ -177,6 +177,8 @@ __global__ void __launch_bounds__(kB2Threads, 1) k_backward2(const __grid_consta
   if (CG > 1) cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  grid_dep_launch();                     // programmatic dependent launch, see k_forward3
+  grid_dep_wait();
 
   const long long n_tiles = (a.n_rows + kTileM - 1) / kTileM;
   const long long n_iter = (n_tiles + gridDim.x - 1) / gridDim.x;

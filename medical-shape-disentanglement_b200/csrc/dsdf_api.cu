@@ -82,6 +82,7 @@ struct dsdf_handle_s {
   DropoutArgs drop{};                  // dsdf_set_dropout; layers == 0: no dropout
   // optional per-kernel timing (CUDA events on the caller's stream), see dsdf_profile_*
   bool profile = false;
+  bool pdl = false;          // chain launches carry the programmatic-serialisation attribute (dsdf_reconstruct's loop)
   std::vector<cudaEvent_t> prof_events;   // one per section boundary of dsdf_train_fwd_bwd
   std::vector<int> prof_ids;              // section that ENDS at the event (-1: start of a call)
 };
@@ -340,13 +341,15 @@ static cudaError_t launch_fwd3_cg(dsdf_handle h, const FwdArgs& a, cudaStream_t 
   cfg.blockDim = dim3(kF3Threads);
   cfg.dynamicSmemBytes = F3<CG>::kSmemBytes;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = CG;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = h->pdl ? 2 : 1;
   return cudaLaunchKernelEx(&cfg, k_forward3<MODE, FOLD, TRAIN, CG, DROP, TAN>, a);
 }
 // pair_ok: both tiles of a pair may share the B operand (always true unless FOLD segments are
@@ -706,13 +709,15 @@ static int launch_backward2(dsdf_handle h, const Bwd2Args& b2, long long tiles, 
   cfg.blockDim = dim3(kB2Threads);
   cfg.dynamicSmemBytes = cg == 2 ? B2<2>::kSmemBytes : B2<1>::kSmemBytes;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = cg;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = h->pdl ? 2 : 1;
   if (b2.eik_row) {
 #ifndef DSDF_ARCH_SIREN
     if (cg == 2) CU(h, (cudaLaunchKernelEx(&cfg, k_backward2<2, false, true>, b2)));
@@ -1169,7 +1174,6 @@ struct RWs {
   float* tile_partials;
   float* tile_colsum;
   float* cta_partials;
-  float* seg_sum;
   uint8_t* scene_e;
   size_t scene_e_bytes;
   uint32_t* relu_mask;
@@ -1193,7 +1197,6 @@ RWs recon_carve(uint8_t* base, long long n_shapes, long long num_samples, int nu
   w.tile_partials = (float*)take(tiles * 2 * 4);
   w.tile_colsum = (float*)take(tiles * 2 * kHidden * 4);
   w.cta_partials = (float*)take((size_t)num_sms * kCtaPartialFloats * 4);
-  w.seg_sum = (float*)take((size_t)n_shapes * kReconParts * kLatent * 4);   // latent-gradient partials
   w.scene_e_bytes = (size_t)n_shapes * kSceneESteps * kStepBytes;
   w.scene_e = take(w.scene_e_bytes);
   w.relu_mask = (uint32_t*)take(tiles * kActAuxTileBytes);
@@ -1268,49 +1271,88 @@ extern "C" int dsdf_reconstruct(dsdf_handle h, const float* params, const dsdf_r
   b2.tile_colsum = w.tile_colsum;
   b2.cta_partials = w.cta_partials;
 
-  ReconUpdateArgs ua;
-  memset(&ua, 0, sizeof(ua));
-  ua.dlat_part = w.seg_sum;
-  ua.tile_partials = w.tile_partials;
-  ua.tiles_per_seg = tiles_per_seg;
-  ua.inv_n = 1.0f / (float)num;
-  ua.reg_kind = cfg->reg_lambda > 0.f ? cfg->reg_kind : 0;
-  ua.reg_lambda = cfg->reg_lambda;
-  ua.dist_kind = (cfg->dist_weight > 0.f && cfg->dist_mean) ? cfg->dist_kind : 0;
-  ua.dist_weight = cfg->dist_weight;
-  ua.dist_mean = cfg->dist_mean;
-  ua.dist_std = cfg->dist_std;
-  ua.b1 = 0.9f;
-  ua.b2 = 0.999f;
-  ua.eps = 1e-8f;
-  ua.code_bound = cfg->code_bound;
-  ua.latents = latents;
-  ua.exp_avg = exp_avg;
-  ua.exp_avg_sq = exp_avg_sq;
+  ReconTailArgs ta;
+  memset(&ta, 0, sizeof(ta));
+  ta.tile_colsum = w.tile_colsum;
+  ta.tile_partials = w.tile_partials;
+  ta.tiles_per_seg = tiles_per_seg;
+  ta.inv_n = 1.0f / (float)num;
+  ta.reg_kind = cfg->reg_lambda > 0.f ? cfg->reg_kind : 0;
+  ta.reg_lambda = cfg->reg_lambda;
+  ta.dist_kind = (cfg->dist_weight > 0.f && cfg->dist_mean) ? cfg->dist_kind : 0;
+  ta.dist_weight = cfg->dist_weight;
+  ta.dist_mean = cfg->dist_mean;
+  ta.dist_std = cfg->dist_std;
+  ta.b1 = 0.9f;
+  ta.b2 = 0.999f;
+  ta.eps = 1e-8f;
+  ta.code_bound = cfg->code_bound;
+  ta.latents = latents;
+  ta.exp_avg = exp_avg;
+  ta.exp_avg_sq = exp_avg_sq;
+  ta.loss_out = w.loss_sink;
+  ta.weff = h->weff;
+  ta.params = params;
+  ta.pl = h->pl;
+  ta.scene_e = w.scene_e;
+  ta.samples = (const float4*)samples;
+  ta.shape_base = (const long long*)shape_base;
+  ta.half = num / 2;
+  ta.rows_pad = rows_pad;
+  ta.sdf = (float4*)w.sdf;
+  ta.ids = w.ids;
 
+  // k_recon_tail: one cluster of kReconParts CTAs per shape.  Inside the loop every launch carries the
+  // programmatic-serialisation attribute: the next grid's prologue (barrier init, TMEM allocation, cluster
+  // handshake) runs on idle SMs under the current grid, and its griddepcontrol.wait orders the data.
+  auto launch_tail = [&](bool do_update, bool do_next, long long e_next, bool pdl) -> cudaError_t {
+    ta.do_update = do_update;
+    ta.do_next = do_next;
+    ta.win = (const long long*)windows + (do_next ? e_next : 0) * n_shapes * 2;
+    cudaLaunchConfig_t lc;
+    memset(&lc, 0, sizeof(lc));
+    lc.gridDim = dim3(kReconParts, (unsigned)n_shapes);
+    lc.blockDim = dim3(kReconThreads);
+    lc.stream = st;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = kReconParts;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    lc.attrs = attr;
+    lc.numAttrs = pdl ? 2 : 1;
+    return cudaLaunchKernelEx(&lc, k_recon_tail, ta);
+  };
+  if (n_shapes > 65535) DSDF_FAIL(h, DSDF_EINVAL, "more than 65535 shapes in one call");
+  if (n_steps == 0) return DSDF_OK;
   long long adjust_every = cfg->num_iterations / 2;
   if (adjust_every < 1) adjust_every = 1;
-  const dim3 ggrid((unsigned)((rows_pad + 255) / 256), (unsigned)n_shapes);
-  for (long long i = 0; i < n_steps; ++i) {
+  // the first launch of the call is ordered the ordinary way behind whatever the caller enqueued before
+  CU(h, launch_tail(false, true, first_step - 1, false));
+#ifndef DSDF_NO_PDL
+  h->pdl = true;
+#endif
+  int rc = DSDF_OK;
+  cudaError_t ce = cudaSuccess;
+  for (long long i = 0; i < n_steps && rc == DSDF_OK && ce == cudaSuccess; ++i) {
     const long long e = first_step - 1 + i;     // 0-based iteration (reconstruct.py:76)
-    k_recon_gather<<<ggrid, 256, 0, st>>>((const float4*)samples, (const long long*)shape_base,
-                                          (const long long*)windows + e * n_shapes * 2, num / 2, rows_pad,
-                                          (float4*)w.sdf, w.ids);
-    k_scene_fold<<<dim3((unsigned)n_shapes, 2, kFoldSplit), 512, 0, st>>>(h->weff, params, h->pl, latents, w.ids,
-                                                             w.scene_e);
-    CU(h, (launch_fwd<MODE_TABLE, true, true>(h, fa, st, true)));
-    int rc = launch_backward2(h, b2, tiles, st, nullptr);
-    if (rc != DSDF_OK) return rc;
-    k_recon_dlat_partial<<<dim3((unsigned)n_shapes, kReconParts), 256, 0, st>>>(w.tile_colsum, tiles_per_seg,
-                                                                             h->weff, w.seg_sum);
+    ce = launch_fwd<MODE_TABLE, true, true>(h, fa, st, true);
+    if (ce != cudaSuccess) break;
+    rc = launch_backward2(h, b2, tiles, st, nullptr);
+    if (rc != DSDF_OK) break;
     const double lr = (double)cfg->lr * pow(0.1, (double)(e / adjust_every));
     const double bc1 = 1.0 - pow(0.9, (double)(e + 1));
     const double bc2 = 1.0 - pow(0.999, (double)(e + 1));
-    ua.step_size = (float)(lr / bc1);
-    ua.bc2_sqrt = (float)sqrt(bc2);
-    ua.loss_out = loss_hist ? loss_hist + e * n_shapes : w.loss_sink;
-    k_recon_update<<<(unsigned)n_shapes, 256, 0, st>>>(ua);
+    ta.step_size = (float)(lr / bc1);
+    ta.bc2_sqrt = (float)sqrt(bc2);
+    ta.loss_out = loss_hist ? loss_hist + e * n_shapes : w.loss_sink;
+    ce = launch_tail(true, i + 1 < n_steps, e + 1, h->pdl);
   }
+  h->pdl = false;
+  if (rc != DSDF_OK) return rc;
+  CU(h, ce);
   CU(h, cudaGetLastError());
   return DSDF_OK;
 }

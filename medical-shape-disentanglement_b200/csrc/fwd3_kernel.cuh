@@ -215,6 +215,10 @@ __global__ void __launch_bounds__(kF3Threads, 1) k_forward3(const __grid_constan
   if (CG > 1) cluster_sync_all();        // the peer's barriers exist before anything is signalled
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  // programmatic dependent launch (dsdf_reconstruct's latency-bound loop; a no-op for ordinary launches): the next
+  // grid may start its own prologue now, and nothing the previous grid wrote is read before it has completed
+  grid_dep_launch();
+  grid_dep_wait();
 
   const long long n_tiles = (a.n_rows + kTileM - 1) / kTileM;
   // every CTA runs the same number of iterations (a pair is lock-stepped through the MMA);

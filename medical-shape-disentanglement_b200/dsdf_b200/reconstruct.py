@@ -191,6 +191,27 @@ def reconstruct_batch(decoder: Decoder, num_iterations: int, shapes: Sequence[Tu
     return hist, lat
 
 
+def reconstruct_sharded(decoder: Decoder, num_iterations: int, shapes: Sequence[Tuple[torch.Tensor, torch.Tensor]],
+                        latents: torch.Tensor, windows: torch.Tensor, clamp_dist: float, rank: int, world_size: int,
+                        **kw):
+    """Shape shard of `reconstruct_batch` (the reference loops over the test split one shape at a time,
+    reconstruct.py:312-420; shapes are independent): rank r optimises the contiguous block
+    [S*r/W, S*(r+1)/W) of the global shape list on its own GPU -- `shapes`, `latents[S,256]` and
+    `windows[num_iterations, S, 2]` are the GLOBAL arguments, identical on every rank.  Returns
+    (lo, hi, loss_hist[num_iterations, hi-lo], latents[hi-lo, 256]); no collective (gather the blocks with
+    all_gather_object / a file per rank if one process needs them all).  A shape's result does not depend on which
+    rank, or which batch mates, it ran with: the blocks concatenated equal the single-GPU call bit for bit."""
+    from .dist import owned_scenes
+    own = owned_scenes(len(shapes), rank, world_size)
+    lo, hi = own.start, own.stop
+    if hi == lo:
+        dev = next(decoder.parameters()).device
+        return lo, hi, torch.zeros(num_iterations, 0, device=dev), torch.zeros(0, LATENT, device=dev)
+    win = torch.as_tensor(windows, dtype=torch.int64).reshape(num_iterations, len(shapes), 2)[:, lo:hi]
+    out = reconstruct_batch(decoder, num_iterations, list(shapes[lo:hi]), latents[lo:hi], win, clamp_dist, **kw)
+    return (lo, hi) + tuple(out)
+
+
 def reconstruct(decoder, num_iterations, latent_size, test_sdf, stat, clamp_dist, num_samples=30000,
                 lr=5e-4, l2reg=False, code_reg_lambda=None, code_reg_type="l2_sq", code_bound=None,
                 return_loss_hist=False, dist_mean=None, dist_std=None, dist_weight=0.0,

@@ -88,6 +88,16 @@ def test_batched_shapes_equal_single_runs_bit_exactly():
                                              lr=5e-3, l2reg=True)
         assert torch.equal(h1[:, 0], hist[:, i])
         assert torch.equal(l1[0], lat[i])
+    # shape-sharded over 2 ranks (no collective: rank r takes a contiguous block of the shape list)
+    got_h, got_l, seen = [], [], []
+    for r in range(2):
+        lo, hi, hr, lr_ = dsdf_b200.reconstruct_sharded(dec, iters, shapes, lat0, wt, 0.1, r, 2, num_samples=num,
+                                                        lr=5e-3, l2reg=True)
+        seen += list(range(lo, hi)); got_h.append(hr); got_l.append(lr_)
+    assert seen == [0, 1, 2]
+    assert torch.equal(torch.cat(got_h, 1), hist) and torch.equal(torch.cat(got_l, 0), lat)
+    lo, hi, hr, lr_ = dsdf_b200.reconstruct_sharded(dec, iters, shapes[:1], lat0[:1], wt[:, :1], 0.1, 0, 2, num_samples=num)
+    assert (lo, hi) == (0, 0) and hr.shape == (iters, 0) and lr_.shape == (0, 256)      # more ranks than shapes
 
 
 def test_reference_signature_consumes_the_same_random_streams():
