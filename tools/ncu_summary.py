@@ -24,3 +24,8 @@ for r in rows[2:]:
     for w in want:
         if w in idx:
             print(f"  {w:95s} {r[idx[w]]:>16s} {units[idx[w]]}")
+    if len(sys.argv) > 2:       # extra columns by regular expression, e.g. 'pipe_.*pct|issue_active|stall'
+        import re
+        for h in hdr:
+            if h not in want and re.search(sys.argv[2], h):
+                print(f"  {h:95s} {r[idx[h]]:>16s} {units[idx[h]]}")
