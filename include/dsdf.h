@@ -304,6 +304,13 @@ int dsdf_sample_points(const float* verts, const int32_t* faces, const float* cd
                        float* surf_out, void* stream);
 int dsdf_knn_sdf(const float* xyz, int64_t n, const float* pts, const float* normals, int64_t n_pts, float stdv,
                  float* sdf_out, int32_t* nn_out, void* stream);
+/* dsdf_knn_sdf through a uniform grid over the visible points (replaces the reference's nanoflann kd-tree,
+ * PreprocessMesh.cpp:137-146): same arguments, same results bit for bit (exact neighbours, ties to the lower index), about
+ * a thousand candidates per near-surface query instead of every point.  workspace: dsdf_knn_grid_workspace_bytes(n_pts)
+ * bytes of device memory (the cell table and the cell-sorted copy of the points), rebuilt by every call. */
+size_t dsdf_knn_grid_workspace_bytes(int64_t n_pts);
+int dsdf_knn_sdf_grid(const float* xyz, int64_t n, const float* pts, const float* normals, int64_t n_pts, float stdv,
+                      void* workspace, size_t workspace_bytes, float* sdf_out, int32_t* nn_out, void* stream);
 int dsdf_gather_windows(const float* samples, const int64_t* base, const int64_t* win, int64_t n_scenes, int64_t half,
                         float* out, void* stream);
 

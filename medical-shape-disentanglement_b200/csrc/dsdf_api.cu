@@ -1552,6 +1552,57 @@ extern "C" int dsdf_knn_sdf(const float* xyz, int64_t n, const float* pts, const
   MC_CU(cudaGetLastError());
   return DSDF_OK;
 }
+// ---- the same query through a uniform grid (exact; bit-identical results).  Workspace: header | counts / cursors |
+// cell starts | block sums | cell-sorted points
+namespace {
+struct KnnWs { KnnGridHdr* hdr; int* cnt; int* start; int* block_sum; float4* sorted; size_t total; };
+KnnWs knn_carve(uint8_t* base, long long n_pts) {
+  KnnWs w;
+  size_t o = 0;
+  auto take = [&](size_t bytes) { uint8_t* p = base ? base + o : nullptr; o += (bytes + 255) & ~(size_t)255; return p; };
+  w.hdr = (KnnGridHdr*)take(sizeof(KnnGridHdr));
+  w.cnt = (int*)take((size_t)(kKnnCells + 1) * 4);
+  w.start = (int*)take((size_t)(kKnnCells + 1) * 4);
+  w.block_sum = (int*)take((size_t)kKnnScanBlocks * 4);
+  w.sorted = (float4*)take((size_t)n_pts * 16);
+  w.total = o;
+  return w;
+}
+}  // namespace
+extern "C" size_t dsdf_knn_grid_workspace_bytes(int64_t n_pts) {
+  if (n_pts <= 0) return 0;
+  return knn_carve(nullptr, n_pts).total + 256;
+}
+extern "C" int dsdf_knn_sdf_grid(const float* xyz, int64_t n, const float* pts, const float* normals, int64_t n_pts,
+                                 float stdv, void* workspace, size_t workspace_bytes, float* sdf_out, int32_t* nn_out,
+                                 void* stream) {
+  if (!xyz || !pts || !normals || !sdf_out || !workspace) { g_err = "null argument"; return DSDF_EINVAL; }
+  if (n <= 0 || n_pts <= 0 || n_pts > (1ll << 31) - 2) { g_err = "bad sizes"; return DSDF_EINVAL; }
+  uint8_t* base = (uint8_t*)(((uintptr_t)workspace + 255) & ~(uintptr_t)255);
+  KnnWs w = knn_carve(base, n_pts);
+  if ((size_t)(base - (uint8_t*)workspace) + w.total > workspace_bytes) {
+    g_err = "workspace too small: need " + std::to_string(w.total + 256) + " bytes, have " + std::to_string(workspace_bytes);
+    return DSDF_ENOMEM;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  const int np = (int)n_pts;
+  const float4* p4 = (const float4*)pts;
+  MC_CU(cudaMemsetAsync(w.cnt, 0, (size_t)(kKnnCells + 1) * 4, st));
+  k_knn_grid_init<<<1, 32, 0, st>>>(w.hdr);
+  int bb = (np + 255) / 256;
+  if (bb > 1184) bb = 1184;
+  k_knn_grid_bbox<<<bb, 256, 0, st>>>(p4, np, w.hdr);
+  k_knn_grid_setup<<<1, 32, 0, st>>>(w.hdr);
+  k_knn_grid_count<<<(np + 255) / 256, 256, 0, st>>>(p4, np, w.hdr, w.cnt);
+  k_knn_scan_local<<<kKnnScanBlocks, kKnnScanBlock, 0, st>>>(w.cnt, w.start, w.block_sum);
+  k_knn_scan_blocks<<<1, kKnnScanBlock, 0, st>>>(w.block_sum);
+  k_knn_scan_add<<<kKnnScanBlocks, kKnnScanBlock, 0, st>>>(w.start, w.block_sum, w.cnt);   // counts become the cursors
+  k_knn_grid_fill<<<(np + 255) / 256, 256, 0, st>>>(p4, np, w.hdr, w.start, w.cnt, w.sorted);
+  k_knn_sdf_grid<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(xyz, n, w.sorted, w.start, w.hdr, p4, (const float4*)normals,
+                                                             stdv, sdf_out, nn_out);
+  MC_CU(cudaGetLastError());
+  return DSDF_OK;
+}
 extern "C" int dsdf_gather_windows(const float* samples, const int64_t* base, const int64_t* win, int64_t n_scenes,
                                    int64_t half, float* out, void* stream) {
   if (!samples || !base || !win || !out) { g_err = "null argument"; return DSDF_EINVAL; }

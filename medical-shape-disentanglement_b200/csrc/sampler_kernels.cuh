@@ -231,6 +231,34 @@ __global__ void __launch_bounds__(256) k_sample_points(const float* __restrict__
 
 // ---- nearest visible points, distance, sign vote ------------------------------------------------------------------
 constexpr int kVotes = 11;                                       // PreprocessMesh.cpp:537
+// distance + sign vote from the 11 nearest (bi sorted nearest first), SampleSDFNearSurface :147-172
+__device__ __forceinline__ void knn_vote(long long q, float qx, float qy, float qz, const int (&bi)[kVotes],
+                                         const float4* __restrict__ pts, const float4* __restrict__ nrm, float stdv,
+                                         float* __restrict__ sdf_out, int* __restrict__ nn_out) {
+  int num_pos = 0;
+  float sdf = 0.f;
+#pragma unroll
+  for (int k = 0; k < kVotes; ++k) {
+    const int ci = bi[k];
+    if (nn_out) nn_out[q * kVotes + k] = ci;
+    if (ci < 0) continue;                                        // fewer than 11 visible points: cannot be unanimous
+    const float4 p = pts[ci], m = nrm[ci];
+    const float rx = __fadd_rn(qx, -p.x), ry = __fadd_rn(qy, -p.y), rz = __fadd_rn(qz, -p.z);
+    const float len = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(rx, rx), __fmul_rn(ry, ry)), __fmul_rn(rz, rz)));
+    if (k == 0) {
+      const float pl = __fadd_rn(__fadd_rn(__fmul_rn(m.x, rx), __fmul_rn(m.y, ry)), __fmul_rn(m.z, rz));
+      sdf = len < stdv ? fabsf(pl) : len;                        // close to the surface: point-plane distance
+    }
+    const float d = __fadd_rn(__fadd_rn(__fmul_rn(m.x, __fdiv_rn(rx, len)), __fmul_rn(m.y, __fdiv_rn(ry, len))),
+                              __fmul_rn(m.z, __fdiv_rn(rz, len)));
+    if (d > 0.f) ++num_pos;
+  }
+  const bool full = bi[kVotes - 1] >= 0;
+  if (full && (num_pos == 0 || num_pos == kVotes)) sdf_out[q] = num_pos <= kVotes / 2 ? -sdf : sdf;
+  else sdf_out[q] = __int_as_float(0x7fc00000);
+}
+
+
 constexpr int kKnnTile = 1024;
 // sdf_out[n]: the signed distance, or NaN where the vote was not unanimous (the reference drops those samples);
 // nn_out (nullable) [n][11]: the neighbour indices, nearest first.  Ties in distance go to the lower index.
@@ -261,7 +289,8 @@ __global__ void __launch_bounds__(256) k_knn_sdf(const float* __restrict__ xyz, 
         int ci = base + j;
 #pragma unroll
         for (int k = 0; k < kVotes; ++k) {
-          if (cd < bd[k]) {
+          // (distance, index) order: a displaced entry must not hop over an entry of equal distance and higher index
+          if (cd < bd[k] || (cd == bd[k] && ci < bi[k])) {
             const float td = bd[k]; const int ti = bi[k];
             bd[k] = cd; bi[k] = ci;
             cd = td; ci = ti;
@@ -271,27 +300,259 @@ __global__ void __launch_bounds__(256) k_knn_sdf(const float* __restrict__ xyz, 
     }
   }
   if (!live) return;
-  int num_pos = 0;
-  float sdf = 0.f;
+  knn_vote(q, qx, qy, qz, bi, pts, nrm, stdv, sdf_out, nn_out);
+}
+
+// ---- the same query through a uniform grid over the visible points ------------------------------------------------
+// Exact, and bit-identical to k_knn_sdf (same rounded distance expression, ties to the lower ORIGINAL index): the
+// points are counting-sorted into kKnnGrid^3 cubic cells over their bounding box; a query visits the cells around its
+// own in growing Chebyshev shells and stops once its 11th distance is strictly below the distance to the nearest face of
+// the visited cube that still has cells behind it (minus a margin that covers the rounding of the cell assignment),
+// i.e. once no unvisited point can enter the list.  Within a cell the order of the points is whatever the counting
+// sort's integer atomics produced; the (distance, original index) order of the insertion makes the result independent
+// of it.  ~10^3 candidates per near-surface query instead of every visible point (10^6..10^7).
+constexpr int kKnnGrid = 128;
+constexpr int kKnnCells = kKnnGrid * kKnnGrid * kKnnGrid;
+struct KnnGridHdr {
+  int lo[3], hi[3];           // bounding box as order-preserving integer images of the floats (atomicMin / atomicMax)
+  float origin[3], h, inv_h;  // derived by k_knn_grid_setup
+};
+__device__ __forceinline__ int knn_f2ord(float f) { const int i = __float_as_int(f); return i >= 0 ? i : i ^ 0x7fffffff; }
+__device__ __forceinline__ float knn_ord2f(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); }
+__device__ __forceinline__ int knn_cell_axis(float p, float origin, float inv_h) {
+  const int c = (int)floorf(__fmul_rn(__fadd_rn(p, -origin), inv_h));
+  return min(max(c, 0), kKnnGrid - 1);
+}
+
+__global__ void k_knn_grid_init(KnnGridHdr* hdr) {
+  if (threadIdx.x < 3) { hdr->lo[threadIdx.x] = 0x7fffffff; hdr->hi[threadIdx.x] = (int)0x80000000; }
+}
+__global__ void __launch_bounds__(256) k_knn_grid_bbox(const float4* __restrict__ pts, int n_pts, KnnGridHdr* hdr) {
+  int lo[3] = {0x7fffffff, 0x7fffffff, 0x7fffffff}, hi[3] = {(int)0x80000000, (int)0x80000000, (int)0x80000000};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_pts; i += gridDim.x * blockDim.x) {
+    const float4 p = pts[i];
+    const int o[3] = {knn_f2ord(p.x), knn_f2ord(p.y), knn_f2ord(p.z)};
 #pragma unroll
-  for (int k = 0; k < kVotes; ++k) {
-    const int ci = bi[k];
-    if (nn_out) nn_out[q * kVotes + k] = ci;
-    if (ci < 0) continue;                                        // fewer than 11 visible points: cannot be unanimous
-    const float4 p = pts[ci], m = nrm[ci];
-    const float rx = __fadd_rn(qx, -p.x), ry = __fadd_rn(qy, -p.y), rz = __fadd_rn(qz, -p.z);
-    const float len = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(rx, rx), __fmul_rn(ry, ry)), __fmul_rn(rz, rz)));
-    if (k == 0) {
-      const float pl = __fadd_rn(__fadd_rn(__fmul_rn(m.x, rx), __fmul_rn(m.y, ry)), __fmul_rn(m.z, rz));
-      sdf = len < stdv ? fabsf(pl) : len;                        // close to the surface: point-plane distance
-    }
-    const float d = __fadd_rn(__fadd_rn(__fmul_rn(m.x, __fdiv_rn(rx, len)), __fmul_rn(m.y, __fdiv_rn(ry, len))),
-                              __fmul_rn(m.z, __fdiv_rn(rz, len)));
-    if (d > 0.f) ++num_pos;
+    for (int a = 0; a < 3; ++a) { lo[a] = min(lo[a], o[a]); hi[a] = max(hi[a], o[a]); }
   }
-  const bool full = bi[kVotes - 1] >= 0;
-  if (full && (num_pos == 0 || num_pos == kVotes)) sdf_out[q] = num_pos <= kVotes / 2 ? -sdf : sdf;
-  else sdf_out[q] = __int_as_float(0x7fc00000);
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) {
+      lo[a] = min(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], s));
+      hi[a] = max(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], s));
+    }
+    if ((threadIdx.x & 31) == 0) { atomicMin(&hdr->lo[a], lo[a]); atomicMax(&hdr->hi[a], hi[a]); }
+  }
+}
+__global__ void k_knn_grid_setup(KnnGridHdr* hdr) {
+  if (threadIdx.x != 0) return;
+  float ext = 0.f;
+  for (int a = 0; a < 3; ++a) ext = fmaxf(ext, knn_ord2f(hdr->hi[a]) - knn_ord2f(hdr->lo[a]));
+  ext = fmaxf(ext, 1e-6f);
+  const float h = ext * (1.f + 1e-3f) / kKnnGrid;
+  for (int a = 0; a < 3; ++a) hdr->origin[a] = knn_ord2f(hdr->lo[a]) - 0.5e-3f * ext;
+  hdr->h = h;
+  hdr->inv_h = 1.f / h;
+}
+// cells are numbered block-major: 8 x 8 x 8 cells form a coarse cell whose 512 cells (and so whose points, after the
+// sort) are contiguous -- "is this coarse cell empty" is two loads of the start table
+constexpr int kKnnBlock = 8, kKnnCoarse = kKnnGrid / kKnnBlock, kKnnBlockCells = kKnnBlock * kKnnBlock * kKnnBlock;
+__device__ __forceinline__ int knn_cell_index(int x, int y, int z) {
+  return (((z >> 3) * kKnnCoarse + (y >> 3)) * kKnnCoarse + (x >> 3)) * kKnnBlockCells + (((z & 7) * 8 + (y & 7)) * 8 + (x & 7));
+}
+__device__ __forceinline__ int knn_cell_of(const float4& p, const KnnGridHdr& g) {
+  return knn_cell_index(knn_cell_axis(p.x, g.origin[0], g.inv_h), knn_cell_axis(p.y, g.origin[1], g.inv_h),
+                        knn_cell_axis(p.z, g.origin[2], g.inv_h));
+}
+__global__ void __launch_bounds__(256) k_knn_grid_count(const float4* __restrict__ pts, int n_pts,
+                                                        const KnnGridHdr* __restrict__ hdr, int* __restrict__ cnt) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n_pts) atomicAdd(cnt + knn_cell_of(pts[i], *hdr), 1);
+}
+// exclusive prefix sum over kKnnCells + 1 counts in three launches (1024 values per block)
+constexpr int kKnnScanBlock = 1024;
+constexpr int kKnnScanBlocks = (kKnnCells + 1 + kKnnScanBlock - 1) / kKnnScanBlock;
+__device__ __forceinline__ int knn_block_exscan(int v, int* sh, int& total) {   // 1024 threads
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int inc = v;
+#pragma unroll
+  for (int s = 1; s < 32; s <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, s); if (lane >= s) inc += t; }
+  if (lane == 31) sh[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    int w = sh[lane];
+#pragma unroll
+    for (int s = 1; s < 32; s <<= 1) { const int t = __shfl_up_sync(0xffffffffu, w, s); if (lane >= s) w += t; }
+    sh[lane] = w;
+  }
+  __syncthreads();
+  total = sh[31];
+  const int base = warp ? sh[warp - 1] : 0;
+  __syncthreads();
+  return base + inc - v;
+}
+__global__ void __launch_bounds__(kKnnScanBlock) k_knn_scan_local(const int* __restrict__ cnt, int* __restrict__ start,
+                                                                 int* __restrict__ block_sum) {
+  __shared__ int sh[32];
+  const int i = blockIdx.x * kKnnScanBlock + threadIdx.x;
+  int total;
+  const int ex = knn_block_exscan(i < kKnnCells ? cnt[i] : 0, sh, total);
+  if (i <= kKnnCells) start[i] = ex;
+  if (threadIdx.x == 0) block_sum[blockIdx.x] = total;
+}
+__global__ void __launch_bounds__(kKnnScanBlock) k_knn_scan_blocks(int* __restrict__ block_sum) {
+  __shared__ int sh[32];
+  __shared__ int carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (int b0 = 0; b0 < kKnnScanBlocks; b0 += kKnnScanBlock) {
+    const int i = b0 + threadIdx.x;
+    int total;
+    const int ex = knn_block_exscan(i < kKnnScanBlocks ? block_sum[i] : 0, sh, total);
+    const int c = carry;
+    __syncthreads();
+    if (i < kKnnScanBlocks) block_sum[i] = c + ex;
+    if (threadIdx.x == 0) carry = c + total;
+    __syncthreads();
+  }
+}
+__global__ void __launch_bounds__(kKnnScanBlock) k_knn_scan_add(int* __restrict__ start, const int* __restrict__ block_sum,
+                                                               int* __restrict__ cursor) {
+  const int i = blockIdx.x * kKnnScanBlock + threadIdx.x;
+  if (i <= kKnnCells) start[i] += block_sum[blockIdx.x];
+  if (i < kKnnCells) cursor[i] = 0;
+}
+// sorted[slot] = (x, y, z, original index bits)
+__global__ void __launch_bounds__(256) k_knn_grid_fill(const float4* __restrict__ pts, int n_pts,
+                                                       const KnnGridHdr* __restrict__ hdr, const int* __restrict__ start,
+                                                       int* __restrict__ cursor, float4* __restrict__ sorted) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_pts) return;
+  const float4 p = pts[i];
+  const int c = knn_cell_of(p, *hdr);
+  const int slot = start[c] + atomicAdd(cursor + c, 1);
+  sorted[slot] = make_float4(p.x, p.y, p.z, __int_as_float(i));
+}
+// one thread per query; sdf_out / nn_out as k_knn_sdf
+__global__ void __launch_bounds__(128) k_knn_sdf_grid(const float* __restrict__ xyz, long long n,
+                                                      const float4* __restrict__ sorted, const int* __restrict__ start,
+                                                      const KnnGridHdr* __restrict__ hdr,
+                                                      const float4* __restrict__ pts, const float4* __restrict__ nrm,
+                                                      float stdv, float* __restrict__ sdf_out, int* __restrict__ nn_out) {
+  const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= n) return;
+  const float qv[3] = {xyz[q * 3], xyz[q * 3 + 1], xyz[q * 3 + 2]};
+  const float org[3] = {hdr->origin[0], hdr->origin[1], hdr->origin[2]};
+  const float h = hdr->h, inv_h = hdr->inv_h;
+  int c[3];
+#pragma unroll
+  for (int a = 0; a < 3; ++a) c[a] = knn_cell_axis(qv[a], org[a], inv_h);
+  float bd[kVotes];
+  int bi[kVotes];
+#pragma unroll
+  for (int k = 0; k < kVotes; ++k) { bd[k] = 3.0e38f; bi[k] = -1; }
+  auto scan = [&](int s, int e) {
+    for (int j = s; j < e; ++j) {
+      const float4 p = __ldg(sorted + j);
+      const float dx = __fadd_rn(qv[0], -p.x), dy = __fadd_rn(qv[1], -p.y), dz = __fadd_rn(qv[2], -p.z);
+      const float d = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+      int ci = __float_as_int(p.w);
+      if (d < bd[kVotes - 1] || (d == bd[kVotes - 1] && ci < bi[kVotes - 1])) {
+        float cd = d;
+#pragma unroll
+        for (int k = 0; k < kVotes; ++k) {
+          if (cd < bd[k] || (cd == bd[k] && ci < bi[k])) {
+            const float td = bd[k]; const int ti = bi[k];
+            bd[k] = cd; bi[k] = ci;
+            cd = td; ci = ti;
+          }
+        }
+      }
+    }
+  };
+  auto visit = [&](int cx, int cy, int cz) {
+    const int cell = knn_cell_index(cx, cy, cz);
+    scan(__ldg(start + cell), __ldg(start + cell + 1));
+  };
+  // squared distance from the query to the box [lo, lo + w)^3 along each axis, shrunk by the rounding margin
+  const float margin = 1e-3f * h;
+  auto box_d2 = [&](float lx, float ly, float lz, float w) {
+    const float l[3] = {lx, ly, lz};
+    float d2 = 0.f;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+      const float t = fmaxf(fmaxf(l[a] - qv[a], qv[a] - (l[a] + w)) - margin, 0.f);
+      d2 += t * t;
+    }
+    return d2;
+  };
+  // shells of a cube lattice of `cells` per axis around `ctr`, radius R: f(x, y, z) for every lattice point on the shell
+  auto shell = [&](const int (&ctr)[3], int R, int cells, auto&& f) {
+    const int lo[3] = {ctr[0] - R, ctr[1] - R, ctr[2] - R}, hi[3] = {ctr[0] + R, ctr[1] + R, ctr[2] + R};
+    const int z0 = max(lo[2], 0), z1 = min(hi[2], cells - 1);
+    const int y0 = max(lo[1], 0), y1 = min(hi[1], cells - 1);
+    const int x0 = max(lo[0], 0), x1 = min(hi[0], cells - 1);
+    for (int z = z0; z <= z1; ++z)
+      for (int y = y0; y <= y1; ++y) {
+        if (z == lo[2] || z == hi[2] || y == lo[1] || y == hi[1]) {
+          for (int x = x0; x <= x1; ++x) f(x, y, z);
+        } else {
+          if (lo[0] >= 0) f(lo[0], y, z);
+          if (R > 0 && hi[0] <= cells - 1) f(hi[0], y, z);
+        }
+      }
+  };
+  // true once no point outside the cube of lattice cells [ctr - R, ctr + R] (cell width w) can enter the list
+  auto finished = [&](const int (&ctr)[3], int R, int cells, float w, bool& all_visited) {
+    float df = 3.0e38f;
+    bool open = false;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+      const int lo = ctr[a] - R, hi = ctr[a] + R;
+      if (lo > 0) { df = fminf(df, qv[a] - (org[a] + (float)lo * w)); open = true; }
+      if (hi < cells - 1) { df = fminf(df, (org[a] + (float)(hi + 1) * w) - qv[a]); open = true; }
+    }
+    all_visited = !open;
+    if (!open) return true;
+    df -= margin;
+    return bi[kVotes - 1] >= 0 && df > 0.f && bd[kVotes - 1] < df * df;
+  };
+  // ---- fine phase: the query's own cell and the 26 around it (enough for a query close to the surface)
+  constexpr int kFineR = 1;
+  bool done = false, all = false;
+  for (int R = 0; R <= kFineR && !done; ++R) {
+    shell(c, R, kKnnGrid, visit);
+    done = finished(c, R, kKnnGrid, h, all);
+  }
+  // ---- coarse phase: shells of 8^3-cell blocks; empty blocks cost two loads, blocks and cells that cannot hold a
+  // closer point are skipped by their box distance, cells of the fine phase are not visited twice
+  if (!done) {
+    const int cc[3] = {c[0] >> 3, c[1] >> 3, c[2] >> 3};
+    const float wc = (float)kKnnBlock * h;
+    auto visit_block = [&](int X, int Y, int Z) {
+      const int cb = ((Z * kKnnCoarse + Y) * kKnnCoarse + X) * kKnnBlockCells;
+      if (__ldg(start + cb) == __ldg(start + cb + kKnnBlockCells)) return;
+      const float bx = org[0] + (float)(X * kKnnBlock) * h, by = org[1] + (float)(Y * kKnnBlock) * h,
+                  bz = org[2] + (float)(Z * kKnnBlock) * h;
+      if (bi[kVotes - 1] >= 0 && box_d2(bx, by, bz, wc) > bd[kVotes - 1]) return;
+      for (int l = 0; l < kKnnBlockCells; ++l) {
+        const int s0 = __ldg(start + cb + l), e0 = __ldg(start + cb + l + 1);
+        if (s0 == e0) continue;
+        const int fx = X * kKnnBlock + (l & 7), fy = Y * kKnnBlock + ((l >> 3) & 7), fz = Z * kKnnBlock + (l >> 6);
+        if (max(max(abs(fx - c[0]), abs(fy - c[1])), abs(fz - c[2])) <= kFineR) continue;
+        if (bi[kVotes - 1] >= 0 &&
+            box_d2(org[0] + (float)fx * h, org[1] + (float)fy * h, org[2] + (float)fz * h, h) > bd[kVotes - 1])
+          continue;
+        scan(s0, e0);
+      }
+    };
+    for (int R = 0; R < kKnnCoarse; ++R) {
+      shell(cc, R, kKnnCoarse, visit_block);
+      if (finished(cc, R, kKnnCoarse, wc, all)) break;
+    }
+  }
+  knn_vote(q, qv[0], qv[1], qv[2], bi, pts, nrm, stdv, sdf_out, nn_out);
 }
 
 // ---- GPU-resident sample windows (deep_sdf/data.py:112-136 for a batch) ----------------------------------------------

@@ -13,4 +13,4 @@ from .mesh import (convert_sdf_samples_to_ply, create_mesh, create_mesh_sdf, dec
 from .reconstruct import reconstruct, reconstruct_batch, reconstruct_sharded, draw_windows, plan_samples  # noqa: F401
 from . import data, siren  # noqa: F401,E402  (sample-file contract; SIREN decoder family)
 from .autograd_fn import decode_segments  # noqa: F401,E402
-from .preprocess import GpuSDFSamples, preprocess_mesh, sample_sdf_near_surface, visible_surface_points  # noqa: F401,E402
+from .preprocess import GpuSDFSamples, nearest_visible_sdf, preprocess_mesh, sample_sdf_near_surface, visible_surface_points  # noqa: F401,E402

@@ -23,7 +23,7 @@ EXPORTS = [
     "dsdf_segments_forward_train", "dsdf_segments_backward", "dsdf_set_dropout", "dsdf_dropout_keep", "dsdf_reconstruct_workspace_bytes", "dsdf_reconstruct",
     "dsdf_selftest_gemm", "dsdf_profile_enable", "dsdf_profile_read", "dsdf_debug_read", "dsdf_selftest_mma_rate", "dsdf_debug_hang_buffer",
     "dsdf_debug_progress_buffer", "dsdf_mc_classify", "dsdf_mc_emit",
-    "dsdf_rasterize_views", "dsdf_rasterize_views_static", "dsdf_sample_points", "dsdf_knn_sdf", "dsdf_gather_windows",
+    "dsdf_rasterize_views", "dsdf_rasterize_views_static", "dsdf_sample_points", "dsdf_knn_sdf", "dsdf_knn_grid_workspace_bytes", "dsdf_knn_sdf_grid", "dsdf_gather_windows",
 ]
 
 
@@ -134,6 +134,10 @@ def lib(arch: str = "deep_sdf_decoder"):
     L.dsdf_sample_points.restype = C.c_int
     L.dsdf_knn_sdf.argtypes = [vp, i64, vp, vp, i64, f32, vp, vp, vp]
     L.dsdf_knn_sdf.restype = C.c_int
+    L.dsdf_knn_grid_workspace_bytes.argtypes = [i64]
+    L.dsdf_knn_grid_workspace_bytes.restype = C.c_size_t
+    L.dsdf_knn_sdf_grid.argtypes = [vp, i64, vp, vp, i64, f32, vp, C.c_size_t, vp, vp, vp]
+    L.dsdf_knn_sdf_grid.restype = C.c_int
     L.dsdf_gather_windows.argtypes = [vp, vp, vp, i64, i64, vp, vp]
     L.dsdf_gather_windows.restype = C.c_int
     _libs[arch] = L

@@ -117,9 +117,40 @@ def visible_surface_points(verts: torch.Tensor, faces: torch.Tensor, views: Opti
 
 
 @torch.no_grad()
+def nearest_visible_sdf(xyz: torch.Tensor, pts: torch.Tensor, nrm: torch.Tensor, stdv: float, method: str = "grid",
+                        return_neighbours: bool = False):
+    """SampleSDFNearSurface :137-172 for every row of xyz [n,3]: the signed distance from the 11 nearest visible points
+    (pts / nrm float4 rows), NaN where the sign vote is split.  method "grid" (uniform grid, dsdf_knn_sdf_grid) and
+    "brute" (all pairs, dsdf_knn_sdf) give bit-identical results; the reference uses a nanoflann kd-tree."""
+    L = _lib.lib()
+    dev = xyz.device
+    if dev.type != "cuda":
+        raise _lib.DsdfError("nearest_visible_sdf needs CUDA tensors (there is no CPU path)")
+    q = xyz.contiguous().float()
+    p4, n4 = pts.contiguous().float(), nrm.contiguous().float()
+    n = q.shape[0]
+    with torch.cuda.device(dev):
+        sdf = torch.empty(n, dtype=torch.float32, device=dev)
+        nn = torch.empty(n, NUM_VOTES, dtype=torch.int32, device=dev) if return_neighbours else None
+        nn_ptr = nn.data_ptr() if nn is not None else None
+        if method == "brute":
+            _lib.check(L.dsdf_knn_sdf(q.data_ptr(), n, p4.data_ptr(), n4.data_ptr(), p4.shape[0], float(stdv), sdf.data_ptr(),
+                                      nn_ptr, _st(dev)), None, L)
+        elif method == "grid":
+            ws = torch.empty(L.dsdf_knn_grid_workspace_bytes(p4.shape[0]), dtype=torch.uint8, device=dev)
+            _lib.check(L.dsdf_knn_sdf_grid(q.data_ptr(), n, p4.data_ptr(), n4.data_ptr(), p4.shape[0], float(stdv),
+                                           ws.data_ptr(), ws.numel(), sdf.data_ptr(), nn_ptr, _st(dev)), None, L)
+            torch.cuda.current_stream(dev).synchronize()      # the workspace must outlive the enqueued kernels
+        else:
+            raise ValueError(f"unknown method {method!r} (grid | brute)")
+    return (sdf, nn) if return_neighbours else sdf
+
+
+@torch.no_grad()
 def sample_sdf_near_surface(verts: torch.Tensor, faces: torch.Tensor, pts: torch.Tensor, nrm: torch.Tensor,
                             num_sample: int = 500000, variance: float = 0.005, second_variance: Optional[float] = None,
-                            seed: int = 0, near_ratio: Tuple[int, int] = (47, 50), return_all: bool = False):
+                            seed: int = 0, near_ratio: Tuple[int, int] = (47, 50), return_all: bool = False,
+                            knn: str = "grid"):
     """SampleFromSurface + SampleSDFNearSurface (PreprocessMesh.cpp:22-178, call site :516-537).  Returns (xyz [n,3],
     sdf [n]) of the samples whose 11-neighbour vote was unanimous, in generation order."""
     L = _lib.lib()
@@ -139,10 +170,7 @@ def sample_sdf_near_surface(verts: torch.Tensor, faces: torch.Tensor, pts: torch
         _lib.check(L.dsdf_sample_points(v.data_ptr(), f.data_ptr(), cdf.data_ptr(), f.shape[0], n_surf, n_rand,
                                         float(np.float32(stdv)), float(np.float32(math.sqrt(second_variance))), 2.0,
                                         int(seed) & 0xFFFFFFFFFFFFFFFF, xyz.data_ptr(), None, _st(dev)), None, L)
-        sdf = torch.empty(n, dtype=torch.float32, device=dev)
-        p4, n4 = pts.contiguous().float(), nrm.contiguous().float()
-        _lib.check(L.dsdf_knn_sdf(xyz.data_ptr(), n, p4.data_ptr(), n4.data_ptr(), p4.shape[0], float(np.float32(stdv)),
-                                  sdf.data_ptr(), None, _st(dev)), None, L)
+    sdf = nearest_visible_sdf(xyz, pts, nrm, float(np.float32(stdv)), method=knn)
     if return_all:
         return xyz, sdf
     keep = ~torch.isnan(sdf)

@@ -91,6 +91,59 @@ def test_knn_sign_vote_equals_the_oracle_on_the_same_inputs():
     assert 0.005 < np.isnan(got).mean() < 0.6                   # both outcomes of the vote are exercised
 
 
+def _same_knn(q, pts, nrm, stdv):
+    a, ann = P.nearest_visible_sdf(q, pts, nrm, stdv, method="brute", return_neighbours=True)
+    b, bnn = P.nearest_visible_sdf(q, pts, nrm, stdv, method="grid", return_neighbours=True)
+    assert torch.equal(ann, bnn)
+    assert torch.equal(a.view(torch.int32), b.view(torch.int32))             # NaNs included
+    return a, ann
+
+
+def test_grid_search_equals_the_all_pairs_search_bit_for_bit():
+    """dsdf_knn_sdf_grid (uniform grid, growing shells) against dsdf_knn_sdf (all pairs), itself pinned to the oracle
+    above: neighbour lists and distances identical -- near and far queries, queries outside the points' bounding box,
+    duplicated points (distance ties go to the lower index), fewer than 11 points, degenerate point sets."""
+    v, f = icosphere(3, 0.5, (0.05, 0.0, -0.02))
+    vd, fd = torch.from_numpy(v).cuda(), torch.from_numpy(f).cuda()
+    pts, nrm = P.visible_surface_points(vd, fd, P.look_at_views(P.equidist_points_on_sphere(100, 1.1)[::5]))
+    assert pts.shape[0] > 200000
+    g = torch.Generator().manual_seed(7)
+    q = torch.cat([torch.rand(3000, 3, generator=g) * 2 - 1,                              # uniform in the cube
+                   torch.nn.functional.normalize(torch.randn(6000, 3, generator=g), dim=1) * 0.5 +
+                   torch.randn(6000, 3, generator=g) * 0.02,                              # hugging the surface
+                   torch.randn(500, 3, generator=g) * 3.0,                                # far outside the bounding box
+                   pts[::997, :3].cpu()]).cuda()                                          # exactly on visible points
+    stdv = float(np.float32(math.sqrt(0.005)))
+    sdf, nn = _same_knn(q, pts, nrm, stdv)
+    assert 0.0 < float(torch.isnan(sdf).float().mean()) < 0.6
+    # ties: every point three times (and shuffled), so each distance occurs at three indices
+    perm = torch.randperm(3 * 20000, generator=g).cuda()
+    p3 = pts[:20000].repeat(3, 1)[perm].contiguous()
+    n3 = nrm[:20000].repeat(3, 1)[perm].contiguous()
+    _, nn3 = _same_knn(q[:4000], p3, n3, stdv)
+    d = (q[:4000, None, :] - p3[nn3.long()][:, :, :3]).norm(dim=2)
+    assert bool((d[:, 1:] >= d[:, :-1] - 1e-6).all())
+    same_pt = (p3[nn3[:, 1:].long()][:, :, :3] == p3[nn3[:, :-1].long()][:, :, :3]).all(2)   # copies of one point: exact ties
+    assert bool(same_pt.any()) and bool((nn3[:, 1:][same_pt] > nn3[:, :-1][same_pt]).all())  # ... lower index first
+    # the same tie rule as the oracle's stable argsort, on a set small enough for it (each point three times)
+    perm_s = torch.randperm(3 * 1500, generator=g).cuda()
+    ps = pts[::400][:1500].repeat(3, 1)[perm_s].contiguous()
+    ns = nrm[::400][:1500].repeat(3, 1)[perm_s].contiguous()
+    qs = torch.cat([q[:150], q[3000:3150]])
+    s_s, nn_s = _same_knn(qs, ps, ns, stdv)
+    want_s, want_nn = opp.knn_sdf(qs.cpu().numpy(), ps.cpu().numpy(), ns.cpu().numpy(), np.float32(stdv))
+    assert np.array_equal(nn_s.cpu().numpy(), want_nn)
+    assert np.array_equal(s_s.cpu().numpy().view(np.int32), want_s.view(np.int32))
+    # fewer than 11 points: every vote is incomplete -> NaN, the list is padded with -1
+    s7, nn7 = _same_knn(q[:100], pts[:7].contiguous(), nrm[:7].contiguous(), stdv)
+    assert bool(torch.isnan(s7).all()) and bool((nn7[:, 7:] == -1).all()) and bool((nn7[:, :7] >= 0).all())
+    # degenerate sets: all points identical; all points in one plane
+    one = pts[:1].repeat(50, 1).contiguous()
+    _same_knn(q[:200], one, nrm[:50].contiguous(), stdv)
+    flat = pts[:5000].clone(); flat[:, 2] = 0.125
+    _same_knn(q[:2000], flat.contiguous(), nrm[:5000].contiguous(), stdv)
+
+
 def test_preprocess_mesh_end_to_end_against_the_analytic_sphere():
     v, f = icosphere(4, 0.5, (0.2, -0.1, 0.05))                  # 5120 faces; the pipeline re-centres it
     pos, neg = dsdf_b200.preprocess_mesh(v, f, num_sample=60000, seed=3)
