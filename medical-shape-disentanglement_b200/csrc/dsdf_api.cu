@@ -71,6 +71,8 @@ struct dsdf_handle_s {
   uint8_t* wg2_stage = nullptr;        // pinned host staging for both arrays
   cudaEvent_t wg2_uploaded = nullptr;  // last upload has been consumed by the copy engine
   long long wg2_tiles = -1;
+  int wg2_max_quads = 0;         // 4-CTA clusters of k_wgrad2<.., QUAD> the device can hold at once (GPC granularity)
+  bool wg2_mc = false;           // schedule is for k_wgrad2<.., QUAD>: 4-CTA clusters, multicast X loads
   int wg2_with_l8 = -1;          // schedule currently holds a lin8 item (autograd entries) or not (fused step)
   int wg2_pairs = 0;
   int wg2_slots = 0;
@@ -192,6 +194,28 @@ static int set_kernel_attrs(dsdf_handle h) {
   CU(h, cudaFuncSetAttribute(k_backward2<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, B2<2>::kSmemBytes));
   CU(h, cudaFuncSetAttribute(k_wgrad2<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kW2SmemBytes));
   CU(h, cudaFuncSetAttribute(k_wgrad2<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kW2SmemBytes));
+  CU(h, (cudaFuncSetAttribute(k_wgrad2<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kW2SmemBytes)));
+  CU(h, (cudaFuncSetAttribute(k_wgrad2<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kW2SmemBytes)));
+  {
+    // a 4-CTA cluster must sit inside one GPC, and the GPCs' SM counts are not all multiples of 4: fewer than
+    // num_sms / 4 clusters fit at once.  The static wgrad schedule must not have more work ranges than that, or the
+    // surplus clusters run as a second wave behind the first.
+    cudaLaunchConfig_t oc;
+    memset(&oc, 0, sizeof(oc));
+    oc.gridDim = dim3((unsigned)(h->num_sms / 4 * 4));
+    oc.blockDim = dim3(kW2Threads);
+    oc.dynamicSmemBytes = kW2SmemBytes;
+    cudaLaunchAttribute oa[1];
+    oa[0].id = cudaLaunchAttributeClusterDimension;
+    oa[0].val.clusterDim.x = 4;
+    oa[0].val.clusterDim.y = 1;
+    oa[0].val.clusterDim.z = 1;
+    oc.attrs = oa;
+    oc.numAttrs = 1;
+    int nq = 0;
+    if (cudaOccupancyMaxActiveClusters(&nq, k_wgrad2<true, true>, &oc) != cudaSuccess) { nq = 0; cudaGetLastError(); }
+    h->wg2_max_quads = nq < h->num_sms / 4 ? nq : h->num_sms / 4;
+  }
   h->attrs_set = true;
   return DSDF_OK;
 }
@@ -557,6 +581,10 @@ static int build_wg2_schedule(dsdf_handle h, long long tiles, cudaStream_t st, b
   if (n_pairs < 1) n_pairs = 1;
   std::vector<WgSeg> segs;
   std::vector<int> seg_begin;
+  // multicast variant (fused step: no lin8 item): the two pairs of a quad run as one 4-CTA cluster in lock step, so
+  // every segment of a quad must give both pairs the same tile range
+  const bool mc = !with_l8 && h->wg_quad && h->wg2_max_quads >= 1;
+  if (mc) n_pairs = 2 * h->wg2_max_quads;                  // every cluster resident from the start
   if (h->wg_quad && n_pairs >= 2) {
     // "quad" schedule: two CTA pairs walk the SAME tile range of a layer side by side, one per
     // 256-row out chunk, so the X tiles the second pair needs are L2 hits behind the first pair's
@@ -584,6 +612,12 @@ static int build_wg2_schedule(dsdf_handle h, long long tiles, cudaStream_t st, b
         if (two) {
           a.ocp = 0; a.tile_lo = t0; a.tile_hi = t0 + take; per_pair[2 * q].push_back(a);
           a.ocp = 1; per_pair[2 * q + 1].push_back(a);
+        } else if (mc) {
+          // lin3 (one out chunk): both pairs walk the whole range; pair 0 contracts X columns 0..255, pair 1 256..511
+          // (n_sub 4 each) and they fill the two column halves of ONE partial slot
+          a.ocp = 0; a.n_sub = 4; a.tile_lo = t0; a.tile_hi = t0 + take;
+          per_pair[2 * q].push_back(a);
+          per_pair[2 * q + 1].push_back(a);
         } else {
           const long long mid = t0 + (take + 1) / 2;
           a.ocp = 0; a.tile_lo = t0; a.tile_hi = mid; per_pair[2 * q].push_back(a);
@@ -597,13 +631,18 @@ static int build_wg2_schedule(dsdf_handle h, long long tiles, cudaStream_t st, b
     if (l <= l_last) DSDF_FAIL(h, DSDF_EINVAL, "internal: wgrad schedule did not cover all layers");
     // slots: contiguous per item (layer, ocp), in item order
     std::vector<int> next_slot(items.size(), 0), base_slot(items.size(), 0), cnt(items.size(), 0);
-    for (auto& v : per_pair) for (WgSeg& sg : v) ++cnt[h->wg2_layout.item_base[sg.layer] + sg.ocp];
+    auto shares_slot = [&](int p, const WgSeg& sg) { return mc && sg.layer == 3 && (p & 1); };   // slot of pair p - 1
+    for (int p = 0; p < n_pairs; ++p)
+      for (WgSeg& sg : per_pair[p])
+        if (!shares_slot(p, sg)) ++cnt[h->wg2_layout.item_base[sg.layer] + sg.ocp];
     for (size_t i = 1; i < items.size(); ++i) base_slot[i] = base_slot[i - 1] + cnt[i - 1];
     for (int p = 0; p < n_pairs; ++p) {
       seg_begin.push_back((int)segs.size());
-      for (WgSeg& sg : per_pair[p]) {
+      for (size_t k = 0; k < per_pair[p].size(); ++k) {
+        WgSeg& sg = per_pair[p][k];
         const int item = h->wg2_layout.item_base[sg.layer] + sg.ocp;
-        sg.slot = base_slot[item] + next_slot[item]++;
+        if (shares_slot(p, sg)) sg.slot = per_pair[p - 1][k].slot;   // mc: both lists have the same shape
+        else sg.slot = base_slot[item] + next_slot[item]++;
         segs.push_back(sg);
       }
     }
@@ -657,6 +696,7 @@ static int build_wg2_schedule(dsdf_handle h, long long tiles, cudaStream_t st, b
   h->wg2_slots = (int)segs.size();
   h->wg2_tiles = tiles;
   h->wg2_with_l8 = (int)with_l8;
+  h->wg2_mc = mc;
   return DSDF_OK;
 }
 
@@ -684,12 +724,15 @@ static int launch_wgrad2(dsdf_handle h, const uint8_t* xstash, const uint8_t* dy
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.x = h->wg2_mc ? 4 : 2;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  if (rebuild) CU(h, cudaLaunchKernelEx(&cfg, k_wgrad2<true>, w2));
+  if (h->wg2_mc) {
+    if (rebuild) CU(h, (cudaLaunchKernelEx(&cfg, k_wgrad2<true, true>, w2)));
+    else CU(h, (cudaLaunchKernelEx(&cfg, k_wgrad2<false, true>, w2)));
+  } else if (rebuild) CU(h, cudaLaunchKernelEx(&cfg, k_wgrad2<true>, w2));
   else CU(h, cudaLaunchKernelEx(&cfg, k_wgrad2<false>, w2));
   if (prof) prof_mark(h, st, 4);
   k_reduce_wgrad2<<<dim3(kHidden, h->wg2_with_l8 ? 8 : 7), kHidden, 0, st>>>(partials, h->wg2_layout, dweff);

@@ -58,7 +58,13 @@ constexpr uint32_t kW2StageBytes = 6 * kW2Slice;           // 2 A slices + 4 B s
 constexpr uint32_t kW2SmemAux = kW2Ring * kW2StageBytes;   // 196608
 constexpr uint32_t kW2SmemBytes = kW2SmemAux + 512;
 
-template <bool REBUILD>
+// QUAD: clusters of 4 CTAs = the two pairs of a quad (ranks 0,1: out chunk 0; ranks 2,3: out chunk 1) walking the same
+// tile range.  The X slices both pairs need (ranks r and r ^ 2 hold the same half of X's columns) are loaded ONCE:
+// each of the two CTAs fetches half of them and multicasts to both, so an X tile leaves HBM and the L2 exactly once;
+// a stage may only be overwritten when BOTH pairs have consumed it, so both issuers commit every stage's `empty`
+// barrier to all four CTAs (count 2).  lin3 (one out chunk) is split by X columns instead: both pairs read the same
+// dY3 and their own half of X3 (no multicast) and write the two column halves of one partial slot.
+template <bool REBUILD, bool QUAD = false>
 __global__ void __launch_bounds__(kW2Threads, 1) k_wgrad2(const Wg2Args a) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const uint32_t s_base = smem_u32(smem);
@@ -72,14 +78,17 @@ __global__ void __launch_bounds__(kW2Threads, 1) k_wgrad2(const Wg2Args a) {
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + kW2SmemAux + 256);
 
   if ((s_base & 1023u) != 0) __trap();
-  const uint32_t crank = cluster_ctarank();
+  const uint32_t rank_all = cluster_ctarank();
+  const uint32_t crank = QUAD ? (rank_all & 1u) : rank_all;      // rank inside the CTA pair
+  const uint32_t pr = QUAD ? (rank_all >> 1) : 0u;               // which pair of the quad
+  const uint32_t lead_rank = 2u * pr;                            // cluster rank of this pair's leader
   const bool leader = crank == 0;
   if (threadIdx.x == 0) {
     // full: the producer's arrive.expect_tx (+ the relayed arrive of the peer in the leader) and, REBUILD, one more
     // arrival per stage: the dY7 generator warps for a lin7 stage, the producer itself otherwise
     for (int i = 0; i < kW2Ring; ++i) {
       mbar_init(&full[i], (leader ? 2 : 1) + (REBUILD ? 1 : 0));
-      mbar_init(&empty[i], 1);
+      mbar_init(&empty[i], QUAD ? 2 : 1);
     }
     mbar_init(d_done, 1);
     mbar_init(d_free, 8);                 // 4 epilogue warps of each CTA
@@ -91,8 +100,10 @@ __global__ void __launch_bounds__(kW2Threads, 1) k_wgrad2(const Wg2Args a) {
   cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
-  const uint32_t full_c = mapa_u32(smem_u32(full), 0);
-  const uint32_t d_free_c = mapa_u32(smem_u32(d_free), 0);
+  const uint32_t full_c = mapa_u32(smem_u32(full), lead_rank);
+  const uint32_t d_free_c = mapa_u32(smem_u32(d_free), lead_rank);
+  const uint16_t pair_mask = (uint16_t)(3u << (2u * pr));        // this pair's two CTAs
+  const uint16_t stage_mask = QUAD ? (uint16_t)0xF : (uint16_t)3;
 
   const int pair = blockIdx.x >> 1;
   const int seg_lo = a.seg_begin[pair], seg_hi = a.seg_begin[pair + 1];
@@ -117,8 +128,11 @@ __global__ void __launch_bounds__(kW2Threads, 1) k_wgrad2(const Wg2Args a) {
                  (size_t)(4 * sg.ocp + 2 * crank) * kSubBytes;
             dy_sub2 = kSubBytes;
           }
-          const uint8_t* x = a.xstash + (size_t)tile * kStashTileBytes +
-                             (size_t)(sg.layer - 1) * kTileBytes + (size_t)(2 * crank) * kSubBytes;
+          // QUAD lin3: pair pr contracts X columns 256 pr .. (SUBs 4 pr ..)
+          const uint8_t* x = a.xstash + (size_t)tile * kStashTileBytes + (size_t)(sg.layer - 1) * kTileBytes +
+                             (size_t)(2 * crank + ((QUAD && sg.layer == 3) ? 4 * pr : 0)) * kSubBytes;
+          const bool share_x = QUAD && sg.layer != 3;         // the partner pair needs the same X slices
+          const uint16_t x_mask = (uint16_t)((1u << crank) | (1u << (crank + 2)));
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
             const uint32_t st = par * 4 + u;
@@ -131,11 +145,20 @@ __global__ void __launch_bounds__(kW2Threads, 1) k_wgrad2(const Wg2Args a) {
               bulk_g2s(dst + kW2Slice, dy + dy_sub2 + u * kW2Slice, kW2Slice, &full[st]);
             }
             // N half hf covers X SUBs 4hf..4hf+3; this CTA provides SUBs 4hf+2c, 4hf+2c+1
-            for (int hf = 0; hf < nb; ++hf) {
-              bulk_g2s(dst + (2 + 2 * hf) * kW2Slice, x + (size_t)(4 * hf) * kSubBytes + u * kW2Slice,
-                       kW2Slice, &full[st]);
-              bulk_g2s(dst + (3 + 2 * hf) * kW2Slice, x + (size_t)(4 * hf + 1) * kSubBytes + u * kW2Slice,
-                       kW2Slice, &full[st]);
+            if (share_x) {
+              // 2 nb slices per CTA and stage; this CTA fetches every other one (slice parity = pr) for both holders
+              for (int sl = (int)pr; sl < 2 * nb; sl += 2) {
+                const int hf = sl >> 1, w = sl & 1;
+                bulk_g2s_mc(dst + (2 + sl) * kW2Slice, x + (size_t)(4 * hf + w) * kSubBytes + u * kW2Slice, kW2Slice,
+                            &full[st], x_mask);
+              }
+            } else {
+              for (int hf = 0; hf < nb; ++hf) {
+                bulk_g2s(dst + (2 + 2 * hf) * kW2Slice, x + (size_t)(4 * hf) * kSubBytes + u * kW2Slice,
+                         kW2Slice, &full[st]);
+                bulk_g2s(dst + (3 + 2 * hf) * kW2Slice, x + (size_t)(4 * hf + 1) * kSubBytes + u * kW2Slice,
+                         kW2Slice, &full[st]);
+              }
             }
           }
           par ^= 1;
@@ -197,12 +220,12 @@ __global__ void __launch_bounds__(kW2Threads, 1) k_wgrad2(const Wg2Args a) {
                            bd + (uint64_t)((2 * kW2Slice + ks * 2048) >> 4), idesc, acc | (uint32_t)ks);
             }
             acc = 1;
-            umma2_commit_mc(&empty[par * 4 + u], (uint16_t)3);
+            umma2_commit_mc(&empty[par * 4 + u], stage_mask);
           }
           par ^= 1;
           ph ^= (par == 0);
         }
-        umma2_commit_mc(d_done, (uint16_t)3);
+        umma2_commit_mc(d_done, pair_mask);
       }
     }
   } else if (warp >= 4) {
@@ -253,7 +276,8 @@ __global__ void __launch_bounds__(kW2Threads, 1) k_wgrad2(const Wg2Args a) {
           g_par ^= (uint32_t)nt & 1u;
         }
       }
-      float* out = a.partials + ((size_t)sg.slot * 256 + crank * 128 + r) * kHidden;
+      float* out = a.partials + ((size_t)sg.slot * 256 + crank * 128 + r) * kHidden +
+                   ((QUAD && sg.layer == 3) ? 256 * pr : 0);
       const int ncols = sg.n_sub * 64;
       mbar_wait(d_done, par_done);
       par_done ^= 1;
