@@ -52,6 +52,8 @@ struct dsdf_handle_s {
   // caller's stream, so the call is still ordered on that stream alone
   cudaStream_t side = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  cudaStream_t side2 = nullptr;             // the wgrad pairs on the SMs the 4-CTA clusters cannot cover
+  cudaEvent_t ev_wg_fork = nullptr, ev_wg_join = nullptr;
   CUtensorMap tmap_w{}, tmap_dg{}, tmap_e{};
   struct MapCache { const void* base = nullptr; size_t bytes = 0; CUtensorMap map{}; } ws_map[3];
   // A/B knobs: fixed in the product build; the diagnostics variant (-DDSDF_DIAG_BUILD) reads DSDF_FWD_CG,
@@ -71,6 +73,8 @@ struct dsdf_handle_s {
   uint8_t* wg2_stage = nullptr;        // pinned host staging for both arrays
   cudaEvent_t wg2_uploaded = nullptr;  // last upload has been consumed by the copy engine
   long long wg2_tiles = -1;
+  int wg2_extra_pairs = 0;       // CTA pairs that fit on the SMs left over by wg2_max_quads clusters (0: unknown / none)
+  int wg2_quads = 0;             // clusters of the current multicast schedule
   int wg2_max_quads = 0;         // 4-CTA clusters of k_wgrad2<.., QUAD> the device can hold at once (GPC granularity)
   bool wg2_mc = false;           // schedule is for k_wgrad2<.., QUAD>: 4-CTA clusters, multicast X loads
   int wg2_with_l8 = -1;          // schedule currently holds a lin8 item (autograd entries) or not (fused step)
@@ -215,6 +219,14 @@ static int set_kernel_attrs(dsdf_handle h) {
     int nq = 0;
     if (cudaOccupancyMaxActiveClusters(&nq, k_wgrad2<true, true>, &oc) != cudaSuccess) { nq = 0; cudaGetLastError(); }
     h->wg2_max_quads = nq < h->num_sms / 4 ? nq : h->num_sms / 4;
+    // the SMs those clusters leave over (GPC size mod 4) can still hold CTA pairs -- all of them if every GPC has an
+    // even number of SMs, which is what "num_sms / 2 two-CTA clusters fit" says
+    oc.gridDim = dim3((unsigned)(h->num_sms / 2 * 2));
+    oa[0].val.clusterDim.x = 2;
+    int np = 0;
+    if (cudaOccupancyMaxActiveClusters(&np, k_wgrad2<true, false>, &oc) != cudaSuccess) { np = 0; cudaGetLastError(); }
+    h->wg2_extra_pairs = (np == h->num_sms / 2 && h->wg2_max_quads >= 1) ? (h->num_sms - 4 * h->wg2_max_quads) / 2 : 0;
+    h->wg2_extra_pairs &= ~1;                                  // whole (old-style) quads only
   }
   h->attrs_set = true;
   return DSDF_OK;
@@ -271,6 +283,9 @@ extern "C" int dsdf_create(const dsdf_config* cfg, dsdf_handle* out) {
             cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking) == cudaSuccess &&
             cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming) == cudaSuccess &&
             cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming) == cudaSuccess &&
+            cudaStreamCreateWithFlags(&h->side2, cudaStreamNonBlocking) == cudaSuccess &&
+            cudaEventCreateWithFlags(&h->ev_wg_fork, cudaEventDisableTiming) == cudaSuccess &&
+            cudaEventCreateWithFlags(&h->ev_wg_join, cudaEventDisableTiming) == cudaSuccess &&
             cudaMalloc(&h->weff, (size_t)(kWeffElems + 16) * 4) == cudaSuccess &&
             cudaMalloc(&h->scale, (size_t)kScaleElems * 4) == cudaSuccess &&
             cudaMalloc(&h->inv_norm, (size_t)kScaleElems * 4) == cudaSuccess &&
@@ -298,6 +313,9 @@ extern "C" int dsdf_destroy(dsdf_handle h) {
   if (h->side) cudaStreamDestroy(h->side);
   if (h->ev_fork) cudaEventDestroy(h->ev_fork);
   if (h->ev_join) cudaEventDestroy(h->ev_join);
+  if (h->side2) cudaStreamDestroy(h->side2);
+  if (h->ev_wg_fork) cudaEventDestroy(h->ev_wg_fork);
+  if (h->ev_wg_join) cudaEventDestroy(h->ev_wg_join);
   cudaFree(h->w2_img);
   cudaFree(h->dg2_img);
   cudaFree(h->scene_e);
@@ -584,7 +602,9 @@ static int build_wg2_schedule(dsdf_handle h, long long tiles, cudaStream_t st, b
   // multicast variant (fused step: no lin8 item): the two pairs of a quad run as one 4-CTA cluster in lock step, so
   // every segment of a quad must give both pairs the same tile range
   const bool mc = !with_l8 && h->wg_quad && h->wg2_max_quads >= 1;
-  if (mc) n_pairs = 2 * h->wg2_max_quads;                  // every cluster resident from the start
+  // every cluster resident from the start; the left-over SMs run ordinary pairs (old-style quads: separate loads)
+  const int mc_pairs = mc ? 2 * h->wg2_max_quads : 0;
+  if (mc) n_pairs = mc_pairs + h->wg2_extra_pairs;
   if (h->wg_quad && n_pairs >= 2) {
     // "quad" schedule: two CTA pairs walk the SAME tile range of a layer side by side, one per
     // 256-row out chunk, so the X tiles the second pair needs are L2 hits behind the first pair's
@@ -612,7 +632,7 @@ static int build_wg2_schedule(dsdf_handle h, long long tiles, cudaStream_t st, b
         if (two) {
           a.ocp = 0; a.tile_lo = t0; a.tile_hi = t0 + take; per_pair[2 * q].push_back(a);
           a.ocp = 1; per_pair[2 * q + 1].push_back(a);
-        } else if (mc) {
+        } else if (mc && 2 * q < mc_pairs) {
           // lin3 (one out chunk): both pairs walk the whole range; pair 0 contracts X columns 0..255, pair 1 256..511
           // (n_sub 4 each) and they fill the two column halves of ONE partial slot
           a.ocp = 0; a.n_sub = 4; a.tile_lo = t0; a.tile_hi = t0 + take;
@@ -631,7 +651,7 @@ static int build_wg2_schedule(dsdf_handle h, long long tiles, cudaStream_t st, b
     if (l <= l_last) DSDF_FAIL(h, DSDF_EINVAL, "internal: wgrad schedule did not cover all layers");
     // slots: contiguous per item (layer, ocp), in item order
     std::vector<int> next_slot(items.size(), 0), base_slot(items.size(), 0), cnt(items.size(), 0);
-    auto shares_slot = [&](int p, const WgSeg& sg) { return mc && sg.layer == 3 && (p & 1); };   // slot of pair p - 1
+    auto shares_slot = [&](int p, const WgSeg& sg) { return p < mc_pairs && sg.layer == 3 && (p & 1); };   // slot of pair p - 1
     for (int p = 0; p < n_pairs; ++p)
       for (WgSeg& sg : per_pair[p])
         if (!shares_slot(p, sg)) ++cnt[h->wg2_layout.item_base[sg.layer] + sg.ocp];
@@ -697,6 +717,7 @@ static int build_wg2_schedule(dsdf_handle h, long long tiles, cudaStream_t st, b
   h->wg2_tiles = tiles;
   h->wg2_with_l8 = (int)with_l8;
   h->wg2_mc = mc;
+  h->wg2_quads = mc_pairs / 2;
   return DSDF_OK;
 }
 
@@ -718,7 +739,7 @@ static int launch_wgrad2(dsdf_handle h, const uint8_t* xstash, const uint8_t* dy
   w2.relu_mask = relu_mask;
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
-  cfg.gridDim = dim3((unsigned)(2 * h->wg2_pairs));
+  cfg.gridDim = dim3((unsigned)(h->wg2_mc ? 4 * h->wg2_quads : 2 * h->wg2_pairs));
   cfg.blockDim = dim3(kW2Threads);
   cfg.dynamicSmemBytes = kW2SmemBytes;
   cfg.stream = st;
@@ -730,8 +751,24 @@ static int launch_wgrad2(dsdf_handle h, const uint8_t* xstash, const uint8_t* dy
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   if (h->wg2_mc) {
+    const int extra = h->wg2_pairs - 2 * h->wg2_quads;       // pairs for the SMs the clusters leave over
+    if (extra > 0) {
+      CU(h, cudaEventRecord(h->ev_wg_fork, st));
+      CU(h, cudaStreamWaitEvent(h->side2, h->ev_wg_fork, 0));
+    }
+    // the clusters first: they must find their GPC slots free (the pairs then take what is left)
     if (rebuild) CU(h, (cudaLaunchKernelEx(&cfg, k_wgrad2<true, true>, w2)));
     else CU(h, (cudaLaunchKernelEx(&cfg, k_wgrad2<false, true>, w2)));
+    if (extra > 0) {
+      w2.pair_base = 2 * h->wg2_quads;
+      cfg.gridDim = dim3((unsigned)(2 * extra));
+      cfg.stream = h->side2;
+      attr[0].val.clusterDim.x = 2;
+      if (rebuild) CU(h, cudaLaunchKernelEx(&cfg, k_wgrad2<true>, w2));
+      else CU(h, cudaLaunchKernelEx(&cfg, k_wgrad2<false>, w2));
+      CU(h, cudaEventRecord(h->ev_wg_join, h->side2));
+      CU(h, cudaStreamWaitEvent(st, h->ev_wg_join, 0));
+    }
   } else if (rebuild) CU(h, cudaLaunchKernelEx(&cfg, k_wgrad2<true>, w2));
   else CU(h, cudaLaunchKernelEx(&cfg, k_wgrad2<false>, w2));
   if (prof) prof_mark(h, st, 4);

@@ -49,6 +49,7 @@ struct Wg2Args {
   const float* g;            // [n] dL/ds
   const float* w8;           // [512]
   const uint32_t* relu_mask; // forward ReLU bit-masks [tiles][8][16][128]
+  int pair_base;             // schedule index of this launch's first CTA pair
 };
 
 constexpr int kW2Ring = 8;
@@ -105,7 +106,7 @@ __global__ void __launch_bounds__(kW2Threads, 1) k_wgrad2(const Wg2Args a) {
   const uint16_t pair_mask = (uint16_t)(3u << (2u * pr));        // this pair's two CTAs
   const uint16_t stage_mask = QUAD ? (uint16_t)0xF : (uint16_t)3;
 
-  const int pair = blockIdx.x >> 1;
+  const int pair = a.pair_base + (int)(blockIdx.x >> 1);
   const int seg_lo = a.seg_begin[pair], seg_hi = a.seg_begin[pair + 1];
 
   if (warp == 0) {
