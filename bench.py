@@ -729,7 +729,8 @@ def main():
         # launches per step, counted from the ncu launch list (profiles/): renorm | sanitize, scene_fold, fwd, bwd, wgrad,
         # reduce_wgrad2 + 4 decoder-grad + 3 latent-grad/loss (+ memset node) | latent adam | decoder sqnorm, adam |
         # rowscale_weff, fold_images   (+ recompute pass and k_eik_corr with --eikonal)
-        launches_per_step = 1 + 13 + 1 + 2 + 2 + (2 if args.eikonal else 0)
+        # wgrad is two concurrent launches on B200: 33 four-CTA clusters + 8 CTA pairs on the SMs those cannot cover
+        launches_per_step = 1 + 14 + 1 + 2 + 2 + (2 if args.eikonal else 0)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
