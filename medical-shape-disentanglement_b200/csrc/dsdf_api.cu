@@ -928,10 +928,10 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
   b2.tile_colsum = w.tile_colsum;
   b2.cta_partials = w.cta_partials;
   b2.drop = h->drop;
-  // dY7 = g w8^T . mask7 is rebuilt inside the wgrad kernel (ReLU family, no dropout, no Eikonal correction pass that
-  // reads the stash): the dgrad chain then does not stash it
+  // dY7 = g w8^T . mask7 is rebuilt inside the wgrad kernel (ReLU family, no dropout): the dgrad chain then does not
+  // stash it; with the Eikonal term k_eik_corr takes lin7's share of the corrections from the masks as well
 #ifndef DSDF_ARCH_SIREN
-  const bool rebuild_dy7 = !eik && h->drop.layers == 0;
+  const bool rebuild_dy7 = h->drop.layers == 0;     // (the Eikonal correction pass takes lin7's share from the masks)
 #else
   const bool rebuild_dy7 = false;
 #endif
@@ -968,7 +968,8 @@ extern "C" int dsdf_train_fwd_bwd(dsdf_handle h, const float* params, const floa
     // ---- eps-weighted corrections of the row sums that are not GEMMs (bias grads, colsum(dY4), dW4[:, xyz])
     n_corr = eik_corr_blocks(h->num_sms);
     if (n_corr > tiles) n_corr = (int)tiles;
-    k_eik_corr<<<n_corr, 256, 0, st>>>(w.dystash, w.eik_row, sdf_data, tiles, w.tile_colsum, w.eik_corr);
+    k_eik_corr<<<n_corr, 256, 0, st>>>(w.dystash, w.eik_row, sdf_data, tiles, w.tile_colsum, w.eik_corr,
+                                       rebuild_dy7 ? w.g : nullptr, w.relu_mask, h->weff + weff_off(8));
     if (prof) prof_mark(h, st, 3);
 #endif
   }

@@ -200,7 +200,10 @@ constexpr int kCorrFloats = 6 * kHidden + kHidden * 3;
 __global__ void __launch_bounds__(256, 4) k_eik_corr(const uint8_t* __restrict__ dystash,
                                                      const float4* __restrict__ eik_row,
                                                      const float* __restrict__ sdf_data, long long n_tiles,
-                                                     float* __restrict__ tile_colsum, float* __restrict__ corr) {
+                                                     float* __restrict__ tile_colsum, float* __restrict__ corr,
+                                                     const float* __restrict__ g = nullptr,
+                                                     const uint32_t* __restrict__ relu_mask = nullptr,
+                                                     const float* __restrict__ w8 = nullptr) {
   __shared__ float w_eps[kTileM], w_dx[kTileM], w_dy[kTileM], w_dz[kTileM];
   __shared__ float red[8][4][64];
   __shared__ float db_acc[6][kHidden];
@@ -220,7 +223,7 @@ __global__ void __launch_bounds__(256, 4) k_eik_corr(const uint8_t* __restrict__
     __syncthreads();
     const uint8_t* dy_tile = dystash + (size_t)tile * kStashTileBytes;
 #pragma unroll 1
-    for (int l = 1; l <= 7; ++l) {
+    for (int l = 1; l <= (g ? 6 : 7); ++l) {
       const int nsub = l == 3 ? 4 : 8;
       const bool skip = l == kSkipLayer;
 #pragma unroll 1
@@ -286,6 +289,34 @@ __global__ void __launch_bounds__(256, 4) k_eik_corr(const uint8_t* __restrict__
           }
         }
         __syncthreads();
+      }
+    }
+    if (g) {
+      // lin7 when the dgrad chain does not stash dY7 (the wgrad kernel rebuilds it): dY7[r, c] = g_r w8[c] where the
+      // ReLU bit of X8[r, c] is set, so sum_r eps_r dY7[r, c] = w8[c] sum_{r: bit} eps_r g_r -- 2 KB of mask words per
+      // tile instead of 128 KB of dY7.  thread = (32-column block cb, 8 rows); bit 31 - j of a word = column 32 cb + j
+      const int cb = t >> 4, rq = t & 15;
+      const uint32_t* mt = relu_mask + (size_t)tile * (8 * 16 * kTileM) + (size_t)(7 * 16 + cb) * kTileM;
+      float acc7[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) acc7[j] = 0.f;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int r = rq + 16 * i;
+        const uint32_t m = __ldg(mt + r);
+        const float v = w_eps[r] * __ldg(g + tile * kTileM + r);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) acc7[j] += (m & (0x80000000u >> j)) ? v : 0.f;
+      }
+      // the 16 row groups of a column block are 16 consecutive lanes: fixed-order butterfly, lane rq == 0 holds the sum
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        float a0 = acc7[j];
+        a0 += __shfl_xor_sync(0xffffffffu, a0, 1);
+        a0 += __shfl_xor_sync(0xffffffffu, a0, 2);
+        a0 += __shfl_xor_sync(0xffffffffu, a0, 4);
+        a0 += __shfl_xor_sync(0xffffffffu, a0, 8);
+        if (rq == 0) db_acc[db_slot(7)][cb * 32 + j] += a0 * __ldg(w8 + cb * 32 + j);
       }
     }
   }
