@@ -52,8 +52,6 @@ struct dsdf_handle_s {
   // caller's stream, so the call is still ordered on that stream alone
   cudaStream_t side = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
-  cudaStream_t side2 = nullptr;             // the wgrad pairs on the SMs the 4-CTA clusters cannot cover
-  cudaEvent_t ev_wg_fork = nullptr, ev_wg_join = nullptr;
   CUtensorMap tmap_w{}, tmap_dg{}, tmap_e{};
   struct MapCache { const void* base = nullptr; size_t bytes = 0; CUtensorMap map{}; } ws_map[3];
   // A/B knobs: fixed in the product build; the diagnostics variant (-DDSDF_DIAG_BUILD) reads DSDF_FWD_CG,
@@ -283,9 +281,6 @@ extern "C" int dsdf_create(const dsdf_config* cfg, dsdf_handle* out) {
             cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking) == cudaSuccess &&
             cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming) == cudaSuccess &&
             cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming) == cudaSuccess &&
-            cudaStreamCreateWithFlags(&h->side2, cudaStreamNonBlocking) == cudaSuccess &&
-            cudaEventCreateWithFlags(&h->ev_wg_fork, cudaEventDisableTiming) == cudaSuccess &&
-            cudaEventCreateWithFlags(&h->ev_wg_join, cudaEventDisableTiming) == cudaSuccess &&
             cudaMalloc(&h->weff, (size_t)(kWeffElems + 16) * 4) == cudaSuccess &&
             cudaMalloc(&h->scale, (size_t)kScaleElems * 4) == cudaSuccess &&
             cudaMalloc(&h->inv_norm, (size_t)kScaleElems * 4) == cudaSuccess &&
@@ -313,9 +308,6 @@ extern "C" int dsdf_destroy(dsdf_handle h) {
   if (h->side) cudaStreamDestroy(h->side);
   if (h->ev_fork) cudaEventDestroy(h->ev_fork);
   if (h->ev_join) cudaEventDestroy(h->ev_join);
-  if (h->side2) cudaStreamDestroy(h->side2);
-  if (h->ev_wg_fork) cudaEventDestroy(h->ev_wg_fork);
-  if (h->ev_wg_join) cudaEventDestroy(h->ev_wg_join);
   cudaFree(h->w2_img);
   cudaFree(h->dg2_img);
   cudaFree(h->scene_e);
@@ -743,31 +735,32 @@ static int launch_wgrad2(dsdf_handle h, const uint8_t* xstash, const uint8_t* dy
   cfg.blockDim = dim3(kW2Threads);
   cfg.dynamicSmemBytes = kW2SmemBytes;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = h->wg2_mc ? 4 : 2;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   if (h->wg2_mc) {
-    const int extra = h->wg2_pairs - 2 * h->wg2_quads;       // pairs for the SMs the clusters leave over
-    if (extra > 0) {
-      CU(h, cudaEventRecord(h->ev_wg_fork, st));
-      CU(h, cudaStreamWaitEvent(h->side2, h->ev_wg_fork, 0));
-    }
-    // the clusters first: they must find their GPC slots free (the pairs then take what is left)
     if (rebuild) CU(h, (cudaLaunchKernelEx(&cfg, k_wgrad2<true, true>, w2)));
     else CU(h, (cudaLaunchKernelEx(&cfg, k_wgrad2<false, true>, w2)));
+    // The pairs for the SMs the clusters leave over: same stream, launched with the programmatic-serialisation
+    // attribute and never waiting on the grid dependency.  They become eligible when every CTA of the cluster launch
+    // has executed griddepcontrol.launch_dependents, i.e. when all clusters are resident in their GPC slots (had the
+    // pairs been placed first -- a second stream cannot exclude that -- a GPC could come up one cluster short and
+    // that cluster would run as a second wave), and then run beside them.  Everything they read was complete before
+    // the cluster launch started; the next ordinary launch in the stream waits for both.
+    const int extra = h->wg2_pairs - 2 * h->wg2_quads;
     if (extra > 0) {
       w2.pair_base = 2 * h->wg2_quads;
       cfg.gridDim = dim3((unsigned)(2 * extra));
-      cfg.stream = h->side2;
       attr[0].val.clusterDim.x = 2;
+      cfg.numAttrs = 2;
       if (rebuild) CU(h, cudaLaunchKernelEx(&cfg, k_wgrad2<true>, w2));
       else CU(h, cudaLaunchKernelEx(&cfg, k_wgrad2<false>, w2));
-      CU(h, cudaEventRecord(h->ev_wg_join, h->side2));
-      CU(h, cudaStreamWaitEvent(st, h->ev_wg_join, 0));
     }
   } else if (rebuild) CU(h, cudaLaunchKernelEx(&cfg, k_wgrad2<true>, w2));
   else CU(h, cudaLaunchKernelEx(&cfg, k_wgrad2<false>, w2));

@@ -107,6 +107,7 @@ __global__ void __launch_bounds__(kW2Threads, 1) k_wgrad2(const Wg2Args a) {
   const uint16_t stage_mask = QUAD ? (uint16_t)0xF : (uint16_t)3;
 
   const int pair = a.pair_base + (int)(blockIdx.x >> 1);
+  grid_dep_launch();   // every CTA of this launch is resident: a programmatically dependent launch may start beside it
   const int seg_lo = a.seg_begin[pair], seg_hi = a.seg_begin[pair + 1];
 
   if (warp == 0) {
