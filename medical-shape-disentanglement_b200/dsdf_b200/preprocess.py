@@ -137,9 +137,23 @@ def nearest_visible_sdf(xyz: torch.Tensor, pts: torch.Tensor, nrm: torch.Tensor,
             _lib.check(L.dsdf_knn_sdf(q.data_ptr(), n, p4.data_ptr(), n4.data_ptr(), p4.shape[0], float(stdv), sdf.data_ptr(),
                                       nn_ptr, _st(dev)), None, L)
         elif method == "grid":
+            # one thread walks one query's cells: hand the kernel the queries in cell order (a 64^3 key over the
+            # points' bounding box) so that the threads of a warp walk the same neighbourhood; every query's result is
+            # independent of its position in the batch, so this changes nothing but the memory behaviour
+            lo = p4[:, :3].amin(0)
+            span = (p4[:, :3].amax(0) - lo).clamp_min(1e-12)
+            cell = ((q - lo) / span * 64.0).clamp_(0.0, 63.0).long()
+            perm = torch.argsort((cell[:, 2] * 64 + cell[:, 1]) * 64 + cell[:, 0])
+            qs = q[perm].contiguous()
+            sdf_s = torch.empty_like(sdf)
+            nn_s = torch.empty_like(nn) if nn is not None else None
             ws = torch.empty(L.dsdf_knn_grid_workspace_bytes(p4.shape[0]), dtype=torch.uint8, device=dev)
-            _lib.check(L.dsdf_knn_sdf_grid(q.data_ptr(), n, p4.data_ptr(), n4.data_ptr(), p4.shape[0], float(stdv),
-                                           ws.data_ptr(), ws.numel(), sdf.data_ptr(), nn_ptr, _st(dev)), None, L)
+            _lib.check(L.dsdf_knn_sdf_grid(qs.data_ptr(), n, p4.data_ptr(), n4.data_ptr(), p4.shape[0], float(stdv),
+                                           ws.data_ptr(), ws.numel(), sdf_s.data_ptr(),
+                                           nn_s.data_ptr() if nn_s is not None else None, _st(dev)), None, L)
+            sdf[perm] = sdf_s
+            if nn is not None:
+                nn[perm] = nn_s
             torch.cuda.current_stream(dev).synchronize()      # the workspace must outlive the enqueued kernels
         else:
             raise ValueError(f"unknown method {method!r} (grid | brute)")
