@@ -1,7 +1,7 @@
 """SDF sample-file contract of the reference (deep_sdf/data.py:76-136, 268-304; writer
 src/PreprocessMesh.cpp:196-226): one `.npz` per shape with `pos` and `neg`, each [n, 4] fp32 rows
 (x, y, z, sdf), sdf > 0 in `pos`.  Host-side I/O only (numpy + torch tensors); the per-iteration
-window gather itself runs on the GPU (k_recon_gather / the fused step's A-tile load).
+window gather itself runs on the GPU (k_recon_tail / the fused step's A-tile load).
 
 Same function names, arguments and RNG consumption as the reference module, minus its mesh helpers
 (trimesh / marching-cubes utilities are outside the path).
