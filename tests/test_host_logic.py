@@ -69,6 +69,24 @@ def test_no_cpu_fallback():
         dec(torch.zeros(4, 259))
 
 
+def test_mesh_and_sampler_entries_have_no_cpu_path_either():
+    from dsdf_b200 import preprocess as P
+    with pytest.raises(dsdf_b200.DsdfError):
+        dsdf_b200.marching_cubes(torch.zeros(4, 4, 4))
+    with pytest.raises(dsdf_b200.DsdfError):
+        P.nearest_visible_sdf(torch.zeros(5, 3), torch.zeros(20, 4), torch.zeros(20, 4), 0.07)
+    with pytest.raises(dsdf_b200.DsdfError):
+        dsdf_b200.reconstruct_batch(dsdf_b200.Decoder(256, norm_layers=[], **KW), 2,
+                                    [(torch.zeros(8, 4), torch.zeros(8, 4))], torch.zeros(1, 256),
+                                    torch.zeros(2, 1, 2, dtype=torch.int64), 0.1, num_samples=4)
+    # argument checks that need no device: sizes beyond the static scratch, null pointers, empty inputs
+    L = _lib.lib()
+    assert L.dsdf_rasterize_views_static(1, 3, 1, 1, 1, 9, 1, 1, 1, None) != 0
+    assert b"exceeds the static depth buffer" in L.dsdf_last_error(None)
+    assert L.dsdf_knn_sdf_grid(None, 1, None, None, 1, 0.1, None, 0, None, None, None) != 0
+    assert L.dsdf_knn_grid_workspace_bytes(0) == 0 and L.dsdf_knn_grid_workspace_bytes(1000) > 2 * 4 * 128 ** 3
+
+
 def test_library_loads_and_exports_every_declared_symbol():
     hdr = open(os.path.join(ROOT, "include", "dsdf.h")).read()
     declared = sorted(set(re.findall(r"\b(dsdf_[a-z_0-9]+)\s*\(", hdr)))
