@@ -83,12 +83,19 @@ __device__ __forceinline__ void setmaxnreg_dec() {
 }
 
 #ifdef DSDF_ARCH_SIREN
-// 32 fp32 dX columns * stashed activation derivative 30 cos(30 x) (16 packed bf16x2) -> 16 packed bf16x2
+// 32 fp32 dX columns * stashed activation derivative 30 cos(30 x) -> 16 packed bf16x2.  The stash holds
+// round(127 cos) as signed bytes (sine_pack32, fwd3_kernel.cuh): byte b -> float by the exponent trick
+// float(0x4B400000 | (b ^ 0x80)) - (1.5 * 2^23 + 128), no conversion instruction; the factor 30 / 127 rides on dX.
 __device__ __forceinline__ void deriv_mul_pack32(const uint32_t (&v)[32], const uint32_t* d, uint32_t* p) {
+  constexpr float kScale = 30.f / 127.f;
 #pragma unroll
-  for (int i = 0; i < 16; ++i)
-    p[i] = pack_bf16x2(__uint_as_float(v[2 * i]) * __uint_as_float(d[i] << 16),
-                       __uint_as_float(v[2 * i + 1]) * __uint_as_float(d[i] & 0xFFFF0000u));
+  for (int i = 0; i < 16; ++i) {
+    const uint32_t w = d[i >> 1] ^ 0x80808080u;
+    const uint32_t b0 = __byte_perm(w, 0x4B400000u, (i & 1) ? 0x7652 : 0x7650);   // [w.b(2 or 0), 00, 40, 4B]
+    const uint32_t b1 = __byte_perm(w, 0x4B400000u, (i & 1) ? 0x7653 : 0x7651);
+    const float c0 = __uint_as_float(b0) - 12583040.f, c1 = __uint_as_float(b1) - 12583040.f;
+    p[i] = pack_bf16x2(__uint_as_float(v[2 * i]) * kScale * c0, __uint_as_float(v[2 * i + 1]) * kScale * c1);
+  }
 }
 #endif
 

@@ -110,8 +110,11 @@ __device__ __forceinline__ void sincos_reduced(float y, float& s, float& c) {
   r = fmaf(-k, 1.9353071795864769e-3f, r);
   __sincosf(r, &s, &c);
 }
-// networks/modules.py:4-14 Sine: 32 fp32 pre-activations -> sin(30 x) (16 packed bf16x2 in p) and the
-// derivative 30 cos(30 x) (16 packed bf16x2 in d); returns sum_i sin(30 x_i) w[i] when w != nullptr.
+// networks/modules.py:4-14 Sine: 32 fp32 pre-activations -> sin(30 x) (16 packed bf16x2 in p) and the derivative's
+// cos(30 x) as 32 signed bytes round(127 cos) in d[0..7] (cos is bounded, so a linear 8-bit code has the absolute
+// error of bf16 at |cos| ~ 1 and a smaller one elsewhere: half the stash bytes of a bf16 derivative; the backward
+// chain applies the factor 30 / 127); returns sum_i sin(30 x_i) w[i] when w != nullptr.
+// byte = low 8 bits of float_as_int(127 c + 1.5 * 2^23): rounding on the FMA pipe, no conversion instruction.
 __device__ __forceinline__ float sine_pack32(const uint32_t (&v)[32], uint32_t* p, uint32_t* d, const float* w) {
   float acc = 0.f;
 #pragma unroll
@@ -120,21 +123,24 @@ __device__ __forceinline__ float sine_pack32(const uint32_t (&v)[32], uint32_t* 
     sincos_reduced(30.f * __uint_as_float(v[2 * i]), s0, c0);
     sincos_reduced(30.f * __uint_as_float(v[2 * i + 1]), s1, c1);
     p[i] = pack_bf16x2(s0, s1);
-    d[i] = pack_bf16x2(30.f * c0, 30.f * c1);
+    const uint32_t q0 = __float_as_uint(fmaf(c0, 127.f, 12582912.f)), q1 = __float_as_uint(fmaf(c1, 127.f, 12582912.f));
+    const uint32_t two = __byte_perm(q0, q1, 0x0040);            // bytes [q0.b0, q1.b0, q0.b0, q0.b0] -> low 16 bits used
+    if (i & 1) d[i >> 1] = __byte_perm(d[i >> 1], two, 0x5410);  // [old.b0, old.b1, two.b0, two.b1]
+    else d[i >> 1] = two;
     if (w) acc = fmaf(s1, w[2 * i + 1], fmaf(s0, w[2 * i], acc));
   }
   return acc;
 }
 __device__ __forceinline__ void deriv_store(uint8_t* aux_tile, int l, int chunk, uint32_t r, const uint32_t* d) {
-  uint8_t* b = aux_tile + (size_t)(l * 16 + chunk) * (4 * kTileM * 16) + (size_t)r * 16;
+  uint8_t* b = aux_tile + (size_t)(l * 16 + chunk) * (2 * kTileM * 16) + (size_t)r * 16;
 #pragma unroll
-  for (int i = 0; i < 4; ++i)
+  for (int i = 0; i < 2; ++i)
     *reinterpret_cast<uint4*>(b + (size_t)i * kTileM * 16) = make_uint4(d[4 * i], d[4 * i + 1], d[4 * i + 2], d[4 * i + 3]);
 }
 __device__ __forceinline__ void deriv_load(const uint8_t* aux_tile, int l, int chunk, uint32_t r, uint32_t* d) {
-  const uint8_t* b = aux_tile + (size_t)(l * 16 + chunk) * (4 * kTileM * 16) + (size_t)r * 16;
+  const uint8_t* b = aux_tile + (size_t)(l * 16 + chunk) * (2 * kTileM * 16) + (size_t)r * 16;
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
+  for (int i = 0; i < 2; ++i) {
     const uint4 q = __ldg(reinterpret_cast<const uint4*>(b + (size_t)i * kTileM * 16));
     d[4 * i] = q.x; d[4 * i + 1] = q.y; d[4 * i + 2] = q.z; d[4 * i + 3] = q.w;
   }

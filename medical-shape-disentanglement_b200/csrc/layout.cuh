@@ -135,10 +135,10 @@ constexpr size_t kStashTileBytes = 8 * (size_t)kTileBytes;  // 1 MiB per 128-row
 // ---- activation-derivative side channel forward -> backward, per 128-row tile ----------------------
 // ReLU nets : 1 bit / element: [8 layers][16 chunks of 32 columns][128 rows] words, bit (31-i) = column
 //             32*chunk+i active (and kept by dropout)
-// SIREN     : bf16 30*cos(30 x) / element: [8 layers][16 chunks][4][128 rows][16 B] (a warp's 32 rows
-//             write 512 contiguous bytes per store instruction)
+// SIREN     : round(127 cos(30 x)) as a signed byte / element: [8 layers][16 chunks][2][128 rows][16 B] (a warp's
+//             32 rows write 512 contiguous bytes per store instruction)
 #ifdef DSDF_ARCH_SIREN
-constexpr size_t kActAuxTileBytes = 8 * 16 * (size_t)kTileM * 64;   // 1 MiB
+constexpr size_t kActAuxTileBytes = 8 * 16 * (size_t)kTileM * 32;   // 512 KiB: one signed byte per activation
 #else
 constexpr size_t kActAuxTileBytes = 8 * 16 * (size_t)kTileM * 4;    // 64 KB
 #endif
