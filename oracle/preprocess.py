@@ -153,6 +153,105 @@ def knn_sdf(xyz, pts, nrm, stdv, k=11):
     return out, nn
 
 
+def knn_grid_neighbours(xyz, pts, k=11, grid=128, block=8, fine_r=1):
+    """The visiting order and the stopping rule of k_knn_sdf_grid (csrc/sampler_kernels.cuh), restated for small inputs:
+    cubic cells over the points' bounding box (block^3 cells = one coarse block), the query's own cell and fine_r shells
+    around it, then shells of blocks with box-distance pruning of blocks and cells; stop when the k-th distance is
+    strictly below the distance to the nearest face that still has cells behind it (minus the rounding margin).  Returns
+    nn [n, k] (-1 padded).  Its claim -- tested in tests/test_preprocess_cpu.py -- is that this equals the stable
+    argsort of all distances (knn_sdf above) whatever the geometry."""
+    xyz = np.asarray(xyz, dtype=np.float32)
+    p = np.asarray(pts, dtype=np.float32)[:, :3]
+    G, B = grid, block
+    C = G // B
+    lo = p.min(0)
+    ext = F(max(float((p.max(0) - lo).max()), 1e-6))
+    h = F(F(ext * F(1 + 1e-3)) / F(G))
+    inv_h = F(F(1) / h)
+    org = (lo - F(0.5e-3) * ext).astype(np.float32)
+    margin = F(F(1e-3) * h)
+
+    def axis_cell(v, a):
+        return int(min(max(np.floor(F(F(v - org[a]) * inv_h)), 0), G - 1))
+
+    cells = {}
+    for i, q in enumerate(p):
+        cells.setdefault(tuple(axis_cell(q[a], a) for a in range(3)), []).append(i)
+    blocks = {}
+    for c in cells:
+        blocks.setdefault(tuple(v // B for v in c), []).append(c)
+
+    def shell(ctr, R, n):
+        l, u = [c - R for c in ctr], [c + R for c in ctr]
+        for z in range(max(l[2], 0), min(u[2], n - 1) + 1):
+            for y in range(max(l[1], 0), min(u[1], n - 1) + 1):
+                if z in (l[2], u[2]) or y in (l[1], u[1]):
+                    xs = range(max(l[0], 0), min(u[0], n - 1) + 1)
+                else:
+                    xs = ([l[0]] if l[0] >= 0 else []) + ([u[0]] if R > 0 and u[0] <= n - 1 else [])
+                for x in xs:
+                    yield x, y, z
+
+    def box_d2(q, corner, w):
+        d2 = F(0)
+        for a in range(3):
+            t = max(max(F(corner[a] - q[a]), F(q[a] - F(corner[a] + w))) - margin, F(0))
+            d2 = F(d2 + F(t * t))
+        return d2
+
+    nn = np.full((len(xyz), k), -1, dtype=np.int32)
+    for qi, q in enumerate(xyz):
+        d = (q - p).astype(np.float32)
+        d2 = (((d[:, 0] * d[:, 0]).astype(np.float32) + (d[:, 1] * d[:, 1]).astype(np.float32)).astype(np.float32)
+              + (d[:, 2] * d[:, 2]).astype(np.float32)).astype(np.float32)
+        best = []                                               # sorted (distance, index) pairs, at most k
+
+        def scan(idx):
+            nonlocal best
+            best = sorted(best + [(d2[i], i) for i in idx])[:k]
+
+        def finished(ctr, R, n, w):
+            df, op = F(3e38), False
+            for a in range(3):
+                if ctr[a] - R > 0:
+                    df, op = min(df, F(q[a] - F(org[a] + F(ctr[a] - R) * w))), True
+                if ctr[a] + R < n - 1:
+                    df, op = min(df, F(F(org[a] + F(ctr[a] + R + 1) * w) - q[a])), True
+            if not op:
+                return True
+            df = F(df - margin)
+            return len(best) == k and df > 0 and best[k - 1][0] < F(df * df)
+
+        c = [axis_cell(q[a], a) for a in range(3)]
+        done = False
+        for R in range(fine_r + 1):
+            for cell in shell(c, R, G):
+                scan(cells.get(cell, []))
+            done = finished(c, R, G, h)
+            if done:
+                break
+        if not done:
+            cc, wc = [v // B for v in c], F(F(B) * h)
+            for R in range(C):
+                for blk in shell(cc, R, C):
+                    if blk not in blocks:
+                        continue
+                    corner = [F(org[a] + F(blk[a] * B) * h) for a in range(3)]
+                    if len(best) == k and box_d2(q, corner, wc) > best[k - 1][0]:
+                        continue
+                    for cell in sorted(blocks[blk], key=lambda t: (t[2] % B, t[1] % B, t[0] % B)):
+                        if max(abs(cell[a] - c[a]) for a in range(3)) <= fine_r:
+                            continue
+                        if len(best) == k and box_d2(q, [F(org[a] + F(cell[a]) * h) for a in range(3)], h) > best[k - 1][0]:
+                            continue
+                        scan(cells[cell])
+                if finished(cc, R, C, wc):
+                    break
+        for j, (_, i) in enumerate(best):
+            nn[qi, j] = i
+    return nn
+
+
 def sample_points(verts, faces, cdf, n_surf, n_rand, stdv1, stdv2, cube_dim, seed):
     """The sample cloud of k_sample_points from the same Philox words (oracle/philox.py); libm calls (sqrt / log / sin /
     cos) are numpy's, so values agree with the device's to ~1e-6, not bit for bit."""

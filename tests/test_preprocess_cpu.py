@@ -59,3 +59,23 @@ def test_oracle_knn_sign_vote_on_a_sphere_point_cloud():
     assert np.all(np.sign(sdf[ok]) == np.sign(true[ok]))
     assert np.abs(sdf[ok] - true[ok]).max() < 0.03                       # point spacing of a 4000-point cloud
     assert np.all(nn[:, 0] == np.argmin(((q[:, None] - p[None]) ** 2).sum(-1), 1))
+
+
+def test_grid_search_order_and_stopping_rule_give_the_exact_neighbours():
+    """The algorithm of k_knn_sdf_grid, restated in numpy (oracle.preprocess.knn_grid_neighbours), against the stable
+    argsort of all distances: points on a sphere with every point duplicated (distance ties), queries near the surface,
+    far inside, outside the points' bounding box, and exactly on points; coarse and fine grids."""
+    rng = np.random.default_rng(3)
+    p = rng.normal(size=(1500, 3)); p = (0.5 * p / np.linalg.norm(p, axis=1, keepdims=True)).astype(np.float32)
+    p = np.concatenate([p, p[::3]])[rng.permutation(2000)]
+    n = (p / np.linalg.norm(p, axis=1, keepdims=True)).astype(np.float32)
+    q = np.concatenate([rng.uniform(-1, 1, (40, 3)), p[:40] + rng.normal(size=(40, 3)) * 0.03, rng.normal(size=(15, 3)) * 3,
+                        p[100:110], np.zeros((1, 3))]).astype(np.float32)
+    _, want = opp.knn_sdf(q, np.c_[p, np.zeros(len(p))], np.c_[n, np.zeros(len(p))], np.float32(0.07))
+    for grid, block in ((16, 4), (32, 8), (8, 2)):
+        got = opp.knn_grid_neighbours(q, p, grid=grid, block=block)
+        assert np.array_equal(got, want), (grid, block)
+    # fewer points than neighbours; all points in one spot
+    assert np.array_equal(opp.knn_grid_neighbours(q[:5], p[:7], grid=16, block=4)[:, 7:], np.full((5, 4), -1))
+    one = np.repeat(p[:1], 30, 0)
+    assert np.array_equal(opp.knn_grid_neighbours(q[:5], one, grid=16, block=4), np.tile(np.arange(11), (5, 1)))
